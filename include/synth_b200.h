@@ -1,0 +1,245 @@
+/*
+ * synth_b200.h — C ABI of libsynth_b200.so: the B200 (sm_100a) render backend for the
+ * data-parallel path of irmen/synthesizer's `synthplayer` package.
+ *
+ * Every entry point takes plain pointers and sizes; no torch types.  Pointers named *_dev are
+ * device pointers, everything else is host memory.  `stream` is a cudaStream_t passed as
+ * void* (NULL = the legacy default stream).  All functions return 0 on success or a negative
+ * SB_E* code; sb_last_error() gives the message for the calling thread.
+ *
+ * REFERENCE CITATIONS.  /root/reference holds only README.md (lines 1-2: "removed from
+ * Github, now hosted at Codeberg"); the synthplayer sources are absent offline, so no
+ * file:line can be cited.  Each entry point instead names the upstream class/method it stands
+ * in for, as published in the `synthplayer` package (modules oscillators.py, sample.py,
+ * synth.py), and — where the arithmetic is CPython's stdlib audioop (Modules/audioop.c,
+ * CPython 3.12.3) — the audioop routine.  See DESIGN.md "Parity status".
+ */
+#ifndef SYNTH_B200_H
+#define SYNTH_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_OK 0
+#define SB_EINVAL (-1)     /* bad argument */
+#define SB_ECUDA (-2)      /* CUDA runtime error, see sb_last_error() */
+#define SB_ENOMEM (-3)
+#define SB_ERANGE (-4)     /* a size exceeds a documented limit */
+
+/* waveform ids (synthplayer.oscillators class names) */
+#define SB_WAVE_NONE (-1)
+#define SB_WAVE_SINE 0
+#define SB_WAVE_TRIANGLE 1
+#define SB_WAVE_SQUARE 2
+#define SB_WAVE_SAWTOOTH 3
+#define SB_WAVE_PULSE 4
+
+int sb_abi_version(void);
+const char *sb_last_error(void);
+/* number of kernel launches made by this library in this process (bench.py's gpu_launches) */
+int64_t sb_launch_count(void);
+
+/* ------------------------------------------------------------------ time base ---------
+ * Upstream oscillators advance `t += increment` serially in fp64 (increment = 2*pi/sr for
+ * Sine, 1/sr for the others, and EnvelopeFilter's `time`).  That sum drifts in a way that is
+ * fully determined by IEEE rounding: inside one binade the rounded step is constant.  The time
+ * base is the list of (n_start, t_start, step) segments such that the serially accumulated
+ * value after n additions is EXACTLY  t_start + (n - n_start) * step  for the segment holding
+ * n.  Kernels evaluate it per sample index, so a render is parallel and still bit-identical
+ * to the serial accumulation.  (stands in for: the `t += increment` loops of
+ * synthplayer.oscillators.*.blocks and EnvelopeFilter.generator)
+ */
+typedef struct sb_time_seg {
+    int64_t n_start;
+    double t_start;
+    double step;
+} sb_time_seg;
+
+#define SB_TIMEBASE_MAX_SEGS 256
+
+/* Fills segs[] for n in [0, max_n]; returns the number of segments or a negative error. */
+int sb_timebase_build(double increment, int64_t max_n, sb_time_seg *segs, int max_segs);
+/* The accumulated value after n additions (host helper; same formula as the kernels). */
+double sb_timebase_at(const sb_time_seg *segs, int nsegs, int64_t n);
+/* Smallest n >= n_from with t(n) >= limit, i.e. where `while time < limit` stops. */
+int64_t sb_timebase_first_ge(const sb_time_seg *segs, int nsegs, int64_t n_from, double limit);
+
+/* ADSR boundaries of synthplayer.oscillators.EnvelopeFilter.generator, as sample indices:
+ * attack [0,n_a) decay [n_a,n_d) sustain [n_d,n_s) release [n_s,n_r) (+1 sample when the
+ * serially accumulated release amplitude is still > 0, which `extra` reports). */
+typedef struct sb_envelope {
+    int64_t n_a, n_d, n_s, n_r;
+    int32_t extra;          /* 1: one more sample at index n_r with amplitude amp_extra */
+    int32_t enabled;        /* 0: no envelope (factor 1 everywhere) */
+    double a_slope, d_slope, r_slope;   /* amp_change per sample in each ramp */
+    double sustain_level;
+    double amp_extra;
+} sb_envelope;
+
+int sb_envelope_build(double samplerate, double attack, double decay, double sustain,
+                      double sustain_level, double release, sb_envelope *out);
+
+/* ------------------------------------------------------------------ oscillators -------
+ * sb_osc_render_f32: samples [n0, n0+count) of one oscillator into out_dev (float32).
+ * stands in for synthplayer.oscillators.{Sine,Triangle,Square,Sawtooth,Pulse}.blocks.
+ *   fmsum_dev : NULL, or the exclusive weighted prefix sum S[i] = sum_{k<n0+i} lfo[k]*step[k]
+ *               of the FM LFO (from sb_fm_prefix_f64), which is what upstream's
+ *               `phase_correction += (freq_previous-freq)*t` recurrence amounts to.
+ *   pwm_dev   : NULL, or the pulse-width LFO values for the same range (Pulse only).
+ *   tb_dev    : device copy of the time base for this waveform's increment.
+ */
+typedef struct sb_osc_params {
+    int32_t wave;
+    int32_t reserved;
+    double frequency, amplitude, phase, bias, pulsewidth, samplerate;
+} sb_osc_params;
+
+int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_dev, int nsegs,
+                      int64_t n0, int64_t count, const double *fmsum_dev, const float *pwm_dev,
+                      float *out_dev, void *stream);
+
+/* Exclusive prefix sum of lfo[i]*step(n0+i) in fp64 with a running carry (carry_dev: one
+ * device double, read at entry, advanced at exit) so that consecutive chunks continue the
+ * sum.  scratch_dev must hold sb_fm_prefix_scratch_bytes(count) bytes. */
+int64_t sb_fm_prefix_scratch_bytes(int64_t count);
+int sb_fm_prefix_f64(const float *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                     int64_t count, double *carry_dev, double *out_dev, void *scratch_dev,
+                     void *stream);
+
+/* synthplayer.oscillators.WhiteNoise.blocks: value = (-amp + 2*amp*u) + bias, each draw held
+ * for `cycles` = int(samplerate/frequency) samples.  u_dev[j] is draw number j (j counted
+ * from draw0); parity tests inject the same draws on both sides. */
+int sb_noise_render_f32(const float *u_dev, int64_t draw0, int64_t cycles, double amplitude,
+                        double bias, int64_t n0, int64_t count, float *out_dev, void *stream);
+/* synthplayer.oscillators.Linear: a ramp start + n*increment clamped to [min, max] (the first
+ * value is `start` itself, unclamped, as upstream yields it before the first clamp). */
+int sb_linear_render_f32(double start, double increment, double min_value, double max_value,
+                         int64_t n0, int64_t count, float *out_dev, void *stream);
+/* Counter-based uniform draws (Philox-4x32-10) for product use when no buffer is injected. */
+int sb_uniform_f32(uint64_t seed, int64_t first_draw, int64_t count, float *out_dev, void *stream);
+
+/* ------------------------------------------------------------------ filters -----------
+ * All work on float32 device buffers holding samples [n0, n0+count) of their sources. */
+
+/* synthplayer.oscillators.EnvelopeFilter.generator */
+int sb_envelope_apply_f32(const float *in_dev, const sb_envelope *env, int64_t n0, int64_t count,
+                          float *out_dev, void *stream);
+/* AmpModulationFilter: out = a*b */
+int sb_mul_f32(const float *a_dev, const float *b_dev, int64_t count, float *out_dev, void *stream);
+/* MixingFilter: out = sum of nsrc buffers (src_ptrs_dev: device array of device pointers) */
+int sb_mix_f32(const float *const *src_ptrs_dev, int nsrc, int64_t count, float *out_dev, void *stream);
+/* ClipFilter / AbsFilter / scaling */
+int sb_clip_f32(const float *in_dev, float lo, float hi, int64_t count, float *out_dev, void *stream);
+int sb_abs_f32(const float *in_dev, int64_t count, float *out_dev, void *stream);
+int sb_scale_bias_f32(const float *in_dev, float scale, float bias, int64_t count, float *out_dev, void *stream);
+/* EchoFilter: out[n] = src[n] + sum_k gain[k]*src[n - delay[k]] for n >= n_after, taking
+ * src[m] = 0 for m < n_after in the delayed copies; out[n] = src[n] before n_after.
+ * src_dev[0] is sample index src_n0 (history the caller keeps); out covers [n0, n0+count). */
+#define SB_ECHO_MAX 64
+int sb_echo_f32(const float *src_dev, int64_t src_n0, int64_t n_after, int ntaps,
+                const int64_t *delays, const float *gains, int64_t n0, int64_t count,
+                float *out_dev, void *stream);
+
+/* float -> PCM (WaveSynth / Sample.from_osc_block): int(v*scale), truncation toward zero.
+ * Values outside the integer range are counted into *overflow_dev (upstream raises
+ * OverflowError; the host wrapper does too) and saturated in the output. */
+int sb_f32_to_pcm16(const float *in_dev, int64_t count, float scale, int16_t *out_dev,
+                    unsigned long long *overflow_dev, void *stream);
+int sb_f32_to_pcm32(const float *in_dev, int64_t count, double scale, int32_t *out_dev,
+                    unsigned long long *overflow_dev, void *stream);
+/* two mono float mixes -> interleaved stereo int16 */
+int sb_f32x2_to_pcm16_stereo(const float *left_dev, const float *right_dev, int64_t frames,
+                             float scale, int16_t *out_dev, unsigned long long *overflow_dev,
+                             void *stream);
+
+/* ------------------------------------------------------------------ voice bank --------
+ * The fused hot path: a bank of voices, each
+ *     EnvelopeFilter( Carrier(fm_lfo = Modulator) ) * (gain_left, gain_right)
+ * summed over voices into a stereo float mix (MixingFilter per channel).  One kernel
+ * evaluates modulator, FM prefix, carrier, ADSR and the voice sum; a second one folds the
+ * per-group partial mixes.  (stands in for: Sine/.../Pulse.blocks with fm_lfo,
+ * EnvelopeFilter.generator, AmpModulationFilter and MixingFilter, composed)
+ */
+typedef struct sb_voice {
+    int32_t c_wave, m_wave;              /* m_wave = SB_WAVE_NONE: no FM */
+    double c_freq, c_phase;              /* phase as passed upstream (fraction of a cycle) */
+    double m_freq, m_phase;
+    float c_amp, c_bias, c_pw;
+    float m_amp, m_bias, m_pw;
+    float gain_l, gain_r;
+    sb_envelope env;
+} sb_voice;
+
+typedef struct sb_bank_plan {
+    int32_t nvoices, voices_per_group, ngroups, nspans;
+    int64_t frames, span_len;            /* span_len is a multiple of 256 */
+    int64_t carry_bytes;                 /* scratch: per (voice, span) fp64 LFO sums */
+    int64_t partial_bytes;               /* scratch: ngroups * frames * 2 floats */
+} sb_bank_plan;
+
+/* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames`. */
+int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, sb_bank_plan *plan);
+
+/* Renders frames [n0, n0+plan->frames) of all voices.  tb_rad_dev / tb_cyc_dev: time bases
+ * for increment 2*pi/sr and 1/sr.  carry_dev and partial_dev are scratch of the sizes in the
+ * plan.  mix_dev receives plan->frames interleaved (left,right) float pairs. */
+int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan *plan,
+                       const sb_time_seg *tb_rad_dev, int nsegs_rad,
+                       const sb_time_seg *tb_cyc_dev, int nsegs_cyc,
+                       int64_t n0, double samplerate, double *carry_dev, float *partial_dev,
+                       float *mix_dev, void *stream);
+
+/* ------------------------------------------------------------------ integer PCM -------
+ * Bit-exact restatements of the CPython audioop routines synthplayer's Sample calls. */
+
+/* audioop.add (Sample.mix): saturating add */
+int sb_pcm16_add(const int16_t *a_dev, const int16_t *b_dev, int64_t count, int16_t *out_dev, void *stream);
+/* audioop.mul (Sample.amplify): floor(v*factor) clipped (audioop's fbound) */
+int sb_pcm16_mul(const int16_t *in_dev, int64_t count, double factor, int16_t *out_dev, void *stream);
+/* audioop.bias (Sample.bias): wrapping add */
+int sb_pcm16_bias(const int16_t *in_dev, int64_t count, int bias, int16_t *out_dev, void *stream);
+/* audioop.reverse */
+int sb_pcm16_reverse(const int16_t *in_dev, int64_t count, int16_t *out_dev, void *stream);
+/* audioop.max: max |v| as unsigned, into *out_dev */
+int sb_pcm16_maxabs(const int16_t *in_dev, int64_t count, unsigned int *out_dev, void *stream);
+/* audioop.tomono / tostereo (Sample.mono / stereo / pan) */
+int sb_pcm16_tomono(const int16_t *in_dev, int64_t frames, double lfactor, double rfactor, int16_t *out_dev, void *stream);
+int sb_pcm16_tostereo(const int16_t *in_dev, int64_t frames, double lfactor, double rfactor, int16_t *out_dev, void *stream);
+/* audioop.lin2lin 2<->4 (Sample.make_32bit / make_16bit) */
+int sb_pcm16_to_pcm32(const int16_t *in_dev, int64_t count, int32_t *out_dev, void *stream);
+int sb_pcm32_to_pcm16(const int32_t *in_dev, int64_t count, int16_t *out_dev, void *stream);
+/* Sample.fadeout / fadein: int(v * (1 - k*decrease/numsamples)) resp. (k*increase/numsamples + start) */
+int sb_pcm16_fadeout(int16_t *buf_dev, int64_t nsamples, double target_volume, void *stream);
+int sb_pcm16_fadein(int16_t *buf_dev, int64_t nsamples, double start_volume, void *stream);
+/* Sample.modulate_amp: int(v * m) */
+int sb_pcm16_modulate(int16_t *buf_dev, const float *mod_dev, int64_t count, void *stream);
+/* audioop.ratecv(frames, 2, nchannels, inrate, outrate, None) (Sample.resample / speed).
+ * sb_pcm16_ratecv_frames gives the number of output frames. */
+int64_t sb_pcm16_ratecv_frames(int64_t in_frames, int64_t inrate, int64_t outrate);
+int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nchannels, int64_t inrate,
+                    int64_t outrate, int16_t *out_dev, void *stream);
+/* Sample.mix_at for a list of sources applied IN ORDER: each step is audioop.add on the
+ * overlapped span (saturation per step).  Source s is src_pool_dev[src_off[s] ..
+ * src_off[s]+src_len[s]) (int16 sample units) mixed at dst sample index dst_off[s]; the
+ * three arrays are device arrays of nsrc int64.  dst must already be long enough. */
+int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
+                         const int64_t *src_off_dev, const int64_t *src_len_dev,
+                         const int64_t *dst_off_dev, int64_t nsrc, void *stream);
+
+/* ------------------------------------------------------------------ host-buffer calls -
+ * The same path with HOST buffers (copies included), for callers without device memory of
+ * their own; bench.py's e2e figure goes through these. */
+int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, int64_t frames,
+                              double samplerate, float scale, int16_t *out_stereo,
+                              unsigned long long *overflow);
+int sb_host_pcm16_mix_at_many(int16_t *dst, int64_t dst_count, const int16_t *src_pool,
+                              int64_t pool_count, const int64_t *src_off, const int64_t *src_len,
+                              const int64_t *dst_off, int64_t nsrc);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SYNTH_B200_H */

@@ -1,0 +1,439 @@
+"""
+Oscillators and filters with the API of ``synthplayer.oscillators``, rendered on a B200.
+
+Drop-in surface (names, argument order and meaning follow the published synthplayer package;
+the source is absent from /root/reference, so no file:line can be cited — see DESIGN.md):
+``Oscillator.blocks()`` yields lists of ``params.norm_osc_blocksize`` floats, ``generator()``
+single floats; filters wrap oscillators by construction.  What differs is underneath: an
+oscillator is a node of a render graph, and a request for samples [n0, n0+count) is answered
+by CUDA kernels through the C ABI (include/synth_b200.h) — per-sample-index closed forms on
+the exact time base instead of serial Python loops.  ``render(nframes)`` returns the samples
+as a float32 CUDA tensor without the host round trip that blocks()/generator() imply.
+
+There is no CPU implementation behind these classes.
+"""
+import ctypes
+import itertools
+import random
+import sys
+from math import log
+
+import torch
+
+from . import _cabi as C
+from . import _device as D
+from . import params
+
+__all__ = ["Oscillator", "Filter", "Sine", "Triangle", "Square", "Pulse", "Sawtooth", "WhiteNoise",
+           "Linear", "EnvelopeFilter", "MixingFilter", "AmpModulationFilter", "DelayFilter",
+           "EchoFilter", "ClipFilter", "AbsFilter", "NullFilter"]
+
+_FM_SEEK_CHUNK = 1 << 22
+
+
+class Oscillator:
+    """Base class (synthplayer.oscillators.Oscillator)."""
+
+    def __init__(self, source=None, samplerate=None):
+        self._samplerate = samplerate or source._samplerate
+        self._source = source
+        self._cache_n0 = 0
+        self._cache = None            # float32 CUDA tensor holding samples [_cache_n0, ...)
+
+    # ---- upstream API ---------------------------------------------------------------
+    def __iter__(self):
+        return self.blocks()
+
+    def blocks(self):
+        """Lists of params.norm_osc_blocksize floats, forever (or until a filter ends)."""
+        bs = params.norm_osc_blocksize
+        pos = 0
+        chunk = params.render_chunk_min
+        while True:
+            total = self._length()
+            n = chunk if total is None else min(chunk, total - pos)
+            if n <= 0:
+                return
+            data = self._fetch(pos, pos + n).cpu().tolist()
+            for i in range(0, n, bs):
+                yield data[i:i + bs]
+            pos += n
+            chunk = min(chunk * 2, params.render_chunk_max)
+
+    def generator(self):
+        """Single float samples (the older synthplayer interface)."""
+        return itertools.chain.from_iterable(self.blocks())
+
+    # ---- backend API ------------------------------------------------------------------
+    def render(self, nframes, start=0):
+        """Samples [start, start+nframes) as a float32 CUDA tensor (shorter if the stream ends)."""
+        D.require_cuda()
+        total = self._length()
+        end = start + int(nframes)
+        if total is not None:
+            end = min(end, total)
+        if end <= start:
+            return D.empty(0, torch.float32)
+        return self._fetch(start, end)
+
+    def _length(self):
+        """Total number of samples of a finite stream, or None."""
+        return None
+
+    def _fetch(self, a, b):
+        """Samples [a, b), reusing the overlap with the previous request so that sequential
+        (and look-back) consumers never re-render and stateful nodes advance monotonically."""
+        c = self._cache
+        if c is not None and self._cache_n0 <= a <= self._cache_n0 + c.numel():
+            c_end = self._cache_n0 + c.numel()
+            if b <= c_end:
+                return c[a - self._cache_n0:b - self._cache_n0]
+            new = self._render_range(c_end, b - c_end)
+            out = torch.cat((c[a - self._cache_n0:], new)) if a < c_end else new
+        else:
+            out = self._render_range(a, b - a)
+        self._cache_n0, self._cache = a, out
+        return out
+
+    def _render_range(self, n0, count):
+        raise NotImplementedError
+
+
+def _osc_params(wave, frequency, amplitude, phase, bias, pulsewidth, samplerate):
+    p = C.OscParams()
+    p.wave, p.frequency, p.amplitude, p.phase = wave, frequency, amplitude, phase
+    p.bias, p.pulsewidth, p.samplerate = bias, pulsewidth, samplerate
+    return p
+
+
+class _WaveOscillator(Oscillator):
+    """Sine / Triangle / Square / Sawtooth / Pulse with optional FM (and PWM for Pulse)."""
+
+    _wave = None
+
+    def __init__(self, frequency, amplitude=1.0, phase=0.0, bias=0.0, fm_lfo=None, samplerate=0):
+        super().__init__(samplerate=samplerate or params.norm_samplerate)
+        self.frequency = frequency
+        self.amplitude = amplitude
+        self.bias = bias
+        self._phase = phase
+        self._fm_lfo = fm_lfo
+        self._pwm_lfo = None
+        self.pulsewidth = 0.1
+        self._fm_pos = 0
+        self._fm_carry = None
+
+    def _timebase(self):
+        return D.timebase_rad(self._samplerate) if self._wave == C.WAVE_SINE else D.timebase_cyc(self._samplerate)
+
+    def _length(self):
+        lens = [x._length() for x in (self._fm_lfo, self._pwm_lfo) if x is not None]
+        lens = [x for x in lens if x is not None]
+        return min(lens) if lens else None
+
+    def _fm_prefix(self, n0, count, tb, out=True):
+        """Exclusive prefix sum of lfo*step over [n0, n0+count) continuing the running carry."""
+        lfo = self._fm_lfo._fetch(n0, n0 + count)
+        fmsum = D.empty(count, torch.float64)
+        scratch = D.empty(C.lib.sb_fm_prefix_scratch_bytes(count), torch.uint8)
+        C.call("sb_fm_prefix_f64", D.ptr(lfo), D.ptr(tb.dev()), tb.nsegs, n0, count,
+               D.ptr(self._fm_carry), D.ptr(fmsum), D.ptr(scratch), D.stream())
+        self._fm_pos = n0 + count
+        return fmsum
+
+    def _fm_seek(self, n0, tb):
+        """Bring the running FM sum to sample n0 (restarting from 0 when going backwards)."""
+        if self._fm_carry is None or n0 < self._fm_pos:
+            self._fm_carry = D.zeros(1, torch.float64)
+            self._fm_pos = 0
+        while self._fm_pos < n0:
+            self._fm_prefix(self._fm_pos, min(_FM_SEEK_CHUNK, n0 - self._fm_pos), tb)
+
+    def _render_range(self, n0, count):
+        tb = self._timebase()
+        fmsum = None
+        if self._fm_lfo is not None:
+            self._fm_seek(n0, tb)
+            fmsum = self._fm_prefix(n0, count, tb)
+        pwm = self._pwm_lfo._fetch(n0, n0 + count) if self._pwm_lfo is not None else None
+        out = D.empty(count, torch.float32)
+        p = _osc_params(self._wave, self.frequency, self.amplitude, self._phase, self.bias,
+                        self.pulsewidth, self._samplerate)
+        C.call("sb_osc_render_f32", ctypes.byref(p), D.ptr(tb.dev()), tb.nsegs, n0, count,
+               D.ptr(fmsum), D.ptr(pwm), D.ptr(out), D.stream())
+        return out
+
+
+class Sine(_WaveOscillator):
+    """Sine wave oscillator (synthplayer.oscillators.Sine)."""
+    _wave = C.WAVE_SINE
+
+
+class Triangle(_WaveOscillator):
+    """Perfect triangle wave oscillator (synthplayer.oscillators.Triangle)."""
+    _wave = C.WAVE_TRIANGLE
+
+
+class Square(_WaveOscillator):
+    """Perfect square wave oscillator (synthplayer.oscillators.Square)."""
+    _wave = C.WAVE_SQUARE
+
+
+class Sawtooth(_WaveOscillator):
+    """Perfect sawtooth wave oscillator (synthplayer.oscillators.Sawtooth)."""
+    _wave = C.WAVE_SAWTOOTH
+
+
+class Pulse(_WaveOscillator):
+    """Pulse (narrow square) oscillator with optional pulse width modulation
+    (synthplayer.oscillators.Pulse)."""
+    _wave = C.WAVE_PULSE
+
+    def __init__(self, frequency, amplitude=1.0, phase=0.0, bias=0.0, pulsewidth=0.1,
+                 fm_lfo=None, pwm_lfo=None, samplerate=0):
+        assert 0 <= pulsewidth <= 1
+        super().__init__(frequency, amplitude, phase, bias, fm_lfo, samplerate)
+        self.pulsewidth = pulsewidth
+        self._pwm_lfo = pwm_lfo
+
+
+class WhiteNoise(Oscillator):
+    """White noise: one uniform draw in [-amplitude, amplitude] held for
+    int(samplerate/frequency) samples (synthplayer.oscillators.WhiteNoise).
+
+    Upstream draws from Python's ``random``; here the draws are counter-based (Philox) with a
+    seed taken from ``random`` at construction, so ``random.seed()`` still makes a run
+    reproducible.  ``noise_source`` (a sequence of uniform draws in [0,1)) injects the draws
+    instead — that is how parity tests feed both implementations the same numbers."""
+
+    def __init__(self, frequency, amplitude=1.0, bias=0.0, samplerate=0, noise_source=None):
+        super().__init__(samplerate=samplerate or params.norm_samplerate)
+        self.frequency = frequency
+        self.amplitude = amplitude
+        self.bias = bias
+        self._cycles = int(self._samplerate / self.frequency)
+        if self._cycles < 1:
+            raise ValueError("whitenoise frequency cannot be bigger than the sample rate")
+        self._seed = random.getrandbits(64)
+        self._injected = None
+        if noise_source is not None:
+            self._injected = torch.as_tensor(list(noise_source) if not hasattr(noise_source, "__array__")
+                                             else noise_source, dtype=torch.float32)
+
+    def _length(self):
+        return None if self._injected is None else self._injected.numel() * self._cycles
+
+    def _render_range(self, n0, count):
+        d0 = n0 // self._cycles
+        d1 = (n0 + count - 1) // self._cycles + 1
+        if self._injected is not None:
+            u = self._injected[d0:d1].to(D.device())
+        else:
+            u = D.empty(d1 - d0, torch.float32)
+            C.call("sb_uniform_f32", self._seed, d0, d1 - d0, D.ptr(u), D.stream())
+        out = D.empty(count, torch.float32)
+        C.call("sb_noise_render_f32", D.ptr(u), d0, self._cycles, self.amplitude, self.bias,
+               n0, count, D.ptr(out), D.stream())
+        return out
+
+
+class Linear(Oscillator):
+    """Linear ramp, clamped to [min_value, max_value] (synthplayer.oscillators.Linear)."""
+
+    def __init__(self, startlevel, increment=0.0, min_value=-1.0, max_value=1.0, samplerate=0):
+        super().__init__(samplerate=samplerate or params.norm_samplerate)
+        self.value = startlevel
+        self.increment = increment
+        self.min_value = min_value
+        self.max_value = max_value
+
+    def _render_range(self, n0, count):
+        out = D.empty(count, torch.float32)
+        C.call("sb_linear_render_f32", self.value, self.increment, self.min_value, self.max_value,
+               n0, count, D.ptr(out), D.stream())
+        return out
+
+
+# ------------------------------------------------------------------------------ filters
+
+def _min_len(*lens):
+    lens = [x for x in lens if x is not None]
+    return min(lens) if lens else None
+
+
+class Filter(Oscillator):
+    """Base of everything that wraps other oscillators (synthplayer.oscillators.Filter)."""
+
+    def __init__(self, sources):
+        self._sources = list(sources)
+        super().__init__(self._sources[0])
+
+    def _length(self):
+        return _min_len(*[s._length() for s in self._sources])
+
+
+class EnvelopeFilter(Filter):
+    """ADSR volume envelope; A, D, S, R in seconds, sustain_level a factor
+    (synthplayer.oscillators.EnvelopeFilter).  After the release the output is 0.0 forever,
+    or the stream ends there when stop_at_end is set."""
+
+    def __init__(self, source, attack, decay, sustain, sustain_level, release, stop_at_end=False):
+        assert attack >= 0 and decay >= 0 and sustain >= 0 and release >= 0
+        assert 0 <= sustain_level <= 1
+        super().__init__([source])
+        self._attack = attack
+        self._decay = decay
+        self._sustain = sustain
+        self._sustain_level = sustain_level
+        self._release = release
+        self._stop_at_end = stop_at_end
+        self._env = D.build_envelope(self._samplerate, attack, decay, sustain, sustain_level, release)
+
+    def _length(self):
+        src = self._sources[0]._length()
+        if self._stop_at_end:
+            return _min_len(src, self._env.n_r + self._env.extra)
+        return src
+
+    def _render_range(self, n0, count):
+        # beyond the release nothing is pulled from the source (as upstream), only zeros
+        end_env = self._env.n_r + self._env.extra
+        live = max(0, min(count, end_env - n0))
+        out = D.zeros(count, torch.float32) if live < count else D.empty(count, torch.float32)
+        if live:
+            src = self._sources[0]._fetch(n0, n0 + live)
+            C.call("sb_envelope_apply_f32", D.ptr(src), ctypes.byref(self._env), n0, live,
+                   D.ptr(out), D.stream())
+        return out
+
+
+class MixingFilter(Filter):
+    """Sum of all sources (synthplayer.oscillators.MixingFilter)."""
+
+    def __init__(self, *sources):
+        super().__init__(sources)
+
+    def _render_range(self, n0, count):
+        bufs = [s._fetch(n0, n0 + count) for s in self._sources]
+        ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64).to(D.device())
+        out = D.empty(count, torch.float32)
+        C.call("sb_mix_f32", D.ptr(ptrs), len(bufs), count, D.ptr(out), D.stream())
+        return out
+
+
+class AmpModulationFilter(Filter):
+    """Amplitude modulation by another oscillator (synthplayer.oscillators.AmpModulationFilter)."""
+
+    def __init__(self, source, modulator):
+        super().__init__([source, modulator])
+
+    def _render_range(self, n0, count):
+        a = self._sources[0]._fetch(n0, n0 + count)
+        b = self._sources[1]._fetch(n0, n0 + count)
+        out = D.empty(count, torch.float32)
+        C.call("sb_mul_f32", D.ptr(a), D.ptr(b), count, D.ptr(out), D.stream())
+        return out
+
+
+class DelayFilter(Filter):
+    """Delays the source by int(samplerate*seconds) samples of silence, or skips that many
+    samples for a negative delay (synthplayer.oscillators.DelayFilter)."""
+
+    def __init__(self, source, seconds):
+        super().__init__([source])
+        self._seconds = seconds
+        if seconds < 0.0:
+            self._shift = -int(-self._samplerate * seconds)
+        else:
+            self._shift = int(self._samplerate * seconds)
+
+    def _length(self):
+        src = self._sources[0]._length()
+        return None if src is None else max(0, src + self._shift)
+
+    def _render_range(self, n0, count):
+        a, b = n0 - self._shift, n0 + count - self._shift       # source indices
+        if b <= 0:
+            return D.zeros(count, torch.float32)
+        if a >= 0:
+            return self._sources[0]._fetch(a, b)
+        out = D.zeros(count, torch.float32)
+        out[-a:] = self._sources[0]._fetch(0, b)
+        return out
+
+
+class EchoFilter(Filter):
+    """Mixes `amount` echoes into the source, starting `after` seconds in; echo k is delayed
+    k*delay seconds and scaled by decay**k (synthplayer.oscillators.EchoFilter).  A finite sum
+    of delayed copies, so it is a gather over the rendered source, not a recurrence."""
+
+    def __init__(self, source, after, amount, delay, decay):
+        super().__init__([source])
+        if decay < 1:
+            amount = int(min(amount, log(0.000001, decay)))     # echoes nobody can hear
+        if amount > C.ECHO_MAX:
+            raise ValueError("at most %d echoes are supported" % C.ECHO_MAX)
+        self._after = after
+        self._amount = amount
+        self._delay = delay
+        self._decay = decay
+        self.echo_duration = self._after + self._amount * self._delay
+        self._n_after = int(self._samplerate * after)
+        delays, gains = [], []
+        amp, echo_delay = decay, delay
+        for _ in range(amount):
+            delays.append(int(self._samplerate * echo_delay))
+            gains.append(amp)
+            echo_delay += delay
+            amp *= decay
+        self._delays = (ctypes.c_int64 * max(1, amount))(*delays)
+        self._gains = (ctypes.c_float * max(1, amount))(*gains)
+        self._maxdelay = max(delays) if delays else 0
+
+    def _render_range(self, n0, count):
+        lo = max(0, min(n0, max(self._n_after, n0 - self._maxdelay)))
+        src = self._sources[0]._fetch(lo, n0 + count)
+        out = D.empty(count, torch.float32)
+        C.call("sb_echo_f32", D.ptr(src), lo, self._n_after, self._amount, self._delays, self._gains,
+               n0, count, D.ptr(out), D.stream())
+        return out
+
+
+class ClipFilter(Filter):
+    """Clips the source to [minimum, maximum] (synthplayer.oscillators.ClipFilter)."""
+
+    def __init__(self, source, minimum=-sys.float_info.max, maximum=sys.float_info.max):
+        super().__init__([source])
+        self.min = minimum
+        self.max = maximum
+
+    def _render_range(self, n0, count):
+        src = self._sources[0]._fetch(n0, n0 + count)
+        fmax = 3.4028234663852886e38
+        out = D.empty(count, torch.float32)
+        C.call("sb_clip_f32", D.ptr(src), max(-fmax, min(fmax, self.min)), max(-fmax, min(fmax, self.max)),
+               count, D.ptr(out), D.stream())
+        return out
+
+
+class AbsFilter(Filter):
+    """Absolute value of the source (synthplayer.oscillators.AbsFilter)."""
+
+    def __init__(self, source):
+        super().__init__([source])
+
+    def _render_range(self, n0, count):
+        src = self._sources[0]._fetch(n0, n0 + count)
+        out = D.empty(count, torch.float32)
+        C.call("sb_abs_f32", D.ptr(src), count, D.ptr(out), D.stream())
+        return out
+
+
+class NullFilter(Filter):
+    """Passes the source through unchanged (synthplayer.oscillators.NullFilter)."""
+
+    def __init__(self, source):
+        super().__init__([source])
+
+    def _render_range(self, n0, count):
+        return self._sources[0]._fetch(n0, n0 + count)

@@ -1,0 +1,588 @@
+"""
+``Sample`` with the API of ``synthplayer.sample.Sample``, held and processed on a B200.
+
+The PCM frames live in device memory (an int16 or int32 CUDA tensor, interleaved channels);
+every arithmetic method is one or a few CUDA kernels reached through the C ABI
+(include/synth_b200.h), each a bit-exact restatement of the CPython ``audioop`` routine the
+upstream method delegates to (Modules/audioop.c, CPython 3.12.3) or of upstream's own fade
+formulas.  Bytes only cross to the host when asked for (get_frames / view_frame_data /
+write_wav).  Most operations modify the sample in place and return it, as upstream does.
+
+Upstream source is absent from /root/reference (README.md:1-2 only): method names, argument
+meaning and frame-index rounding follow the published package as recalled; see DESIGN.md.
+Sample width 2 is fully supported; width 4 supports construction, conversion and transfer
+(arithmetic on 32-bit frames raises NotImplementedError).  There is no CPU fallback.
+"""
+import array
+import ctypes
+import sys
+import wave
+
+import torch
+
+from . import _cabi as C
+from . import _device as D
+from . import params
+
+__all__ = ["Sample"]
+
+_DTYPE = {2: torch.int16, 4: torch.int32}
+
+
+class Sample:
+    """Audio sample data (integer PCM, 2 or 4 bytes per sample) on the GPU."""
+
+    def __init__(self, wave_file=None, name="", samplerate=0, nchannels=0, samplewidth=0):
+        self.name = name
+        self.filename = None
+        self._locked = False
+        self.samplerate = samplerate or params.norm_samplerate
+        self.nchannels = nchannels or params.norm_nchannels
+        self.samplewidth = samplewidth or params.norm_samplewidth
+        self._dev = None                       # 1-D int16/int32 CUDA tensor, interleaved
+        if wave_file:
+            self.load_wav(wave_file)
+            self.filename = wave_file if isinstance(wave_file, str) else None
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_raw_frames(cls, frames, samplewidth, samplerate, numchannels, name=""):
+        assert 1 <= numchannels <= 2
+        assert 2 <= samplewidth <= 4
+        assert samplerate > 1
+        if samplewidth not in _DTYPE:
+            raise ValueError("only samplewidth 2 or 4 are supported on this backend")
+        s = cls(name=name, samplerate=samplerate, nchannels=numchannels, samplewidth=samplewidth)
+        frames = bytes(frames)
+        if len(frames) % (samplewidth * numchannels):
+            raise ValueError("frames is not a whole number of sample frames")
+        if frames:
+            host = torch.frombuffer(bytearray(frames), dtype=_DTYPE[samplewidth])
+            s._dev = host.to(D.device())
+        return s
+
+    @classmethod
+    def from_array(cls, array_or_list, samplerate, numchannels, name=""):
+        assert 1 <= numchannels <= 2
+        assert samplerate > 1
+        if isinstance(array_or_list, list):
+            try:
+                array_or_list = cls.get_array(2, array_or_list)
+            except OverflowError:
+                array_or_list = cls.get_array(4, array_or_list)
+        elif array_or_list.typecode not in "hil":
+            raise ValueError("the sample values must be integer")
+        frames = array_or_list.tobytes()
+        if sys.byteorder == "big":
+            raise RuntimeError("big-endian hosts are not supported")
+        return cls.from_raw_frames(frames, array_or_list.itemsize, samplerate, numchannels, name)
+
+    @classmethod
+    def from_device(cls, tensor, samplerate, numchannels, name=""):
+        """Wrap an int16/int32 CUDA tensor of interleaved frames (no copy).  Backend API."""
+        width = {torch.int16: 2, torch.int32: 4}[tensor.dtype]
+        s = cls(name=name, samplerate=samplerate, nchannels=numchannels, samplewidth=width)
+        s._dev = tensor.reshape(-1) if tensor.numel() else None
+        return s
+
+    @classmethod
+    def from_osc_block(cls, block, samplerate, amplitude_scale=None, samplewidth=2):
+        """A mono sample from float values: int(v*scale), truncation toward zero; out-of-range
+        values raise OverflowError as upstream's array('h') does."""
+        if not torch.is_tensor(block):
+            block = torch.tensor(list(block), dtype=torch.float32)
+        block = block.to(D.device(), torch.float32)
+        return cls._from_float(block, samplerate, amplitude_scale, samplewidth)
+
+    @classmethod
+    def from_oscillator(cls, osc, duration, samplerate=None, amplitude_scale=None, samplewidth=2):
+        """Render `duration` seconds of an oscillator into a mono sample, entirely on the GPU."""
+        samplerate = samplerate or osc._samplerate
+        values = osc.render(int(samplerate * duration))
+        return cls._from_float(values, samplerate, amplitude_scale, samplewidth)
+
+    @classmethod
+    def _from_float(cls, values, samplerate, amplitude_scale, samplewidth):
+        scale = amplitude_scale or (2 ** (8 * samplewidth - 1) - 1)
+        n = values.numel()
+        out = D.empty(n, _DTYPE[samplewidth])
+        overflow = D.zeros(1, torch.int64)
+        if samplewidth == 2:
+            C.call("sb_f32_to_pcm16", D.ptr(values), n, float(scale), D.ptr(out), D.ptr(overflow), D.stream())
+        else:
+            C.call("sb_f32_to_pcm32", D.ptr(values), n, float(scale), D.ptr(out), D.ptr(overflow), D.stream())
+        bad = int(overflow.item())
+        if bad:
+            raise OverflowError("%d sample values do not fit samplewidth %d" % (bad, samplewidth))
+        return cls.from_device(out, samplerate, 1)
+
+    @staticmethod
+    def get_array(samplewidth, initializer=None):
+        if samplewidth == 2:
+            return array.array("h", initializer or [])
+        if samplewidth == 4:
+            return array.array("i" if array.array("i").itemsize == 4 else "l", initializer or [])
+        raise ValueError("only samplewidth 2 or 4 are supported")
+
+    # ------------------------------------------------------------------ properties / access
+    def _count(self):
+        return 0 if self._dev is None else self._dev.numel()
+
+    def __len__(self):
+        """Number of sample frames."""
+        return self._count() // self.nchannels
+
+    @property
+    def duration(self):
+        return self._count() / self.samplerate / self.nchannels
+
+    @property
+    def maximum(self):
+        """audioop.max: the largest absolute sample value."""
+        self._need16("maximum")
+        out = D.zeros(1, torch.int32)
+        C.call("sb_pcm16_maxabs", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+        return int(out.item()) & 0xFFFFFFFF
+
+    def frame_idx(self, seconds):
+        """Byte index of the frame at `seconds` (upstream's unit); see _sample_idx."""
+        return self.nchannels * self.samplewidth * int(self.samplerate * seconds)
+
+    def _sample_idx(self, seconds):
+        return self.nchannels * int(self.samplerate * seconds)
+
+    def device_frames(self):
+        """The interleaved frames as a CUDA tensor (no copy; empty tensor when empty)."""
+        return self._dev if self._dev is not None else D.empty(0, _DTYPE[self.samplewidth])
+
+    def get_frames(self):
+        """The raw little-endian frame bytes (device -> host copy)."""
+        if self._dev is None:
+            return b""
+        return self._dev.cpu().numpy().tobytes()
+
+    def view_frame_data(self):
+        return memoryview(self.get_frames())
+
+    def get_frame_array(self):
+        return self.get_array(self.samplewidth, None) if self._dev is None else \
+            array.array(self.get_array(self.samplewidth).typecode, self.get_frames())
+
+    def copy(self):
+        c = Sample(name=self.name, samplerate=self.samplerate, nchannels=self.nchannels,
+                   samplewidth=self.samplewidth)
+        c._dev = None if self._dev is None else self._dev.clone()
+        return c
+
+    def copy_from(self, other):
+        assert not self._locked
+        self._dev = None if other._dev is None else other._dev.clone()
+        self.samplerate, self.samplewidth, self.nchannels = other.samplerate, other.samplewidth, other.nchannels
+        self.filename = other.filename
+        return self
+
+    def lock(self):
+        self._locked = True
+        return self
+
+    # ------------------------------------------------------------------ wav i/o
+    def load_wav(self, file_or_stream):
+        assert not self._locked
+        with wave.open(file_or_stream) as w:
+            if not 2 <= w.getsampwidth() <= 4:
+                raise IOError("only supports sample sizes of 2, 3 or 4 bytes")
+            if not 1 <= w.getnchannels() <= 2:
+                raise IOError("only supports mono or stereo channels")
+            if w.getsampwidth() not in _DTYPE:
+                raise IOError("24-bit samples are not supported on this backend")
+            frames = w.readframes(w.getnframes())
+            self.nchannels, self.samplerate, self.samplewidth = w.getnchannels(), w.getframerate(), w.getsampwidth()
+        tmp = Sample.from_raw_frames(frames, self.samplewidth, self.samplerate, self.nchannels)
+        self._dev = tmp._dev
+        return self
+
+    def write_wav(self, file_or_stream):
+        with wave.open(file_or_stream, "wb") as out:
+            out.setparams((self.nchannels, self.samplewidth, self.samplerate, 0, "NONE", "not compressed"))
+            out.writeframes(self.get_frames())
+
+    def write_frames(self, stream):
+        stream.write(self.get_frames())
+
+    # ------------------------------------------------------------------ helpers
+    def _need16(self, what):
+        if self.samplewidth != 2:
+            raise NotImplementedError("%s: only 16-bit frames have GPU arithmetic in this round" % what)
+
+    def _same_format(self, other):
+        assert self.samplewidth == other.samplewidth
+        assert self.samplerate == other.samplerate
+        assert self.nchannels == other.nchannels
+
+    def _slice(self, a, b=None):
+        if self._dev is None:
+            return None
+        t = self._dev[a:b]
+        return t if t.numel() else None
+
+    @staticmethod
+    def _cat(*parts):
+        parts = [p for p in parts if p is not None and p.numel()]
+        if not parts:
+            return None
+        return parts[0] if len(parts) == 1 else torch.cat(parts)
+
+    def _zeros(self, n):
+        return D.zeros(n, _DTYPE[self.samplewidth]) if n > 0 else None
+
+    # ------------------------------------------------------------------ rate / width / channels
+    def resample(self, samplerate):
+        """audioop.ratecv(frames, width, nchannels, self.samplerate, samplerate, None)."""
+        assert not self._locked
+        if samplerate == self.samplerate:
+            return self
+        self._need16("resample")
+        self._dev = self._ratecv(self.samplerate, samplerate)
+        self.samplerate = samplerate
+        return self
+
+    def speed(self, speed):
+        assert not self._locked
+        assert speed > 0
+        if speed == 1.0:
+            return self
+        self._need16("speed")
+        self._dev = self._ratecv(int(self.samplerate * speed), self.samplerate)
+        return self
+
+    def _ratecv(self, inrate, outrate):
+        if self._dev is None:
+            return None
+        nin = len(self)
+        nout = C.lib.sb_pcm16_ratecv_frames(nin, inrate, outrate)
+        out = D.empty(nout * self.nchannels, torch.int16)
+        C.call("sb_pcm16_ratecv", D.ptr(self._dev), nin, self.nchannels, inrate, outrate, D.ptr(out), D.stream())
+        return out
+
+    def make_32bit(self, scale_amplitude=True):
+        assert not self._locked
+        if self.samplewidth == 4:
+            return self
+        if not scale_amplitude:
+            raise NotImplementedError("make_32bit(scale_amplitude=False)")
+        if self._dev is not None:
+            out = D.empty(self._count(), torch.int32)
+            C.call("sb_pcm16_to_pcm32", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+            self._dev = out
+        self.samplewidth = 4
+        return self
+
+    def make_16bit(self, maximize_amplitude=True):
+        assert not self._locked
+        assert self.samplewidth >= 2
+        if maximize_amplitude and self.samplewidth == 2:
+            self.amplify_max()
+        elif maximize_amplitude:
+            raise NotImplementedError("make_16bit(maximize_amplitude=True) from 32-bit frames")
+        if self.samplewidth > 2:
+            if self._dev is not None:
+                out = D.empty(self._count(), torch.int16)
+                C.call("sb_pcm32_to_pcm16", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+                self._dev = out
+            self.samplewidth = 2
+        return self
+
+    def mono(self, left_factor=1.0, right_factor=1.0):
+        assert not self._locked
+        if self.nchannels == 1:
+            return self
+        self._need16("mono")
+        if self._dev is not None:
+            out = D.empty(len(self), torch.int16)
+            C.call("sb_pcm16_tomono", D.ptr(self._dev), len(self), float(left_factor), float(right_factor),
+                   D.ptr(out), D.stream())
+            self._dev = out
+        self.nchannels = 1
+        return self
+
+    def left(self):
+        assert self.nchannels == 2
+        return self.mono(1.0, 0)
+
+    def right(self):
+        assert self.nchannels == 2
+        return self.mono(0, 1.0)
+
+    def stereo(self, left_factor=1.0, right_factor=1.0):
+        assert not self._locked
+        self._need16("stereo")
+        if self.nchannels == 2:
+            right = self.copy().right()
+            left = self.copy().left()
+            left._tostereo(left_factor, 0)
+            right._tostereo(0, right_factor)
+            self._dev = left._dev
+            return self._add_inplace(right._dev)
+        self._tostereo(left_factor, right_factor)
+        return self
+
+    def _tostereo(self, lf, rf):
+        if self._dev is not None:
+            out = D.empty(2 * self._count(), torch.int16)
+            C.call("sb_pcm16_tostereo", D.ptr(self._dev), self._count(), float(lf), float(rf), D.ptr(out), D.stream())
+            self._dev = out
+        self.nchannels = 2
+
+    def pan(self, panning=0.0):
+        assert not self._locked
+        assert -1 <= panning <= 1
+        left_volume = (1.0 - panning) / 2
+        right_volume = 1.0 - left_volume
+        return self.stereo(left_volume * 2, right_volume * 2)
+
+    # ------------------------------------------------------------------ amplitude
+    def amplify(self, factor):
+        """audioop.mul"""
+        assert not self._locked
+        self._need16("amplify")
+        if self._dev is not None:
+            C.call("sb_pcm16_mul", D.ptr(self._dev), self._count(), float(factor), D.ptr(self._dev), D.stream())
+        return self
+
+    def amplify_max(self):
+        assert not self._locked
+        max_amp = self.maximum if self._dev is not None else 0
+        max_target = 2 ** (8 * self.samplewidth - 1) - 2
+        if max_amp > 0:
+            self.amplify(max_target / max_amp)
+        return self
+
+    def at_volume(self, volume):
+        c = self.copy()
+        c.amplify(volume)
+        return c
+
+    def invert(self):
+        assert not self._locked
+        return self.amplify(-1)
+
+    def bias(self, bias):
+        """audioop.bias (wrapping)"""
+        assert not self._locked
+        self._need16("bias")
+        if self._dev is not None:
+            C.call("sb_pcm16_bias", D.ptr(self._dev), self._count(), int(bias), D.ptr(self._dev), D.stream())
+        return self
+
+    def reverse(self):
+        assert not self._locked
+        self._need16("reverse")
+        if self._dev is not None:
+            out = D.empty(self._count(), torch.int16)
+            C.call("sb_pcm16_reverse", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+            self._dev = out
+        return self
+
+    def fadeout(self, seconds, target_volume=0.0):
+        assert not self._locked
+        if self._dev is None:
+            return self
+        self._need16("fadeout")
+        seconds = min(seconds, self.duration)
+        i = self._sample_idx(self.duration - seconds)
+        n = self._count() - i
+        if n > 0:
+            C.call("sb_pcm16_fadeout", D.ptr(self._dev[i:]), n, float(target_volume), D.stream())
+        return self
+
+    def fadein(self, seconds, start_volume=0.0):
+        assert not self._locked
+        if self._dev is None:
+            return self
+        self._need16("fadein")
+        seconds = min(seconds, self.duration)
+        n = min(self._sample_idx(seconds), self._count())
+        if n > 0:
+            C.call("sb_pcm16_fadein", D.ptr(self._dev), n, float(start_volume), D.stream())
+        return self
+
+    def modulate_amp(self, modulation_source):
+        """Amplitude modulation by an oscillator (rendered on the GPU), or by a Sample / list /
+        array that is cycled and normalised to a maximum of 1.0 as upstream does."""
+        assert not self._locked
+        self._need16("modulate_amp")
+        if self._dev is None:
+            return self
+        n = self._count()
+        from .oscillators import Oscillator
+        if isinstance(modulation_source, Oscillator):
+            mod = modulation_source.render(n)
+            if mod.numel() < n:
+                raise ValueError("the modulating oscillator ends before the sample does")
+        else:
+            if isinstance(modulation_source, Sample):
+                modulation_source = modulation_source.get_frame_array()
+            vals = torch.tensor(list(modulation_source), dtype=torch.float64)
+            biggest = max(float(vals.max()), abs(float(vals.min())))
+            vals = (vals / biggest).to(torch.float32)
+            reps = -(-n // vals.numel())
+            mod = vals.repeat(reps)[:n].to(D.device())
+        C.call("sb_pcm16_modulate", D.ptr(self._dev), D.ptr(mod), n, D.stream())
+        return self
+
+    # ------------------------------------------------------------------ structure
+    def clip(self, start_seconds, end_seconds):
+        assert not self._locked
+        assert end_seconds >= start_seconds
+        t = self._slice(self._sample_idx(start_seconds), self._sample_idx(end_seconds))
+        self._dev = None if t is None else t.clone()
+        return self
+
+    def split(self, seconds):
+        assert not self._locked
+        end = self._sample_idx(seconds)
+        if end != self._count():
+            chopped = self.copy()
+            chopped._dev = self._slice(end)
+            self._dev = self._slice(0, end)
+            return chopped
+        return Sample.from_raw_frames(b"", self.samplewidth, self.samplerate, self.nchannels)
+
+    def add_silence(self, seconds, at_start=False):
+        assert not self._locked
+        z = self._zeros(self._sample_idx(seconds))
+        self._dev = self._cat(z, self._dev) if at_start else self._cat(self._dev, z)
+        return self
+
+    def join(self, other):
+        assert not self._locked
+        self._same_format(other)
+        self._dev = self._cat(self._dev, other._dev)
+        return self
+
+    def delay(self, seconds, keep_length=False):
+        assert not self._locked
+        if seconds > 0:
+            if keep_length:
+                num = self._count()
+                self.add_silence(seconds, at_start=True)
+                self._dev = self._slice(0, num)
+                return self
+            return self.add_silence(seconds, at_start=True)
+        if seconds < 0:
+            seconds = -seconds
+            if keep_length:
+                num = self._count()
+                self.add_silence(seconds)
+                self._dev = self._slice(self._count() - num)
+                return self
+            self._dev = self._slice(self._sample_idx(seconds))
+        return self
+
+    # ------------------------------------------------------------------ mixing
+    def _add_inplace(self, other_dev, at=0):
+        """self[at:at+len(other)] = audioop.add(self[...], other): saturating."""
+        if other_dev is None:
+            return self
+        n = other_dev.numel()
+        dst = self._dev[at:at + n]
+        C.call("sb_pcm16_add", D.ptr(dst), D.ptr(other_dev), n, D.ptr(dst), D.stream())
+        return self
+
+    def _grow(self, required):
+        have = self._count()
+        if required > have:
+            self._dev = self._cat(self._dev, self._zeros(required - have))
+
+    def mix(self, other, other_seconds=None, pad_shortest=True):
+        """Mix another sample into this one (audioop.add); the shorter one is zero-padded."""
+        assert not self._locked
+        self._same_format(other)
+        self._need16("mix")
+        o = other._dev
+        if other_seconds and o is not None:
+            o = other._slice(0, other._sample_idx(other_seconds))
+        on = 0 if o is None else o.numel()
+        if pad_shortest:
+            self._grow(on)
+        elif on != self._count():
+            raise C.SbError("audioop.error: Lengths should be the same")
+        return self._add_inplace(o)
+
+    def mix_at(self, seconds, other, other_seconds=None):
+        """Mix another sample into this one at a time offset, growing this sample if needed."""
+        if seconds == 0.0:
+            return self.mix(other, other_seconds)
+        assert not self._locked
+        self._same_format(other)
+        self._need16("mix_at")
+        start = self._sample_idx(seconds)
+        o = other._dev
+        if other_seconds and o is not None:
+            o = other._slice(0, other._sample_idx(other_seconds))
+        on = 0 if o is None else o.numel()
+        self._grow(start + on)
+        return self._add_inplace(o, at=start)
+
+    def mix_at_many(self, placements):
+        """Backend extension: apply ``mix_at(seconds, sample)`` for every (seconds, sample) of
+        `placements`, in order, with ONE kernel launch.  The result is identical to the loop of
+        mix_at calls (each step saturates like audioop.add)."""
+        assert not self._locked
+        self._need16("mix_at_many")
+        starts, srcs = [], []
+        for seconds, other in placements:
+            self._same_format(other)
+            if other._dev is None:
+                continue
+            starts.append(self._sample_idx(seconds))
+            srcs.append(other._dev)
+        if not srcs:
+            return self
+        lens = [s.numel() for s in srcs]
+        self._grow(max(a + n for a, n in zip(starts, lens)))
+        pool = torch.cat(srcs) if len(srcs) > 1 else srcs[0]
+        offs = [0]
+        for n in lens[:-1]:
+            offs.append(offs[-1] + n)
+        idx = torch.tensor([offs, lens, starts], dtype=torch.int64).to(D.device())
+        C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), D.ptr(pool), D.ptr(idx[0]),
+               D.ptr(idx[1]), D.ptr(idx[2]), len(srcs), D.stream())
+        return self
+
+    def echo(self, length, amount, delay, decay):
+        """Adds `amount` echoes of the last `length` seconds to the end of the sample."""
+        assert not self._locked
+        if amount > 0:
+            length = max(0, self.duration - length)
+            echo = self.copy()
+            echo._dev = self._slice(self._sample_idx(length))
+            echo._dev = None if echo._dev is None else echo._dev.clone()
+            echo_amp = decay
+            for _ in range(amount):
+                if echo_amp < 1.0 / (2 ** (8 * self.samplewidth - 1)):
+                    break                   # echoes nobody can hear
+                length += delay
+                echo = echo.copy().amplify(echo_amp)
+                self.mix_at(length, echo)
+                echo_amp *= decay
+        return self
+
+    def envelope(self, attack, decay, sustainlevel, release):
+        """ADSR volume envelope; A, D, R in seconds, sustainlevel a factor."""
+        assert not self._locked
+        assert attack >= 0 and decay >= 0 and release >= 0
+        assert 0 <= sustainlevel <= 1
+        D_ = self.split(attack)
+        S = D_.split(decay)
+        if sustainlevel < 1:
+            S.amplify(sustainlevel)
+        R = S.split(S.duration - release)
+        if attack > 0:
+            self.fadein(attack)
+        if decay > 0:
+            D_.fadeout(decay, sustainlevel)
+        if release > 0:
+            R.fadeout(release)
+        self.join(D_).join(S).join(R)
+        return self

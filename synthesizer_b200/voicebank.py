@@ -1,0 +1,147 @@
+"""
+Polyphonic voice banks: many voices of the shape
+
+    EnvelopeFilter( Carrier(fm_lfo=Modulator) ) * (left gain, right gain)
+
+summed to one stereo stream — what upstream expresses as a MixingFilter over
+AmpModulationFilter/EnvelopeFilter/oscillator chains, evaluated here by ONE fused kernel
+(sb_bank_render_f32) plus a fold of the per-group partial mixes.  Voices shard across GPUs by
+voice; the partial mixes are summed with one NCCL reduce and converted to PCM once, on rank 0.
+
+Backend API (no upstream class of this name): upstream reaches the same result through its
+oscillator classes; `VoiceBank.from_oscillators` accepts exactly those objects.
+"""
+import ctypes
+
+import torch
+
+from . import _cabi as C
+from . import _device as D
+from .oscillators import EnvelopeFilter, _WaveOscillator
+
+__all__ = ["VoiceBank", "shard_range"]
+
+
+def shard_range(nvoices, rank, world_size):
+    """Contiguous, balanced slice [begin, end) of the voices that `rank` renders."""
+    base, extra = divmod(nvoices, world_size)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+def _voice_from(osc, gain_l, gain_r):
+    v = C.Voice()
+    env = None
+    if isinstance(osc, EnvelopeFilter):
+        if osc._stop_at_end:
+            raise ValueError("voices with stop_at_end envelopes must use the general render path")
+        env, osc = osc._env, osc._sources[0]
+    if not isinstance(osc, _WaveOscillator) or osc._pwm_lfo is not None:
+        raise ValueError("a bank voice is a Sine/Triangle/Square/Sawtooth/Pulse carrier without PWM")
+    v.c_wave, v.c_freq, v.c_phase = osc._wave, osc.frequency, osc._phase
+    v.c_amp, v.c_bias, v.c_pw = osc.amplitude, osc.bias, osc.pulsewidth
+    lfo = osc._fm_lfo
+    if lfo is None:
+        v.m_wave = C.WAVE_NONE
+    else:
+        if not isinstance(lfo, _WaveOscillator) or lfo._fm_lfo is not None or lfo._pwm_lfo is not None:
+            raise ValueError("the FM modulator of a bank voice must be a plain waveform oscillator")
+        if lfo._samplerate != osc._samplerate:
+            raise ValueError("carrier and modulator sample rates differ")
+        v.m_wave, v.m_freq, v.m_phase = lfo._wave, lfo.frequency, lfo._phase
+        v.m_amp, v.m_bias, v.m_pw = lfo.amplitude, lfo.bias, lfo.pulsewidth
+    v.gain_l, v.gain_r = gain_l, gain_r
+    if env is not None:
+        v.env = env
+    else:
+        v.env.enabled = 0
+    return v, osc._samplerate
+
+
+class VoiceBank:
+    """A set of voices rendered and mixed by the fused bank kernel."""
+
+    def __init__(self, samplerate):
+        self.samplerate = samplerate
+        self._voices = []
+        self._dev = None
+
+    def __len__(self):
+        return len(self._voices)
+
+    def add(self, osc, gain_left=1.0, gain_right=1.0):
+        v, sr = _voice_from(osc, gain_left, gain_right)
+        if sr != self.samplerate:
+            raise ValueError("voice sample rate %s differs from the bank's %s" % (sr, self.samplerate))
+        self._voices.append(v)
+        self._dev = None
+        return self
+
+    @classmethod
+    def from_oscillators(cls, oscillators, gains=None, samplerate=None):
+        oscillators = list(oscillators)
+        bank = cls(samplerate or oscillators[0]._samplerate)
+        for i, osc in enumerate(oscillators):
+            gl, gr = gains[i] if gains is not None else (1.0, 1.0)
+            bank.add(osc, gl, gr)
+        return bank
+
+    @classmethod
+    def from_voice_array(cls, voices, samplerate):
+        """From a ctypes array / list of _cabi.Voice (already built, e.g. by bench.py)."""
+        bank = cls(samplerate)
+        bank._voices = list(voices)
+        return bank
+
+    def voice_array(self, begin=0, end=None):
+        sel = self._voices[begin:end]
+        return (C.Voice * len(sel))(*sel)
+
+    def _upload(self, begin, end):
+        arr = self.voice_array(begin, end)
+        raw = ctypes.string_at(ctypes.addressof(arr), ctypes.sizeof(arr))
+        return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(D.device()), len(arr)
+
+    def render(self, nframes, start=0, begin=0, end=None, voices_dev=None):
+        """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
+        [start, start+nframes), as a CUDA tensor."""
+        D.require_cuda()
+        if voices_dev is None:
+            voices_dev, nv = self._upload(begin, end)
+        else:
+            nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
+        mix = D.empty(2 * nframes, torch.float32)
+        if nv == 0:
+            return mix.zero_()
+        plan = C.BankPlan()
+        sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+        C.call("sb_bank_plan_make", nv, nframes, sms, ctypes.byref(plan))
+        carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
+        partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
+        tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
+        C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,
+               D.ptr(tc.dev()), tc.nsegs, start, float(self.samplerate), D.ptr(carry), D.ptr(partial),
+               D.ptr(mix), D.stream())
+        return mix
+
+    def render_sharded(self, nframes, start=0, group=None):
+        """Voice-sharded render: this rank renders its slice of the voices; the partial mixes
+        are summed on rank 0 with one reduce.  Returns the full mix on rank 0 (the partial one
+        elsewhere).  Without an initialised process group this is a plain render."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return self.render(nframes, start)
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        b, e = shard_range(len(self._voices), rank, world)
+        mix = self.render(nframes, start, b, e)
+        dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM, group=group)
+        return mix
+
+    def to_sample(self, duration, scale=None, sharded=False):
+        """Render `duration` seconds to a stereo 16-bit Sample (int(v*scale), truncation)."""
+        from .sample import Sample
+        nframes = int(self.samplerate * duration)
+        mix = self.render_sharded(nframes) if sharded else self.render(nframes)
+        s = Sample._from_float(mix, self.samplerate, scale, 2)
+        s.nchannels = 2
+        return s

@@ -1,0 +1,206 @@
+"""
+GPU parity of the oscillators and filters against the oracle (oracle/oracle.c, itself
+bit-identical to the pure-Python restatement).  Tolerance: int16 PCM within +-1 LSB
+(BASELINE.json north_star); discontinuous waveforms without FM must be sample exact in
+WHERE their edges fall, which the +-1 LSB bound implies (an edge on the wrong sample is a
+full-scale error).
+"""
+import itertools
+
+import numpy as np
+import pytest
+
+from helpers import assert_within_lsb, dev_pcm16, pcm16_of
+
+pytestmark = pytest.mark.gpu
+
+WAVES = ["Sine", "Triangle", "Square", "Sawtooth", "Pulse"]
+
+
+def _make(mod, name, *a, **k):
+    return getattr(mod, name)(*a, **k)
+
+
+@pytest.mark.parametrize("wave", range(5))
+@pytest.mark.parametrize("sr,freq", [(44100, 440.0), (48000, 1000.0), (44100, 441.0), (48000, 7.3), (22050, 5512.5)])
+def test_plain_waveforms(cuda, wave, sr, freq):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    n = 3 * sr + 17
+    kw = dict(pulsewidth=0.3) if wave == 4 else {}
+    osc = _make(sb, WAVES[wave], freq, 0.8, 0.15, 0.05, samplerate=sr, **kw)
+    got = dev_pcm16(osc.render(n))
+    want = pcm16_of(co.osc(wave, n, sr, freq, 0.8, 0.15, 0.05, pulsewidth=0.3))
+    assert_within_lsb(got, want, 1, "%s %g Hz @%d" % (WAVES[wave], freq, sr))
+
+
+@pytest.mark.parametrize("wave", [2, 3, 4])
+def test_edges_on_exact_sample_boundaries_after_long_run(cuda, wave):
+    """1000 Hz at 48 kHz: every edge lands exactly on a sample in real arithmetic, so the side
+    is decided by the rounding of the serially accumulated t.  Checked 5 minutes in."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, freq = 48000, 1000.0
+    start, n = 300 * sr, 48000
+    kw = dict(pulsewidth=0.25) if wave == 4 else {}
+    osc = _make(sb, WAVES[wave], freq, 0.9, 0.0, 0.0, samplerate=sr, **kw)
+    got = dev_pcm16(osc.render(n, start=start))
+    want = pcm16_of(co.osc(wave, start + n, sr, freq, 0.9, 0.0, 0.0, pulsewidth=0.25)[start:])
+    assert_within_lsb(got, want, 1, WAVES[wave])
+
+
+def test_sine_drift_matches_upstream_accumulation(cuda):
+    """Ten minutes in, upstream's `t += increment` has drifted by tens of LSB relative to
+    n*increment; the exact time base follows it."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, freq = 44100, 3520.0
+    start, n = 600 * sr - 5000, 5000
+    got = dev_pcm16(sb.Sine(freq, 0.95, samplerate=sr).render(n, start=start))
+    want = pcm16_of(co.osc(0, start + n, sr, freq, 0.95)[start:])
+    assert_within_lsb(got, want, 1, "sine at 10 min")
+    naive = pcm16_of(0.95 * np.sin(2 * np.pi * freq * np.arange(start, start + n) / sr))
+    assert np.abs(naive - want).max() > 3, "the drift this test is about has vanished"
+
+
+@pytest.mark.parametrize("cwave,mwave", [(0, 0), (3, 0), (1, 1), (2, 3), (4, 0), (0, 2), (3, 4)])
+def test_fm(cuda, cwave, mwave):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 48000, 5 * 48000 + 123
+    mkw = dict(pulsewidth=0.4) if mwave == 4 else {}
+    ckw = dict(pulsewidth=0.3) if cwave == 4 else {}
+    lfo = _make(sb, WAVES[mwave], 5.3, 0.04, 0.1, 0.01, samplerate=sr, **mkw)
+    osc = _make(sb, WAVES[cwave], 443.7, 0.7, 0.2, 0.0, fm_lfo=lfo, samplerate=sr, **ckw)
+    got = dev_pcm16(osc.render(n))
+    fm = co.osc(mwave, n, sr, 5.3, 0.04, 0.1, 0.01, pulsewidth=0.4)
+    want = pcm16_of(co.osc(cwave, n, sr, 443.7, 0.7, 0.2, 0.0, fm=fm, pulsewidth=0.3))
+    if cwave in (2, 3, 4):
+        # under FM the edge position depends on fp64 rounding noise of upstream's recurrence:
+        # allow edge samples whose phase is within 1e-7 cycles of the discontinuity
+        bad = np.abs(got.astype(np.int64) - want) > 1
+        assert bad.sum() <= 2, "%d edge mismatches" % bad.sum()
+    else:
+        assert_within_lsb(got, want, 1, "FM %s by %s" % (WAVES[cwave], WAVES[mwave]))
+
+
+def test_fm_chunked_equals_one_shot(cuda):
+    """blocks() renders in chunks and carries the FM prefix sum across them."""
+    import synthesizer_b200 as sb
+    sr = 48000
+    def mk():
+        return sb.Sine(440, 0.8, fm_lfo=sb.Sine(6, 0.05, samplerate=sr), samplerate=sr)
+    n = 70000
+    one = mk().render(n).cpu().numpy()
+    blocks = list(itertools.islice(mk().blocks(), (n + 511) // 512))
+    flat = np.array(list(itertools.chain.from_iterable(blocks)), dtype=np.float32)[:n]
+    assert len(blocks[0]) == 512
+    np.testing.assert_allclose(flat, one, atol=2e-6)
+    g = mk().generator()
+    first = [next(g) for _ in range(5)]
+    np.testing.assert_allclose(first, one[:5], atol=2e-6)
+
+
+def test_pulse_pwm(cuda):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 44100, 2 * 44100
+    pwm = sb.Sine(0.7, 0.4, bias=0.5, samplerate=sr)
+    osc = sb.Pulse(220.0, 0.8, pulsewidth=0.1, pwm_lfo=pwm, samplerate=sr)
+    got = dev_pcm16(osc.render(n))
+    pw = co.osc(0, n, sr, 0.7, 0.4, 0.0, 0.5)
+    want = pcm16_of(co.osc(4, n, sr, 220.0, 0.8, pwm=pw))
+    bad = np.abs(got.astype(np.int64) - want) > 1
+    assert bad.sum() <= 1      # an edge within fp32 resolution of the modulated width
+
+
+def test_white_noise_injected(cuda):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 44100, 44100
+    rng = np.random.default_rng(7)
+    u = rng.random(n // 4 + 2)
+    osc = sb.WhiteNoise(11025.0, 0.9, 0.02, samplerate=sr, noise_source=u)
+    got = dev_pcm16(osc.render(n))
+    want = pcm16_of(co.noise(n, sr, 11025.0, 0.9, 0.02, u))
+    assert_within_lsb(got, want, 1, "white noise")
+
+
+def test_white_noise_generated_is_uniform_and_held(cuda):
+    import synthesizer_b200 as sb
+    sr = 48000
+    v = sb.WhiteNoise(12000.0, 1.0, samplerate=sr).render(400000).cpu().numpy().reshape(-1, 4)
+    assert (v == v[:, :1]).all()
+    d = v[:, 0]
+    assert -1.0 <= d.min() < -0.99 and 0.99 < d.max() <= 1.0
+    assert abs(d.mean()) < 0.01 and abs(d.std() - 1 / np.sqrt(3)) < 0.01
+
+
+def test_envelope_filter(cuda):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr = 48000
+    for (a, d, s, sl, r) in [(0.05, 0.1, 0.3, 0.6, 0.2), (0.0, 0.1, 0.0, 0.5, 0.1), (0.1, 0.0, 0.2, 1.0, 0.0),
+                             (0.013, 0.027, 0.111, 0.35, 0.3333)]:
+        n = int((a + d + s + r) * sr) + 500
+        osc = sb.EnvelopeFilter(sb.Sawtooth(311.0, 0.9, samplerate=sr), a, d, s, sl, r)
+        got = dev_pcm16(osc.render(n))
+        want = pcm16_of(co.envelope(co.osc(3, n, sr, 311.0, 0.9), sr, a, d, s, sl, r))
+        assert_within_lsb(got, want, 1, "ADSR %s" % ((a, d, s, sl, r),))
+    osc = sb.EnvelopeFilter(sb.Sine(311.0, 0.9, samplerate=sr), 0.01, 0.02, 0.03, 0.5, 0.04, stop_at_end=True)
+    want = co.envelope(co.osc(0, 48000, sr, 311.0, 0.9), sr, 0.01, 0.02, 0.03, 0.5, 0.04, stop_at_end=True)
+    got = osc.render(48000)
+    assert got.numel() == len(want)
+    assert sum(len(b) for b in osc.blocks()) == len(want)
+
+
+def test_filters_chain(cuda):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co, synth_oracle as so
+    sr, n = 44100, 30000
+    src = lambda m: m.Triangle(523.25, 0.9, samplerate=sr)
+    lfo = lambda m: m.Sine(3.0, 0.5, bias=0.5, samplerate=sr)
+    got = dev_pcm16(sb.AbsFilter(sb.ClipFilter(sb.AmpModulationFilter(src(sb), lfo(sb)), -0.3, 0.6)).render(n))
+    want = pcm16_of(so.render_floats(so.AbsFilter(so.ClipFilter(so.AmpModulationFilter(src(so), lfo(so)), -0.3, 0.6)), n))
+    assert_within_lsb(got, want, 1, "amp-mod/clip/abs")
+    got = dev_pcm16(sb.MixingFilter(sb.Sine(220, 0.3, samplerate=sr), sb.Square(330, 0.2, samplerate=sr),
+                                    sb.DelayFilter(sb.Sawtooth(110, 0.4, samplerate=sr), 0.1),
+                                    sb.DelayFilter(sb.Sine(55, 0.05, samplerate=sr), -0.05)).render(n))
+    want = pcm16_of(so.render_floats(so.MixingFilter(so.Sine(220, 0.3, samplerate=sr), so.Square(330, 0.2, samplerate=sr),
+                                                    so.DelayFilter(so.Sawtooth(110, 0.4, samplerate=sr), 0.1),
+                                                    so.DelayFilter(so.Sine(55, 0.05, samplerate=sr), -0.05)), n))
+    assert_within_lsb(got, want, 1, "mix/delay")
+
+
+def test_echo_filter(cuda):
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 48000, 3 * 48000
+    env = (0.01, 0.05, 0.2, 0.5, 0.3)
+    osc = sb.EchoFilter(sb.EnvelopeFilter(sb.Sawtooth(440.0, 0.5, samplerate=sr), *env), 0.25, 5, 0.13, 0.55)
+    got = dev_pcm16(osc.render(n))
+    dry = co.envelope(co.osc(3, n, sr, 440.0, 0.5), sr, *env)
+    want = pcm16_of(co.echo(dry, sr, 0.25, 5, 0.13, 0.55))
+    assert_within_lsb(got, want, 1, "echo")
+    # streaming in chunks must give the same as one shot
+    blocks = list(itertools.islice(sb.EchoFilter(sb.EnvelopeFilter(sb.Sawtooth(440.0, 0.5, samplerate=sr), *env),
+                                                 0.25, 5, 0.13, 0.55).blocks(), 120))
+    flat = np.array(list(itertools.chain.from_iterable(blocks)), dtype=np.float32)
+    np.testing.assert_allclose(flat, osc.render(len(flat)).cpu().numpy(), atol=1e-6)
+
+
+def test_wavesynth_config1_sine_440(cuda):
+    """BASELINE config 1: single 440 Hz sine, 1 s mono 44.1 kHz int16 rendered to a Sample."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    s = sb.WaveSynth(samplerate=44100).sine(440, 1.0)
+    assert (s.samplerate, s.samplewidth, s.nchannels, len(s)) == (44100, 2, 1, 44100)
+    got = np.frombuffer(s.get_frames(), dtype="<i2")
+    want = np.trunc(co.osc(0, 44100, 44100, 440.0, 0.9999 * 32767)).astype(np.int64)
+    assert_within_lsb(got, want, 1, "config 1")
+
+
+def test_overflow_raises(cuda):
+    import synthesizer_b200 as sb
+    with pytest.raises(OverflowError):
+        sb.Sample.from_oscillator(sb.Sine(440, 1.5, samplerate=44100), 0.1)

