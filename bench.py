@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""
+bench.py — the headline measurement (BASELINE.json: "Msamples/s rendered (FM+ADSR+mix) at
+1/2/4/8 B200; % HBM/SFU roofline").
+
+Workload (config.workload): the per-GPU share of BASELINE config 5 — 8192 independent FM
+voices (Sine carrier FM'd by a Sine, per-voice ADSR, stereo pan) x 10 s at 48 kHz per GPU,
+weak scaling; at N=8 that is exactly config 5 (65,536 voices, voice-sharded, one NCCL reduce
+of the partial mixes, PCM conversion once on rank 0).  A step = one full render of the bank.
+Msamples/s counts voice-samples (voices x frames) per second, whole job.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          our arm
+  python bench.py --impl reference ...                          the CPU arm (see below)
+
+The reference arm times the pure-Python restatement of synthplayer's own algorithm
+(oracle/synth_oracle.py — the reference itself is absent offline, so kind="port") on all host
+cores, on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR = 48000
+SECONDS = 10.0
+VOICES_PER_GPU = 8192
+METRIC = "Msamples/s rendered (FM+ADSR+mix)"
+UNIT = "Msamples/s"
+
+
+# ----------------------------------------------------------------------------- workload
+def voice_params(nvoices, seed=5):
+    """Synthetic, seeded voice parameters (pure numpy; shared by both arms)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    p = {
+        "c_freq": rng.uniform(55.0, 3520.0, nvoices),
+        "c_phase": rng.random(nvoices),
+        "m_freq": rng.uniform(0.5, 220.0, nvoices),
+        "m_phase": rng.random(nvoices),
+        "depth": rng.uniform(0.002, 0.05, nvoices),
+        "amp": rng.uniform(0.3, 1.0, nvoices),
+        # the envelope spans the whole 10 s so no voice goes silent early (no skipped work)
+        "attack": rng.uniform(0.01, 1.0, nvoices),
+        "decay": rng.uniform(0.05, 1.0, nvoices),
+        "sustain_level": rng.uniform(0.3, 1.0, nvoices),
+        "release": rng.uniform(0.5, 3.0, nvoices),
+        "pan": rng.uniform(-1.0, 1.0, nvoices),
+    }
+    p["sustain"] = SECONDS - p["attack"] - p["decay"] - p["release"]
+    return p
+
+
+def build_voices(p, lo, hi, total_voices):
+    """ctypes array of sb_voice for voices [lo, hi)."""
+    from synthesizer_b200 import _cabi as C, _device as D
+    arr = (C.Voice * (hi - lo))()
+    for i, v in enumerate(range(lo, hi)):
+        a = arr[i]
+        a.c_wave, a.m_wave = C.WAVE_SINE, C.WAVE_SINE
+        a.c_freq, a.c_phase = p["c_freq"][v], p["c_phase"][v]
+        a.m_freq, a.m_phase = p["m_freq"][v], p["m_phase"][v]
+        a.c_amp, a.c_bias, a.c_pw = p["amp"][v] / total_voices * 8.0, 0.0, 0.1
+        a.m_amp, a.m_bias, a.m_pw = p["depth"][v], 0.0, 0.1
+        a.gain_l, a.gain_r = (1 - p["pan"][v]) / 2, (1 + p["pan"][v]) / 2
+        a.env = D.build_envelope(SR, p["attack"][v], p["decay"][v], p["sustain"][v],
+                                 p["sustain_level"][v], p["release"][v])
+    return arr
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, x in zip(names, r[2:6]) if x.lower() == "active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+CPU_VOICES_PER_PROC = 8
+CPU_FRAMES = 96000
+
+
+def _cpu_worker(args):
+    """Pure-Python port: render `hi-lo` voices x `frames`, pan and mix them, convert to PCM."""
+    lo, hi, frames, seed = args
+    from oracle import synth_oracle as so
+    p = voice_params(VOICES_PER_GPU, seed)
+    left, right = [0.0] * frames, [0.0] * frames
+    t0 = time.perf_counter()
+    for v in range(lo, hi):
+        lfo = so.Sine(p["m_freq"][v], p["depth"][v], p["m_phase"][v], samplerate=SR)
+        car = so.Sine(p["c_freq"][v], p["amp"][v] / VOICES_PER_GPU * 8.0, p["c_phase"][v], fm_lfo=lfo, samplerate=SR)
+        env = so.EnvelopeFilter(car, p["attack"][v], p["decay"][v], p["sustain"][v], p["sustain_level"][v], p["release"][v])
+        gl, gr = (1 - p["pan"][v]) / 2, (1 + p["pan"][v]) / 2
+        for i, x in enumerate(so.render_floats(env, frames)):
+            left[i] += x * gl
+            right[i] += x * gr
+    so.to_pcm(left)
+    so.to_pcm(right)
+    return time.perf_counter() - t0
+
+
+def cpu_port_throughput(cores, voices_per_core=CPU_VOICES_PER_PROC, frames=CPU_FRAMES):
+    """Msamples/s (voice-samples) of the pure-Python port on `cores` processes."""
+    import multiprocessing as mp
+    jobs = [(c * voices_per_core, (c + 1) * voices_per_core, frames, 5) for c in range(cores)]
+    t0 = time.perf_counter()
+    if cores == 1:
+        _cpu_worker(jobs[0])
+    else:
+        with mp.get_context("fork").Pool(cores) as pool:
+            pool.map(_cpu_worker, jobs)
+    dt = time.perf_counter() - t0
+    return cores * voices_per_core * frames / dt / 1e6, dt
+
+
+def cpu_c_port_throughput(voices=48, frames=int(SR * SECONDS)):
+    """The same algorithm compiled (oracle/oracle.c), one thread — reported beside the Python figure."""
+    import numpy as np
+    from oracle import coracle as co
+    p = voice_params(VOICES_PER_GPU)
+    P = np.zeros((voices, co.VOICE_STRIDE))
+    for v in range(voices):
+        P[v] = [0, p["c_freq"][v], p["amp"][v] / VOICES_PER_GPU * 8.0, p["c_phase"][v], 0, 0.1, 0, p["m_freq"][v],
+                p["depth"][v], p["m_phase"][v], 0, p["attack"][v], p["decay"][v], p["sustain"][v],
+                p["sustain_level"][v], p["release"][v], (1 - p["pan"][v]) / 2, (1 + p["pan"][v]) / 2]
+    t0 = time.perf_counter()
+    co.voice_bank(P, frames, SR)
+    dt = time.perf_counter() - t0
+    return voices * frames / dt / 1e6, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    frames = CPU_FRAMES
+    for _ in range(args.warmup and 1):
+        cpu_port_throughput(cores, 1, 4000)
+    vals = []
+    t_all = time.perf_counter()
+    for _ in range(args.steps):
+        v, dt = cpu_port_throughput(cores, CPU_VOICES_PER_PROC, frames)
+        vals.append(v)
+    wall = time.perf_counter() - t_all
+    value = sum(vals) / len(vals)
+    sample = "%d processes x %d voices x %d frames per step (pure-Python port of the FM+ADSR+mix chain)" % (
+        cores, CPU_VOICES_PER_PROC, frames)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference source absent offline (/root/reference holds only README.md): this is the oracle port",
+    }))
+
+
+def workload_config(n):
+    return {"workload": "config5-share: %d FM voices/GPU (Sine carrier FM by Sine, ADSR, pan) x %g s @ %d Hz stereo, "
+                        "voice-sharded over %d GPU(s), NCCL reduce of partial mixes, int16 PCM on rank 0"
+                        % (VOICES_PER_GPU, SECONDS, SR, n),
+            "voices_total": VOICES_PER_GPU * n, "frames": int(SR * SECONDS), "samplerate": SR, "channels": 2,
+            "l2": "no flush: each step writes and re-reads %d MB of per-group partial mixes (> 126 MB L2); "
+                  "inputs are 1.3 MB of voice parameters" % (VOICES_PER_GPU // 64 * int(SR * SECONDS) * 8 // 1000000)}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C, _device as D
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    frames = int(SR * SECONDS)
+    total_voices = VOICES_PER_GPU * world
+    p = voice_params(total_voices)
+    lo, hi = sb.voicebank.shard_range(total_voices, rank, world)
+    arr = build_voices(p, lo, hi, total_voices)
+    nbytes_voices = ctypes.sizeof(arr)
+    host_voices = torch.frombuffer(bytearray(ctypes.string_at(ctypes.addressof(arr), nbytes_voices)),
+                                   dtype=torch.uint8).pin_memory()
+    bank = sb.VoiceBank(SR)
+    voices_dev = host_voices.to(D.device())
+    pcm = D.empty(2 * frames, torch.int16)
+    ovf = D.zeros(1, torch.int64)
+    host_pcm = torch.empty(2 * frames, dtype=torch.int16).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        mix = bank.render(frames, voices_dev=voices_dev)
+        if world > 1:
+            dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            C.call("sb_f32_to_pcm16", D.ptr(mix), 2 * frames, 32767.0, D.ptr(pcm), D.ptr(ovf), D.stream())
+
+    def step_e2e():
+        vd = host_voices.to(D.device(), non_blocking=True)       # H2D of this step's inputs
+        mix = bank.render(frames, voices_dev=vd)
+        if world > 1:
+            dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            C.call("sb_f32_to_pcm16", D.ptr(mix), 2 * frames, 32767.0, D.ptr(pcm), D.ptr(ovf), D.stream())
+            host_pcm.copy_(pcm, non_blocking=True)                # D2H of the step's result
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=D.device())
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = D.launch_count()
+    ms = timed(step_resident, args.steps)
+    launches = D.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    assert int(ovf.item()) == 0, "PCM overflow in the bench mix"
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    samples_per_step = total_voices * frames
+    value = samples_per_step * args.steps / (ms / 1e3) / 1e6
+    e2e_value = samples_per_step * args.steps / (ms_e2e / 1e3) / 1e6
+
+    # ---- roofline of the dominant kernel, timed alone on this rank ------------------
+    roofline = None
+    extra = {}
+    if rank == 0:
+        plan = C.BankPlan()
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        C.call("sb_bank_plan_make", hi - lo, frames, sms, ctypes.byref(plan))
+        reps = 3
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        l0 = D.launch_count()
+        ev[0].record()
+        for _ in range(reps):
+            bank.render(frames, voices_dev=voices_dev)
+        ev[1].record()
+        torch.cuda.synchronize()
+        render_ms = ev[0].elapsed_time(ev[1]) / reps
+        kernels_per_render = (D.launch_count() - l0) // reps
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        # SFU roofline (north_star: "for transcendental-heavy FM it is SFU/FP32 pipe utilisation"):
+        # 2 sine evaluations per voice-sample (modulator + carrier); peak = 16 MUFU/clk/SM
+        # x SMs x the SM clock measured under this load.
+        sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965
+        peak_gsin = 16 * sms * sm_mhz * 1e6 / 1e9
+        achieved_gsin = 2 * (hi - lo) * frames / (render_ms / 1e3) / 1e9
+        roofline = {"bound": "sfu", "kernel": "bank_render (carry pre-pass + render + fold)",
+                    "achieved": achieved_gsin, "peak": peak_gsin, "unit": "Gsin/s",
+                    "frac": achieved_gsin / peak_gsin, "traffic": None,
+                    "peak_source": "16 MUFU lanes/clk/SM x %d SMs x %d MHz (clock sampled under load)" % (sms, sm_mhz),
+                    "kernels_per_render": kernels_per_render, "render_ms": render_ms,
+                    "hbm_algorithmic_bytes": int(plan.partial_bytes * 2 + 2 * frames * 4 * 2),
+                    "hbm_peak_gbs": peaks.get("hbm_gbs", 6650.0),
+                    "hbm_peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"}
+        extra["plan"] = {"voices_per_group": plan.voices_per_group, "ngroups": plan.ngroups, "nspans": plan.nspans,
+                         "span_len": plan.span_len}
+        # ---- CPU baseline (bounded sample, rank 0, N=1 only) -------------------------
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            v1, dt1 = cpu_port_throughput(1)
+            vn, dtn = cpu_port_throughput(cores)
+            vc, dtc = cpu_c_port_throughput()
+            cpu = {"value": vn, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": "pure-Python port (oracle/synth_oracle.py), %d processes x 8 voices x 96000 frames (%.1f s); "
+                             "single process: %.4f Msamples/s (%.1f s); compiled C port, 1 thread, 48 voices x 10 s: "
+                             "%.2f Msamples/s (%.1f s)" % (cores, dtn, v1, dt1, vc, dtc),
+                   "single_process_value": v1, "c_port_1thread_value": vc}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 values / f64 phase", "data": "synthetic",
+            "config": workload_config(world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_voices,
+                    "d2h_bytes_per_step": 2 * frames * 2, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "parity": "unpinned (reference source absent offline; oracle = restatement)", **extra,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)  # reference arm: each step is ~5 s of CPU work
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
