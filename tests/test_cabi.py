@@ -1,0 +1,129 @@
+"""
+CPU-only checks of the boundary: the library loads, exports every symbol the header declares
+(and nothing the binding lacks), the host-only helpers (time base, ADSR boundaries) agree with
+the serial loops they stand in for, and argument validation fails loudly.  No GPU calls.
+"""
+import ctypes
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+
+from synthesizer_b200 import _cabi as C
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "synth_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(sb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    syms = header_symbols()
+    assert len(syms) > 40
+    for s in syms:
+        assert hasattr(C.lib, s), "header declares %s but the library does not export it" % s
+    assert sorted(C.EXPORTED) == syms, "ctypes binding and header disagree: %s" % (
+        set(C.EXPORTED) ^ set(syms))
+    assert C.lib.sb_abi_version() == 1
+
+
+def test_struct_sizes_match_the_c_side():
+    # sizes the kernels assume (sb_voice is copied to shared memory word by word)
+    assert ctypes.sizeof(C.TimeSeg) == 24
+    assert ctypes.sizeof(C.Envelope) == 80
+    assert ctypes.sizeof(C.Voice) == 152
+    assert ctypes.sizeof(C.OscParams) == 56
+
+
+@pytest.mark.parametrize("inc", [1 / 48000, 2 * math.pi / 44100, 1 / 22050, 2 * math.pi / 96000, 0.1])
+def test_timebase_is_bit_identical_to_serial_accumulation(inc):
+    segs = (C.TimeSeg * 256)()
+    n = C.lib.sb_timebase_build(inc, 1 << 40, segs, 256)
+    assert 0 < n < 100
+    N = 3_000_000
+    serial = np.concatenate([[0.0], np.cumsum(np.full(N - 1, inc))])      # cumsum adds sequentially
+    starts = np.array([segs[i].n_start for i in range(n)])
+    ts = np.array([segs[i].t_start for i in range(n)])
+    st = np.array([segs[i].step for i in range(n)])
+    idx = np.searchsorted(starts, np.arange(N), side="right") - 1
+    closed = ts[idx] + (np.arange(N) - starts[idx]).astype(np.float64) * st[idx]
+    assert np.array_equal(serial, closed)
+    for k in (0, 1, 2, 12345, N - 1):
+        assert C.lib.sb_timebase_at(segs, n, k) == serial[k]
+    lim = serial[54321]
+    assert C.lib.sb_timebase_first_ge(segs, n, 0, lim) == 54321
+    assert C.lib.sb_timebase_first_ge(segs, n, 0, np.nextafter(lim, 1e9)) == 54322
+    assert C.lib.sb_timebase_first_ge(segs, n, 60000, lim) == 60000
+
+
+@pytest.mark.parametrize("adsr", [(0.05, 0.1, 0.3, 0.6, 0.2), (0.0, 0.1, 0.0, 0.5, 0.1), (0.1, 0.0, 0.2, 1.0, 0.0),
+                                  (0.013, 0.027, 0.111, 0.35, 0.3333), (1 / 48000, 2 / 48000, 0.0, 0.0, 0.01)])
+def test_envelope_boundaries_match_the_serial_generator(adsr):
+    """Replays upstream's EnvelopeFilter loop (oracle) and compares segment boundaries."""
+    from oracle import coracle as co
+    sr = 48000
+    env = C.Envelope()
+    C.call("sb_envelope_build", float(sr), *[float(x) for x in adsr], ctypes.byref(env))
+    n = int(sum(adsr[:3] + adsr[4:]) * sr) + 100
+    ones = np.ones(n)
+    shape = co.envelope(ones, sr, *adsr)                      # the envelope itself
+    cut = co.envelope(ones, sr, *adsr, stop_at_end=True)
+    assert len(cut) == env.n_r + env.extra
+    k = np.arange(n)
+    model = np.where(k < env.n_a, k * env.a_slope,
+             np.where(k < env.n_d, 1.0 + (k - env.n_a) * env.d_slope,
+              np.where(k < env.n_s, env.sustain_level,
+               np.where(k < env.n_r, env.sustain_level + (k - env.n_s) * env.r_slope,
+                np.where((k == env.n_r) & (env.extra == 1), env.amp_extra, 0.0)))))
+    np.testing.assert_allclose(model, shape, rtol=0, atol=1e-9)
+    # the zero / non-zero pattern (where segments start and stop) is exact
+    assert np.array_equal(model != 0, shape != 0)
+
+
+def test_bad_arguments_fail_loudly():
+    segs = (C.TimeSeg * 4)()
+    assert C.lib.sb_timebase_build(-1.0, 10, segs, 4) < 0
+    assert b"bad arguments" in C.lib.sb_last_error()
+    with pytest.raises(C.SbError):
+        C.call("sb_envelope_build", 48000.0, -1.0, 0.0, 0.0, 0.5, 0.0, ctypes.byref(C.Envelope()))
+    plan = C.BankPlan()
+    with pytest.raises(C.SbError):
+        C.call("sb_bank_plan_make", 0, 100, 148, ctypes.byref(plan))
+    assert C.lib.sb_pcm16_ratecv_frames(8, 44100, 48000) == 8
+    assert C.lib.sb_pcm16_ratecv_frames(8, 48000, 22050) == 4
+    assert C.lib.sb_pcm16_ratecv_frames(0, 48000, 22050) == 0
+
+
+def test_bank_plan_covers_the_work():
+    for nv, frames in [(1, 100), (1, 2_880_000), (128, 480_000), (8192, 480_000), (65536, 480_000), (3, 257)]:
+        plan = C.BankPlan()
+        C.call("sb_bank_plan_make", nv, frames, 148, ctypes.byref(plan))
+        assert plan.voices_per_group * plan.ngroups >= nv
+        assert plan.span_len % 256 == 0 and plan.span_len * plan.nspans >= frames
+        assert plan.span_len * (plan.nspans - 1) < frames
+        assert 1 <= plan.voices_per_group <= 64
+
+
+def test_no_gpu_means_loud_failure_not_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import synthesizer_b200 as sb
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        sb.Sine(440).render(16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        sb.Sample.from_raw_frames(b"\0\0", 2, 44100, 1)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "synthesizer_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".sh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("no CPU", ""), "%s mentions the oracle" % f
