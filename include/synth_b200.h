@@ -109,6 +109,33 @@ int sb_fm_prefix_f64(const float *lfo_dev, const sb_time_seg *tb_dev, int nsegs,
                      int64_t count, double *carry_dev, double *out_dev, void *scratch_dev,
                      void *stream);
 
+/* sb_fm_prefix_f64_noalloc — no counterpart in the reference; an addition of this library.
+ *
+ * The same FM prefix sum as sb_fm_prefix_f64, for callers that are not allowed to allocate
+ * device memory at all: a real-time audio callback (cudaMalloc/cudaFree synchronise the device
+ * and can stall the audio thread for milliseconds), a plugin host or engine that hands each
+ * component a fixed memory budget up front, or a process whose allocator already owns the
+ * whole GPU.  Such callers cannot provide the scratch buffer sb_fm_prefix_f64 asks for, so this
+ * variant keeps its scratch inside the library: a fixed 64 KiB array that is part of the
+ * loaded module on every GPU and lives until the process exits.  It allocates nothing — no
+ * cudaMalloc, no cudaFree, no library routine that would.  Inputs and outputs are still yours.
+ *
+ *  - Limit: count <= sb_fm_prefix_noalloc_max_count() (16,777,216 samples = 8192 tiles of
+ *    2048).  A larger count is refused with SB_ERANGE and a message; split the range into
+ *    consecutive calls (the carry continues the sum) or use sb_fm_prefix_f64.
+ *  - The first call on each device looks up the device address of the built-in array (a cheap
+ *    one-time runtime query, made with that device current).  Make that first call during
+ *    set-up, before you begin capturing a stream.
+ *  - All calls on a device share the one array, and it keeps whatever the previous call left
+ *    in it.  That is harmless for a single call (every slot is written before it is read,
+ *    nothing needs to start at zero), but two calls whose kernels overlap on the GPU — on
+ *    different streams, or from different threads — would overwrite each other's tile sums.
+ *    Keep calls to this entry point on one stream, or order them yourself.
+ */
+int64_t sb_fm_prefix_noalloc_max_count(void);
+int sb_fm_prefix_f64_noalloc(const float *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                             int64_t count, double *carry_dev, double *out_dev, void *stream);
+
 /* synthplayer.oscillators.WhiteNoise.blocks: value = (-amp + 2*amp*u) + bias, each draw held
  * for `cycles` = int(samplerate/frequency) samples.  u_dev[j] is draw number j (j counted
  * from draw0); parity tests inject the same draws on both sides. */

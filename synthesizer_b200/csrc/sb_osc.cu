@@ -2,6 +2,7 @@
 // Every kernel maps one thread to a run of consecutive sample indices, so the exact time
 // base cursor moves forward only, and global accesses are coalesced 128-bit where the
 // element type allows.
+#include <mutex>
 #include "sb_common.cuh"
 
 namespace sb {
@@ -379,6 +380,75 @@ extern "C" int sb_fm_prefix_f64(const float *lfo_dev, const sb_time_seg *tb_dev,
     if (count == 0) return SB_OK;
     int64_t ntiles = (count + kScanTile - 1) / kScanTile;
     double *tiles = (double *)scratch_dev;
+    int grid = grid_for(ntiles, 1, kMaxBlocks);
+    cudaStream_t s = (cudaStream_t)stream;
+    fm_tile_sums_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
+    SB_LAUNCH_CHECK();
+    fm_scan_tiles_kernel<<<1, kBlock, 0, s>>>(tiles, ntiles, carry_dev);
+    SB_LAUNCH_CHECK();
+    fm_scan_apply_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+// ------------------------------------------------------------------ FM prefix sum, no allocation
+// The same three kernels as sb_fm_prefix_f64, but the tile-sum scratch is this fixed array in
+// the library's device image instead of a buffer the caller has to allocate.  It exists once
+// per GPU that loads the library and stays resident until the process exits (64 KiB + 8 B).
+// One slot per 2048-sample tile plus one spare, hence the per-call limit below.
+#define SB_NOALLOC_MAX_TILES 8192
+static __device__ __align__(256) double g_noalloc_tile_sums[SB_NOALLOC_MAX_TILES + 1];
+
+namespace sb {
+constexpr int kNoallocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static double *g_noalloc_ptr[kNoallocMaxDevices] = {nullptr};
+
+// `g_noalloc_tile_sums` as written in host code is only a handle for the runtime; the address
+// kernels can dereference has to be asked for, per device, with that device current.
+static int noalloc_scratch(double **out)
+{
+    int dev = -1;
+    SB_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoallocMaxDevices) {
+        set_error("sb_fm_prefix_f64_noalloc: device ordinal %d is outside 0..%d", dev, kNoallocMaxDevices - 1);
+        return SB_ERANGE;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        SB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_tile_sums));
+        g_noalloc_ptr[dev] = static_cast<double *>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return SB_OK;
+}
+}  // namespace sb
+
+extern "C" int64_t sb_fm_prefix_noalloc_max_count(void)
+{
+    return (int64_t)SB_NOALLOC_MAX_TILES * kScanTile;
+}
+
+extern "C" int sb_fm_prefix_f64_noalloc(const float *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                                        int64_t count, double *carry_dev, double *out_dev, void *stream)
+{
+    SB_REQUIRE(lfo_dev && tb_dev && carry_dev && out_dev, "sb_fm_prefix_f64_noalloc: null pointer");
+    SB_REQUIRE(nsegs > 0 && nsegs <= kMaxSegs && n0 >= 0 && count >= 0, "sb_fm_prefix_f64_noalloc: bad range");
+    const int64_t max_count = (int64_t)SB_NOALLOC_MAX_TILES * kScanTile;
+    if (count > max_count) {
+        set_error("sb_fm_prefix_f64_noalloc: count %lld exceeds the built-in scratch (at most %lld samples per "
+                  "call); split the range or use sb_fm_prefix_f64 with caller-provided scratch",
+                  (long long)count, (long long)max_count);
+        return SB_ERANGE;
+    }
+    if (count == 0) return SB_OK;
+    double *tiles = nullptr;
+    int rc = noalloc_scratch(&tiles);
+    if (rc) return rc;
+    // Nothing in the scratch has to start at zero: phase 1 writes slot [0, ntiles) before
+    // phase 2 reads exactly those slots, so whatever an earlier call left behind is never seen.
+    int64_t ntiles = (count + kScanTile - 1) / kScanTile;
     int grid = grid_for(ntiles, 1, kMaxBlocks);
     cudaStream_t s = (cudaStream_t)stream;
     fm_tile_sums_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
