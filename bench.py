@@ -239,7 +239,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step_resident():
-        mix = bank.render(frames, voices_dev=voices_dev)
+        mix = bank.render(frames, voices_dev=voices_dev, generic_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -247,7 +247,7 @@ def run_ours(args):
 
     def step_e2e():
         vd = host_voices.to(D.device(), non_blocking=True)       # H2D of this step's inputs
-        mix = bank.render(frames, voices_dev=vd)
+        mix = bank.render(frames, voices_dev=vd, generic_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -292,14 +292,14 @@ def run_ours(args):
     if rank == 0:
         plan = C.BankPlan()
         sms = torch.cuda.get_device_properties(local).multi_processor_count
-        C.call("sb_bank_plan_make", hi - lo, frames, sms, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", hi - lo, frames, sms, D.timebase_rad(SR).nsegs, ctypes.byref(plan))
         reps = 3
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         l0 = D.launch_count()
         ev[0].record()
         for _ in range(reps):
-            bank.render(frames, voices_dev=voices_dev)
+            bank.render(frames, voices_dev=voices_dev, generic_voices=0)
         ev[1].record()
         torch.cuda.synchronize()
         render_ms = ev[0].elapsed_time(ev[1]) / reps
@@ -324,7 +324,7 @@ def run_ours(args):
                     "hbm_peak_gbs": peaks.get("hbm_gbs", 6650.0),
                     "hbm_peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"}
         extra["plan"] = {"voices_per_group": plan.voices_per_group, "ngroups": plan.ngroups, "nspans": plan.nspans,
-                         "span_len": plan.span_len}
+                         "span_len": plan.span_len, "fast_nspans": plan.fast_nspans, "fast_span_len": plan.fast_span_len}
         # ---- CPU baseline (bounded sample, rank 0, N=1 only) -------------------------
         cpu = None
         if world == 1 and not args.no_cpu_baseline:

@@ -202,21 +202,35 @@ typedef struct sb_voice {
 
 typedef struct sb_bank_plan {
     int32_t nvoices, voices_per_group, ngroups, nspans;
-    int64_t frames, span_len;            /* span_len is a multiple of 256 */
-    int64_t carry_bytes;                 /* scratch: per (voice, span) fp64 LFO sums */
-    int64_t partial_bytes;               /* scratch: ngroups * frames * 2 floats */
+    int64_t frames, span_len;            /* generic path: span_len is a multiple of 256 */
+    int64_t fast_span_len;               /* fast path: a multiple of 256, at most 8*256 */
+    int32_t fast_nspans;
+    int32_t nsegs_rad;                   /* width of the closed-form FM table */
+    int32_t generic_voices;              /* hint: 0 = every voice is fast (skip the generic kernels),
+                                            -1 = unknown (run them; they exit early per group) */
+    int32_t reserved;
+    int64_t off_fastv, off_tab;          /* layout of the scratch buffer */
+    int64_t carry_bytes;                 /* size of scratch_dev: span sums + per-voice constants + FM tables */
+    int64_t partial_bytes;               /* size of partial_dev: ngroups * (2*frames rounded up to 4) floats */
 } sb_bank_plan;
 
-/* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames`. */
-int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, sb_bank_plan *plan);
+/* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames`.
+ * nsegs_rad = segment count of the 2*pi/samplerate time base. */
+int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, int nsegs_rad, sb_bank_plan *plan);
+
+/* 1 when the voice takes the fast path (Sine/Triangle carrier, no FM or a Sine modulator):
+ * fp32 per-sample arithmetic off one fp64 base per 8 samples, SFU sine, closed-form FM sums.
+ * Other voices take the generic path (per-sample fp64 phase, exact edge positions). */
+int sb_voice_is_fast(const sb_voice *voice, double samplerate);
 
 /* Renders frames [n0, n0+plan->frames) of all voices.  tb_rad_dev / tb_cyc_dev: time bases
- * for increment 2*pi/sr and 1/sr.  carry_dev and partial_dev are scratch of the sizes in the
- * plan.  mix_dev receives plan->frames interleaved (left,right) float pairs. */
+ * for increment 2*pi/sr and 1/sr.  scratch_dev (plan->carry_bytes) and partial_dev
+ * (plan->partial_bytes, may be NULL when ngroups == 1) are caller-provided scratch.
+ * mix_dev receives plan->frames interleaved (left,right) float pairs. */
 int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan *plan,
                        const sb_time_seg *tb_rad_dev, int nsegs_rad,
                        const sb_time_seg *tb_cyc_dev, int nsegs_cyc,
-                       int64_t n0, double samplerate, double *carry_dev, float *partial_dev,
+                       int64_t n0, double samplerate, void *scratch_dev, float *partial_dev,
                        float *mix_dev, void *stream);
 
 /* ------------------------------------------------------------------ integer PCM -------

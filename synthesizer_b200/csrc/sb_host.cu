@@ -75,8 +75,11 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     SB_CUDA_CHECK(cudaGetDevice(&dev));
     SB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     sb_bank_plan plan;
-    rc = sb_bank_plan_make(nvoices, frames, sms, &plan);
+    rc = sb_bank_plan_make(nvoices, frames, sms, (int)g_tb.rad.size(), &plan);
     if (rc) return rc;
+    plan.generic_voices = 0;
+    for (int v = 0; v < nvoices; v++)
+        if (!sb_voice_is_fast(&voices[v], samplerate)) plan.generic_voices++;
 
     const size_t b_voices = align256((size_t)nvoices * sizeof(sb_voice));
     const size_t b_rad = align256(g_tb.rad.size() * sizeof(sb_time_seg));
@@ -92,7 +95,7 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     sb_voice *d_voices = (sb_voice *)p; p += b_voices;
     sb_time_seg *d_rad = (sb_time_seg *)p; p += b_rad;
     sb_time_seg *d_cyc = (sb_time_seg *)p; p += b_cyc;
-    double *d_carry = (double *)p; p += b_carry;
+    void *d_carry = (void *)p; p += b_carry;
     float *d_partial = (float *)p; p += b_partial;
     float *d_mix = (float *)p; p += b_mix;
     int16_t *d_pcm = (int16_t *)p; p += b_pcm;

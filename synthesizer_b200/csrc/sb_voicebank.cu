@@ -1,20 +1,63 @@
 // The fused hot path: a bank of FM voices with ADSR, mixed to stereo.
 //
 // Decomposition: work unit = (group of voices) x (span of consecutive frames), one WARP per
-// unit.  A warp walks its span in sub-tiles of 256 frames (8 consecutive frames per lane) and,
-// for every voice of its group, evaluates modulator -> weighted prefix sum (the FM recurrence
-// in closed form) -> carrier -> ADSR -> pan, accumulating the voice sum in registers.  The
-// only cross-lane step is one fp64 warp scan per voice per sub-tile; warps never synchronise
-// with each other.  The running FM sum of each voice lives in shared memory (one fp64 per
-// voice per warp) and starts from a per-(voice, span) carry computed by a pre-pass.
+// unit; warps never synchronise with each other.  A warp walks its span in sub-tiles of 256
+// frames (8 consecutive frames per lane) and, for every voice of its group, evaluates
+// modulator -> FM prefix sum -> carrier -> ADSR -> pan, accumulating the voice sum in
+// registers; one coalesced 128-bit store per lane pair of frames writes the group's partial
+// mix, and a fold kernel sums the groups.
+//
+// Two voice classes share that decomposition:
+//
+//  FAST    continuous carrier (Sine, Triangle) with no FM or a Sine modulator.  Everything
+//          that needs fp64 is done once per lane per sub-tile (exact time base, phase base
+//          reduced mod one turn); the 8 samples of the run advance in fp32 from that base and
+//          use the SFU sine.  The FM prefix sum has a closed form for a Sine modulator
+//          (sum of sin over an arithmetic progression), evaluated in fp64 at every sub-tile
+//          start ("anchor") from a per-(voice, time-base segment) table; inside the sub-tile
+//          an fp32 warp scan supplies the rest.  No pre-pass over the samples, no running
+//          carry, and float error cannot build up over more than 256 frames.
+//
+//  GENERIC anything else (Square/Sawtooth/Pulse carriers, whose edges must fall on exactly
+//          the sample upstream's fp64 arithmetic puts them on; non-sine modulators).  Phase
+//          arithmetic per sample in explicitly rounded fp64, FM prefix by fp64 warp scan with
+//          a running carry that starts from per-(voice, span) sums computed by a pre-pass.
+//
+// The generic kernel runs after the fast one and adds into the same partial mixes.
 #include "sb_common.cuh"
 
 namespace sb {
 
-constexpr int kWarpsPerCta = 8;
 constexpr int kItems = 8;
 constexpr int kSub = 32 * kItems;            // frames per warp step
 constexpr int kMaxVoicesPerGroup = 64;
+
+constexpr int kGenWarps = 8;                 // generic kernel: warps per CTA
+constexpr int kFastWarps = 4;                // fast kernel: warps per CTA
+constexpr int kFastMaxSub = 8;               // fast kernel: sub-tiles per span (anchors in smem)
+
+enum : int {
+    FV_FAST = 1,
+    FV_HAS_MOD = 2,
+    FV_TRIANGLE = 4,
+    FV_ENV = 8,
+    FV_ENV_EXTRA = 16,
+    FV_BIAS = 32,
+};
+
+// Per-voice constants of the fast path, derived once per render by bank_prepare_kernel.
+struct FastVoice {
+    double fm, pcm;          // modulator frequency and start phase (radians)
+    double f0b, pc0;         // carrier frequency * (1 + modulator bias), start phase
+    double gd;               // carrier phase per unit of (sum of sin(theta_k)): f0 * inc_c * depth
+    long long n_a, n_d, n_s, n_r;
+    float wm, wc, gdf;       // fp32 per-sample increments: fm*inc_rad, f0b*inc_c, gd
+    float aL, aR, bL, bR;    // c_amp*gain, c_bias*gain
+    float a_slope, d_slope, r_slope, sl, amp_extra;
+    int flags;
+    int pad;
+};
+static_assert(sizeof(FastVoice) == 136 || sizeof(FastVoice) == 128, "FastVoice layout");
 
 struct BankArgs {
     const sb_voice *voices;
@@ -24,11 +67,292 @@ struct BankArgs {
     int nsegs_rad;
     const sb_time_seg *tb_cyc;
     int nsegs_cyc;
-    double *carry;        // [nvoices][nspans] per-span LFO sums (pre-pass), or null
+    double samplerate;
+    double *carry;        // [nvoices][nspans] per-span LFO sums of generic voices (pre-pass), or null
+    FastVoice *fastv;     // [nvoices]
+    double2 *tab;         // [nvoices][nsegs_rad]: closed-form table (A, C) per modulator segment
+    int fast_nspans;
+    int64_t fast_span_len;
     float *out;           // [ngroups][stride] partial mixes (or the mix itself if ngroups==1)
     int64_t out_stride;   // floats between groups: 2*frames rounded up to a multiple of 4
 };
 
+// ------------------------------------------------------------------ classification
+__host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplerate)
+{
+    if (V.c_wave != SB_WAVE_SINE && V.c_wave != SB_WAVE_TRIANGLE) return false;
+    const double inc_c = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0) / samplerate;
+    const double turns = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0);
+    // carrier advance per 8-sample run must stay small enough for fp32 increments
+    if (!(fabs(V.c_freq) * inc_c * 8.0 < 64.0 * turns)) return false;
+    if (V.m_wave == SB_WAVE_NONE) return true;
+    if (V.m_wave != SB_WAVE_SINE) return false;
+    const double w = V.m_freq * 6.283185307179586 / samplerate;      // modulator phase step
+    if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return false;            // closed form needs sin(w/2) != 0
+    if (!(fabs((double)V.m_amp) <= 4.0 && fabs((double)V.m_bias) <= 4.0)) return false;
+    return true;
+}
+
+// cos(r) for |r| <= pi + small, fp64 Taylor to r^26 (error < 1e-13)
+__device__ __forceinline__ double cos_reduced(double r)
+{
+    const double x = r * r;
+    double p = -1.0 / 403291461126605635584000000.0;           // -1/26!
+    p = fma(p, x, 1.0 / 620448401733239439360000.0);           // 1/24!
+    p = fma(p, x, -1.0 / 1124000727777607680000.0);            // -1/22!
+    p = fma(p, x, 1.0 / 2432902008176640000.0);                // 1/20!
+    p = fma(p, x, -1.0 / 6402373705728000.0);                  // -1/18!
+    p = fma(p, x, 1.0 / 20922789888000.0);                     // 1/16!
+    p = fma(p, x, -1.0 / 87178291200.0);                       // -1/14!
+    p = fma(p, x, 1.0 / 479001600.0);                          // 1/12!
+    p = fma(p, x, -1.0 / 3628800.0);                           // -1/10!
+    p = fma(p, x, 1.0 / 40320.0);                              // 1/8!
+    p = fma(p, x, -1.0 / 720.0);                               // -1/6!
+    p = fma(p, x, 1.0 / 24.0);                                 // 1/4!
+    p = fma(p, x, -0.5);
+    return fma(p, x, 1.0);
+}
+
+__device__ __forceinline__ double reduce_two_pi(double x)
+{
+    double k = rint(x * kInvTwoPi);
+    double r = fma(-k, kTwoPiHi, x);
+    return fma(-k, kTwoPiLo, r);
+}
+
+// ------------------------------------------------------------------ prepare (one thread per voice)
+__global__ void bank_prepare_kernel(BankArgs a)
+{
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= a.nvoices) return;
+    const sb_voice V = a.voices[v];
+    FastVoice F;
+    F.flags = 0;
+    F.pad = 0;
+    const bool fast = voice_is_fast(V, a.samplerate);
+    const bool tri = (V.c_wave == SB_WAVE_TRIANGLE);
+    const double inc_rad = 6.283185307179586 / a.samplerate;
+    const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
+    const bool has_mod = (V.m_wave != SB_WAVE_NONE);
+    const double mbias = has_mod ? (double)V.m_bias : 0.0;
+    F.fm = V.m_freq;
+    F.pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
+    F.f0b = V.c_freq * (1.0 + mbias);
+    F.pc0 = phase0_of(V.c_wave, V.c_phase);
+    F.gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
+    F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
+    F.wm = (float)(V.m_freq * inc_rad);
+    F.wc = (float)(F.f0b * inc_c);
+    F.gdf = (float)F.gd;
+    F.aL = V.c_amp * V.gain_l; F.aR = V.c_amp * V.gain_r;
+    F.bL = V.c_bias * V.gain_l; F.bR = V.c_bias * V.gain_r;
+    F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
+    F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
+    if (fast) F.flags |= FV_FAST;
+    if (has_mod) F.flags |= FV_HAS_MOD;
+    if (tri) F.flags |= FV_TRIANGLE;
+    if (V.env.enabled) F.flags |= FV_ENV;
+    if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
+    if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
+    a.fastv[v] = F;
+
+    if (fast && has_mod) {
+        // Closed form of sum_{k<n} sin(theta_k), theta_k = fm*t(k) + pcm, t piecewise linear:
+        // inside segment b (start n_b, t_b, step_b): theta_k = theta_b + (k-n_b)*w_b and
+        //   sum_{k=n_b}^{n-1} sin(theta_k) = [cos(theta_b - w_b/2) - cos(theta_b + (n-n_b-1/2) w_b)] / (2 sin(w_b/2)).
+        // tab[b] = (A_b, C_b) with C_b = 1/(2 sin(w_b/2)) and A_b = (sum over earlier segments)
+        // + C_b cos(theta_b - w_b/2), so the sum up to n in segment b is A_b - C_b cos(fm*(t(n) - step_b/2) + pcm).
+        double2 *row = a.tab + (int64_t)v * a.nsegs_rad;
+        double before = 0.0;
+        for (int b = 0; b < a.nsegs_rad; b++) {
+            const sb_time_seg s = a.tb_rad[b];
+            const double w = F.fm * s.step;
+            const double half = 0.5 * w;
+            const double sh = sin(half);
+            double C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
+            const double th_lo = F.fm * (s.t_start - 0.5 * s.step) + F.pcm;
+            double A = before + C * cos(th_lo);
+            row[b] = make_double2(A, C);
+            if (b + 1 < a.nsegs_rad) {
+                const double len = (double)(a.tb_rad[b + 1].n_start - s.n_start);
+                const double th_hi = F.fm * (s.t_start + (len - 0.5) * s.step) + F.pcm;
+                before = (C != 0.0) ? A - C * cos(th_hi) : before + len * sin(F.fm * s.t_start + F.pcm);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ float warp_scan_incl_f(float v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        float o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += o;
+    }
+    return v;
+}
+
+__device__ __forceinline__ float tri_shape(float cycles)
+{
+    // 4*(|((tt+0.75) % 1.0) - 0.5| - 0.25)
+    float t = cycles + 0.75f;
+    float f = t - floorf(t);
+    return 4.0f * (fabsf(f - 0.5f) - 0.25f);
+}
+
+// ------------------------------------------------------------------ fast kernel
+__global__ void __launch_bounds__(kFastWarps * 32)
+bank_fast_kernel(BankArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(smem);
+    sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
+    FastVoice *s_fv = reinterpret_cast<FastVoice *>(s_cyc + a.nsegs_cyc);
+    double *s_anchor_all = reinterpret_cast<double *>(s_fv + a.voices_per_group);
+
+    const int group = blockIdx.y;
+    const int v_begin = group * a.voices_per_group;
+    int nv = a.nvoices - v_begin;
+    if (nv > a.voices_per_group) nv = a.voices_per_group;
+
+    for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
+    for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
+    {
+        const int words = (int)(sizeof(FastVoice) / 4);
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.fastv + v_begin);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(s_fv);
+        for (int i = threadIdx.x; i < nv * words; i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int span = blockIdx.x * kFastWarps + warp;
+    if (span >= a.fast_nspans) return;                 // no block-wide sync after this point
+    double *s_anchor = s_anchor_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
+
+    const int64_t span_begin = (int64_t)span * a.fast_span_len;
+    int64_t span_end = span_begin + a.fast_span_len;
+    if (span_end > a.frames) span_end = a.frames;
+    const int nsub = (int)((span_end - span_begin + kSub - 1) / kSub);
+
+    // ---- anchors: closed-form FM sums at every sub-tile start, all lanes busy ------------
+    for (int idx = lane; idx < nv * nsub; idx += 32) {
+        const int v = idx / nsub, s = idx - v * nsub;
+        const FastVoice &F = s_fv[v];
+        double A = 0.0;
+        if ((F.flags & (FV_FAST | FV_HAS_MOD)) == (FV_FAST | FV_HAS_MOD)) {
+            const int64_t n = a.n0 + span_begin + (int64_t)s * kSub;
+            TimeCursor c;
+            c.seek(s_rad, a.nsegs_rad, n);
+            const double t = c.at(n);
+            const double arg = fma(F.fm, t - 0.5 * c.step, F.pcm);
+            const double2 ac = a.tab[(int64_t)(v_begin + v) * a.nsegs_rad + c.idx];
+            A = ac.x - ac.y * cos_reduced(reduce_two_pi(arg));
+        }
+        s_anchor[v * kFastMaxSub + s] = A;
+    }
+    __syncwarp();
+
+    float *out = a.out + (int64_t)group * a.out_stride;
+    TimeCursor cur_rad, cur_cyc;
+    cur_rad.seek(s_rad, a.nsegs_rad, a.n0 + span_begin + lane * kItems);
+    cur_cyc.seek(s_cyc, a.nsegs_cyc, a.n0 + span_begin + lane * kItems);
+    const float lane8 = (float)(lane * kItems);
+
+    for (int s = 0; s < nsub; s++) {
+        const int64_t sub = span_begin + (int64_t)s * kSub;
+        const int64_t nsub0 = a.n0 + sub;              // absolute index of the sub-tile's first frame
+        const int64_t i0 = sub + lane * kItems;
+        const int64_t n = a.n0 + i0;
+        const double Tr0 = cur_rad.at(n);              // exact serial time, radians base
+        const double Tc0 = cur_cyc.at(n);              // exact serial time, cycles base
+        float accL[kItems], accR[kItems];
+#pragma unroll
+        for (int j = 0; j < kItems; j++) accL[j] = accR[j] = 0.0f;
+
+        for (int v = 0; v < nv; v++) {
+            const FastVoice &F = s_fv[v];
+            const int flags = F.flags;
+            if (!(flags & FV_FAST)) continue;
+            // ---- ADSR over this sub-tile (warp-uniform): e(i) = e_sub + i*de when the 256
+            //      frames sit inside one segment, else per-sample below
+            float e_sub = 1.0f, de = 0.0f;
+            bool env_slow = false;
+            if (flags & FV_ENV) {
+                const int64_t lo = nsub0, hi = nsub0 + kSub;
+                if (lo > F.n_r) continue;                                   // silent: nothing to add
+                if (hi <= F.n_a) { e_sub = (float)lo * F.a_slope; de = F.a_slope; }
+                else if (lo >= F.n_a && hi <= F.n_d) { e_sub = 1.0f + (float)(lo - F.n_a) * F.d_slope; de = F.d_slope; }
+                else if (lo >= F.n_d && hi <= F.n_s) { e_sub = F.sl; }
+                else if (lo >= F.n_s && hi <= F.n_r) { e_sub = F.sl + (float)(lo - F.n_s) * F.r_slope; de = F.r_slope; }
+                else env_slow = true;
+            }
+            const float e0 = fmaf(lane8, de, e_sub);
+            const bool tri = flags & FV_TRIANGLE;
+            const double Tc = tri ? Tc0 : Tr0;
+
+            // ---- modulator: 8 sines from one fp64 phase base; exclusive sums for the FM prefix
+            float ps[kItems];
+            double B;
+            if (flags & FV_HAS_MOD) {
+                const float th0 = (float)reduce_two_pi(fma(F.fm, Tr0, F.pcm));
+                float run = 0.0f;
+#pragma unroll
+                for (int j = 0; j < kItems; j++) {
+                    ps[j] = run;
+                    run += __sinf(fmaf((float)j, F.wm, th0));
+                }
+                const float incl = warp_scan_incl_f(run, lane);
+                const double before = s_anchor[v * kFastMaxSub + s] + (double)(incl - run);
+                B = fma(F.gd, before, fma(F.f0b, Tc, F.pc0));
+            } else {
+#pragma unroll
+                for (int j = 0; j < kItems; j++) ps[j] = 0.0f;
+                B = fma(F.f0b, Tc, F.pc0);
+            }
+            // ---- carrier: phase base reduced to one turn, fp32 from there
+            const float b0 = tri ? (float)(B - rint(B)) : (float)reduce_two_pi(B);
+#pragma unroll
+            for (int j = 0; j < kItems; j++) {
+                const float ph = fmaf(F.gdf, ps[j], fmaf((float)j, F.wc, b0));
+                const float w = tri ? tri_shape(ph) : __sinf(ph);
+                float e = fmaf((float)j, de, e0);
+                if (env_slow) {
+                    const int64_t k = n + j;
+                    if (k < F.n_a) e = (float)k * F.a_slope;
+                    else if (k < F.n_d) e = 1.0f + (float)(k - F.n_a) * F.d_slope;
+                    else if (k < F.n_s) e = F.sl;
+                    else if (k < F.n_r) e = F.sl + (float)(k - F.n_s) * F.r_slope;
+                    else if (k == F.n_r && (flags & FV_ENV_EXTRA)) e = F.amp_extra;
+                    else e = 0.0f;
+                }
+                const float we = w * e;
+                accL[j] = fmaf(we, F.aL, accL[j]);
+                accR[j] = fmaf(we, F.aR, accR[j]);
+                if (flags & FV_BIAS) {
+                    accL[j] = fmaf(e, F.bL, accL[j]);
+                    accR[j] = fmaf(e, F.bR, accR[j]);
+                }
+            }
+        }
+
+        if (i0 + kItems <= span_end) {
+            float4 *dst = reinterpret_cast<float4 *>(out + i0 * 2);
+#pragma unroll
+            for (int q = 0; q < kItems / 2; q++)
+                dst[q] = make_float4(accL[2 * q], accR[2 * q], accL[2 * q + 1], accR[2 * q + 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < kItems; j++)
+                if (i0 + j < span_end) {
+                    out[(i0 + j) * 2] = accL[j];
+                    out[(i0 + j) * 2 + 1] = accR[j];
+                }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ generic path
 // Base value and step of a time base for a run of kItems+1 consecutive indices.
 struct TimeRun {
     double tb, step;
@@ -78,8 +402,8 @@ __device__ __forceinline__ float lfo_value(const sb_voice &V, double t)
     return __fadd_rn(__fmul_rn(s, V.m_amp), V.m_bias);
 }
 
-// ---------------------------------------------------------------- pre-pass: per-span LFO sums
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+// pre-pass: per-(voice, span) LFO sums of the generic FM voices
+__global__ void __launch_bounds__(kGenWarps * 32)
 bank_carry_kernel(BankArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -89,10 +413,11 @@ bank_carry_kernel(BankArgs a)
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int64_t unit = ((int64_t)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5));
+    const int64_t unit = ((int64_t)blockIdx.x * kGenWarps + (threadIdx.x >> 5));
     const int64_t nunits = (int64_t)a.nvoices * a.nspans;
     if (unit >= nunits) return;
     const int v = (int)(unit / a.nspans), span = (int)(unit % a.nspans);
+    if (a.fastv[v].flags & FV_FAST) return;            // closed form, no pre-pass
     const sb_voice V = a.voices[v];
     double acc = 0.0;
     if (V.m_wave != SB_WAVE_NONE) {
@@ -116,33 +441,46 @@ bank_carry_kernel(BankArgs a)
     if (lane == 0) a.carry[(int64_t)v * a.nspans + span] = acc;
 }
 
-// ---------------------------------------------------------------- main kernel
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-bank_render_kernel(BankArgs a)
+__global__ void __launch_bounds__(kGenWarps * 32)
+bank_generic_kernel(BankArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(smem);
     sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
     sb_voice *s_voices = reinterpret_cast<sb_voice *>(s_cyc + a.nsegs_cyc);
     double *s_carry = reinterpret_cast<double *>(s_voices + a.voices_per_group);
+    int *s_vidx = reinterpret_cast<int *>(s_carry + kGenWarps * a.voices_per_group);
+    __shared__ int s_ngeneric;
 
     const int group = blockIdx.y;
     const int v_begin = group * a.voices_per_group;
-    int nv = a.nvoices - v_begin;
-    if (nv > a.voices_per_group) nv = a.voices_per_group;
+    int nvg = a.nvoices - v_begin;
+    if (nvg > a.voices_per_group) nvg = a.voices_per_group;
+
+    // compact the generic voices of this group into shared memory (in voice order)
+    if (threadIdx.x == 0) {
+        int c = 0;
+        for (int v = 0; v < nvg; v++)
+            if (!(a.fastv[v_begin + v].flags & FV_FAST)) s_vidx[c++] = v_begin + v;
+        s_ngeneric = c;
+    }
+    __syncthreads();
+    const int nv = s_ngeneric;
+    if (nv == 0) return;                               // block-uniform
 
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
     {
         const int words = (int)(sizeof(sb_voice) / 4);
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.voices + v_begin);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(s_voices);
-        for (int i = threadIdx.x; i < nv * words; i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < nv * words; i += blockDim.x) {
+            const int v = i / words, w = i - v * words;
+            reinterpret_cast<uint32_t *>(s_voices)[i] = reinterpret_cast<const uint32_t *>(a.voices + s_vidx[v])[w];
+        }
     }
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int span = blockIdx.x * kWarpsPerCta + warp;
+    const int span = blockIdx.x * kGenWarps + warp;
     if (span >= a.nspans) return;                      // no block-wide sync after this point
     double *carry = s_carry + warp * a.voices_per_group;
 
@@ -150,7 +488,7 @@ bank_render_kernel(BankArgs a)
     for (int v = 0; v < nv; v++) {
         double c = 0.0;
         if (a.carry && s_voices[v].m_wave != SB_WAVE_NONE) {
-            const double *row = a.carry + (int64_t)(v_begin + v) * a.nspans;
+            const double *row = a.carry + (int64_t)s_vidx[v] * a.nspans;
             for (int s = lane; s < span; s += 32) c += row[s];
             c = warp_sum(c);
         }
@@ -232,18 +570,20 @@ bank_render_kernel(BankArgs a)
             }
         }
 
-        // 8 frames x 2 channels = 16 consecutive floats per lane
+        // add to what the fast kernel wrote: 8 frames x 2 channels = 16 consecutive floats per lane
         if (i0 + kItems <= span_end) {
             float4 *dst = reinterpret_cast<float4 *>(out + i0 * 2);
 #pragma unroll
-            for (int q = 0; q < kItems / 2; q++)
-                dst[q] = make_float4(accL[2 * q], accR[2 * q], accL[2 * q + 1], accR[2 * q + 1]);
+            for (int q = 0; q < kItems / 2; q++) {
+                float4 o = dst[q];
+                dst[q] = make_float4(o.x + accL[2 * q], o.y + accR[2 * q], o.z + accL[2 * q + 1], o.w + accR[2 * q + 1]);
+            }
         } else {
 #pragma unroll
             for (int j = 0; j < kItems; j++)
                 if (i0 + j < span_end) {
-                    out[(i0 + j) * 2] = accL[j];
-                    out[(i0 + j) * 2 + 1] = accR[j];
+                    out[(i0 + j) * 2] += accL[j];
+                    out[(i0 + j) * 2 + 1] += accR[j];
                 }
         }
     }
@@ -270,17 +610,26 @@ __global__ void bank_fold_kernel(const float *__restrict__ partial, int ngroups,
     }
 }
 
+static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
 }  // namespace sb
 
 using namespace sb;
 
-extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, sb_bank_plan *plan)
+extern "C" int sb_voice_is_fast(const sb_voice *voice, double samplerate)
 {
-    SB_REQUIRE(plan && nvoices >= 1 && frames >= 1, "sb_bank_plan_make: bad arguments");
+    if (!voice || !(samplerate > 1)) return 0;
+    return voice_is_fast(*voice, samplerate) ? 1 : 0;
+}
+
+extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, int nsegs_rad, sb_bank_plan *plan)
+{
+    SB_REQUIRE(plan && nvoices >= 1 && frames >= 1 && nsegs_rad >= 1 && nsegs_rad <= kMaxSegs,
+               "sb_bank_plan_make: bad arguments");
     if (sm_count <= 0) sm_count = 148;
     // target: several waves of warps per SM (each warp is an independent unit, so many short
     // units balance the tail), but spans of at least 4 sub-tiles so that the per-span set-up
-    // (summing the carry row) stays ~1% of the work.
+    // stays ~1% of the work.
     const int64_t target_warps = (int64_t)sm_count * 192;
     int vpg = kMaxVoicesPerGroup;
     if (nvoices < vpg) vpg = nvoices;
@@ -301,13 +650,23 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, sb_b
     if (nspans < 1) nspans = 1;
     int64_t span_len = ((nsub + nspans - 1) / nspans) * kSub;
     nspans = (frames + span_len - 1) / span_len;
+    // fast path: spans of at most kFastMaxSub sub-tiles (their anchors sit in shared memory)
+    int64_t fast_sub = span_len / kSub;
+    if (fast_sub > kFastMaxSub) fast_sub = kFastMaxSub;
+    if (fast_sub < 1) fast_sub = 1;
     plan->nvoices = nvoices;
     plan->voices_per_group = vpg;
     plan->ngroups = ngroups;
     plan->nspans = (int32_t)nspans;
     plan->frames = frames;
     plan->span_len = span_len;
-    plan->carry_bytes = (int64_t)nvoices * nspans * (int64_t)sizeof(double);
+    plan->fast_span_len = fast_sub * kSub;
+    plan->fast_nspans = (int32_t)((frames + plan->fast_span_len - 1) / plan->fast_span_len);
+    plan->nsegs_rad = nsegs_rad;
+    plan->generic_voices = -1;
+    plan->off_fastv = align_up((int64_t)nvoices * nspans * (int64_t)sizeof(double), 256);
+    plan->off_tab = align_up(plan->off_fastv + (int64_t)nvoices * (int64_t)sizeof(FastVoice), 256);
+    plan->carry_bytes = align_up(plan->off_tab + (int64_t)nvoices * nsegs_rad * (int64_t)sizeof(double2), 256);
     plan->partial_bytes = (ngroups > 1) ? (int64_t)ngroups * ((frames * 2 + 3) / 4 * 4) * (int64_t)sizeof(float) : 0;
     return SB_OK;
 }
@@ -315,19 +674,23 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, sb_b
 extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan *plan,
                                   const sb_time_seg *tb_rad_dev, int nsegs_rad,
                                   const sb_time_seg *tb_cyc_dev, int nsegs_cyc,
-                                  int64_t n0, double samplerate, double *carry_dev, float *partial_dev,
+                                  int64_t n0, double samplerate, void *scratch_dev, float *partial_dev,
                                   float *mix_dev, void *stream)
 {
-    (void)samplerate;
-    SB_REQUIRE(voices_dev && plan && tb_rad_dev && tb_cyc_dev && mix_dev, "sb_bank_render_f32: null pointer");
-    SB_REQUIRE(nsegs_rad > 0 && nsegs_rad <= kMaxSegs && nsegs_cyc > 0 && nsegs_cyc <= kMaxSegs,
+    SB_REQUIRE(voices_dev && plan && tb_rad_dev && tb_cyc_dev && mix_dev && scratch_dev,
+               "sb_bank_render_f32: null pointer");
+    SB_REQUIRE(nsegs_rad > 0 && nsegs_rad <= kMaxSegs && nsegs_cyc > 0 && nsegs_cyc <= kMaxSegs &&
+                   nsegs_rad == plan->nsegs_rad && samplerate > 1,
                "sb_bank_render_f32: bad time base");
     SB_REQUIRE(plan->voices_per_group >= 1 && plan->voices_per_group <= kMaxVoicesPerGroup &&
-                   plan->span_len % kSub == 0 && plan->nspans >= 1 && plan->ngroups >= 1 && n0 >= 0,
+                   plan->span_len % kSub == 0 && plan->nspans >= 1 && plan->ngroups >= 1 && n0 >= 0 &&
+                   plan->fast_span_len % kSub == 0 && plan->fast_span_len / kSub <= kFastMaxSub &&
+                   plan->fast_nspans >= 1,
                "sb_bank_render_f32: bad plan");
-    SB_REQUIRE(plan->nspans == 1 || carry_dev, "sb_bank_render_f32: carry scratch missing");
     SB_REQUIRE(plan->ngroups == 1 || partial_dev, "sb_bank_render_f32: partial scratch missing");
+    SB_REQUIRE(plan->ngroups <= 65535, "sb_bank_render_f32: too many voice groups");
     cudaStream_t s = (cudaStream_t)stream;
+    unsigned char *scratch = (unsigned char *)scratch_dev;
     BankArgs a;
     a.voices = voices_dev;
     a.nvoices = plan->nvoices;
@@ -341,24 +704,41 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.nsegs_rad = nsegs_rad;
     a.tb_cyc = tb_cyc_dev;
     a.nsegs_cyc = nsegs_cyc;
-    a.carry = (plan->nspans > 1) ? carry_dev : nullptr;
+    a.samplerate = samplerate;
+    a.carry = (plan->nspans > 1) ? (double *)scratch : nullptr;
+    a.fastv = (FastVoice *)(scratch + plan->off_fastv);
+    a.tab = (double2 *)(scratch + plan->off_tab);
+    a.fast_nspans = plan->fast_nspans;
+    a.fast_span_len = plan->fast_span_len;
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
     a.out_stride = (plan->frames * 2 + 3) / 4 * 4;
 
-    size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);
-    if (a.carry) {
-        int64_t nunits = (int64_t)a.nvoices * a.nspans;
-        int64_t blocks = (nunits + kWarpsPerCta - 1) / kWarpsPerCta;
-        SB_REQUIRE(blocks < 0x7fffffff, "sb_bank_render_f32: too many (voice, span) units");
-        bank_carry_kernel<<<(unsigned)blocks, kWarpsPerCta * 32, tb_bytes, s>>>(a);
+    bank_prepare_kernel<<<(a.nvoices + 127) / 128, 128, 0, s>>>(a);
+    SB_LAUNCH_CHECK();
+
+    const size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);
+    {
+        size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(FastVoice) +
+                      (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * sizeof(double);
+        dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
+        bank_fast_kernel<<<grid, kFastWarps * 32, smem, s>>>(a);
         SB_LAUNCH_CHECK();
     }
-    size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(sb_voice) +
-                  (size_t)kWarpsPerCta * a.voices_per_group * sizeof(double);
-    dim3 grid((unsigned)((a.nspans + kWarpsPerCta - 1) / kWarpsPerCta), (unsigned)a.ngroups);
-    SB_REQUIRE(a.ngroups <= 65535, "sb_bank_render_f32: too many voice groups");
-    bank_render_kernel<<<grid, kWarpsPerCta * 32, smem, s>>>(a);
-    SB_LAUNCH_CHECK();
+    if (plan->generic_voices != 0) {
+        if (a.carry) {
+            int64_t nunits = (int64_t)a.nvoices * a.nspans;
+            int64_t blocks = (nunits + kGenWarps - 1) / kGenWarps;
+            SB_REQUIRE(blocks < 0x7fffffff, "sb_bank_render_f32: too many (voice, span) units");
+            bank_carry_kernel<<<(unsigned)blocks, kGenWarps * 32, tb_bytes, s>>>(a);
+            SB_LAUNCH_CHECK();
+        }
+        size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(sb_voice) +
+                      (size_t)kGenWarps * a.voices_per_group * sizeof(double) +
+                      (size_t)a.voices_per_group * sizeof(int);
+        dim3 grid((unsigned)((a.nspans + kGenWarps - 1) / kGenWarps), (unsigned)a.ngroups);
+        bank_generic_kernel<<<grid, kGenWarps * 32, smem, s>>>(a);
+        SB_LAUNCH_CHECK();
+    }
     if (a.ngroups > 1) {
         int64_t nfloats = a.frames * 2;
         bank_fold_kernel<<<grid_for(nfloats / 4 + 1, 256, 148 * 8), 256, 0, s>>>(partial_dev, a.ngroups,

@@ -102,12 +102,18 @@ class VoiceBank:
         raw = ctypes.string_at(ctypes.addressof(arr), ctypes.sizeof(arr))
         return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(D.device()), len(arr)
 
-    def render(self, nframes, start=0, begin=0, end=None, voices_dev=None):
+    def count_generic(self, begin=0, end=None):
+        """Voices of [begin, end) that need the generic (per-sample fp64) kernel."""
+        return sum(1 for v in self._voices[begin:end]
+                   if not C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)))
+
+    def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None):
         """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
         if voices_dev is None:
             voices_dev, nv = self._upload(begin, end)
+            generic_voices = self.count_generic(begin, end)
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
         mix = D.empty(2 * nframes, torch.float32)
@@ -115,10 +121,12 @@ class VoiceBank:
             return mix.zero_()
         plan = C.BankPlan()
         sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
-        C.call("sb_bank_plan_make", nv, nframes, sms, ctypes.byref(plan))
+        tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
+        C.call("sb_bank_plan_make", nv, nframes, sms, tr.nsegs, ctypes.byref(plan))
+        if generic_voices is not None:
+            plan.generic_voices = generic_voices
         carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
         partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
-        tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,
                D.ptr(tc.dev()), tc.nsegs, start, float(self.samplerate), D.ptr(carry), D.ptr(partial),
                D.ptr(mix), D.stream())

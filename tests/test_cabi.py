@@ -93,7 +93,7 @@ def test_bad_arguments_fail_loudly():
         C.call("sb_envelope_build", 48000.0, -1.0, 0.0, 0.0, 0.5, 0.0, ctypes.byref(C.Envelope()))
     plan = C.BankPlan()
     with pytest.raises(C.SbError):
-        C.call("sb_bank_plan_make", 0, 100, 148, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", 0, 100, 148, 40, ctypes.byref(plan))
     assert C.lib.sb_pcm16_ratecv_frames(8, 44100, 48000) == 8
     assert C.lib.sb_pcm16_ratecv_frames(8, 48000, 22050) == 4
     assert C.lib.sb_pcm16_ratecv_frames(0, 48000, 22050) == 0
@@ -102,10 +102,14 @@ def test_bad_arguments_fail_loudly():
 def test_bank_plan_covers_the_work():
     for nv, frames in [(1, 100), (1, 2_880_000), (128, 480_000), (8192, 480_000), (65536, 480_000), (3, 257)]:
         plan = C.BankPlan()
-        C.call("sb_bank_plan_make", nv, frames, 148, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", nv, frames, 148, 40, ctypes.byref(plan))
         assert plan.voices_per_group * plan.ngroups >= nv
         assert plan.span_len % 256 == 0 and plan.span_len * plan.nspans >= frames
         assert plan.span_len * (plan.nspans - 1) < frames
+        assert plan.fast_span_len % 256 == 0 and 1 <= plan.fast_span_len // 256 <= 8
+        assert plan.fast_span_len * plan.fast_nspans >= frames > plan.fast_span_len * (plan.fast_nspans - 1)
+        assert plan.off_fastv >= nv * plan.nspans * 8 and plan.off_tab >= plan.off_fastv + nv * 128
+        assert plan.carry_bytes >= plan.off_tab + nv * 40 * 16
         assert 1 <= plan.voices_per_group <= 64
 
 
