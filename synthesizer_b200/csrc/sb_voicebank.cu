@@ -46,18 +46,33 @@ enum : int {
 };
 
 // Per-voice constants of the fast path, derived once per render by bank_prepare_kernel.
-struct FastVoice {
-    double fm, pcm;          // modulator frequency and start phase (radians)
-    double f0b, pc0;         // carrier frequency * (1 + modulator bias), start phase
-    double gd;               // carrier phase per unit of (sum of sin(theta_k)): f0 * inc_c * depth
-    long long n_a, n_d, n_s, n_r;
-    float wm, wc, gdf;       // fp32 per-sample increments: fm*inc_rad, f0b*inc_c, gd
-    float aL, aR, bL, bR;    // c_amp*gain, c_bias*gain
-    float a_slope, d_slope, r_slope, sl, amp_extra;
+// The first five 128-bit words are everything the per-sample loop needs and are read with five
+// vector loads per (voice, sub-tile); the rest is the envelope description, used by the
+// per-span precompute and by the rare sub-tile that straddles an envelope segment.
+struct alignas(16) FastVoice {
+    double2 mod;             // fm, pcm: modulator frequency and start phase (radians)
+    double2 car;             // f0b, pc0: carrier frequency * (1 + modulator bias), start phase
+    double gd;               // carrier phase per unit of sum(sin(theta_k)): f0 * inc_c * depth
     int flags;
-    int pad;
+    int pad0;
+    float4 inc;              // wm, wc, gdf, -: fp32 per-sample increments fm*inc_rad, f0b*inc_c, gd
+    float4 gain;             // aL, aR, bL, bR: c_amp*gain, c_bias*gain
+    long long n_a, n_d, n_s, n_r;
+    float a_slope, d_slope, r_slope, sl;
+    float amp_extra;
+    int pad1[3];
 };
-static_assert(sizeof(FastVoice) == 136 || sizeof(FastVoice) == 128, "FastVoice layout");
+static_assert(sizeof(FastVoice) == 144, "FastVoice layout");
+
+// Per-(voice, sub-tile) record precomputed at the start of a span, one 128-bit word:
+// the closed-form FM sum at the sub-tile's first frame and the ADSR line over the sub-tile
+// (e(i) = e_sub + i*de), or e_sub = kEnvSilent / kEnvSlow.
+struct alignas(16) SubRec {
+    double anchor;
+    float e_sub, de;
+};
+constexpr float kEnvSilent = -1.0f;          // after the release: the voice adds nothing here
+constexpr float kEnvSlow = -2.0f;            // an envelope corner falls inside: per-sample ADSR
 
 struct BankArgs {
     const sb_voice *voices;
@@ -128,24 +143,22 @@ __global__ void bank_prepare_kernel(BankArgs a)
     const sb_voice V = a.voices[v];
     FastVoice F;
     F.flags = 0;
-    F.pad = 0;
+    F.pad0 = 0;
+    F.pad1[0] = F.pad1[1] = F.pad1[2] = 0;
     const bool fast = voice_is_fast(V, a.samplerate);
     const bool tri = (V.c_wave == SB_WAVE_TRIANGLE);
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
-    F.fm = V.m_freq;
-    F.pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
-    F.f0b = V.c_freq * (1.0 + mbias);
-    F.pc0 = phase0_of(V.c_wave, V.c_phase);
+    const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
+    const double f0b = V.c_freq * (1.0 + mbias);
+    F.mod = make_double2(fm, pcm);
+    F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
     F.gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
     F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
-    F.wm = (float)(V.m_freq * inc_rad);
-    F.wc = (float)(F.f0b * inc_c);
-    F.gdf = (float)F.gd;
-    F.aL = V.c_amp * V.gain_l; F.aR = V.c_amp * V.gain_r;
-    F.bL = V.c_bias * V.gain_l; F.bR = V.c_bias * V.gain_r;
+    F.inc = make_float4((float)(fm * inc_rad), (float)(f0b * inc_c), (float)F.gd, 0.0f);
+    F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_bias * V.gain_l, V.c_bias * V.gain_r);
     F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
     F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
     if (fast) F.flags |= FV_FAST;
@@ -166,17 +179,17 @@ __global__ void bank_prepare_kernel(BankArgs a)
         double before = 0.0;
         for (int b = 0; b < a.nsegs_rad; b++) {
             const sb_time_seg s = a.tb_rad[b];
-            const double w = F.fm * s.step;
+            const double w = fm * s.step;
             const double half = 0.5 * w;
             const double sh = sin(half);
             double C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
-            const double th_lo = F.fm * (s.t_start - 0.5 * s.step) + F.pcm;
+            const double th_lo = fm * (s.t_start - 0.5 * s.step) + pcm;
             double A = before + C * cos(th_lo);
             row[b] = make_double2(A, C);
             if (b + 1 < a.nsegs_rad) {
                 const double len = (double)(a.tb_rad[b + 1].n_start - s.n_start);
-                const double th_hi = F.fm * (s.t_start + (len - 0.5) * s.step) + F.pcm;
-                before = (C != 0.0) ? A - C * cos(th_hi) : before + len * sin(F.fm * s.t_start + F.pcm);
+                const double th_hi = fm * (s.t_start + (len - 0.5) * s.step) + pcm;
+                before = (C != 0.0) ? A - C * cos(th_hi) : before + len * sin(fm * s.t_start + pcm);
             }
         }
     }
@@ -201,14 +214,70 @@ __device__ __forceinline__ float tri_shape(float cycles)
 }
 
 // ------------------------------------------------------------------ fast kernel
+// ADSR factor at absolute frame k, fp32 (the fast path's envelope; corners handled per sample)
+__device__ __forceinline__ float fast_env_at(const FastVoice &F, int64_t k)
+{
+    if (k < F.n_a) return (float)k * F.a_slope;
+    if (k < F.n_d) return 1.0f + (float)(k - F.n_a) * F.d_slope;
+    if (k < F.n_s) return F.sl;
+    if (k < F.n_r) return F.sl + (float)(k - F.n_s) * F.r_slope;
+    if (k == F.n_r && (F.flags & FV_ENV_EXTRA)) return F.amp_extra;
+    return 0.0f;
+}
+
+// One voice over one lane's run of kItems frames.  MOD: Sine modulator present.  TRI: Triangle
+// carrier (else Sine).  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
+template <bool MOD, bool TRI, bool RARE>
+__device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
+                                               const double Tc0, const int lane, const float lane8,
+                                               const int64_t n, float (&accL)[kItems], float (&accR)[kItems])
+{
+    const double2 car = F.car;
+    const float4 inc = F.inc;               // wm, wc, gdf
+    const float4 gain = F.gain;             // aL, aR, bL, bR
+    float ps[kItems];
+    double B = fma(car.x, TRI ? Tc0 : Tr0, car.y);
+    if (MOD) {
+        // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
+        const double2 mod = F.mod;
+        const float th0 = (float)reduce_two_pi(fma(mod.x, Tr0, mod.y));
+        float run = 0.0f;
+#pragma unroll
+        for (int j = 0; j < kItems; j++) {
+            ps[j] = run;
+            run += __sinf(fmaf((float)j, inc.x, th0));
+        }
+        const float incl = warp_scan_incl_f(run, lane);
+        B = fma(F.gd, rec.anchor + (double)(incl - run), B);
+    }
+    // carrier: phase base reduced to one turn in fp64, fp32 from there
+    const float b0 = TRI ? (float)(B - rint(B)) : (float)reduce_two_pi(B);
+    const float e0 = fmaf(lane8, rec.de, rec.e_sub);
+#pragma unroll
+    for (int j = 0; j < kItems; j++) {
+        float ph = fmaf((float)j, inc.y, b0);
+        if (MOD) ph = fmaf(inc.z, ps[j], ph);
+        const float w = TRI ? tri_shape(ph) : __sinf(ph);
+        float e = fmaf((float)j, rec.de, e0);
+        if (RARE) {
+            if (rec.e_sub == kEnvSlow) e = fast_env_at(F, n + j);
+            accL[j] = fmaf(e, gain.z, accL[j]);
+            accR[j] = fmaf(e, gain.w, accR[j]);
+        }
+        const float we = w * e;
+        accL[j] = fmaf(we, gain.x, accL[j]);
+        accR[j] = fmaf(we, gain.y, accR[j]);
+    }
+}
+
 __global__ void __launch_bounds__(kFastWarps * 32)
 bank_fast_kernel(BankArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
-    sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(smem);
+    FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
+    SubRec *s_rec_all = reinterpret_cast<SubRec *>(s_fv + a.voices_per_group);
+    sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(s_rec_all + (size_t)kFastWarps * a.voices_per_group * kFastMaxSub);
     sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
-    FastVoice *s_fv = reinterpret_cast<FastVoice *>(s_cyc + a.nsegs_cyc);
-    double *s_anchor_all = reinterpret_cast<double *>(s_fv + a.voices_per_group);
 
     const int group = blockIdx.y;
     const int v_begin = group * a.voices_per_group;
@@ -218,9 +287,9 @@ bank_fast_kernel(BankArgs a)
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
     {
-        const int words = (int)(sizeof(FastVoice) / 4);
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.fastv + v_begin);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(s_fv);
+        const int words = (int)(sizeof(FastVoice) / 16);
+        const int4 *src = reinterpret_cast<const int4 *>(a.fastv + v_begin);
+        int4 *dst = reinterpret_cast<int4 *>(s_fv);
         for (int i = threadIdx.x; i < nv * words; i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
@@ -228,28 +297,40 @@ bank_fast_kernel(BankArgs a)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
     if (span >= a.fast_nspans) return;                 // no block-wide sync after this point
-    double *s_anchor = s_anchor_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
+    SubRec *s_rec = s_rec_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
 
     const int64_t span_begin = (int64_t)span * a.fast_span_len;
     int64_t span_end = span_begin + a.fast_span_len;
     if (span_end > a.frames) span_end = a.frames;
     const int nsub = (int)((span_end - span_begin + kSub - 1) / kSub);
 
-    // ---- anchors: closed-form FM sums at every sub-tile start, all lanes busy ------------
+    // ---- per-(voice, sub-tile) records, all lanes busy: closed-form FM sum at the sub-tile
+    //      start and the ADSR line across the sub-tile
     for (int idx = lane; idx < nv * nsub; idx += 32) {
         const int v = idx / nsub, s = idx - v * nsub;
         const FastVoice &F = s_fv[v];
-        double A = 0.0;
+        const int64_t lo = a.n0 + span_begin + (int64_t)s * kSub, hi = lo + kSub;
+        SubRec r;
+        r.anchor = 0.0;
+        r.e_sub = 1.0f;
+        r.de = 0.0f;
         if ((F.flags & (FV_FAST | FV_HAS_MOD)) == (FV_FAST | FV_HAS_MOD)) {
-            const int64_t n = a.n0 + span_begin + (int64_t)s * kSub;
             TimeCursor c;
-            c.seek(s_rad, a.nsegs_rad, n);
-            const double t = c.at(n);
-            const double arg = fma(F.fm, t - 0.5 * c.step, F.pcm);
+            c.seek(s_rad, a.nsegs_rad, lo);
+            const double t = c.at(lo);
+            const double arg = fma(F.mod.x, t - 0.5 * c.step, F.mod.y);
             const double2 ac = a.tab[(int64_t)(v_begin + v) * a.nsegs_rad + c.idx];
-            A = ac.x - ac.y * cos_reduced(reduce_two_pi(arg));
+            r.anchor = ac.x - ac.y * cos_reduced(reduce_two_pi(arg));
         }
-        s_anchor[v * kFastMaxSub + s] = A;
+        if (F.flags & FV_ENV) {
+            if (lo > F.n_r) r.e_sub = kEnvSilent;
+            else if (hi <= F.n_a) { r.e_sub = (float)lo * F.a_slope; r.de = F.a_slope; }
+            else if (lo >= F.n_a && hi <= F.n_d) { r.e_sub = 1.0f + (float)(lo - F.n_a) * F.d_slope; r.de = F.d_slope; }
+            else if (lo >= F.n_d && hi <= F.n_s) { r.e_sub = F.sl; }
+            else if (lo >= F.n_s && hi <= F.n_r) { r.e_sub = F.sl + (float)(lo - F.n_s) * F.r_slope; r.de = F.r_slope; }
+            else r.e_sub = kEnvSlow;
+        }
+        s_rec[v * kFastMaxSub + s] = r;
     }
     __syncwarp();
 
@@ -260,9 +341,7 @@ bank_fast_kernel(BankArgs a)
     const float lane8 = (float)(lane * kItems);
 
     for (int s = 0; s < nsub; s++) {
-        const int64_t sub = span_begin + (int64_t)s * kSub;
-        const int64_t nsub0 = a.n0 + sub;              // absolute index of the sub-tile's first frame
-        const int64_t i0 = sub + lane * kItems;
+        const int64_t i0 = span_begin + (int64_t)s * kSub + lane * kItems;
         const int64_t n = a.n0 + i0;
         const double Tr0 = cur_rad.at(n);              // exact serial time, radians base
         const double Tc0 = cur_cyc.at(n);              // exact serial time, cycles base
@@ -273,66 +352,20 @@ bank_fast_kernel(BankArgs a)
         for (int v = 0; v < nv; v++) {
             const FastVoice &F = s_fv[v];
             const int flags = F.flags;
-            if (!(flags & FV_FAST)) continue;
-            // ---- ADSR over this sub-tile (warp-uniform): e(i) = e_sub + i*de when the 256
-            //      frames sit inside one segment, else per-sample below
-            float e_sub = 1.0f, de = 0.0f;
-            bool env_slow = false;
-            if (flags & FV_ENV) {
-                const int64_t lo = nsub0, hi = nsub0 + kSub;
-                if (lo > F.n_r) continue;                                   // silent: nothing to add
-                if (hi <= F.n_a) { e_sub = (float)lo * F.a_slope; de = F.a_slope; }
-                else if (lo >= F.n_a && hi <= F.n_d) { e_sub = 1.0f + (float)(lo - F.n_a) * F.d_slope; de = F.d_slope; }
-                else if (lo >= F.n_d && hi <= F.n_s) { e_sub = F.sl; }
-                else if (lo >= F.n_s && hi <= F.n_r) { e_sub = F.sl + (float)(lo - F.n_s) * F.r_slope; de = F.r_slope; }
-                else env_slow = true;
-            }
-            const float e0 = fmaf(lane8, de, e_sub);
-            const bool tri = flags & FV_TRIANGLE;
-            const double Tc = tri ? Tc0 : Tr0;
-
-            // ---- modulator: 8 sines from one fp64 phase base; exclusive sums for the FM prefix
-            float ps[kItems];
-            double B;
-            if (flags & FV_HAS_MOD) {
-                const float th0 = (float)reduce_two_pi(fma(F.fm, Tr0, F.pcm));
-                float run = 0.0f;
-#pragma unroll
-                for (int j = 0; j < kItems; j++) {
-                    ps[j] = run;
-                    run += __sinf(fmaf((float)j, F.wm, th0));
-                }
-                const float incl = warp_scan_incl_f(run, lane);
-                const double before = s_anchor[v * kFastMaxSub + s] + (double)(incl - run);
-                B = fma(F.gd, before, fma(F.f0b, Tc, F.pc0));
+            const SubRec rec = s_rec[v * kFastMaxSub + s];
+            if (!(flags & FV_FAST) || rec.e_sub == kEnvSilent) continue;       // warp-uniform
+            const bool rare = (flags & FV_BIAS) || rec.e_sub == kEnvSlow;
+            const int kind = (flags & (FV_HAS_MOD | FV_TRIANGLE));
+            if (rare) {
+                if (kind == FV_HAS_MOD) fast_voice_run<true, false, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else if (kind == 0) fast_voice_run<false, false, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else if (kind == FV_TRIANGLE) fast_voice_run<false, true, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else fast_voice_run<true, true, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
             } else {
-#pragma unroll
-                for (int j = 0; j < kItems; j++) ps[j] = 0.0f;
-                B = fma(F.f0b, Tc, F.pc0);
-            }
-            // ---- carrier: phase base reduced to one turn, fp32 from there
-            const float b0 = tri ? (float)(B - rint(B)) : (float)reduce_two_pi(B);
-#pragma unroll
-            for (int j = 0; j < kItems; j++) {
-                const float ph = fmaf(F.gdf, ps[j], fmaf((float)j, F.wc, b0));
-                const float w = tri ? tri_shape(ph) : __sinf(ph);
-                float e = fmaf((float)j, de, e0);
-                if (env_slow) {
-                    const int64_t k = n + j;
-                    if (k < F.n_a) e = (float)k * F.a_slope;
-                    else if (k < F.n_d) e = 1.0f + (float)(k - F.n_a) * F.d_slope;
-                    else if (k < F.n_s) e = F.sl;
-                    else if (k < F.n_r) e = F.sl + (float)(k - F.n_s) * F.r_slope;
-                    else if (k == F.n_r && (flags & FV_ENV_EXTRA)) e = F.amp_extra;
-                    else e = 0.0f;
-                }
-                const float we = w * e;
-                accL[j] = fmaf(we, F.aL, accL[j]);
-                accR[j] = fmaf(we, F.aR, accR[j]);
-                if (flags & FV_BIAS) {
-                    accL[j] = fmaf(e, F.bL, accL[j]);
-                    accR[j] = fmaf(e, F.bR, accR[j]);
-                }
+                if (kind == FV_HAS_MOD) fast_voice_run<true, false, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else if (kind == 0) fast_voice_run<false, false, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else if (kind == FV_TRIANGLE) fast_voice_run<false, true, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+                else fast_voice_run<true, true, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
             }
         }
 
@@ -719,7 +752,9 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     const size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);
     {
         size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(FastVoice) +
-                      (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * sizeof(double);
+                      (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * sizeof(SubRec);
+        if (smem > 48 * 1024)
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
         bank_fast_kernel<<<grid, kFastWarps * 32, smem, s>>>(a);
         SB_LAUNCH_CHECK();
