@@ -171,17 +171,19 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     frames = CPU_FRAMES
-    for _ in range(args.warmup and 1):
+    v0, _ = cpu_port_throughput(1, 1, 12000)          # warm-up, and sizes the sample: ~5 s per step
+    nv = max(1, min(64, int(round(v0 * 1e6 * 5.0 / CPU_FRAMES))))
+    for _ in range(max(0, args.warmup - 1) and 1):
         cpu_port_throughput(cores, 1, 4000)
     vals = []
     t_all = time.perf_counter()
     for _ in range(args.steps):
-        v, dt = cpu_port_throughput(cores, CPU_VOICES_PER_PROC, frames)
+        v, dt = cpu_port_throughput(cores, nv, frames)
         vals.append(v)
     wall = time.perf_counter() - t_all
     value = sum(vals) / len(vals)
     sample = "%d processes x %d voices x %d frames per step (pure-Python port of the FM+ADSR+mix chain)" % (
-        cores, CPU_VOICES_PER_PROC, frames)
+        cores, nv, frames)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
@@ -315,9 +317,13 @@ def run_ours(args):
         sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965
         peak_gsin = 16 * sms * sm_mhz * 1e6 / 1e9
         achieved_gsin = 2 * (hi - lo) * frames / (render_ms / 1e3) / 1e9
-        roofline = {"bound": "sfu", "kernel": "bank_render (carry pre-pass + render + fold)",
+        # DRAM traffic of the dominant kernel from the committed ncu capture
+        # (profiles/r1f_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
+        # of bank_fast_kernel on this workload): 4.2 MB read + 434.8 MB written
+        ncu_traffic = 4195328 + 434848512 if (hi - lo) == VOICES_PER_GPU else None
+        roofline = {"bound": "sfu", "kernel": "bank_fast_kernel (+ bank_prepare, bank_fold: 95/1/4 % of the step)",
                     "achieved": achieved_gsin, "peak": peak_gsin, "unit": "Gsin/s",
-                    "frac": achieved_gsin / peak_gsin, "traffic": None,
+                    "frac": achieved_gsin / peak_gsin, "traffic": ncu_traffic,
                     "peak_source": "16 MUFU lanes/clk/SM x %d SMs x %d MHz (clock sampled under load)" % (sms, sm_mhz),
                     "kernels_per_render": kernels_per_render, "render_ms": render_ms,
                     "hbm_algorithmic_bytes": int(plan.partial_bytes * 2 + 2 * frames * 4 * 2),
@@ -329,13 +335,16 @@ def run_ours(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            v1, dt1 = cpu_port_throughput(1)
-            vn, dtn = cpu_port_throughput(cores)
+            # size the sample for ~10 s of work per process on this host
+            v0, _ = cpu_port_throughput(1, 1, 12000)
+            nv = max(1, min(64, int(round(v0 * 1e6 * 10.0 / CPU_FRAMES))))
+            v1, dt1 = cpu_port_throughput(1, nv)
+            vn, dtn = cpu_port_throughput(cores, nv)
             vc, dtc = cpu_c_port_throughput()
             cpu = {"value": vn, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": "pure-Python port (oracle/synth_oracle.py), %d processes x 8 voices x 96000 frames (%.1f s); "
+                   "sample": "pure-Python port (oracle/synth_oracle.py), %d processes x %d voices x %d frames (%.1f s); "
                              "single process: %.4f Msamples/s (%.1f s); compiled C port, 1 thread, 48 voices x 10 s: "
-                             "%.2f Msamples/s (%.1f s)" % (cores, dtn, v1, dt1, vc, dtc),
+                             "%.2f Msamples/s (%.1f s)" % (cores, nv, CPU_FRAMES, dtn, v1, dt1, vc, dtc),
                    "single_process_value": v1, "c_port_1thread_value": vc}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -11,7 +11,7 @@ from ctypes import (POINTER, Structure, c_char_p, c_double, c_float, c_int, c_in
                     c_uint, c_uint64, c_ulonglong, c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsynth_b200.so")
+LIB_PATH = os.environ.get("SYNTH_B200_LIB") or os.path.join(_HERE, "libsynth_b200.so")
 
 WAVE_NONE, WAVE_SINE, WAVE_TRIANGLE, WAVE_SQUARE, WAVE_SAWTOOTH, WAVE_PULSE = -1, 0, 1, 2, 3, 4
 TIMEBASE_MAX_SEGS = 256

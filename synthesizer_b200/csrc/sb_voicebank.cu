@@ -34,7 +34,13 @@ constexpr int kMaxVoicesPerGroup = 64;
 
 constexpr int kGenWarps = 8;                 // generic kernel: warps per CTA
 constexpr int kFastWarps = 4;                // fast kernel: warps per CTA
-constexpr int kFastMaxSub = 8;               // fast kernel: sub-tiles per span (anchors in smem)
+#ifndef FAST_MAX_SUB
+#define FAST_MAX_SUB 4
+#endif
+constexpr int kFastMaxSub = FAST_MAX_SUB;    // fast kernel: sub-tiles per span (anchors in smem)
+#ifndef FAST_MIN_BLOCKS
+#define FAST_MIN_BLOCKS 7      /* measured on B200: 3/4/5/6/7/8 CTAs per SM -> 3.84/3.84/3.50/3.21/3.13/3.29 ms */
+#endif
 
 enum : int {
     FV_FAST = 1,
@@ -55,14 +61,16 @@ struct alignas(16) FastVoice {
     double gd;               // carrier phase per unit of sum(sin(theta_k)): f0 * inc_c * depth
     int flags;
     int pad0;
-    float4 inc;              // wm, wc, gdf, -: fp32 per-sample increments fm*inc_rad, f0b*inc_c, gd
-    float4 gain;             // aL, aR, bL, bR: c_amp*gain, c_bias*gain
+    float4 inc;              // wm, wm, wc, wc: fp32 phase steps per frame fm*inc_rad, f0b*inc_c (pairs for fp32x2)
+    float4 g2;               // gdf, gdf, 4wm, 4wc: gd in fp32 (pair); phase steps of four frames
+    float4 gain;             // aL, aL, aR, aR: c_amp*gain (as pairs for the packed fp32x2 FMAs)
     long long n_a, n_d, n_s, n_r;
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
-    int pad1[3];
+    float bL, bR;            // c_bias*gain
+    int pad1;
 };
-static_assert(sizeof(FastVoice) == 144, "FastVoice layout");
+static_assert(sizeof(FastVoice) == 160, "FastVoice layout");
 
 // Per-(voice, sub-tile) record precomputed at the start of a span, one 128-bit word:
 // the closed-form FM sum at the sub-tile's first frame and the ADSR line over the sub-tile
@@ -144,7 +152,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
     FastVoice F;
     F.flags = 0;
     F.pad0 = 0;
-    F.pad1[0] = F.pad1[1] = F.pad1[2] = 0;
+    F.pad1 = 0;
     const bool fast = voice_is_fast(V, a.samplerate);
     const bool tri = (V.c_wave == SB_WAVE_TRIANGLE);
     const double inc_rad = 6.283185307179586 / a.samplerate;
@@ -157,8 +165,12 @@ __global__ void bank_prepare_kernel(BankArgs a)
     F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
     F.gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
     F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
-    F.inc = make_float4((float)(fm * inc_rad), (float)(f0b * inc_c), (float)F.gd, 0.0f);
-    F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_bias * V.gain_l, V.c_bias * V.gain_r);
+    const float wm = (float)(fm * inc_rad), wc = (float)(f0b * inc_c);
+    F.inc = make_float4(wm, wm, wc, wc);
+    F.g2 = make_float4((float)F.gd, (float)F.gd, 4.0f * wm, 4.0f * wc);
+    F.bL = V.c_bias * V.gain_l;
+    F.bR = V.c_bias * V.gain_r;
+    F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_amp * V.gain_r);
     F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
     F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
     if (fast) F.flags |= FV_FAST;
@@ -225,52 +237,130 @@ __device__ __forceinline__ float fast_env_at(const FastVoice &F, int64_t k)
     return 0.0f;
 }
 
+// x mod 2*pi into [-pi, pi] without the FRND (XU pipe) that rint() costs: magic-number rounding
+__device__ __forceinline__ double reduce_two_pi_fast(double x)
+{
+    const double M = 6755399441055744.0;                       // 1.5 * 2^52
+    const double k = __dadd_rn(__fma_rn(x, kInvTwoPi, M), -M);
+    const double r = fma(-k, kTwoPiHi, x);
+    return fma(-k, kTwoPiLo, r);
+}
+
+// Inclusive warp scan, two instructions per step: shfl.up reports through a predicate whether
+// the source lane exists, and the add is predicated on it.
+__device__ __forceinline__ float warp_scan_incl_ptx(float v)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        asm volatile("{\n\t"
+                     ".reg .pred p;\n\t"
+                     ".reg .f32 t;\n\t"
+                     "shfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t"
+                     "@p add.f32 %0, %0, t;\n\t"
+                     "}"
+                     : "+f"(v) : "r"(d));
+    }
+    return v;
+}
+
 // One voice over one lane's run of kItems frames.  MOD: Sine modulator present.  TRI: Triangle
 // carrier (else Sine).  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
+// Frames are handled in pairs (j, j+1) with Blackwell's packed fp32x2 FMAs; accL2[q] holds the
+// left-channel sums of frames (2q, 2q+1), accR2[q] the right-channel ones.
+// Frame pairing: the packed fp32x2 operations work on frames (q, q+4) of the lane's run of 8,
+// so that the exclusive sums of the modulator advance through both halves of the run in one
+// dependent chain of 4 packed adds (the second half's offset joins the carrier phase later).
+// accL2[q] = left-channel sums of frames (q, q+4), accR2[q] the right-channel ones.
 template <bool MOD, bool TRI, bool RARE>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
-                                               const double Tc0, const int lane, const float lane8,
-                                               const int64_t n, float (&accL)[kItems], float (&accR)[kItems])
+                                               const double Tc0, const float lane8, const int64_t n,
+                                               float2 (&accL2)[kItems / 2], float2 (&accR2)[kItems / 2])
 {
+    constexpr int H = kItems / 2;
     const double2 car = F.car;
-    const float4 inc = F.inc;               // wm, wc, gdf
-    const float4 gain = F.gain;             // aL, aR, bL, bR
-    float ps[kItems];
+    const float4 inc = F.inc;               // wm, wm, wc, wc
+    const float4 g2 = F.g2;                 // gdf, gdf, 4wm, 4wc
+    const float4 gain = F.gain;             // aL, aL, aR, aR
+    float2 ps[H];                           // exclusive sums within each half: (frames q, q+4)
+    float2 base;                            // carrier phase of frames (q, q+4), fp32, within a turn
     double B = fma(car.x, TRI ? Tc0 : Tr0, car.y);
+    float half_gd = 0.0f;                   // gd * (sum of the first half's sines)
     if (MOD) {
         // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
         const double2 mod = F.mod;
-        const float th0 = (float)reduce_two_pi(fma(mod.x, Tr0, mod.y));
-        float run = 0.0f;
+        const float th0 = (float)reduce_two_pi_fast(fma(mod.x, Tr0, mod.y));
+        float2 th = make_float2(th0, th0 + g2.z);
+        const float2 step = make_float2(inc.x, inc.y);
+        float2 run = make_float2(0.0f, 0.0f);
 #pragma unroll
-        for (int j = 0; j < kItems; j++) {
-            ps[j] = run;
-            run += __sinf(fmaf((float)j, inc.x, th0));
+        for (int q = 0; q < H; q++) {
+            ps[q] = run;
+            run = __fadd2_rn(run, make_float2(__sinf(th.x), __sinf(th.y)));
+            th = __fadd2_rn(th, step);
         }
-        const float incl = warp_scan_incl_f(run, lane);
-        B = fma(F.gd, rec.anchor + (double)(incl - run), B);
+        const float total = run.x + run.y;
+        const float incl = warp_scan_incl_ptx(total);
+        B = fma(F.gd, rec.anchor + (double)(incl - total), B);
+        half_gd = g2.x * run.x;
     }
     // carrier: phase base reduced to one turn in fp64, fp32 from there
-    const float b0 = TRI ? (float)(B - rint(B)) : (float)reduce_two_pi(B);
+    float b0;
+    if (TRI) {
+        const double M = 6755399441055744.0;
+        b0 = (float)(B - __dadd_rn(__dadd_rn(B, M), -M));
+    } else {
+        b0 = (float)reduce_two_pi_fast(B);
+    }
+    base = make_float2(b0, b0 + g2.w + half_gd);
     const float e0 = fmaf(lane8, rec.de, rec.e_sub);
+    float2 e = make_float2(e0, fmaf(4.0f, rec.de, e0));
+    const float2 cstep = make_float2(inc.z, inc.w), gd2 = make_float2(g2.x, g2.y);
+    const float2 estep = make_float2(rec.de, rec.de);
+    const float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
 #pragma unroll
-    for (int j = 0; j < kItems; j++) {
-        float ph = fmaf((float)j, inc.y, b0);
-        if (MOD) ph = fmaf(inc.z, ps[j], ph);
-        const float w = TRI ? tri_shape(ph) : __sinf(ph);
-        float e = fmaf((float)j, rec.de, e0);
+    for (int q = 0; q < H; q++) {
+        float2 ph = base;
+        if (MOD) ph = __ffma2_rn(gd2, ps[q], base);
+        float2 w;
+        w.x = TRI ? tri_shape(ph.x) : __sinf(ph.x);
+        w.y = TRI ? tri_shape(ph.y) : __sinf(ph.y);
+        float2 ee = e;
         if (RARE) {
-            if (rec.e_sub == kEnvSlow) e = fast_env_at(F, n + j);
-            accL[j] = fmaf(e, gain.z, accL[j]);
-            accR[j] = fmaf(e, gain.w, accR[j]);
+            if (rec.e_sub == kEnvSlow) {
+                ee.x = fast_env_at(F, n + q);
+                ee.y = fast_env_at(F, n + q + H);
+            }
+            accL2[q] = __ffma2_rn(ee, make_float2(F.bL, F.bL), accL2[q]);
+            accR2[q] = __ffma2_rn(ee, make_float2(F.bR, F.bR), accR2[q]);
         }
-        const float we = w * e;
-        accL[j] = fmaf(we, gain.x, accL[j]);
-        accR[j] = fmaf(we, gain.y, accR[j]);
+        const float2 we = __fmul2_rn(w, ee);
+        accL2[q] = __ffma2_rn(we, aL2, accL2[q]);
+        accR2[q] = __ffma2_rn(we, aR2, accR2[q]);
+        base = __fadd2_rn(base, cstep);
+        e = __fadd2_rn(e, estep);
     }
 }
 
-__global__ void __launch_bounds__(kFastWarps * 32)
+// The four non-rare instantiations, picked by a voice's kind index (bit0 = MOD, bit1 = TRI).
+template <int KIND>
+__device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const SubRec *s_rec, int begin, int end,
+                                                int s, const double Tr0, const double Tc0, const float lane8,
+                                                const int64_t n, float2 (&accL2)[kItems / 2],
+                                                float2 (&accR2)[kItems / 2])
+{
+    constexpr bool MOD = (KIND & 1) != 0, TRI = (KIND & 2) != 0;
+    for (int v = begin; v < end; v++) {
+        const FastVoice &F = s_fv[v];
+        const SubRec rec = s_rec[v * kFastMaxSub + s];
+        if (rec.e_sub == kEnvSilent) continue;                                  // warp-uniform
+        if (rec.e_sub == kEnvSlow || (F.flags & FV_BIAS))
+            fast_voice_run<MOD, TRI, true>(F, rec, Tr0, Tc0, lane8, n, accL2, accR2);
+        else
+            fast_voice_run<MOD, TRI, false>(F, rec, Tr0, Tc0, lane8, n, accL2, accR2);
+    }
+}
+
+__global__ void __launch_bounds__(kFastWarps * 32, FAST_MIN_BLOCKS)
 bank_fast_kernel(BankArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -278,6 +368,7 @@ bank_fast_kernel(BankArgs a)
     SubRec *s_rec_all = reinterpret_cast<SubRec *>(s_fv + a.voices_per_group);
     sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(s_rec_all + (size_t)kFastWarps * a.voices_per_group * kFastMaxSub);
     sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
+    __shared__ int s_kind_end[4];      // voices are stored sorted by kind: [0,e0) [e0,e1) [e1,e2) [e2,e3)
 
     const int group = blockIdx.y;
     const int v_begin = group * a.voices_per_group;
@@ -286,13 +377,41 @@ bank_fast_kernel(BankArgs a)
 
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
-    {
-        const int words = (int)(sizeof(FastVoice) / 16);
-        const int4 *src = reinterpret_cast<const int4 *>(a.fastv + v_begin);
-        int4 *dst = reinterpret_cast<int4 *>(s_fv);
-        for (int i = threadIdx.x; i < nv * words; i += blockDim.x) dst[i] = src[i];
+    // Copy this group's fast voices into shared memory sorted by kind (no FM / FM x sine /
+    // triangle), so that the inner loops are branch-free runs of one instantiation each.
+    for (int v = threadIdx.x; v < nv; v += blockDim.x) {
+        const FastVoice *src = a.fastv + v_begin;
+        const int fl = src[v].flags;
+        if (fl & FV_FAST) {
+            const int kind = ((fl & FV_HAS_MOD) ? 1 : 0) | ((fl & FV_TRIANGLE) ? 2 : 0);
+            int pos = 0;
+            for (int u = 0; u < nv; u++) {
+                const int fu = src[u].flags;
+                if (!(fu & FV_FAST)) continue;
+                const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | ((fu & FV_TRIANGLE) ? 2 : 0);
+                pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
+            }
+            const int4 *w = reinterpret_cast<const int4 *>(src + v);
+            int4 *dst = reinterpret_cast<int4 *>(s_fv + pos);
+#pragma unroll
+            for (int i = 0; i < (int)(sizeof(FastVoice) / 16); i++) dst[i] = w[i];
+            // s_fv[pos].pad0 remembers the voice's index in the bank (for its FM table row)
+            s_fv[pos].pad0 = v_begin + v;
+        }
+    }
+    if (threadIdx.x < 4) {
+        int c = 0;
+        for (int u = 0; u < nv; u++) {
+            const int fu = a.fastv[v_begin + u].flags;
+            if (!(fu & FV_FAST)) continue;
+            const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | ((fu & FV_TRIANGLE) ? 2 : 0);
+            c += (ku <= (int)threadIdx.x) ? 1 : 0;
+        }
+        s_kind_end[threadIdx.x] = c;
     }
     __syncthreads();
+    const int e0 = s_kind_end[0], e1 = s_kind_end[1], e2 = s_kind_end[2], e3 = s_kind_end[3];
+    nv = e3;                                           // fast voices only from here on
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
@@ -314,12 +433,12 @@ bank_fast_kernel(BankArgs a)
         r.anchor = 0.0;
         r.e_sub = 1.0f;
         r.de = 0.0f;
-        if ((F.flags & (FV_FAST | FV_HAS_MOD)) == (FV_FAST | FV_HAS_MOD)) {
+        if (F.flags & FV_HAS_MOD) {
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, lo);
             const double t = c.at(lo);
             const double arg = fma(F.mod.x, t - 0.5 * c.step, F.mod.y);
-            const double2 ac = a.tab[(int64_t)(v_begin + v) * a.nsegs_rad + c.idx];
+            const double2 ac = a.tab[(int64_t)F.pad0 * a.nsegs_rad + c.idx];
             r.anchor = ac.x - ac.y * cos_reduced(reduce_two_pi(arg));
         }
         if (F.flags & FV_ENV) {
@@ -335,52 +454,54 @@ bank_fast_kernel(BankArgs a)
     __syncwarp();
 
     float *out = a.out + (int64_t)group * a.out_stride;
-    TimeCursor cur_rad, cur_cyc;
-    cur_rad.seek(s_rad, a.nsegs_rad, a.n0 + span_begin + lane * kItems);
-    cur_cyc.seek(s_cyc, a.nsegs_cyc, a.n0 + span_begin + lane * kItems);
     const float lane8 = (float)(lane * kItems);
 
     for (int s = 0; s < nsub; s++) {
         const int64_t i0 = span_begin + (int64_t)s * kSub + lane * kItems;
         const int64_t n = a.n0 + i0;
-        const double Tr0 = cur_rad.at(n);              // exact serial time, radians base
-        const double Tc0 = cur_cyc.at(n);              // exact serial time, cycles base
-        float accL[kItems], accR[kItems];
-#pragma unroll
-        for (int j = 0; j < kItems; j++) accL[j] = accR[j] = 0.0f;
-
-        for (int v = 0; v < nv; v++) {
-            const FastVoice &F = s_fv[v];
-            const int flags = F.flags;
-            const SubRec rec = s_rec[v * kFastMaxSub + s];
-            if (!(flags & FV_FAST) || rec.e_sub == kEnvSilent) continue;       // warp-uniform
-            const bool rare = (flags & FV_BIAS) || rec.e_sub == kEnvSlow;
-            const int kind = (flags & (FV_HAS_MOD | FV_TRIANGLE));
-            if (rare) {
-                if (kind == FV_HAS_MOD) fast_voice_run<true, false, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else if (kind == 0) fast_voice_run<false, false, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else if (kind == FV_TRIANGLE) fast_voice_run<false, true, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else fast_voice_run<true, true, true>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-            } else {
-                if (kind == FV_HAS_MOD) fast_voice_run<true, false, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else if (kind == 0) fast_voice_run<false, false, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else if (kind == FV_TRIANGLE) fast_voice_run<false, true, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
-                else fast_voice_run<true, true, false>(F, rec, Tr0, Tc0, lane, lane8, n, accL, accR);
+        // exact serial time at this lane's first frame in both bases (a fresh look-up per
+        // sub-tile costs ~40 instructions per 64 voices and keeps no cursor state in registers)
+        double Tr0, Tc0 = 0.0;
+        {
+            TimeCursor c;
+            c.seek(s_rad, a.nsegs_rad, n);
+            Tr0 = c.at(n);
+            if (e3 > e1) {                              // triangle carriers present
+                c.seek(s_cyc, a.nsegs_cyc, n);
+                Tc0 = c.at(n);
             }
         }
+        // keep both in registers for the voice loops (the compiler would otherwise recompute
+        // the int64 -> fp64 conversion per voice)
+        asm volatile("" : "+d"(Tr0), "+d"(Tc0));
+        float2 accL2[kItems / 2], accR2[kItems / 2];
+#pragma unroll
+        for (int q = 0; q < kItems / 2; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
+        fast_voice_loop<0>(s_fv, s_rec, 0, e0, s, Tr0, Tc0, lane8, n, accL2, accR2);
+        fast_voice_loop<1>(s_fv, s_rec, e0, e1, s, Tr0, Tc0, lane8, n, accL2, accR2);
+        fast_voice_loop<2>(s_fv, s_rec, e1, e2, s, Tr0, Tc0, lane8, n, accL2, accR2);
+        fast_voice_loop<3>(s_fv, s_rec, e2, e3, s, Tr0, Tc0, lane8, n, accL2, accR2);
+
+        // frame j of the run is accL2[j].x for j < 4 and accL2[j-4].y above; two frames per float4
         if (i0 + kItems <= span_end) {
             float4 *dst = reinterpret_cast<float4 *>(out + i0 * 2);
-#pragma unroll
-            for (int q = 0; q < kItems / 2; q++)
-                dst[q] = make_float4(accL[2 * q], accR[2 * q], accL[2 * q + 1], accR[2 * q + 1]);
+            dst[0] = make_float4(accL2[0].x, accR2[0].x, accL2[1].x, accR2[1].x);
+            dst[1] = make_float4(accL2[2].x, accR2[2].x, accL2[3].x, accR2[3].x);
+            dst[2] = make_float4(accL2[0].y, accR2[0].y, accL2[1].y, accR2[1].y);
+            dst[3] = make_float4(accL2[2].y, accR2[2].y, accL2[3].y, accR2[3].y);
         } else {
 #pragma unroll
-            for (int j = 0; j < kItems; j++)
-                if (i0 + j < span_end) {
-                    out[(i0 + j) * 2] = accL[j];
-                    out[(i0 + j) * 2 + 1] = accR[j];
+            for (int q = 0; q < kItems / 2; q++) {
+                if (i0 + q < span_end) {
+                    out[(i0 + q) * 2] = accL2[q].x;
+                    out[(i0 + q) * 2 + 1] = accR2[q].x;
                 }
+                if (i0 + q + kItems / 2 < span_end) {
+                    out[(i0 + q + kItems / 2) * 2] = accL2[q].y;
+                    out[(i0 + q + kItems / 2) * 2 + 1] = accR2[q].y;
+                }
+            }
         }
     }
 }
