@@ -149,6 +149,13 @@ def cpu_port_throughput(cores, voices_per_core=CPU_VOICES_PER_PROC, frames=CPU_F
     return cores * voices_per_core * frames / dt / 1e6, dt
 
 
+def cpu_sample_voices(seconds_of_work):
+    """Voices per process so that one process works for about `seconds_of_work` on this host."""
+    dt = _cpu_worker((0, 1, 12000, 5))                 # core loop time of 1 voice x 12000 frames
+    rate = 12000 / dt                                   # voice-samples per second, one process
+    return max(1, min(64, int(round(rate * seconds_of_work / CPU_FRAMES))))
+
+
 def cpu_c_port_throughput(voices=48, frames=int(SR * SECONDS)):
     """The same algorithm compiled (oracle/oracle.c), one thread — reported beside the Python figure."""
     import numpy as np
@@ -171,8 +178,7 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     frames = CPU_FRAMES
-    v0, _ = cpu_port_throughput(1, 1, 12000)          # warm-up, and sizes the sample: ~5 s per step
-    nv = max(1, min(64, int(round(v0 * 1e6 * 5.0 / CPU_FRAMES))))
+    nv = cpu_sample_voices(5.0)                        # warm-up, and sizes the sample: ~5 s per step
     for _ in range(max(0, args.warmup - 1) and 1):
         cpu_port_throughput(cores, 1, 4000)
     vals = []
@@ -336,8 +342,7 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             # size the sample for ~10 s of work per process on this host
-            v0, _ = cpu_port_throughput(1, 1, 12000)
-            nv = max(1, min(64, int(round(v0 * 1e6 * 10.0 / CPU_FRAMES))))
+            nv = cpu_sample_voices(10.0)
             v1, dt1 = cpu_port_throughput(1, nv)
             vn, dtn = cpu_port_throughput(cores, nv)
             vc, dtc = cpu_c_port_throughput()

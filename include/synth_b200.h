@@ -265,10 +265,15 @@ int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nchannels, int
 /* Sample.mix_at for a list of sources applied IN ORDER: each step is audioop.add on the
  * overlapped span (saturation per step).  Source s is src_pool_dev[src_off[s] ..
  * src_off[s]+src_len[s]) (int16 sample units) mixed at dst sample index dst_off[s]; the
- * three arrays are device arrays of nsrc int64.  dst must already be long enough. */
+ * three arrays are device arrays of nsrc int64.  dst must already be long enough.
+ * scratch_dev (sb_pcm16_mix_at_many_scratch_bytes; total_src_samples = sum of src_len) holds the
+ * per-tile source lists; pass NULL to run without an index (each 2048-sample tile then scans
+ * the whole source list — fine for a few sources, slow for thousands). */
+int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t nsrc, int64_t total_src_samples);
 int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
                          const int64_t *src_off_dev, const int64_t *src_len_dev,
-                         const int64_t *dst_off_dev, int64_t nsrc, void *stream);
+                         const int64_t *dst_off_dev, int64_t nsrc, void *scratch_dev,
+                         int64_t scratch_bytes, void *stream);
 
 /* ------------------------------------------------------------------ host-buffer calls -
  * The same path with HOST buffers (copies included), for callers without device memory of

@@ -135,21 +135,25 @@ extern "C" int sb_host_pcm16_mix_at_many(int16_t *dst, int64_t dst_count, const 
     std::lock_guard<std::mutex> lock(g_mu);
     const size_t b_dst = align256((size_t)dst_count * 2), b_pool = align256((size_t)pool_count * 2);
     const size_t b_idx = align256((size_t)nsrc * 8);
-    int rc = g_ws[1].ensure(b_dst + b_pool + 3 * b_idx);
+    int64_t total_len = 0;
+    for (int64_t s = 0; s < nsrc; s++) total_len += src_len[s];
+    const int64_t n_scratch = sb_pcm16_mix_at_many_scratch_bytes(dst_count, nsrc, total_len);
+    int rc = g_ws[1].ensure(b_dst + b_pool + 3 * b_idx + align256((size_t)n_scratch));
     if (rc) return rc;
     unsigned char *p = (unsigned char *)g_ws[1].ptr;
     int16_t *d_dst = (int16_t *)p; p += b_dst;
     int16_t *d_pool = (int16_t *)p; p += b_pool;
     int64_t *d_so = (int64_t *)p; p += b_idx;
     int64_t *d_sl = (int64_t *)p; p += b_idx;
-    int64_t *d_do = (int64_t *)p;
+    int64_t *d_do = (int64_t *)p; p += b_idx;
+    void *d_scratch = (void *)p;
     cudaStream_t s = 0;
     SB_CUDA_CHECK(cudaMemcpyAsync(d_dst, dst, (size_t)dst_count * 2, cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_pool, src_pool, (size_t)pool_count * 2, cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_so, src_off, (size_t)nsrc * 8, cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_sl, src_len, (size_t)nsrc * 8, cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_do, dst_off, (size_t)nsrc * 8, cudaMemcpyHostToDevice, s));
-    rc = sb_pcm16_mix_at_many(d_dst, dst_count, d_pool, d_so, d_sl, d_do, nsrc, s);
+    rc = sb_pcm16_mix_at_many(d_dst, dst_count, d_pool, d_so, d_sl, d_do, nsrc, d_scratch, n_scratch, s);
     if (rc) return rc;
     SB_CUDA_CHECK(cudaMemcpyAsync(dst, d_dst, (size_t)dst_count * 2, cudaMemcpyDeviceToHost, s));
     SB_CUDA_CHECK(cudaStreamSynchronize(s));

@@ -161,22 +161,58 @@ __global__ void pcm32_to_16_kernel(const int32_t *__restrict__ in, int64_t count
 //   d = c*outrate - j*inrate in [0, outrate) the interpolation counter,
 //   out = (int)((prev*d + cur*(outrate-d)) / outrate) on samples widened to 32 bits (<<16),
 //   then >>16.  The fp64 expression is evaluated exactly as audioop.c writes it.
+constexpr int kRcvIters = 16;            // a warp owns 32*kRcvIters consecutive output frames
+
 __global__ void pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t in_frames, int nch, int64_t inrate,
                                     int64_t outrate, int64_t out_frames, int16_t *__restrict__ out)
 {
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const double outr = (double)outrate;
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < out_frames; j += stride) {
-        int64_t num = j * inrate;
-        int64_t c = (num + outrate - 1) / outrate;
-        int64_t d = c * outrate - num;
-        for (int ch = 0; ch < nch; ch++) {
-            int cur = (int)((uint32_t)(int32_t)in[c * nch + ch] << 16);
-            int prev = (c > 0) ? (int)((uint32_t)(int32_t)in[(c - 1) * nch + ch] << 16) : 0;
-            double v = __ddiv_rn(__dadd_rn(__dmul_rn((double)prev, (double)d),
-                                           __dmul_rn((double)cur, (double)(outrate - d))), outr);
-            int o = __double2int_rz(v);
-            out[j * nch + ch] = (int16_t)(o >> 16);
+    // One 64-bit division locates the first frame of a warp's chunk; every other frame is placed
+    // relative to it with 32-bit arithmetic (the reduced rates are below 2^21, so lane*inrate
+    // fits easily).  Lanes map to consecutive output frames: coalesced stores, near-coalesced loads.
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const uint32_t inr = (uint32_t)inrate, outr32 = (uint32_t)outrate;
+    const double rcp_outr = 1.0 / (double)outrate;
+    const int64_t chunk = 32 * kRcvIters;
+    for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk) {
+        const int64_t num0 = jc * inrate;
+        int64_t c0 = (num0 + outrate - 1) / outrate;
+        uint32_t d0 = (uint32_t)(c0 * outrate - num0);
+        for (int it = 0; it < kRcvIters; it++) {
+            const int64_t j = jc + it * 32 + lane;
+            // this lane's frame: num = num_base + lane*inrate
+            const uint32_t k = (uint32_t)lane * inr;
+            const uint32_t adv = (k > d0) ? (k - d0 + outr32 - 1) / outr32 : 0u;
+            const int64_t c = c0 + adv;
+            const uint32_t d = d0 + adv * outr32 - k;
+            if (j < out_frames) {
+                for (int ch = 0; ch < nch; ch++) {
+                    int cur = (int)((uint32_t)(int32_t)in[c * nch + ch] << 16);
+                    int prev = (c > 0) ? (int)((uint32_t)(int32_t)in[(c - 1) * nch + ch] << 16) : 0;
+                    // prev*d + cur*(outrate-d) is below 2^52 in magnitude: audioop's two fp64
+                    // products and their sum are exact, so the integer sum converted once is the
+                    // same double; the division is the IEEE one audioop performs
+                    // same double; and because |quotient| < 2^31 while outrate < 2^21, the correctly
+                    // rounded fp64 quotient truncates to the same integer as the exact quotient
+                    // does (a non-integer quotient is at least 1/outrate > half an ulp away from
+                    // the next integer).  So: exact integer division, via a reciprocal estimate
+                    // and one correction step instead of the ~60-instruction fp64 divide.
+                    const long long num = (long long)prev * (long long)d + (long long)cur * (long long)(outr32 - d);
+                    const long long mag = num < 0 ? -num : num;
+                    long long q = (long long)__double2int_rz(__dmul_rn((double)mag, rcp_outr));
+                    const long long rem = mag - q * (long long)outr32;
+                    if (rem < 0) q -= 1;
+                    else if (rem >= (long long)outr32) q += 1;
+                    int o = (int)(num < 0 ? -q : q);
+                    out[j * nch + ch] = (int16_t)(o >> 16);
+                }
+            }
+            // advance the base by 32 frames
+            const uint32_t kk = 32u * inr;
+            const uint32_t adv0 = (kk > d0) ? (kk - d0 + outr32 - 1) / outr32 : 0u;
+            c0 += adv0;
+            d0 = d0 + adv0 * outr32 - kk;
         }
     }
 }
@@ -255,6 +291,149 @@ pcm16_mix_at_many_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int
                 int64_t i = t0 + threadIdx.x + (int64_t)k * kPBlock;
                 if (i < t1) dst[i] = (int16_t)acc[k];
             }
+        }
+    }
+}
+
+// ---- indexed variant: per-tile source lists built on the device (count, scan, fill), so that a
+// tile only visits the sources that touch it.  The lists come out of the atomics unordered;
+// the apply kernel rank-sorts each (short) list in shared memory to restore source order.
+__global__ void mix_count_kernel(const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
+                                 int64_t nsrc, int64_t dst_count, int *__restrict__ tile_count)
+{
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nsrc) return;
+    int64_t o = dst_off[s], l = src_len[s];
+    if (l <= 0 || o >= dst_count) return;
+    int64_t last = min(o + l, dst_count) - 1;
+    for (int64_t t = o / kMixTile; t <= last / kMixTile; t++) atomicAdd(&tile_count[t], 1);
+}
+
+__global__ void __launch_bounds__(1024)
+mix_scan_kernel(const int *__restrict__ tile_count, int64_t ntiles, int *__restrict__ tile_start, int *__restrict__ tile_fill)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_running;
+    if (threadIdx.x == 0) s_running = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < ntiles; base += 1024) {
+        int64_t i = base + threadIdx.x;
+        int v = (i < ntiles) ? tile_count[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane], winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int o = __shfl_up_sync(0xffffffffu, winc, d);
+                if (lane >= d) winc += o;
+            }
+            s_warp[lane] = winc - w;
+        }
+        __syncthreads();
+        int ex = s_running + s_warp[warp] + inc - v;
+        if (i < ntiles) { tile_start[i] = ex; tile_fill[i] = 0; }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_running = ex + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) tile_start[ntiles] = s_running;
+}
+
+__global__ void mix_fill_kernel(const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
+                                int64_t nsrc, int64_t dst_count, const int *__restrict__ tile_start,
+                                int *__restrict__ tile_fill, int *__restrict__ list)
+{
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nsrc) return;
+    int64_t o = dst_off[s], l = src_len[s];
+    if (l <= 0 || o >= dst_count) return;
+    int64_t last = min(o + l, dst_count) - 1;
+    for (int64_t t = o / kMixTile; t <= last / kMixTile; t++)
+        list[tile_start[t] + atomicAdd(&tile_fill[t], 1)] = (int)s;
+}
+
+__global__ void __launch_bounds__(kPBlock)
+mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__restrict__ pool,
+                 const int64_t *__restrict__ src_off, const int64_t *__restrict__ src_len,
+                 const int64_t *__restrict__ dst_off, const int *__restrict__ tile_start,
+                 const int *__restrict__ list)
+{
+    __shared__ int s_raw[kMixList];
+    __shared__ int s_sorted[kMixList];
+    const int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
+    constexpr int kPer = kMixTile / kPBlock;           // 8 consecutive destination samples per thread
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int begin = tile_start[tile], n = tile_start[tile + 1] - begin;
+        if (n == 0) continue;                          // block-uniform: nothing mixes into this tile
+        const int64_t t0 = tile * kMixTile;
+        const int64_t t1 = min(t0 + (int64_t)kMixTile, dst_count);
+        const int64_t i0 = t0 + (int64_t)threadIdx.x * kPer;
+        int acc[kPer];
+        const bool full = (i0 + kPer <= t1) && ((((uintptr_t)(dst + i0)) & 15) == 0);
+        if (full) {
+            Vec8 v;
+            v.v = *reinterpret_cast<const int4 *>(dst + i0);
+#pragma unroll
+            for (int k = 0; k < kPer; k++) acc[k] = v.s[k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < kPer; k++) acc[k] = (i0 + k < t1) ? dst[i0 + k] : 0;
+        }
+        // the list in chunks of kMixList, each rank-sorted so that sources apply in index order;
+        // chunks themselves are ordered by splitting on the source index range
+        for (int lo = 0; lo < n; lo += kMixList) {
+            // (n > kMixList is rare: then every chunk pass selects the next kMixList smallest)
+            __syncthreads();
+            const int m = min(kMixList, n - lo);
+            if (n <= kMixList) {
+                for (int i = threadIdx.x; i < m; i += kPBlock) s_raw[i] = list[begin + i];
+                __syncthreads();
+                for (int i = threadIdx.x; i < m; i += kPBlock) {
+                    const int mine = s_raw[i];
+                    int rank = 0;
+                    for (int u = 0; u < m; u++) rank += (s_raw[u] < mine) ? 1 : 0;
+                    s_sorted[rank] = mine;
+                }
+            } else {
+                // rank over the whole list in global memory; keep ranks [lo, lo+m)
+                for (int i = threadIdx.x; i < n; i += kPBlock) {
+                    const int mine = list[begin + i];
+                    int rank = 0;
+                    for (int u = 0; u < n; u++) rank += (list[begin + u] < mine) ? 1 : 0;
+                    if (rank >= lo && rank < lo + m) s_sorted[rank - lo] = mine;
+                }
+            }
+            __syncthreads();
+            for (int q = 0; q < m; q++) {
+                const int64_t s = s_sorted[q];
+                const int64_t o = dst_off[s], l = src_len[s];
+                const int16_t *src = pool + src_off[s];
+                const int64_t r0 = i0 - o;
+                if (r0 + kPer <= 0 || r0 >= l) continue;            // this thread's run is outside
+#pragma unroll
+                for (int k = 0; k < kPer; k++) {
+                    const int64_t r = r0 + k;
+                    if (r >= 0 && r < l && i0 + k < t1) acc[k] = sat16(acc[k] + (int)src[r]);
+                }
+            }
+        }
+        if (full) {
+            Vec8 v;
+#pragma unroll
+            for (int k = 0; k < kPer; k++) v.s[k] = (short)acc[k];
+            *reinterpret_cast<int4 *>(dst + i0) = v.v;
+        } else {
+#pragma unroll
+            for (int k = 0; k < kPer; k++)
+                if (i0 + k < t1) dst[i0 + k] = (int16_t)acc[k];
         }
     }
 }
@@ -406,22 +585,54 @@ extern "C" int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nch
     // prev*d + cur*(outrate-d) must stay exact in fp64: |sample<<16| < 2^31, so outrate < 2^21
     SB_REQUIRE(outrate < (1 << 21) && inrate < (1 << 21), "sb_pcm16_ratecv: reduced rates must be below 2^21");
     int64_t out_frames = ((in_frames - 1) * outrate) / inrate + 1;
-    pcm16_ratecv_kernel<<<grid_for(out_frames, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
+    pcm16_ratecv_kernel<<<grid_for((out_frames + kRcvIters - 1) / kRcvIters, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
         in_dev, in_frames, nchannels, inrate, outrate, out_frames, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
 
+extern "C" int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t nsrc, int64_t total_src_samples)
+{
+    if (dst_count <= 0 || nsrc <= 0) return 0;
+    int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
+    int64_t cap = total_src_samples / kMixTile + 2 * nsrc + 1;     // every source touches <= len/tile + 2 tiles
+    return (3 * ntiles + 2 + cap) * (int64_t)sizeof(int);
+}
+
 extern "C" int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
                                     const int64_t *src_off_dev, const int64_t *src_len_dev,
-                                    const int64_t *dst_off_dev, int64_t nsrc, void *stream)
+                                    const int64_t *dst_off_dev, int64_t nsrc, void *scratch_dev,
+                                    int64_t scratch_bytes, void *stream)
 {
     SB_REQUIRE(dst_dev && dst_count >= 0 && nsrc >= 0, "sb_pcm16_mix_at_many: bad arguments");
     if (!nsrc || !dst_count) return SB_OK;
     SB_REQUIRE(src_pool_dev && src_off_dev && src_len_dev && dst_off_dev, "sb_pcm16_mix_at_many: null pointer");
+    SB_REQUIRE(nsrc < 0x7fffffff, "sb_pcm16_mix_at_many: too many sources");
     int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
-    pcm16_mix_at_many_kernel<<<grid_for(ntiles, 1, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
-        dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, nsrc);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!scratch_dev) {
+        // no scratch: every tile scans the whole source list
+        pcm16_mix_at_many_kernel<<<grid_for(ntiles, 1, kPMaxBlocks), kPBlock, 0, s>>>(
+            dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, nsrc);
+        SB_LAUNCH_CHECK();
+        return SB_OK;
+    }
+    SB_REQUIRE(scratch_bytes >= (3 * ntiles + 2) * (int64_t)sizeof(int) + (int64_t)sizeof(int),
+               "sb_pcm16_mix_at_many: scratch too small");
+    int *tile_count = (int *)scratch_dev;
+    int *tile_start = tile_count + ntiles;
+    int *tile_fill = tile_start + ntiles + 1;
+    int *list = tile_fill + ntiles + 1;
+    SB_CUDA_CHECK(cudaMemsetAsync(tile_count, 0, (size_t)ntiles * sizeof(int), s));
+    int sgrid = (int)((nsrc + 255) / 256);
+    mix_count_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_count);
+    SB_LAUNCH_CHECK();
+    mix_scan_kernel<<<1, 1024, 0, s>>>(tile_count, ntiles, tile_start, tile_fill);
+    SB_LAUNCH_CHECK();
+    mix_fill_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_start, tile_fill, list);
+    SB_LAUNCH_CHECK();
+    mix_apply_kernel<<<grid_for(ntiles, 1, kPMaxBlocks * 4), kPBlock, 0, s>>>(
+        dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, tile_start, list);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }

@@ -546,8 +546,10 @@ class Sample:
         for n in lens[:-1]:
             offs.append(offs[-1] + n)
         idx = torch.tensor([offs, lens, starts], dtype=torch.int64).to(D.device())
+        nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), len(srcs), sum(lens))
+        scratch = D.empty(nscratch, torch.uint8)
         C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), D.ptr(pool), D.ptr(idx[0]),
-               D.ptr(idx[1]), D.ptr(idx[2]), len(srcs), D.stream())
+               D.ptr(idx[1]), D.ptr(idx[2]), len(srcs), D.ptr(scratch), nscratch, D.stream())
         return self
 
     def echo(self, length, amount, delay, decay):
