@@ -300,7 +300,7 @@ def run_ours(args):
     if rank == 0:
         plan = C.BankPlan()
         sms = torch.cuda.get_device_properties(local).multi_processor_count
-        C.call("sb_bank_plan_make", hi - lo, frames, sms, D.timebase_rad(SR).nsegs, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", hi - lo, frames, 0, sms, D.timebase_rad(SR).nsegs, ctypes.byref(plan))
         reps = 3
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]

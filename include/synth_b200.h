@@ -208,15 +208,19 @@ typedef struct sb_bank_plan {
     int32_t nsegs_rad;                   /* width of the closed-form FM table */
     int32_t generic_voices;              /* hint: 0 = every voice is fast (skip the generic kernels),
                                             -1 = unknown (run them; they exit early per group) */
-    int32_t reserved;
+    int32_t nprefix;                     /* generic path: spans covering [0, n0), see below */
+    int64_t n0;                          /* first frame of the render the plan was made for */
     int64_t off_fastv, off_tab;          /* layout of the scratch buffer */
     int64_t carry_bytes;                 /* size of scratch_dev: span sums + per-voice constants + FM tables */
     int64_t partial_bytes;               /* size of partial_dev: ngroups * (2*frames rounded up to 4) floats */
 } sb_bank_plan;
 
-/* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames`.
- * nsegs_rad = segment count of the 2*pi/samplerate time base. */
-int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, int nsegs_rad, sb_bank_plan *plan);
+/* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames` starting at
+ * frame n0.  nsegs_rad = segment count of the 2*pi/samplerate time base.
+ * A render that starts at n0 > 0 is exact for every voice: fast voices evaluate their FM sum
+ * in closed form at any frame; generic FM voices get theirs from a pre-pass that also covers
+ * [0, n0) (cost proportional to n0 for those voices only). */
+int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan);
 
 /* 1 when the voice takes the fast path (Sine/Triangle carrier, no FM or a Sine modulator):
  * fp32 per-sample arithmetic off one fp64 base per 8 samples, SFU sine, closed-form FM sums.

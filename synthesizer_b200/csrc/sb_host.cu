@@ -75,7 +75,7 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     SB_CUDA_CHECK(cudaGetDevice(&dev));
     SB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     sb_bank_plan plan;
-    rc = sb_bank_plan_make(nvoices, frames, sms, (int)g_tb.rad.size(), &plan);
+    rc = sb_bank_plan_make(nvoices, frames, 0, sms, (int)g_tb.rad.size(), &plan);
     if (rc) return rc;
     plan.generic_voices = 0;
     for (int v = 0; v < nvoices; v++)

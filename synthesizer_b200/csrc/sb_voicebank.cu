@@ -91,7 +91,8 @@ struct BankArgs {
     const sb_time_seg *tb_cyc;
     int nsegs_cyc;
     double samplerate;
-    double *carry;        // [nvoices][nspans] per-span LFO sums of generic voices (pre-pass), or null
+    double *carry;        // [nvoices][nprefix + nspans] per-span LFO sums of generic voices (pre-pass), or null
+    int nprefix;          // spans of span_len frames covering [0, n0): the FM sum before this render
     FastVoice *fastv;     // [nvoices]
     double2 *tab;         // [nvoices][nsegs_rad]: closed-form table (A, C) per modulator segment
     int fast_nspans;
@@ -568,9 +569,10 @@ bank_carry_kernel(BankArgs a)
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int64_t unit = ((int64_t)blockIdx.x * kGenWarps + (threadIdx.x >> 5));
-    const int64_t nunits = (int64_t)a.nvoices * a.nspans;
+    const int nrow = a.nprefix + a.nspans;
+    const int64_t nunits = (int64_t)a.nvoices * nrow;
     if (unit >= nunits) return;
-    const int v = (int)(unit / a.nspans), span = (int)(unit % a.nspans);
+    const int v = (int)(unit / nrow), row = (int)(unit % nrow);
     if (a.fastv[v].flags & FV_FAST) return;            // closed form, no pre-pass
     const sb_voice V = a.voices[v];
     double acc = 0.0;
@@ -578,13 +580,22 @@ bank_carry_kernel(BankArgs a)
         const bool c_rad = (V.c_wave == SB_WAVE_SINE), m_rad = (V.m_wave == SB_WAVE_SINE);
         const sb_time_seg *cs = c_rad ? s_rad : s_cyc, *ms = m_rad ? s_rad : s_cyc;
         const int cn = c_rad ? a.nsegs_rad : a.nsegs_cyc, mn = m_rad ? a.nsegs_rad : a.nsegs_cyc;
-        int64_t begin = (int64_t)span * a.span_len, end = begin + a.span_len;
-        if (end > a.frames) end = a.frames;
+        // absolute frame range of this row: a piece of [0, n0) (the FM sum accumulated before
+        // this render starts) or a span of the render itself
+        int64_t begin, end;
+        if (row < a.nprefix) {
+            begin = (int64_t)row * a.span_len;
+            end = begin + a.span_len;
+            if (end > a.n0) end = a.n0;
+        } else {
+            begin = a.n0 + (int64_t)(row - a.nprefix) * a.span_len;
+            end = begin + a.span_len;
+            if (end > a.n0 + a.frames) end = a.n0 + a.frames;
+        }
         TimeCursor cc, mc;
-        cc.seek(cs, cn, a.n0 + begin + lane);
-        mc.seek(ms, mn, a.n0 + begin + lane);
-        for (int64_t i = begin + lane; i < end; i += 32) {
-            int64_t n = a.n0 + i;
+        cc.seek(cs, cn, begin + lane);
+        mc.seek(ms, mn, begin + lane);
+        for (int64_t n = begin + lane; n < end; n += 32) {
             double t_n = cc.at(n);                               // cursor only moves forward
             double step = __dadd_rn(cc.at(n + 1), -t_n);         // exact: both on the table
             float m = lfo_value(V, mc.at(n));
@@ -592,7 +603,7 @@ bank_carry_kernel(BankArgs a)
         }
     }
     acc = warp_sum(acc);
-    if (lane == 0) a.carry[(int64_t)v * a.nspans + span] = acc;
+    if (lane == 0) a.carry[(int64_t)v * nrow + row] = acc;
 }
 
 __global__ void __launch_bounds__(kGenWarps * 32)
@@ -642,8 +653,8 @@ bank_generic_kernel(BankArgs a)
     for (int v = 0; v < nv; v++) {
         double c = 0.0;
         if (a.carry && s_voices[v].m_wave != SB_WAVE_NONE) {
-            const double *row = a.carry + (int64_t)s_vidx[v] * a.nspans;
-            for (int s = lane; s < span; s += 32) c += row[s];
+            const double *row = a.carry + (int64_t)s_vidx[v] * (a.nprefix + a.nspans);
+            for (int s = lane; s < a.nprefix + span; s += 32) c += row[s];
             c = warp_sum(c);
         }
         if (lane == 0) carry[v] = c;
@@ -776,9 +787,9 @@ extern "C" int sb_voice_is_fast(const sb_voice *voice, double samplerate)
     return voice_is_fast(*voice, samplerate) ? 1 : 0;
 }
 
-extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, int nsegs_rad, sb_bank_plan *plan)
+extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan)
 {
-    SB_REQUIRE(plan && nvoices >= 1 && frames >= 1 && nsegs_rad >= 1 && nsegs_rad <= kMaxSegs,
+    SB_REQUIRE(plan && nvoices >= 1 && frames >= 1 && n0 >= 0 && nsegs_rad >= 1 && nsegs_rad <= kMaxSegs,
                "sb_bank_plan_make: bad arguments");
     if (sm_count <= 0) sm_count = 148;
     // target: several waves of warps per SM (each warp is an independent unit, so many short
@@ -818,7 +829,11 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int sm_count, int 
     plan->fast_nspans = (int32_t)((frames + plan->fast_span_len - 1) / plan->fast_span_len);
     plan->nsegs_rad = nsegs_rad;
     plan->generic_voices = -1;
-    plan->off_fastv = align_up((int64_t)nvoices * nspans * (int64_t)sizeof(double), 256);
+    plan->n0 = n0;
+    const int64_t nprefix = (n0 + span_len - 1) / span_len;
+    SB_REQUIRE(nprefix < 0x7fffffff, "sb_bank_plan_make: start offset too large");
+    plan->nprefix = (int32_t)nprefix;
+    plan->off_fastv = align_up((int64_t)nvoices * (nprefix + nspans) * (int64_t)sizeof(double), 256);
     plan->off_tab = align_up(plan->off_fastv + (int64_t)nvoices * (int64_t)sizeof(FastVoice), 256);
     plan->carry_bytes = align_up(plan->off_tab + (int64_t)nvoices * nsegs_rad * (int64_t)sizeof(double2), 256);
     plan->partial_bytes = (ngroups > 1) ? (int64_t)ngroups * ((frames * 2 + 3) / 4 * 4) * (int64_t)sizeof(float) : 0;
@@ -859,7 +874,9 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.tb_cyc = tb_cyc_dev;
     a.nsegs_cyc = nsegs_cyc;
     a.samplerate = samplerate;
-    a.carry = (plan->nspans > 1) ? (double *)scratch : nullptr;
+    SB_REQUIRE(plan->n0 == n0, "sb_bank_render_f32: the plan was made for another start offset");
+    a.nprefix = plan->nprefix;
+    a.carry = (plan->nspans + plan->nprefix > 1) ? (double *)scratch : nullptr;
     a.fastv = (FastVoice *)(scratch + plan->off_fastv);
     a.tab = (double2 *)(scratch + plan->off_tab);
     a.fast_nspans = plan->fast_nspans;
@@ -882,7 +899,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     }
     if (plan->generic_voices != 0) {
         if (a.carry) {
-            int64_t nunits = (int64_t)a.nvoices * a.nspans;
+            int64_t nunits = (int64_t)a.nvoices * (a.nprefix + a.nspans);
             int64_t blocks = (nunits + kGenWarps - 1) / kGenWarps;
             SB_REQUIRE(blocks < 0x7fffffff, "sb_bank_render_f32: too many (voice, span) units");
             bank_carry_kernel<<<(unsigned)blocks, kGenWarps * 32, tb_bytes, s>>>(a);

@@ -313,7 +313,24 @@ class MixingFilter(Filter):
     def __init__(self, *sources):
         super().__init__(sources)
 
+    def _as_bank(self):
+        """When every source is a plain voice — [EnvelopeFilter(] waveform oscillator with an
+        optional plain waveform FM LFO [)] — the whole mix is one launch of the fused voice-bank
+        kernel instead of one kernel chain per source.  Rebuilt per request because upstream
+        oscillators may have their public attributes changed between renders."""
+        if len(self._sources) < 2:
+            return None
+        from .voicebank import VoiceBank
+        try:
+            return VoiceBank.from_oscillators(self._sources, gains=[(1.0, 0.0)] * len(self._sources),
+                                              samplerate=self._samplerate)
+        except ValueError:
+            return None
+
     def _render_range(self, n0, count):
+        bank = self._as_bank()
+        if bank is not None:
+            return bank.render(count, start=n0)[0::2].contiguous()      # left channel = the mono mix
         bufs = [s._fetch(n0, n0 + count) for s in self._sources]
         ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64).to(D.device())
         out = D.empty(count, torch.float32)

@@ -122,7 +122,7 @@ class VoiceBank:
         plan = C.BankPlan()
         sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
         tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
-        C.call("sb_bank_plan_make", nv, nframes, sms, tr.nsegs, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", nv, nframes, start, sms, tr.nsegs, ctypes.byref(plan))
         if generic_voices is not None:
             plan.generic_voices = generic_voices
         carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)

@@ -93,7 +93,7 @@ def test_bad_arguments_fail_loudly():
         C.call("sb_envelope_build", 48000.0, -1.0, 0.0, 0.0, 0.5, 0.0, ctypes.byref(C.Envelope()))
     plan = C.BankPlan()
     with pytest.raises(C.SbError):
-        C.call("sb_bank_plan_make", 0, 100, 148, 40, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", 0, 100, 0, 148, 40, ctypes.byref(plan))
     assert C.lib.sb_pcm16_ratecv_frames(8, 44100, 48000) == 8
     assert C.lib.sb_pcm16_ratecv_frames(8, 48000, 22050) == 4
     assert C.lib.sb_pcm16_ratecv_frames(0, 48000, 22050) == 0
@@ -102,7 +102,12 @@ def test_bad_arguments_fail_loudly():
 def test_bank_plan_covers_the_work():
     for nv, frames in [(1, 100), (1, 2_880_000), (128, 480_000), (8192, 480_000), (65536, 480_000), (3, 257)]:
         plan = C.BankPlan()
-        C.call("sb_bank_plan_make", nv, frames, 148, 40, ctypes.byref(plan))
+        C.call("sb_bank_plan_make", nv, frames, 0, 148, 40, ctypes.byref(plan))
+        assert plan.nprefix == 0 and plan.n0 == 0
+        shifted = C.BankPlan()
+        C.call("sb_bank_plan_make", nv, frames, 5 * plan.span_len + 1, 148, 40, ctypes.byref(shifted))
+        assert shifted.nprefix == 6 and shifted.carry_bytes >= plan.carry_bytes
+        assert shifted.off_fastv >= nv * (6 + shifted.nspans) * 8
         assert plan.voices_per_group * plan.ngroups >= nv
         assert plan.span_len % 256 == 0 and plan.span_len * plan.nspans >= frames
         assert plan.span_len * (plan.nspans - 1) < frames

@@ -172,6 +172,35 @@ def test_filters_chain(cuda):
     assert_within_lsb(got, want, 1, "mix/delay")
 
 
+def test_mixing_filter_of_voices_uses_the_fused_bank(cuda):
+    """MixingFilter over plain voices (upstream API, nothing backend specific) is rendered by
+    the fused voice-bank kernel: same result as the oracle's MixingFilter, a handful of
+    launches instead of a kernel chain per source, and chunked blocks() continue correctly."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _device as D
+    from oracle import synth_oracle as so
+    sr, n = 44100, 12000
+
+    def build(m):
+        voices = []
+        for k in range(6):
+            lfo = m.Sine(3.0 + k, 0.02 * (k + 1), samplerate=sr) if k % 2 == 0 else None
+            cls = [m.Sine, m.Triangle, m.Sawtooth][k % 3]
+            osc = cls(110.0 * (k + 1), 0.15, 0.1 * k, 0.0, fm_lfo=lfo, samplerate=sr)
+            voices.append(m.EnvelopeFilter(osc, 0.01, 0.03, 0.1, 0.6, 0.08) if k < 4 else osc)
+        return m.MixingFilter(*voices)
+
+    mix = build(sb)
+    l0 = D.launch_count()
+    got = dev_pcm16(mix.render(n))
+    assert D.launch_count() - l0 <= 7          # prepare, fast, carry, generic, fold(+0), to_pcm
+    want = pcm16_of(so.render_floats(build(so), n))
+    assert_within_lsb(got, want, 1, "MixingFilter via the voice bank")
+    blocks = list(itertools.islice(build(sb).blocks(), 40))
+    flat = np.array(list(itertools.chain.from_iterable(blocks)), dtype=np.float32)
+    np.testing.assert_allclose(flat, mix.render(len(flat)).cpu().numpy(), atol=2e-6)
+
+
 def test_echo_filter(cuda):
     import synthesizer_b200 as sb
     from oracle import coracle as co

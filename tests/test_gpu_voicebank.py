@@ -145,6 +145,24 @@ def test_bank_chunked_start_offsets(cuda):
     np.testing.assert_allclose(np.concatenate([a, b]), whole, rtol=0, atol=1e-7)
 
 
+def test_bank_start_offset_with_fm_voices_of_both_classes(cuda):
+    """A render that starts at n0 > 0 must continue every voice's FM sum from frame 0: fast
+    voices by closed form, generic ones through the pre-pass over [0, n0)."""
+    sr, n, cut = 48000, 40000, 23456
+    bank, P = make_bank(20, sr, 123, 0.8, fm=True)
+    for v in bank._voices:
+        if v.m_wave == 4:
+            v.m_pw = 0.1
+    assert 0 < bank.count_generic() < 20
+    whole = bank.render(n).cpu().numpy()
+    tail = bank.render(n - cut, start=cut).cpu().numpy()
+    off = np.abs(tail - whole[2 * cut:]) > 1e-6
+    assert off.sum() <= 2, "%d samples differ between a whole render and one started at frame %d" % (off.sum(), cut)
+    got = dev_pcm16(bank.render(n - cut, start=cut))
+    bad = np.abs(got.astype(np.int64) - oracle_bank_pcm(P, n, sr)[2 * cut:]) > 1
+    assert bad.mean() < 2e-5
+
+
 def test_config3_128_voice_chord_bank(cuda):
     """BASELINE config 3: 128-voice chord bank, mixed waveforms, per-voice ADSR, stereo 48 kHz
     (10 s)."""
