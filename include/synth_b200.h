@@ -62,6 +62,9 @@ typedef struct sb_time_seg {
 
 /* Fills segs[] for n in [0, max_n]; returns the number of segments or a negative error. */
 int sb_timebase_build(double increment, int64_t max_n, sb_time_seg *segs, int max_segs);
+/* The same for an accumulation that starts at t0 >= 0 instead of 0 (upstream's Fast*
+ * oscillators start their t at phase*2*pi resp. phase/frequency). */
+int sb_timebase_build_from(double t0, double increment, int64_t max_n, sb_time_seg *segs, int max_segs);
 /* The accumulated value after n additions (host helper; same formula as the kernels). */
 double sb_timebase_at(const sb_time_seg *segs, int nsegs, int64_t n);
 /* Smallest n >= n_from with t(n) >= limit, i.e. where `while time < limit` stops. */
@@ -100,6 +103,15 @@ typedef struct sb_osc_params {
 int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_dev, int nsegs,
                       int64_t n0, int64_t count, const double *fmsum_dev, const float *pwm_dev,
                       float *out_dev, void *stream);
+
+/* synthplayer.oscillators.Harmonics.blocks (and SquareH / SawtoothH built on it): the sum over
+ * harmonics k of sin(k*q)*amp_k with q = t*frequency + phase_correction in radians, times
+ * p->amplitude plus p->bias; FM as for Sine (p->wave is ignored).  harm_n / harm_amp are host
+ * arrays of nharm entries, already filtered to the harmonics below Nyquist. */
+#define SB_HARMONICS_MAX 128
+int sb_harmonics_render_f32(const sb_osc_params *p, const int32_t *harm_n, const float *harm_amp,
+                            int nharm, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                            int64_t count, const double *fmsum_dev, float *out_dev, void *stream);
 
 /* Exclusive prefix sum of lfo[i]*step(n0+i) in fp64 with a running carry (carry_dev: one
  * device double, read at entry, advanced at exit) so that consecutive chunks continue the

@@ -72,6 +72,9 @@ _SIGNATURES = {
     "sb_last_error": (c_char_p, []),
     "sb_launch_count": (c_int64, []),
     "sb_timebase_build": (c_int, [c_double, c_int64, POINTER(TimeSeg), c_int]),
+    "sb_timebase_build_from": (c_int, [c_double, c_double, c_int64, POINTER(TimeSeg), c_int]),
+    "sb_harmonics_render_f32": (c_int, [POINTER(OscParams), POINTER(c_int32), POINTER(c_float), c_int, _P, c_int,
+                                        c_int64, c_int64, _P, _P, _P]),
     "sb_timebase_at": (c_double, [POINTER(TimeSeg), c_int, c_int64]),
     "sb_timebase_first_ge": (c_int64, [POINTER(TimeSeg), c_int, c_int64, c_double]),
     "sb_envelope_build": (c_int, [c_double, c_double, c_double, c_double, c_double, c_double, POINTER(Envelope)]),

@@ -47,10 +47,11 @@ def zeros(n, dtype):
 class Timebase:
     """Host copy of the exact time base for one increment, plus lazily made device copies."""
 
-    def __init__(self, increment):
+    def __init__(self, increment, t0=0.0):
         self.increment = increment
+        self.t0 = t0
         self.segs = (C.TimeSeg * C.TIMEBASE_MAX_SEGS)()
-        self.nsegs = C.call("sb_timebase_build", increment, _TB_MAX_N, self.segs, C.TIMEBASE_MAX_SEGS)
+        self.nsegs = C.call("sb_timebase_build_from", t0, increment, _TB_MAX_N, self.segs, C.TIMEBASE_MAX_SEGS)
         self._dev = {}
 
     def at(self, n):
@@ -73,10 +74,13 @@ class Timebase:
 _timebases = {}
 
 
-def timebase(increment):
-    tb = _timebases.get(increment)
+def timebase(increment, t0=0.0):
+    key = (increment, t0)
+    tb = _timebases.get(key)
     if tb is None:
-        tb = _timebases[increment] = Timebase(increment)
+        if len(_timebases) > 4096:          # Fast* oscillators make one per (frequency, phase)
+            _timebases.clear()
+        tb = _timebases[key] = Timebase(increment, t0)
     return tb
 
 

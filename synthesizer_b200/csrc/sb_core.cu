@@ -37,7 +37,13 @@ static inline double fp_add(double a, double b)
 
 extern "C" int sb_timebase_build(double increment, int64_t max_n, sb_time_seg *segs, int max_segs)
 {
-    if (!(increment > 0.0) || !isfinite(increment) || max_n < 0 || !segs || max_segs < 4) {
+    return sb_timebase_build_from(0.0, increment, max_n, segs, max_segs);
+}
+
+extern "C" int sb_timebase_build_from(double t0, double increment, int64_t max_n, sb_time_seg *segs, int max_segs)
+{
+    if (!(increment > 0.0) || !isfinite(increment) || !(t0 >= 0.0) || !isfinite(t0) || max_n < 0 || !segs ||
+        max_segs < 4) {
         sb::set_error("sb_timebase_build: bad arguments");
         return SB_EINVAL;
     }
@@ -56,7 +62,7 @@ extern "C" int sb_timebase_build(double increment, int64_t max_n, sb_time_seg *s
         return true;
     };
     int64_t n = 0;
-    double t = 0.0;
+    double t = t0;
     while (n <= max_n) {
         double t1 = fp_add(t, increment);
         double s1 = t1 - t;

@@ -54,6 +54,43 @@ osc_render_kernel(sb_osc_params p, const sb_time_seg *__restrict__ tb, int nsegs
     }
 }
 
+// ------------------------------------------------------------------ harmonics
+struct HarmonicSet {
+    int n;
+    int k[SB_HARMONICS_MAX];
+    float amp[SB_HARMONICS_MAX];
+};
+
+__global__ void __launch_bounds__(kBlock)
+harmonics_kernel(sb_osc_params p, const __grid_constant__ HarmonicSet hs, const sb_time_seg *__restrict__ tb, int nsegs,
+                 int64_t n0, int64_t count, const double *__restrict__ fmsum, float *__restrict__ out)
+{
+    __shared__ sb_time_seg s_tb[kMaxSegs];
+    for (int i = threadIdx.x; i < nsegs; i += blockDim.x) s_tb[i] = tb[i];
+    __syncthreads();
+    const double pc0 = phase0_of(SB_WAVE_SINE, p.phase);
+    const float amp = (float)p.amplitude, bias = (float)p.bias;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        TimeCursor cur;
+        cur.seek(s_tb, nsegs, n0 + i);
+        const double t = cur.at(n0 + i);
+        const double q = fmsum ? __dadd_rn(pc0, __dmul_rn(p.frequency, __dadd_rn(t, fmsum[i])))
+                               : __dadd_rn(__dmul_rn(t, p.frequency), pc0);
+        float h = 0.0f;
+        for (int j = 0; j < hs.n; j++) {
+            // upstream evaluates sin(q*k) in fp64: form the product in fp64, reduce it to one
+            // turn there, then the SFU sine on the reduced argument
+            const double x = __dmul_rn(q, (double)hs.k[j]);
+            const double kk = rint(x * kInvTwoPi);
+            double r = fma(-kk, kTwoPiHi, x);
+            r = fma(-kk, kTwoPiLo, r);
+            h = fmaf(__sinf((float)r), hs.amp[j], h);
+        }
+        out[i] = fmaf(h, amp, bias);
+    }
+}
+
 // ------------------------------------------------------------------ FM prefix sum
 // Three phases over tiles of kScanTile samples: tile sums -> scan of tile sums (one block)
 // -> per-tile exclusive scan with the tile offset.  All sums in fp64.
@@ -374,6 +411,27 @@ extern "C" int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_d
     int grid = grid_for((count + ITEMS - 1) / ITEMS, kBlock, kMaxBlocks);
     osc_render_kernel<ITEMS><<<grid, kBlock, 0, (cudaStream_t)stream>>>(*p, tb_dev, nsegs, n0, count,
                                                                        fmsum_dev, pwm_dev, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_harmonics_render_f32(const sb_osc_params *p, const int32_t *harm_n, const float *harm_amp,
+                                       int nharm, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                                       int64_t count, const double *fmsum_dev, float *out_dev, void *stream)
+{
+    SB_REQUIRE(p && tb_dev && out_dev, "sb_harmonics_render_f32: null pointer");
+    SB_REQUIRE(nharm >= 0 && nharm <= SB_HARMONICS_MAX && (nharm == 0 || (harm_n && harm_amp)),
+               "sb_harmonics_render_f32: between 0 and 128 harmonics");
+    SB_REQUIRE(nsegs > 0 && nsegs <= kMaxSegs && n0 >= 0 && count >= 0, "sb_harmonics_render_f32: bad range");
+    if (count == 0) return SB_OK;
+    HarmonicSet hs;
+    hs.n = nharm;
+    for (int j = 0; j < nharm; j++) {
+        hs.k[j] = harm_n[j];
+        hs.amp[j] = harm_amp[j];
+    }
+    harmonics_kernel<<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
+        *p, hs, tb_dev, nsegs, n0, count, fmsum_dev, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }

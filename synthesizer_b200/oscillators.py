@@ -14,6 +14,7 @@ There is no CPU implementation behind these classes.
 """
 import ctypes
 import itertools
+import math
 import random
 import sys
 from math import log
@@ -24,8 +25,9 @@ from . import _cabi as C
 from . import _device as D
 from . import params
 
-__all__ = ["Oscillator", "Filter", "Sine", "Triangle", "Square", "Pulse", "Sawtooth", "WhiteNoise",
-           "Linear", "EnvelopeFilter", "MixingFilter", "AmpModulationFilter", "DelayFilter",
+__all__ = ["Oscillator", "Filter", "Sine", "Triangle", "Square", "SquareH", "Harmonics", "Pulse", "Sawtooth",
+           "SawtoothH", "WhiteNoise", "Linear", "FastSine", "FastPulse", "FastTriangle", "FastSawtooth",
+           "FastSquare", "EnvelopeFilter", "MixingFilter", "AmpModulationFilter", "DelayFilter",
            "EchoFilter", "ClipFilter", "AbsFilter", "NullFilter"]
 
 _FM_SEEK_CHUNK = 1 << 22
@@ -195,6 +197,113 @@ class Pulse(_WaveOscillator):
         super().__init__(frequency, amplitude, phase, bias, fm_lfo, samplerate)
         self.pulsewidth = pulsewidth
         self._pwm_lfo = pwm_lfo
+
+
+class Harmonics(_WaveOscillator):
+    """Sum of sine harmonics [(n, amplitude_factor), ...] below Nyquist, with optional FM
+    (synthplayer.oscillators.Harmonics)."""
+    _wave = C.WAVE_SINE
+
+    def __init__(self, frequency, harmonics, amplitude=1.0, phase=0.0, bias=0.0, fm_lfo=None, samplerate=0):
+        super().__init__(frequency, amplitude, phase, bias, fm_lfo, samplerate)
+        nyquist = self._samplerate / 2.0
+        self.harmonics = [(n, a) for n, a in harmonics if n * frequency <= nyquist]
+        if len(self.harmonics) > 128:
+            raise ValueError("at most 128 harmonics are supported")
+
+    def _render_range(self, n0, count):
+        tb = self._timebase()
+        fmsum = None
+        if self._fm_lfo is not None:
+            self._fm_seek(n0, tb)
+            fmsum = self._fm_prefix(n0, count, tb)
+        out = D.empty(count, torch.float32)
+        p = _osc_params(C.WAVE_SINE, self.frequency, self.amplitude, self._phase, self.bias, 0.0, self._samplerate)
+        nh = len(self.harmonics)
+        hn = (ctypes.c_int32 * max(1, nh))(*[int(n) for n, _ in self.harmonics])
+        ha = (ctypes.c_float * max(1, nh))(*[float(a) for _, a in self.harmonics])
+        C.call("sb_harmonics_render_f32", ctypes.byref(p), hn, ha, nh, D.ptr(tb.dev()), tb.nsegs, n0, count,
+               D.ptr(fmsum), D.ptr(out), D.stream())
+        return out
+
+
+class SquareH(Harmonics):
+    """Square wave from odd sine harmonics (synthplayer.oscillators.SquareH)."""
+
+    def __init__(self, frequency, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None, samplerate=0):
+        harmonics = [(n, 1.0 / n) for n in range(1, num_harmonics * 2, 2)]
+        super().__init__(frequency, harmonics, amplitude, phase, bias, fm_lfo, samplerate)
+
+
+class SawtoothH(Harmonics):
+    """Sawtooth wave from sine harmonics (synthplayer.oscillators.SawtoothH)."""
+
+    def __init__(self, frequency, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None, samplerate=0):
+        harmonics = [(n, 1.0 / n) for n in range(1, num_harmonics + 1)]
+        super().__init__(frequency, harmonics, -amplitude, phase + 0.5, bias, fm_lfo, samplerate)
+
+
+class _FastOscillator(Oscillator):
+    """The Fast* oscillators of upstream: no FM, t starts at a phase-dependent value and is
+    advanced serially; here evaluated per sample index on a time base built for that start
+    value, with frequency folded the way each upstream class folds it."""
+    _wave = None
+
+    def __init__(self, frequency, amplitude=1.0, phase=0.0, bias=0.0, samplerate=0):
+        super().__init__(samplerate=samplerate or params.norm_samplerate)
+        self._frequency = frequency
+        self._phase = phase
+        self.amplitude = amplitude
+        self.bias = bias
+        self._pulsewidth = 0.1
+        if phase < 0:
+            raise ValueError("negative phase is not supported for the Fast* oscillators on this backend")
+
+    def _render_range(self, n0, count):
+        if self._wave == C.WAVE_SINE:
+            # FastSine: t0 = phase*2*pi, increment = 2*pi/(samplerate/frequency), value = sin(t)
+            rate = self._samplerate / self._frequency
+            tb = D.timebase(2.0 * math.pi / rate, self._phase * 2.0 * math.pi)
+            freq = 1.0
+        else:
+            # FastTriangle & co: t0 = phase/frequency, increment = 1/samplerate, tt = t*frequency
+            tb = D.timebase(1.0 / self._samplerate, self._phase / self._frequency)
+            freq = self._frequency
+        out = D.empty(count, torch.float32)
+        p = _osc_params(self._wave, freq, self.amplitude, 0.0, self.bias, self._pulsewidth, self._samplerate)
+        C.call("sb_osc_render_f32", ctypes.byref(p), D.ptr(tb.dev()), tb.nsegs, n0, count,
+               D.ptr(None), D.ptr(None), D.ptr(out), D.stream())
+        return out
+
+
+class FastSine(_FastOscillator):
+    """Fast sine wave oscillator, no FM (synthplayer.oscillators.FastSine)."""
+    _wave = C.WAVE_SINE
+
+
+class FastTriangle(_FastOscillator):
+    """Fast triangle wave oscillator, no FM (synthplayer.oscillators.FastTriangle)."""
+    _wave = C.WAVE_TRIANGLE
+
+
+class FastSquare(_FastOscillator):
+    """Fast square wave oscillator, no FM (synthplayer.oscillators.FastSquare)."""
+    _wave = C.WAVE_SQUARE
+
+
+class FastSawtooth(_FastOscillator):
+    """Fast sawtooth wave oscillator, no FM (synthplayer.oscillators.FastSawtooth)."""
+    _wave = C.WAVE_SAWTOOTH
+
+
+class FastPulse(_FastOscillator):
+    """Fast pulse wave oscillator, fixed pulse width, no FM/PWM (synthplayer.oscillators.FastPulse)."""
+    _wave = C.WAVE_PULSE
+
+    def __init__(self, frequency, amplitude=1.0, phase=0.0, bias=0.0, pulsewidth=0.1, samplerate=0):
+        assert 0 <= pulsewidth <= 1
+        super().__init__(frequency, amplitude, phase, bias, samplerate)
+        self._pulsewidth = pulsewidth
 
 
 class WhiteNoise(Oscillator):

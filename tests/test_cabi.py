@@ -61,6 +61,26 @@ def test_timebase_is_bit_identical_to_serial_accumulation(inc):
     assert C.lib.sb_timebase_first_ge(segs, n, 60000, lim) == 60000
 
 
+@pytest.mark.parametrize("t0,inc", [(0.3 * 2 * math.pi, 2 * math.pi * 441.0 / 44100), (0.77 / 50.0, 1 / 44100),
+                                    (123.456, 1 / 48000), (1e-9, 1 / 96000)])
+def test_timebase_from_a_start_value(t0, inc):
+    segs = (C.TimeSeg * 256)()
+    n = C.lib.sb_timebase_build_from(t0, inc, 1 << 40, segs, 256)
+    assert 0 < n < 120
+    N = 2_000_000
+    serial = np.empty(N)
+    serial[0] = t0
+    acc = np.cumsum(np.concatenate([[t0], np.full(N - 1, inc)]))      # sequential adds starting from t0
+    serial[:] = acc
+    starts = np.array([segs[i].n_start for i in range(n)])
+    ts = np.array([segs[i].t_start for i in range(n)])
+    st = np.array([segs[i].step for i in range(n)])
+    idx = np.searchsorted(starts, np.arange(N), side="right") - 1
+    closed = ts[idx] + (np.arange(N) - starts[idx]).astype(np.float64) * st[idx]
+    assert np.array_equal(serial, closed)
+    assert C.lib.sb_timebase_build_from(-1.0, inc, 10, segs, 256) < 0
+
+
 @pytest.mark.parametrize("adsr", [(0.05, 0.1, 0.3, 0.6, 0.2), (0.0, 0.1, 0.0, 0.5, 0.1), (0.1, 0.0, 0.2, 1.0, 0.0),
                                   (0.013, 0.027, 0.111, 0.35, 0.3333), (1 / 48000, 2 / 48000, 0.0, 0.0, 0.01)])
 def test_envelope_boundaries_match_the_serial_generator(adsr):

@@ -218,6 +218,39 @@ def test_echo_filter(cuda):
     np.testing.assert_allclose(flat, osc.render(len(flat)).cpu().numpy(), atol=1e-6)
 
 
+@pytest.mark.parametrize("name", ["FastSine", "FastTriangle", "FastSquare", "FastSawtooth", "FastPulse"])
+def test_fast_oscillators(cuda, name):
+    """The Fast* classes start t at a phase-dependent value; the time base is built from there."""
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    sr, n = 44100, 30000
+    for freq, phase in [(441.0, 0.0), (1234.5, 0.3), (50.0, 0.77)]:
+        kw = dict(pulsewidth=0.3) if name == "FastPulse" else {}
+        got = dev_pcm16(getattr(sb, name)(freq, 0.8, phase, 0.05, samplerate=sr, **kw).render(n))
+        want = pcm16_of(so.render_floats(getattr(so, name)(freq, 0.8, phase, 0.05, samplerate=sr, **kw), n))
+        assert_within_lsb(got, want, 1, "%s %g Hz phase %g" % (name, freq, phase))
+    with pytest.raises(ValueError):
+        getattr(sb, name)(440.0, 0.8, -0.25, samplerate=sr)
+
+
+def test_harmonics_oscillators(cuda):
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    sr, n = 48000, 16000
+
+    def cases(m):
+        lfo = m.Sine(4.0, 0.03, samplerate=sr)
+        return [m.Harmonics(220.0, [(1, 0.5), (2, 0.25), (5, 0.125), (400, 0.9)], 0.8, 0.1, 0.02, samplerate=sr),
+                m.SquareH(330.0, 9, 0.7, 0.2, samplerate=sr),
+                m.SawtoothH(110.0, 12, 0.6, 0.0, 0.01, fm_lfo=lfo, samplerate=sr)]
+
+    for g, o in zip(cases(sb), cases(so)):
+        got = dev_pcm16(g.render(n), scale=20000.0)
+        want = pcm16_of(so.render_floats(o, n), scale=20000.0)
+        assert_within_lsb(got, want, 1, type(g).__name__)
+    assert len(cases(sb)[0].harmonics) == 3          # the 400th harmonic is above Nyquist
+
+
 def test_wavesynth_config1_sine_440(cuda):
     """BASELINE config 1: single 440 Hz sine, 1 s mono 44.1 kHz int16 rendered to a Sample."""
     import synthesizer_b200 as sb
