@@ -77,37 +77,62 @@ def build_voices(p, lo, hi, total_voices):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: NVML polled every ~2 ms
+    from a thread (the timed region is tens of milliseconds, too short for nvidia-smi -lms);
+    falls back to one nvidia-smi query if NVML cannot be loaded."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.sm, self.bits, self.max_mhz = index, [], 0, None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            # torch's device index follows CUDA_VISIBLE_DEVICES; NVML's does not
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.index
+            if vis:
+                ids = [x for x in vis.split(",") if x.strip() != ""]
+                if self.index < len(ids) and ids[self.index].strip().isdigit():
+                    phys = int(ids[self.index])
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self._nvml = pynvml
+            self._thread = threading.Thread(target=self._poll, daemon=True)
+            self._thread.start()
+        except Exception:
+            self._nvml = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+    def _poll(self):
+        nv = self._nvml
+        while not self._stop.is_set():
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+            except Exception:
+                break
+            time.sleep(0.002)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, x in zip(names, r[2:6]) if x.lower() == "active"})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        if self._nvml is None:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+                sm, mx = [int(x) for x in out.strip().split(",")]
+                return {"sm_mhz": sm, "sm_max_mhz": mx, "reasons": ["one nvidia-smi sample after the run"], "samples": 1}
+            except Exception:
+                return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML, no nvidia-smi"], "samples": 0}
+        self._stop.set()
+        self._thread.join(timeout=1.0)
+        sm = sorted(self.sm)
+        reasons = sorted(name for bit, name in self.REASONS.items() if self.bits & bit)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(sm)}
 
 
 # ----------------------------------------------------------------------------- CPU arm
@@ -247,7 +272,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step_resident():
-        mix = bank.render(frames, voices_dev=voices_dev, generic_voices=0)
+        mix = bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -255,7 +280,7 @@ def run_ours(args):
 
     def step_e2e():
         vd = host_voices.to(D.device(), non_blocking=True)       # H2D of this step's inputs
-        mix = bank.render(frames, voices_dev=vd, generic_voices=0)
+        mix = bank.render(frames, voices_dev=vd, generic_voices=0, edged_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -307,7 +332,7 @@ def run_ours(args):
         l0 = D.launch_count()
         ev[0].record()
         for _ in range(reps):
-            bank.render(frames, voices_dev=voices_dev, generic_voices=0)
+            bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0)
         ev[1].record()
         torch.cuda.synchronize()
         render_ms = ev[0].elapsed_time(ev[1]) / reps

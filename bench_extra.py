@@ -189,8 +189,15 @@ def main():
     classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
     bank = sb.VoiceBank(sr)
     for v in range(128):
-        cw, mw = int(rng.integers(0, 5)), int(rng.integers(0, 5))
-        lfo = classes[mw](float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=sr)
+        # mixed carrier waveforms; half of the voices have a sine vibrato, an eighth an LFO of
+        # another waveform (those take the generic per-sample fp64 kernel)
+        cw = int(rng.integers(0, 5))
+        r = rng.random()
+        lfo = None
+        if r < 0.5:
+            lfo = sb.Sine(float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=sr)
+        elif r < 0.625:
+            lfo = classes[int(rng.integers(1, 5))](float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=sr)
         car = classes[cw](float(rng.uniform(55, 1760)), 0.9 / 128, fm_lfo=lfo, samplerate=sr)
         pan = float(rng.uniform(-1, 1))
         bank.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)

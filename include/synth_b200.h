@@ -221,6 +221,9 @@ typedef struct sb_bank_plan {
     int32_t generic_voices;              /* hint: 0 = every voice is fast (skip the generic kernels),
                                             -1 = unknown (run them; they exit early per group) */
     int32_t nprefix;                     /* generic path: spans covering [0, n0), see below */
+    int32_t edged_voices;                /* hint: 0 = no fast voice has a Square/Sawtooth/Pulse carrier
+                                            (skip that kernel), -1 = unknown */
+    int32_t reserved;
     int64_t n0;                          /* first frame of the render the plan was made for */
     int64_t off_fastv, off_tab;          /* layout of the scratch buffer */
     int64_t carry_bytes;                 /* size of scratch_dev: span sums + per-voice constants + FM tables */
@@ -234,9 +237,12 @@ typedef struct sb_bank_plan {
  * [0, n0) (cost proportional to n0 for those voices only). */
 int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan);
 
-/* 1 when the voice takes the fast path (Sine/Triangle carrier, no FM or a Sine modulator):
- * fp32 per-sample arithmetic off one fp64 base per 8 samples, SFU sine, closed-form FM sums.
- * Other voices take the generic path (per-sample fp64 phase, exact edge positions). */
+/* 1 when the voice takes the fast path (any of the five carriers, with no FM or a Sine
+ * modulator): fp32 per-sample arithmetic off one fp64 base per 8 samples, SFU sine, closed-form
+ * FM sums; Square/Sawtooth/Pulse carriers re-evaluate in exact fp64 the few samples whose
+ * phase is within 2e-5 cycles of an edge, so edges fall where upstream puts them.
+ * Other voices (non-sine modulators, negative phases or frequencies on edged carriers) take
+ * the generic path (per-sample fp64 phase). */
 int sb_voice_is_fast(const sb_voice *voice, double samplerate);
 
 /* Renders frames [n0, n0+plan->frames) of all voices.  tb_rad_dev / tb_cyc_dev: time bases

@@ -53,7 +53,8 @@ class BankPlan(Structure):
     _fields_ = [("nvoices", c_int32), ("voices_per_group", c_int32), ("ngroups", c_int32),
                 ("nspans", c_int32), ("frames", c_int64), ("span_len", c_int64),
                 ("fast_span_len", c_int64), ("fast_nspans", c_int32), ("nsegs_rad", c_int32),
-                ("generic_voices", c_int32), ("nprefix", c_int32), ("n0", c_int64),
+                ("generic_voices", c_int32), ("nprefix", c_int32), ("edged_voices", c_int32),
+                ("reserved", c_int32), ("n0", c_int64),
                 ("off_fastv", c_int64), ("off_tab", c_int64),
                 ("carry_bytes", c_int64), ("partial_bytes", c_int64)]
 

@@ -78,8 +78,11 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     rc = sb_bank_plan_make(nvoices, frames, 0, sms, (int)g_tb.rad.size(), &plan);
     if (rc) return rc;
     plan.generic_voices = 0;
-    for (int v = 0; v < nvoices; v++)
+    plan.edged_voices = 0;
+    for (int v = 0; v < nvoices; v++) {
         if (!sb_voice_is_fast(&voices[v], samplerate)) plan.generic_voices++;
+        else if (voices[v].c_wave >= SB_WAVE_SQUARE) plan.edged_voices++;
+    }
 
     const size_t b_voices = align256((size_t)nvoices * sizeof(sb_voice));
     const size_t b_rad = align256(g_tb.rad.size() * sizeof(sb_time_seg));

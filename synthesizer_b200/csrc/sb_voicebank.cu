@@ -49,7 +49,11 @@ enum : int {
     FV_ENV = 8,
     FV_ENV_EXTRA = 16,
     FV_BIAS = 32,
+    FV_WAVE_SHIFT = 8,       // bits 8..10: the carrier's waveform id
 };
+constexpr int kFastKinds = 10;               // kind = MOD | (carrier waveform << 1)
+constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer than this to a
+                                             // discontinuity are re-evaluated exactly in fp64
 
 // Per-voice constants of the fast path, derived once per render by bank_prepare_kernel.
 // The first five 128-bit words are everything the per-sample loop needs and are read with five
@@ -68,7 +72,7 @@ struct alignas(16) FastVoice {
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
-    int pad1;
+    float pw;                // Pulse carriers: the (clamped) pulse width
 };
 static_assert(sizeof(FastVoice) == 160, "FastVoice layout");
 
@@ -104,11 +108,16 @@ struct BankArgs {
 // ------------------------------------------------------------------ classification
 __host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplerate)
 {
-    if (V.c_wave != SB_WAVE_SINE && V.c_wave != SB_WAVE_TRIANGLE) return false;
+    if (V.c_wave < SB_WAVE_SINE || V.c_wave > SB_WAVE_PULSE) return false;
     const double inc_c = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0) / samplerate;
     const double turns = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0);
     // carrier advance per 8-sample run must stay small enough for fp32 increments
     if (!(fabs(V.c_freq) * inc_c * 8.0 < 64.0 * turns)) return false;
+    if (V.c_wave >= SB_WAVE_SQUARE) {
+        // discontinuous carriers: the fp32 run must resolve the phase to ~1e-6 cycles so that only
+        // samples in a narrow guard band around an edge need the exact fp64 evaluation
+        if (!(V.c_freq >= 0.0 && V.c_freq * 2.0 <= samplerate && V.c_phase >= 0.0)) return false;
+    }
     if (V.m_wave == SB_WAVE_NONE) return true;
     if (V.m_wave != SB_WAVE_SINE) return false;
     const double w = V.m_freq * 6.283185307179586 / samplerate;      // modulator phase step
@@ -153,11 +162,11 @@ __global__ void bank_prepare_kernel(BankArgs a)
     FastVoice F;
     F.flags = 0;
     F.pad0 = 0;
-    F.pad1 = 0;
     const bool fast = voice_is_fast(V, a.samplerate);
-    const bool tri = (V.c_wave == SB_WAVE_TRIANGLE);
+    const bool tri = (V.c_wave != SB_WAVE_SINE);         // phase counted in cycles (all but Sine)
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
+    F.pw = (float)clamp_pulsewidth((double)V.c_pw);
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
     const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
@@ -177,6 +186,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
     if (fast) F.flags |= FV_FAST;
     if (has_mod) F.flags |= FV_HAS_MOD;
     if (tri) F.flags |= FV_TRIANGLE;
+    F.flags |= (V.c_wave & 7) << FV_WAVE_SHIFT;
     if (V.env.enabled) F.flags |= FV_ENV;
     if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
     if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
@@ -264,28 +274,75 @@ __device__ __forceinline__ float warp_scan_incl_ptx(float v)
     return v;
 }
 
-// One voice over one lane's run of kItems frames.  MOD: Sine modulator present.  TRI: Triangle
-// carrier (else Sine).  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
-// Frames are handled in pairs (j, j+1) with Blackwell's packed fp32x2 FMAs; accL2[q] holds the
-// left-channel sums of frames (2q, 2q+1), accR2[q] the right-channel ones.
-// Frame pairing: the packed fp32x2 operations work on frames (q, q+4) of the lane's run of 8,
-// so that the exclusive sums of the modulator advance through both halves of the run in one
-// dependent chain of 4 packed adds (the second half's offset joins the carrier phase later).
-// accL2[q] = left-channel sums of frames (q, q+4), accR2[q] the right-channel ones.
-template <bool MOD, bool TRI, bool RARE>
+struct FastCtx {
+    const sb_time_seg *s_cyc;
+    int nsegs_cyc;
+};
+
+// Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
+// way upstream forms it (no FM: fl(fl(t*f) + phase), bit for bit).  Called only for samples
+// whose fp32 run phase is within kEdgeGuard of an edge, or while the phase may still be negative.
+__device__ __noinline__ float exact_shape(int wave, FastCtx ctx, int64_t k, double f0b, double pc0,
+                                          double fm_term, int has_mod, double pw)
+{
+    TimeCursor c;
+    c.seek(ctx.s_cyc, ctx.nsegs_cyc, k);
+    const double t = c.at(k);
+    const double tt = has_mod ? __dadd_rn(pc0, __dadd_rn(__dmul_rn(f0b, t), fm_term))
+                              : __dadd_rn(__dmul_rn(t, f0b), pc0);
+    return wave_shape(wave, tt, pw);
+}
+
+// fp32 shape of a discontinuous waveform from a phase in cycles, plus whether that phase is
+// too close to an edge for fp32 to be trusted
+template <int WAVE>
+__device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
+{
+    if (WAVE == SB_WAVE_SAWTOOTH) {
+        const float g = ph + 0.5f;
+        const float f = g - floorf(g);                     // jumps where 0.5 + tt crosses an integer
+        near = fminf(f, 1.0f - f) < kEdgeGuard;
+        return fmaf(2.0f, f, -1.0f);                       // 2*(tt - floor(0.5 + tt))
+    }
+    const float f = ph - floorf(ph);
+    if (WAVE == SB_WAVE_SQUARE) {
+        near = fminf(fminf(f, 1.0f - f), fabsf(f - 0.5f)) < kEdgeGuard;
+        return f < 0.5f ? 1.0f : -1.0f;                    // int(tt*2) % 2
+    }
+    near = fminf(fminf(f, 1.0f - f), fabsf(f - pw)) < kEdgeGuard;
+    return f < pw ? 1.0f : -1.0f;                          // tt % 1.0 < pulsewidth
+}
+
+// One voice over one lane's run of kItems frames.  MOD: Sine modulator present.  WAVE: the
+// carrier.  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
+// Frame pairing: the packed fp32x2 operations (Blackwell FFMA2/FADD2/FMUL2) work on frames
+// (q, q+4) of the lane's run of 8, so that the exclusive sums of the modulator advance through
+// both halves of the run in one dependent chain of 4 packed adds (the second half's offset
+// joins the carrier phase later).  accL2[q] = left-channel sums of frames (q, q+4), accR2[q]
+// the right-channel ones.
+// Square / Sawtooth / Pulse carriers: their value is evaluated in fp32 like the others, which
+// is exact (+-1, or a continuous ramp) unless the phase sits within kEdgeGuard cycles of a
+// discontinuity; those few samples are redone in fp64 exactly as upstream forms the phase, so
+// every edge lands on the sample upstream puts it on.
+template <bool MOD, int WAVE, bool RARE>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
                                                const double Tc0, const float lane8, const int64_t n,
-                                               float2 (&accL2)[kItems / 2], float2 (&accR2)[kItems / 2])
+                                               const FastCtx ctx, float2 (&accL2)[kItems / 2],
+                                               float2 (&accR2)[kItems / 2])
 {
     constexpr int H = kItems / 2;
+    constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
+    constexpr bool EDGES = (WAVE >= SB_WAVE_SQUARE);
     const double2 car = F.car;
     const float4 inc = F.inc;               // wm, wm, wc, wc
     const float4 g2 = F.g2;                 // gdf, gdf, 4wm, 4wc
     const float4 gain = F.gain;             // aL, aL, aR, aR
     float2 ps[H];                           // exclusive sums within each half: (frames q, q+4)
     float2 base;                            // carrier phase of frames (q, q+4), fp32, within a turn
-    double B = fma(car.x, TRI ? Tc0 : Tr0, car.y);
+    double B = fma(car.x, CYC ? Tc0 : Tr0, car.y);
     float half_gd = 0.0f;                   // gd * (sum of the first half's sines)
+    double before = 0.0;                    // FM sum ahead of this lane's run
+    float half_sum = 0.0f;
     if (MOD) {
         // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
         const double2 mod = F.mod;
@@ -301,30 +358,51 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
         }
         const float total = run.x + run.y;
         const float incl = warp_scan_incl_ptx(total);
-        B = fma(F.gd, rec.anchor + (double)(incl - total), B);
+        before = rec.anchor + (double)(incl - total);
+        B = fma(F.gd, before, B);
         half_gd = g2.x * run.x;
+        half_sum = run.x;
     }
     // carrier: phase base reduced to one turn in fp64, fp32 from there
     float b0;
-    if (TRI) {
+    if (CYC) {
         const double M = 6755399441055744.0;
         b0 = (float)(B - __dadd_rn(__dadd_rn(B, M), -M));
     } else {
         b0 = (float)reduce_two_pi_fast(B);
     }
+    // while the (unreduced) phase may still be negative, Square's int() truncation is not the
+    // periodic rule: take the exact path for the whole run (only the first cycles of a voice)
+    const bool low = EDGES && !(B > 16.0);
     base = make_float2(b0, b0 + g2.w + half_gd);
     const float e0 = fmaf(lane8, rec.de, rec.e_sub);
     float2 e = make_float2(e0, fmaf(4.0f, rec.de, e0));
     const float2 cstep = make_float2(inc.z, inc.w), gd2 = make_float2(g2.x, g2.y);
     const float2 estep = make_float2(rec.de, rec.de);
     const float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
+    const float pw = (WAVE == SB_WAVE_PULSE) ? F.pw : 0.0f;
 #pragma unroll
     for (int q = 0; q < H; q++) {
         float2 ph = base;
         if (MOD) ph = __ffma2_rn(gd2, ps[q], base);
         float2 w;
-        w.x = TRI ? tri_shape(ph.x) : __sinf(ph.x);
-        w.y = TRI ? tri_shape(ph.y) : __sinf(ph.y);
+        if (WAVE == SB_WAVE_SINE) {
+            w.x = __sinf(ph.x);
+            w.y = __sinf(ph.y);
+        } else if (WAVE == SB_WAVE_TRIANGLE) {
+            w.x = tri_shape(ph.x);
+            w.y = tri_shape(ph.y);
+        } else {
+            bool nx, ny;
+            w.x = guarded_shape<WAVE>(ph.x, pw, nx);
+            w.y = guarded_shape<WAVE>(ph.y, pw, ny);
+            if (nx || low)
+                w.x = exact_shape(WAVE, ctx, n + q, car.x, car.y, MOD ? F.gd * (before + (double)ps[q].x) : 0.0,
+                                  MOD, (double)pw);
+            if (ny || low)
+                w.y = exact_shape(WAVE, ctx, n + q + H, car.x, car.y,
+                                  MOD ? F.gd * (before + (double)half_sum + (double)ps[q].y) : 0.0, MOD, (double)pw);
+        }
         float2 ee = e;
         if (RARE) {
             if (rec.e_sub == kEnvSlow) {
@@ -342,34 +420,42 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
     }
 }
 
-// The four non-rare instantiations, picked by a voice's kind index (bit0 = MOD, bit1 = TRI).
+// One instantiation per kind (bit0 = MOD, bits 1.. = carrier waveform); voices are stored
+// sorted by kind, so each loop is a branch-free run.
 template <int KIND>
 __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const SubRec *s_rec, int begin, int end,
                                                 int s, const double Tr0, const double Tc0, const float lane8,
-                                                const int64_t n, float2 (&accL2)[kItems / 2],
-                                                float2 (&accR2)[kItems / 2])
+                                                const int64_t n, const FastCtx ctx,
+                                                float2 (&accL2)[kItems / 2], float2 (&accR2)[kItems / 2])
 {
-    constexpr bool MOD = (KIND & 1) != 0, TRI = (KIND & 2) != 0;
+    constexpr bool MOD = (KIND & 1) != 0;
+    constexpr int WAVE = KIND >> 1;
     for (int v = begin; v < end; v++) {
         const FastVoice &F = s_fv[v];
         const SubRec rec = s_rec[v * kFastMaxSub + s];
         if (rec.e_sub == kEnvSilent) continue;                                  // warp-uniform
         if (rec.e_sub == kEnvSlow || (F.flags & FV_BIAS))
-            fast_voice_run<MOD, TRI, true>(F, rec, Tr0, Tc0, lane8, n, accL2, accR2);
+            fast_voice_run<MOD, WAVE, true>(F, rec, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
         else
-            fast_voice_run<MOD, TRI, false>(F, rec, Tr0, Tc0, lane8, n, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F, rec, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
     }
 }
 
+// EDGED = false: Sine / Triangle carriers; writes the group's partial mix (zeros included).
+// EDGED = true : Square / Sawtooth / Pulse carriers; runs afterwards and adds into it.  Two
+// kernels rather than one so that the exact-fallback call and its register needs stay out of
+// the smooth carriers' loop (the headline path).
+template <bool EDGED>
 __global__ void __launch_bounds__(kFastWarps * 32, FAST_MIN_BLOCKS)
 bank_fast_kernel(BankArgs a)
 {
+    constexpr int kFirstKind = EDGED ? 4 : 0;          // kind = MOD | (waveform << 1); Square is waveform 2
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
     SubRec *s_rec_all = reinterpret_cast<SubRec *>(s_fv + a.voices_per_group);
     sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(s_rec_all + (size_t)kFastWarps * a.voices_per_group * kFastMaxSub);
     sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
-    __shared__ int s_kind_end[4];      // voices are stored sorted by kind: [0,e0) [e0,e1) [e1,e2) [e2,e3)
+    __shared__ int s_kind_end[kFastKinds];     // voices are stored sorted by kind; end index of each kind
 
     const int group = blockIdx.y;
     const int v_begin = group * a.voices_per_group;
@@ -383,13 +469,13 @@ bank_fast_kernel(BankArgs a)
     for (int v = threadIdx.x; v < nv; v += blockDim.x) {
         const FastVoice *src = a.fastv + v_begin;
         const int fl = src[v].flags;
-        if (fl & FV_FAST) {
-            const int kind = ((fl & FV_HAS_MOD) ? 1 : 0) | ((fl & FV_TRIANGLE) ? 2 : 0);
+        const int kind = ((fl & FV_HAS_MOD) ? 1 : 0) | (((fl >> FV_WAVE_SHIFT) & 7) << 1);
+        if ((fl & FV_FAST) && (kind >= 4) == EDGED) {
             int pos = 0;
             for (int u = 0; u < nv; u++) {
                 const int fu = src[u].flags;
-                if (!(fu & FV_FAST)) continue;
-                const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | ((fu & FV_TRIANGLE) ? 2 : 0);
+                const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | (((fu >> FV_WAVE_SHIFT) & 7) << 1);
+                if (!(fu & FV_FAST) || (ku >= 4) != EDGED) continue;
                 pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
             }
             const int4 *w = reinterpret_cast<const int4 *>(src + v);
@@ -400,19 +486,22 @@ bank_fast_kernel(BankArgs a)
             s_fv[pos].pad0 = v_begin + v;
         }
     }
-    if (threadIdx.x < 4) {
+    if (threadIdx.x < kFastKinds) {
         int c = 0;
         for (int u = 0; u < nv; u++) {
             const int fu = a.fastv[v_begin + u].flags;
-            if (!(fu & FV_FAST)) continue;
-            const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | ((fu & FV_TRIANGLE) ? 2 : 0);
+            const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | (((fu >> FV_WAVE_SHIFT) & 7) << 1);
+            if (!(fu & FV_FAST) || (ku >= 4) != EDGED) continue;
             c += (ku <= (int)threadIdx.x) ? 1 : 0;
         }
         s_kind_end[threadIdx.x] = c;
     }
     __syncthreads();
-    const int e0 = s_kind_end[0], e1 = s_kind_end[1], e2 = s_kind_end[2], e3 = s_kind_end[3];
-    nv = e3;                                           // fast voices only from here on
+    const int *ke = s_kind_end;                        // read from shared memory where needed: no registers held
+    nv = ke[kFastKinds - 1];                           // this kernel's voices only from here on
+    if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
+    const bool any_cyc = EDGED || nv > ke[1];
+    const FastCtx ctx = {s_cyc, a.nsegs_cyc};
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
@@ -467,7 +556,7 @@ bank_fast_kernel(BankArgs a)
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, n);
             Tr0 = c.at(n);
-            if (e3 > e1) {                              // triangle carriers present
+            if (any_cyc) {                              // carriers whose phase counts in cycles present
                 c.seek(s_cyc, a.nsegs_cyc, n);
                 Tc0 = c.at(n);
             }
@@ -479,28 +568,48 @@ bank_fast_kernel(BankArgs a)
 #pragma unroll
         for (int q = 0; q < kItems / 2; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
-        fast_voice_loop<0>(s_fv, s_rec, 0, e0, s, Tr0, Tc0, lane8, n, accL2, accR2);
-        fast_voice_loop<1>(s_fv, s_rec, e0, e1, s, Tr0, Tc0, lane8, n, accL2, accR2);
-        fast_voice_loop<2>(s_fv, s_rec, e1, e2, s, Tr0, Tc0, lane8, n, accL2, accR2);
-        fast_voice_loop<3>(s_fv, s_rec, e2, e3, s, Tr0, Tc0, lane8, n, accL2, accR2);
+        if (!EDGED) {
+            fast_voice_loop<0>(s_fv, s_rec, 0, ke[0], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<1>(s_fv, s_rec, ke[0], ke[1], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<2>(s_fv, s_rec, ke[1], ke[2], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<3>(s_fv, s_rec, ke[2], ke[3], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+        } else {
+            fast_voice_loop<4>(s_fv, s_rec, 0, ke[4], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<5>(s_fv, s_rec, ke[4], ke[5], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<6>(s_fv, s_rec, ke[5], ke[6], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<7>(s_fv, s_rec, ke[6], ke[7], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<8>(s_fv, s_rec, ke[7], ke[8], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<9>(s_fv, s_rec, ke[8], ke[9], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+        }
 
         // frame j of the run is accL2[j].x for j < 4 and accL2[j-4].y above; two frames per float4
         if (i0 + kItems <= span_end) {
             float4 *dst = reinterpret_cast<float4 *>(out + i0 * 2);
-            dst[0] = make_float4(accL2[0].x, accR2[0].x, accL2[1].x, accR2[1].x);
-            dst[1] = make_float4(accL2[2].x, accR2[2].x, accL2[3].x, accR2[3].x);
-            dst[2] = make_float4(accL2[0].y, accR2[0].y, accL2[1].y, accR2[1].y);
-            dst[3] = make_float4(accL2[2].y, accR2[2].y, accL2[3].y, accR2[3].y);
+            float4 o0 = make_float4(accL2[0].x, accR2[0].x, accL2[1].x, accR2[1].x);
+            float4 o1 = make_float4(accL2[2].x, accR2[2].x, accL2[3].x, accR2[3].x);
+            float4 o2 = make_float4(accL2[0].y, accR2[0].y, accL2[1].y, accR2[1].y);
+            float4 o3 = make_float4(accL2[2].y, accR2[2].y, accL2[3].y, accR2[3].y);
+            if (EDGED) {                                // add to what the smooth-carrier kernel wrote
+                const float4 p0 = dst[0], p1 = dst[1], p2 = dst[2], p3 = dst[3];
+                o0 = make_float4(o0.x + p0.x, o0.y + p0.y, o0.z + p0.z, o0.w + p0.w);
+                o1 = make_float4(o1.x + p1.x, o1.y + p1.y, o1.z + p1.z, o1.w + p1.w);
+                o2 = make_float4(o2.x + p2.x, o2.y + p2.y, o2.z + p2.z, o2.w + p2.w);
+                o3 = make_float4(o3.x + p3.x, o3.y + p3.y, o3.z + p3.z, o3.w + p3.w);
+            }
+            dst[0] = o0;
+            dst[1] = o1;
+            dst[2] = o2;
+            dst[3] = o3;
         } else {
 #pragma unroll
             for (int q = 0; q < kItems / 2; q++) {
                 if (i0 + q < span_end) {
-                    out[(i0 + q) * 2] = accL2[q].x;
-                    out[(i0 + q) * 2 + 1] = accR2[q].x;
+                    out[(i0 + q) * 2] = accL2[q].x + (EDGED ? out[(i0 + q) * 2] : 0.0f);
+                    out[(i0 + q) * 2 + 1] = accR2[q].x + (EDGED ? out[(i0 + q) * 2 + 1] : 0.0f);
                 }
                 if (i0 + q + kItems / 2 < span_end) {
-                    out[(i0 + q + kItems / 2) * 2] = accL2[q].y;
-                    out[(i0 + q + kItems / 2) * 2 + 1] = accR2[q].y;
+                    out[(i0 + q + kItems / 2) * 2] = accL2[q].y + (EDGED ? out[(i0 + q + kItems / 2) * 2] : 0.0f);
+                    out[(i0 + q + kItems / 2) * 2 + 1] = accR2[q].y + (EDGED ? out[(i0 + q + kItems / 2) * 2 + 1] : 0.0f);
                 }
             }
         }
@@ -829,6 +938,7 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     plan->fast_nspans = (int32_t)((frames + plan->fast_span_len - 1) / plan->fast_span_len);
     plan->nsegs_rad = nsegs_rad;
     plan->generic_voices = -1;
+    plan->edged_voices = -1;
     plan->n0 = n0;
     const int64_t nprefix = (n0 + span_len - 1) / span_len;
     SB_REQUIRE(nprefix < 0x7fffffff, "sb_bank_plan_make: start offset too large");
@@ -892,10 +1002,17 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
         size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(FastVoice) +
                       (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * sizeof(SubRec);
         if (smem > 48 * 1024)
-            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        {
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
         dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
-        bank_fast_kernel<<<grid, kFastWarps * 32, smem, s>>>(a);
+        bank_fast_kernel<false><<<grid, kFastWarps * 32, smem, s>>>(a);
         SB_LAUNCH_CHECK();
+        if (plan->edged_voices != 0) {
+            bank_fast_kernel<true><<<grid, kFastWarps * 32, smem, s>>>(a);
+            SB_LAUNCH_CHECK();
+        }
     }
     if (plan->generic_voices != 0) {
         if (a.carry) {

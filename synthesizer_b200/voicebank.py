@@ -108,13 +108,19 @@ class VoiceBank:
         return sum(1 for v in self._voices[begin:end]
                    if not C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)))
 
-    def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None):
+    def count_edged(self, begin=0, end=None):
+        """Voices of [begin, end) with a Square / Sawtooth / Pulse carrier (the second fast kernel)."""
+        return sum(1 for v in self._voices[begin:end] if v.c_wave >= C.WAVE_SQUARE)
+
+    def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None,
+               edged_voices=None):
         """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
         if voices_dev is None:
             voices_dev, nv = self._upload(begin, end)
             generic_voices = self.count_generic(begin, end)
+            edged_voices = self.count_edged(begin, end)
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
         mix = D.empty(2 * nframes, torch.float32)
@@ -126,6 +132,8 @@ class VoiceBank:
         C.call("sb_bank_plan_make", nv, nframes, start, sms, tr.nsegs, ctypes.byref(plan))
         if generic_voices is not None:
             plan.generic_voices = generic_voices
+        if edged_voices is not None:
+            plan.edged_voices = edged_voices
         carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
         partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,
