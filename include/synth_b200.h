@@ -297,6 +297,21 @@ int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src
                          const int64_t *dst_off_dev, int64_t nsrc, void *scratch_dev,
                          int64_t scratch_bytes, void *stream);
 
+/* The same routines for sample width 4 (audioop with size == 4); a Sample of 32-bit frames
+ * (Sample.make_32bit, WaveSynth(samplewidth=4)) uses these. */
+int sb_pcm32_add(const int32_t *a_dev, const int32_t *b_dev, int64_t count, int32_t *out_dev, void *stream);
+int sb_pcm32_mul(const int32_t *in_dev, int64_t count, double factor, int32_t *out_dev, void *stream);
+int sb_pcm32_bias(const int32_t *in_dev, int64_t count, int bias, int32_t *out_dev, void *stream);
+int sb_pcm32_reverse(const int32_t *in_dev, int64_t count, int32_t *out_dev, void *stream);
+int sb_pcm32_maxabs(const int32_t *in_dev, int64_t count, unsigned int *out_dev, void *stream);
+int sb_pcm32_tomono(const int32_t *in_dev, int64_t frames, double lfactor, double rfactor, int32_t *out_dev, void *stream);
+int sb_pcm32_tostereo(const int32_t *in_dev, int64_t frames, double lfactor, double rfactor, int32_t *out_dev, void *stream);
+int sb_pcm32_fadeout(int32_t *buf_dev, int64_t nsamples, double target_volume, void *stream);
+int sb_pcm32_fadein(int32_t *buf_dev, int64_t nsamples, double start_volume, void *stream);
+int sb_pcm32_modulate(int32_t *buf_dev, const float *mod_dev, int64_t count, void *stream);
+int sb_pcm32_ratecv(const int32_t *in_dev, int64_t in_frames, int nchannels, int64_t inrate,
+                    int64_t outrate, int32_t *out_dev, void *stream);
+
 /* ------------------------------------------------------------------ host-buffer calls -
  * The same path with HOST buffers (copies included), for callers without device memory of
  * their own; bench.py's e2e figure goes through these. */

@@ -116,6 +116,17 @@ _SIGNATURES = {
     "sb_pcm16_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
     "sb_pcm16_mix_at_many_scratch_bytes": (c_int64, [c_int64, c_int64, c_int64]),
     "sb_pcm16_mix_at_many": (c_int, [_P, c_int64, _P, _P, _P, _P, c_int64, _P, c_int64, _P]),
+    "sb_pcm32_add": (c_int, [_P, _P, c_int64, _P, _P]),
+    "sb_pcm32_mul": (c_int, [_P, c_int64, c_double, _P, _P]),
+    "sb_pcm32_bias": (c_int, [_P, c_int64, c_int, _P, _P]),
+    "sb_pcm32_reverse": (c_int, [_P, c_int64, _P, _P]),
+    "sb_pcm32_maxabs": (c_int, [_P, c_int64, _P, _P]),
+    "sb_pcm32_tomono": (c_int, [_P, c_int64, c_double, c_double, _P, _P]),
+    "sb_pcm32_tostereo": (c_int, [_P, c_int64, c_double, c_double, _P, _P]),
+    "sb_pcm32_fadeout": (c_int, [_P, c_int64, c_double, _P]),
+    "sb_pcm32_fadein": (c_int, [_P, c_int64, c_double, _P]),
+    "sb_pcm32_modulate": (c_int, [_P, _P, c_int64, _P]),
+    "sb_pcm32_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
     "sb_host_bank_render_pcm16": (c_int, [POINTER(Voice), c_int, c_int64, c_double, c_float, _P, POINTER(c_ulonglong)]),
     "sb_host_pcm16_mix_at_many": (c_int, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64]),
 }

@@ -10,8 +10,8 @@ write_wav).  Most operations modify the sample in place and return it, as upstre
 
 Upstream source is absent from /root/reference (README.md:1-2 only): method names, argument
 meaning and frame-index rounding follow the published package as recalled; see DESIGN.md.
-Sample width 2 is fully supported; width 4 supports construction, conversion and transfer
-(arithmetic on 32-bit frames raises NotImplementedError).  There is no CPU fallback.
+Sample widths 2 and 4 are supported (upstream also accepts 3-byte frames; this backend does
+not).  There is no CPU fallback.
 """
 import array
 import ctypes
@@ -139,9 +139,8 @@ class Sample:
     @property
     def maximum(self):
         """audioop.max: the largest absolute sample value."""
-        self._need16("maximum")
         out = D.zeros(1, torch.int32)
-        C.call("sb_pcm16_maxabs", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+        C.call(self._k("maxabs"), D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
         return int(out.item()) & 0xFFFFFFFF
 
     def frame_idx(self, seconds):
@@ -212,7 +211,14 @@ class Sample:
     # ------------------------------------------------------------------ helpers
     def _need16(self, what):
         if self.samplewidth != 2:
-            raise NotImplementedError("%s: only 16-bit frames have GPU arithmetic in this round" % what)
+            raise NotImplementedError("%s is only implemented for 16-bit frames" % what)
+
+    def _k(self, op):
+        """Name of the C-ABI routine for this sample's width: sb_pcm16_<op> or sb_pcm32_<op>."""
+        return "sb_pcm%d_%s" % (8 * self.samplewidth, op)
+
+    def _dt(self):
+        return _DTYPE[self.samplewidth]
 
     def _same_format(self, other):
         assert self.samplewidth == other.samplewidth
@@ -241,7 +247,6 @@ class Sample:
         assert not self._locked
         if samplerate == self.samplerate:
             return self
-        self._need16("resample")
         self._dev = self._ratecv(self.samplerate, samplerate)
         self.samplerate = samplerate
         return self
@@ -251,7 +256,6 @@ class Sample:
         assert speed > 0
         if speed == 1.0:
             return self
-        self._need16("speed")
         self._dev = self._ratecv(int(self.samplerate * speed), self.samplerate)
         return self
 
@@ -259,31 +263,31 @@ class Sample:
         if self._dev is None:
             return None
         nin = len(self)
-        nout = C.lib.sb_pcm16_ratecv_frames(nin, inrate, outrate)
-        out = D.empty(nout * self.nchannels, torch.int16)
-        C.call("sb_pcm16_ratecv", D.ptr(self._dev), nin, self.nchannels, inrate, outrate, D.ptr(out), D.stream())
+        nout = C.lib.sb_pcm16_ratecv_frames(nin, inrate, outrate)       # frame count: width independent
+        out = D.empty(nout * self.nchannels, self._dt())
+        C.call(self._k("ratecv"), D.ptr(self._dev), nin, self.nchannels, inrate, outrate, D.ptr(out), D.stream())
         return out
 
     def make_32bit(self, scale_amplitude=True):
         assert not self._locked
         if self.samplewidth == 4:
             return self
-        if not scale_amplitude:
-            raise NotImplementedError("make_32bit(scale_amplitude=False)")
+        old_width = self.samplewidth
         if self._dev is not None:
             out = D.empty(self._count(), torch.int32)
             C.call("sb_pcm16_to_pcm32", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
             self._dev = out
         self.samplewidth = 4
+        if not scale_amplitude:
+            # keep the numeric values instead of the relative level: audioop.mul by 2**(8*w)/2**32
+            self.amplify(2 ** (8 * old_width) / 2 ** 32)
         return self
 
     def make_16bit(self, maximize_amplitude=True):
         assert not self._locked
         assert self.samplewidth >= 2
-        if maximize_amplitude and self.samplewidth == 2:
+        if maximize_amplitude:
             self.amplify_max()
-        elif maximize_amplitude:
-            raise NotImplementedError("make_16bit(maximize_amplitude=True) from 32-bit frames")
         if self.samplewidth > 2:
             if self._dev is not None:
                 out = D.empty(self._count(), torch.int16)
@@ -296,10 +300,9 @@ class Sample:
         assert not self._locked
         if self.nchannels == 1:
             return self
-        self._need16("mono")
         if self._dev is not None:
-            out = D.empty(len(self), torch.int16)
-            C.call("sb_pcm16_tomono", D.ptr(self._dev), len(self), float(left_factor), float(right_factor),
+            out = D.empty(len(self), self._dt())
+            C.call(self._k("tomono"), D.ptr(self._dev), len(self), float(left_factor), float(right_factor),
                    D.ptr(out), D.stream())
             self._dev = out
         self.nchannels = 1
@@ -315,7 +318,6 @@ class Sample:
 
     def stereo(self, left_factor=1.0, right_factor=1.0):
         assert not self._locked
-        self._need16("stereo")
         if self.nchannels == 2:
             right = self.copy().right()
             left = self.copy().left()
@@ -328,8 +330,8 @@ class Sample:
 
     def _tostereo(self, lf, rf):
         if self._dev is not None:
-            out = D.empty(2 * self._count(), torch.int16)
-            C.call("sb_pcm16_tostereo", D.ptr(self._dev), self._count(), float(lf), float(rf), D.ptr(out), D.stream())
+            out = D.empty(2 * self._count(), self._dt())
+            C.call(self._k("tostereo"), D.ptr(self._dev), self._count(), float(lf), float(rf), D.ptr(out), D.stream())
             self._dev = out
         self.nchannels = 2
 
@@ -344,9 +346,8 @@ class Sample:
     def amplify(self, factor):
         """audioop.mul"""
         assert not self._locked
-        self._need16("amplify")
         if self._dev is not None:
-            C.call("sb_pcm16_mul", D.ptr(self._dev), self._count(), float(factor), D.ptr(self._dev), D.stream())
+            C.call(self._k("mul"), D.ptr(self._dev), self._count(), float(factor), D.ptr(self._dev), D.stream())
         return self
 
     def amplify_max(self):
@@ -369,17 +370,17 @@ class Sample:
     def bias(self, bias):
         """audioop.bias (wrapping)"""
         assert not self._locked
-        self._need16("bias")
         if self._dev is not None:
-            C.call("sb_pcm16_bias", D.ptr(self._dev), self._count(), int(bias), D.ptr(self._dev), D.stream())
+            b = int(bias) & 0xFFFFFFFF                      # audioop adds it as an unsigned 32-bit value
+            b = b - (1 << 32) if b >= (1 << 31) else b
+            C.call(self._k("bias"), D.ptr(self._dev), self._count(), b, D.ptr(self._dev), D.stream())
         return self
 
     def reverse(self):
         assert not self._locked
-        self._need16("reverse")
         if self._dev is not None:
-            out = D.empty(self._count(), torch.int16)
-            C.call("sb_pcm16_reverse", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
+            out = D.empty(self._count(), self._dt())
+            C.call(self._k("reverse"), D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
             self._dev = out
         return self
 
@@ -387,30 +388,27 @@ class Sample:
         assert not self._locked
         if self._dev is None:
             return self
-        self._need16("fadeout")
         seconds = min(seconds, self.duration)
         i = self._sample_idx(self.duration - seconds)
         n = self._count() - i
         if n > 0:
-            C.call("sb_pcm16_fadeout", D.ptr(self._dev[i:]), n, float(target_volume), D.stream())
+            C.call(self._k("fadeout"), D.ptr(self._dev[i:]), n, float(target_volume), D.stream())
         return self
 
     def fadein(self, seconds, start_volume=0.0):
         assert not self._locked
         if self._dev is None:
             return self
-        self._need16("fadein")
         seconds = min(seconds, self.duration)
         n = min(self._sample_idx(seconds), self._count())
         if n > 0:
-            C.call("sb_pcm16_fadein", D.ptr(self._dev), n, float(start_volume), D.stream())
+            C.call(self._k("fadein"), D.ptr(self._dev), n, float(start_volume), D.stream())
         return self
 
     def modulate_amp(self, modulation_source):
         """Amplitude modulation by an oscillator (rendered on the GPU), or by a Sample / list /
         array that is cycled and normalised to a maximum of 1.0 as upstream does."""
         assert not self._locked
-        self._need16("modulate_amp")
         if self._dev is None:
             return self
         n = self._count()
@@ -427,7 +425,7 @@ class Sample:
             vals = (vals / biggest).to(torch.float32)
             reps = -(-n // vals.numel())
             mod = vals.repeat(reps)[:n].to(D.device())
-        C.call("sb_pcm16_modulate", D.ptr(self._dev), D.ptr(mod), n, D.stream())
+        C.call(self._k("modulate"), D.ptr(self._dev), D.ptr(mod), n, D.stream())
         return self
 
     # ------------------------------------------------------------------ structure
@@ -486,7 +484,7 @@ class Sample:
             return self
         n = other_dev.numel()
         dst = self._dev[at:at + n]
-        C.call("sb_pcm16_add", D.ptr(dst), D.ptr(other_dev), n, D.ptr(dst), D.stream())
+        C.call(self._k("add"), D.ptr(dst), D.ptr(other_dev), n, D.ptr(dst), D.stream())
         return self
 
     def _grow(self, required):
@@ -498,7 +496,6 @@ class Sample:
         """Mix another sample into this one (audioop.add); the shorter one is zero-padded."""
         assert not self._locked
         self._same_format(other)
-        self._need16("mix")
         o = other._dev
         if other_seconds and o is not None:
             o = other._slice(0, other._sample_idx(other_seconds))
@@ -515,7 +512,6 @@ class Sample:
             return self.mix(other, other_seconds)
         assert not self._locked
         self._same_format(other)
-        self._need16("mix_at")
         start = self._sample_idx(seconds)
         o = other._dev
         if other_seconds and o is not None:
@@ -529,7 +525,10 @@ class Sample:
         `placements`, in order, with ONE kernel launch.  The result is identical to the loop of
         mix_at calls (each step saturates like audioop.add)."""
         assert not self._locked
-        self._need16("mix_at_many")
+        if self.samplewidth != 2:                      # the one-launch kernel is 16-bit; same result by the loop
+            for seconds, other in placements:
+                self.mix_at(seconds, other)
+            return self
         starts, srcs = [], []
         for seconds, other in placements:
             self._same_format(other)

@@ -157,6 +157,53 @@ def test_widths(cuda):
     _same(g, o, "32 -> 16")
 
 
+def test_32bit_samples(cuda):
+    """Sample width 4: every arithmetic routine against stdlib audioop with size 4."""
+    import synthesizer_b200 as sb
+    from oracle.sample_oracle import Sample as OS
+    rng = np.random.default_rng(31)
+
+    def pair(n, ch=1, sr=44100, full=True):
+        lim = 2 ** 31 if full else 2 ** 29
+        x = rng.integers(-lim, lim, size=n * ch, dtype=np.int64)
+        x[:4] = [2 ** 31 - 1, -2 ** 31, -2 ** 31 + 1, 0]
+        raw = x.astype("<i4").tobytes()
+        return sb.Sample.from_raw_frames(raw, 4, sr, ch), OS.from_raw_frames(raw, 4, sr, ch)
+
+    def same(g, o, what):
+        assert (g.samplerate, g.nchannels, g.samplewidth) == (o.samplerate, o.nchannels, o.samplewidth), what
+        dt = "<i4" if g.samplewidth == 4 else "<i2"
+        a, b = np.frombuffer(g.get_frames(), dt), np.frombuffer(o._frames, dt)
+        assert a.shape == b.shape, what
+        assert np.array_equal(a, b), "%s: %d of %d differ" % (what, int((a != b).sum()), a.size)
+
+    g, o = pair(20001)
+    assert g.maximum == o.maximum
+    for f in (0.5, 1.7, -1.0, 0.333, 1e-3):
+        same(g.copy().amplify(f), o.copy().amplify(f), "amplify %r" % f)
+    g2, o2 = pair(20001)
+    same(g.copy().mix(g2), o.copy().mix(o2), "mix")
+    same(g.copy().mix_at(0.1, g2), o.copy().mix_at(0.1, o2), "mix_at")
+    same(g.copy().mix_at_many([(0.05, g2), (0.2, g2)]), o.copy().mix_at(0.05, o2).mix_at(0.2, o2), "mix_at_many")
+    same(g.copy().bias(123456789), o.copy().bias(123456789), "bias")
+    same(g.copy().reverse(), o.copy().reverse(), "reverse")
+    same(g.copy().fadeout(0.2, 0.1), o.copy().fadeout(0.2, 0.1), "fadeout")
+    same(g.copy().fadein(0.2, 0.1), o.copy().fadein(0.2, 0.1), "fadein")
+    same(g.copy().resample(48000), o.copy().resample(48000), "resample")
+    same(g.copy().envelope(0.05, 0.1, 0.6, 0.1), o.copy().envelope(0.05, 0.1, 0.6, 0.1), "envelope")
+    s, so_ = pair(10000, ch=2, full=False)
+    same(s.copy().mono(0.4, 0.7), so_.copy().mono(0.4, 0.7), "mono")
+    same(s.copy().resample(22050), so_.copy().resample(22050), "resample stereo")
+    same(g.copy().stereo(0.7, 1.2), o.copy().stereo(0.7, 1.2), "stereo")
+    same(g.copy().amplify_max(), o.copy().amplify_max(), "amplify_max")
+    same(g.copy().make_16bit(maximize_amplitude=False), o.copy().make_16bit(maximize_amplitude=False), "make_16bit")
+    m, mo = _pair(_rand(5000, 32))
+    same(m.copy().make_32bit(), mo.copy().make_32bit(), "make_32bit")
+    same(m.copy().make_32bit(scale_amplitude=False), mo.copy().make_32bit(scale_amplitude=False), "make_32bit unscaled")
+    ws = sb.WaveSynth(samplerate=44100, samplewidth=4).sine(440, 0.1)
+    assert ws.samplewidth == 4 and len(ws) == 4410 and 2 ** 31 * 0.99 < ws.maximum < 2 ** 31
+
+
 def test_structure_ops(cuda):
     g, o = _pair(_rand(44100, 22))
     _same(g.clip(0.1, 0.7), o.clip(0.1, 0.7), "clip")
