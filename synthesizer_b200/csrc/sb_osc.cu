@@ -649,7 +649,7 @@ extern "C" int sb_echo_f32(const float *src_dev, int64_t src_n0, int64_t n_after
 extern "C" int sb_f32_to_pcm16(const float *in_dev, int64_t count, float scale, int16_t *out_dev,
                                unsigned long long *overflow_dev, void *stream)
 {
-    SB_REQUIRE(in_dev && out_dev && count >= 0, "sb_f32_to_pcm16: bad arguments");
+    SB_REQUIRE(count >= 0 && (count == 0 || (in_dev && out_dev)), "sb_f32_to_pcm16: bad arguments");
     if (count == 0) return SB_OK;
     to_pcm16_kernel<<<grid_for(count / 8 + 1, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
         in_dev, count, scale, out_dev, overflow_dev);

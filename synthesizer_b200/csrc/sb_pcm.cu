@@ -446,7 +446,7 @@ using namespace sb;
 
 extern "C" int sb_pcm16_add(const int16_t *a_dev, const int16_t *b_dev, int64_t count, int16_t *out_dev, void *stream)
 {
-    SB_REQUIRE(a_dev && b_dev && out_dev && count >= 0, "sb_pcm16_add: bad arguments");
+    SB_REQUIRE(count >= 0 && (count == 0 || (a_dev && b_dev && out_dev)), "sb_pcm16_add: bad arguments");
     if (!count) return SB_OK;
     pcm16_add_kernel<<<PCM_GRID(count), kPBlock, 0, (cudaStream_t)stream>>>(a_dev, b_dev, count, out_dev);
     SB_LAUNCH_CHECK();
@@ -455,7 +455,7 @@ extern "C" int sb_pcm16_add(const int16_t *a_dev, const int16_t *b_dev, int64_t 
 
 extern "C" int sb_pcm16_mul(const int16_t *in_dev, int64_t count, double factor, int16_t *out_dev, void *stream)
 {
-    SB_REQUIRE(in_dev && out_dev && count >= 0, "sb_pcm16_mul: bad arguments");
+    SB_REQUIRE(count >= 0 && (count == 0 || (in_dev && out_dev)), "sb_pcm16_mul: bad arguments");
     if (!count) return SB_OK;
     pcm16_mul_kernel<<<PCM_GRID(count), kPBlock, 0, (cudaStream_t)stream>>>(in_dev, count, factor, out_dev);
     SB_LAUNCH_CHECK();
@@ -532,7 +532,7 @@ extern "C" int sb_pcm32_to_pcm16(const int32_t *in_dev, int64_t count, int16_t *
 
 extern "C" int sb_pcm16_fadeout(int16_t *buf_dev, int64_t nsamples, double target_volume, void *stream)
 {
-    SB_REQUIRE(buf_dev && nsamples >= 0, "sb_pcm16_fadeout: bad arguments");
+    SB_REQUIRE(nsamples >= 0 && (nsamples == 0 || buf_dev), "sb_pcm16_fadeout: bad arguments");
     if (!nsamples) return SB_OK;
     pcm16_fadeout_kernel<<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - target_volume);
     SB_LAUNCH_CHECK();

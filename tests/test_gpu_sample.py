@@ -157,6 +157,74 @@ def test_widths(cuda):
     _same(g, o, "32 -> 16")
 
 
+def test_ragged_lengths_and_unaligned_views_through_the_c_abi(cuda):
+    """The 128-bit paths have scalar heads and tails: every length 0..40 at every int16 offset
+    0..8 of a buffer, for the vectorised kernels, against the C oracle / stdlib audioop."""
+    import torch
+    from synthesizer_b200 import _cabi as C, _device as D
+    from oracle import coracle as co
+    rng = np.random.default_rng(77)
+    base_a = rng.integers(-32768, 32768, 64).astype(np.int16)
+    base_b = rng.integers(-32768, 32768, 64).astype(np.int16)
+    base_f = (rng.random(64) * 2.2 - 1.1).astype(np.float32)
+    da, db = torch.tensor(base_a, device="cuda"), torch.tensor(base_b, device="cuda")
+    df = torch.tensor(base_f, device="cuda")
+    for off in range(9):
+        for n in list(range(0, 41)):
+            a, b = da[off:off + n], db[off + 3:off + 3 + n]            # different alignments on purpose
+            out = torch.full((64,), 12345, dtype=torch.int16, device="cuda")
+            o = out[off + 1:off + 1 + n]
+            C.call("sb_pcm16_add", D.ptr(a), D.ptr(b), n, D.ptr(o), D.stream())
+            want = co.pcm16_add(base_a[off:off + n], base_b[off + 3:off + 3 + n]) if n else np.zeros(0, np.int16)
+            got = out.cpu().numpy()
+            assert np.array_equal(got[off + 1:off + 1 + n], want), ("add", off, n)
+            assert (got[:off + 1] == 12345).all() and (got[off + 1 + n:] == 12345).all(), ("add wrote outside", off, n)
+            out.fill_(12345)
+            C.call("sb_pcm16_mul", D.ptr(a), n, 0.77, D.ptr(o), D.stream())
+            want = co.pcm16_mul(base_a[off:off + n], 0.77) if n else np.zeros(0, np.int16)
+            got = out.cpu().numpy()
+            assert np.array_equal(got[off + 1:off + 1 + n], want), ("mul", off, n)
+            assert (got[:off + 1] == 12345).all() and (got[off + 1 + n:] == 12345).all(), ("mul wrote outside", off, n)
+            buf = da.clone()
+            C.call("sb_pcm16_fadeout", D.ptr(buf[off:]), n, 0.25, D.stream())
+            want = base_a.copy()
+            if n:
+                want[off:off + n] = co.pcm16_fadeout(base_a[off:off + n], 0.25)
+            assert np.array_equal(buf.cpu().numpy(), want), ("fadeout", off, n)
+            out.fill_(12345)
+            ovf = torch.zeros(1, dtype=torch.int64, device="cuda")
+            C.call("sb_f32_to_pcm16", D.ptr(df[off:]), n, 20000.0, D.ptr(o), D.ptr(ovf), D.stream())
+            want = np.trunc(base_f[off:off + n].astype(np.float32) * np.float32(20000.0)).astype(np.int64)
+            got = out.cpu().numpy()
+            assert np.array_equal(got[off + 1:off + 1 + n], want), ("to_pcm16", off, n)
+            assert (got[:off + 1] == 12345).all() and (got[off + 1 + n:] == 12345).all(), ("to_pcm16 wrote outside", off, n)
+            assert int(ovf.item()) == 0
+
+
+def test_empty_samples_everywhere(cuda):
+    import synthesizer_b200 as sb
+    e = sb.Sample.from_raw_frames(b"", 2, 44100, 1)
+    for name, op in [("amplify", lambda s: s.amplify(0.5)), ("fadein", lambda s: s.fadein(1.0)),
+                     ("fadeout", lambda s: s.fadeout(1.0)), ("reverse", lambda s: s.reverse()),
+                     ("bias", lambda s: s.bias(5)), ("resample", lambda s: s.resample(48000)),
+                     ("envelope", lambda s: s.envelope(0.1, 0.1, 0.5, 0.1)), ("echo", lambda s: s.echo(1.0, 3, 0.1, 0.5)),
+                     ("stereo", lambda s: s.stereo()), ("amplify_max", lambda s: s.amplify_max()),
+                     ("make_32bit", lambda s: s.make_32bit()), ("clip", lambda s: s.clip(0, 0)),
+                     ("add_silence", lambda s: s.add_silence(0.01)), ("delay", lambda s: s.delay(0.01))]:
+        g, o = _pair([])
+        assert op(g) is g
+        op(o)
+        assert (g.samplerate, g.nchannels, g.samplewidth) == (o.samplerate, o.nchannels, o.samplewidth), name
+        assert g.get_frames() == o._frames, name
+    assert e.copy().mix_at_many([]).get_frames() == b""
+    x = sb.Sample.from_raw_frames(np.arange(10, dtype="<i2").tobytes(), 2, 44100, 1)
+    assert e.copy().mix(x).get_frames() == x.get_frames()
+    assert x.copy().mix(e).get_frames() == x.get_frames()
+    assert e.copy().mix_at(0.0001, x).get_frames()[-20:] == x.get_frames()
+    import synthesizer_b200.oscillators as so_
+    assert so_.Sine(440, samplerate=44100).render(0).numel() == 0
+
+
 def test_32bit_samples(cuda):
     """Sample width 4: every arithmetic routine against stdlib audioop with size 4."""
     import synthesizer_b200 as sb
