@@ -174,6 +174,10 @@ int sb_mix_f32(const float *const *src_ptrs_dev, int nsrc, int64_t count, float 
 int sb_clip_f32(const float *in_dev, float lo, float hi, int64_t count, float *out_dev, void *stream);
 int sb_abs_f32(const float *in_dev, int64_t count, float *out_dev, void *stream);
 int sb_scale_bias_f32(const float *in_dev, float scale, float bias, int64_t count, float *out_dev, void *stream);
+/* One channel of an interleaved float buffer (the mono mix out of sb_bank_render_f32 when a
+ * MixingFilter is rendered through the voice bank). */
+int sb_channel_f32(const float *in_dev, int nchannels, int channel, int64_t frames, float *out_dev,
+                   void *stream);
 /* EchoFilter: out[n] = src[n] + sum_k gain[k]*src[n - delay[k]] for n >= n_after, taking
  * src[m] = 0 for m < n_after in the delayed copies; out[n] = src[n] before n_after.
  * src_dev[0] is sample index src_n0 (history the caller keeps); out covers [n0, n0+count). */

@@ -202,6 +202,39 @@ class Sample:
             return self
         raise ValueError("sample must be mono or stereo already")
 
+    def normalize(self):
+        """synthplayer.sample.Sample.normalize (recalled): to the default rate, width, channels."""
+        assert not self._locked
+        self.resample(self.norm_samplerate)
+        if self.samplewidth != self.norm_samplewidth:
+            self._frames = audioop.lin2lin(self._frames, self.samplewidth, self.norm_samplewidth)
+            self.samplewidth = self.norm_samplewidth
+        if self.nchannels == 1 and self.norm_nchannels == 2:
+            self._frames = audioop.tostereo(self._frames, self.samplewidth, 1, 1)
+            self.nchannels = 2
+        elif self.nchannels == 2 and self.norm_nchannels == 1:
+            self.mono()
+        return self
+
+    def stereo_mix(self, other, other_channel, other_mix_factor=1.0, mix_at=0.0, other_seconds=None):
+        """synthplayer.sample.Sample.stereo_mix (recalled)."""
+        assert not self._locked
+        assert other.nchannels == 1
+        assert other.samplerate == self.samplerate
+        assert other.samplewidth == self.samplewidth
+        assert other_channel in ("L", "R")
+        if self.nchannels == 1:
+            if other_channel == "L":
+                self.stereo(left_factor=0, right_factor=1)
+            else:
+                self.stereo(left_factor=1, right_factor=0)
+        other = other.copy()
+        if other_channel == "L":
+            other.stereo(left_factor=other_mix_factor, right_factor=0)
+        else:
+            other.stereo(left_factor=0, right_factor=other_mix_factor)
+        return self.mix_at(mix_at, other, other_seconds)
+
     def pan(self, panning=0.0):
         assert not self._locked
         assert -1 <= panning <= 1

@@ -93,6 +93,7 @@ _SIGNATURES = {
     "sb_clip_f32": (c_int, [_P, c_float, c_float, c_int64, _P, _P]),
     "sb_abs_f32": (c_int, [_P, c_int64, _P, _P]),
     "sb_scale_bias_f32": (c_int, [_P, c_float, c_float, c_int64, _P, _P]),
+    "sb_channel_f32": (c_int, [_P, c_int, c_int, c_int64, _P, _P]),
     "sb_echo_f32": (c_int, [_P, c_int64, c_int64, c_int, POINTER(c_int64), POINTER(c_float), c_int64, c_int64, _P, _P]),
     "sb_f32_to_pcm16": (c_int, [_P, c_int64, c_float, _P, _P, _P]),
     "sb_f32_to_pcm32": (c_int, [_P, c_int64, c_double, _P, _P, _P]),

@@ -306,6 +306,15 @@ __global__ void mix_kernel(const float *const *__restrict__ srcs, int nsrc, int6
     }
 }
 
+// out[i] = in[i*stride + offset]: one channel of an interleaved buffer
+__global__ void deinterleave_kernel(const float *__restrict__ in, int stride_elems, int offset, int64_t count,
+                                    float *__restrict__ out)
+{
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        out[i] = in[i * stride_elems + offset];
+}
+
 struct EchoTaps {
     int ntaps;
     int64_t delay[SB_ECHO_MAX];
@@ -617,6 +626,18 @@ extern "C" int sb_mix_f32(const float *const *src_ptrs_dev, int nsrc, int64_t co
     if (count == 0) return SB_OK;
     mix_kernel<<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(src_ptrs_dev, nsrc,
                                                                                         count, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_channel_f32(const float *in_dev, int nchannels, int channel, int64_t frames, float *out_dev,
+                              void *stream)
+{
+    SB_REQUIRE(frames >= 0 && nchannels >= 1 && channel >= 0 && channel < nchannels && (frames == 0 || (in_dev && out_dev)),
+               "sb_channel_f32: bad arguments");
+    if (frames == 0) return SB_OK;
+    deinterleave_kernel<<<grid_for(frames, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
+        in_dev, nchannels, channel, frames, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }

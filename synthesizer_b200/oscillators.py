@@ -439,7 +439,10 @@ class MixingFilter(Filter):
     def _render_range(self, n0, count):
         bank = self._as_bank()
         if bank is not None:
-            return bank.render(count, start=n0)[0::2].contiguous()      # left channel = the mono mix
+            mix = bank.render(count, start=n0)
+            out = D.empty(count, torch.float32)
+            C.call("sb_channel_f32", D.ptr(mix), 2, 0, count, D.ptr(out), D.stream())   # left channel = the mono mix
+            return out
         bufs = [s._fetch(n0, n0 + count) for s in self._sources]
         ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64).to(D.device())
         out = D.empty(count, torch.float32)

@@ -335,6 +335,45 @@ class Sample:
             self._dev = out
         self.nchannels = 2
 
+    def normalize(self):
+        """Convert to the default sample rate, sample width and number of channels (params.norm_*)."""
+        assert not self._locked
+        self.resample(params.norm_samplerate)
+        if self.samplewidth != params.norm_samplewidth:
+            if params.norm_samplewidth == 2:
+                self.make_16bit(maximize_amplitude=False)
+            elif params.norm_samplewidth == 4:
+                self.make_32bit()
+            else:
+                raise ValueError("norm_samplewidth has to be 2 or 4 on this backend")
+        if params.norm_nchannels not in (1, 2):
+            raise ValueError("norm_nchannels has to be 1 or 2")
+        if self.nchannels == 1 and params.norm_nchannels == 2:
+            self._tostereo(1, 1)
+        elif self.nchannels == 2 and params.norm_nchannels == 1:
+            self.mono()
+        return self
+
+    def stereo_mix(self, other, other_channel, other_mix_factor=1.0, mix_at=0.0, other_seconds=None):
+        """Mix another mono sample into this one as its left or right channel; a mono self
+        becomes the opposite channel of a stereo sample first."""
+        assert not self._locked
+        assert other.nchannels == 1
+        assert other.samplerate == self.samplerate
+        assert other.samplewidth == self.samplewidth
+        assert other_channel in ("L", "R")
+        if self.nchannels == 1:
+            if other_channel == "L":
+                self.stereo(left_factor=0, right_factor=1)
+            else:
+                self.stereo(left_factor=1, right_factor=0)
+        other = other.copy()
+        if other_channel == "L":
+            other.stereo(left_factor=other_mix_factor, right_factor=0)
+        else:
+            other.stereo(left_factor=0, right_factor=other_mix_factor)
+        return self.mix_at(mix_at, other, other_seconds)
+
     def pan(self, panning=0.0):
         assert not self._locked
         assert -1 <= panning <= 1

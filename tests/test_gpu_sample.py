@@ -147,6 +147,17 @@ def test_channels(cuda):
     _same(m.copy().pan(-0.4), mo.copy().pan(-0.4), "pan")
 
 
+def test_normalize_and_stereo_mix(cuda):
+    g, o = _pair(_rand(22050, 40), sr=22050, ch=1)
+    _same(g.normalize(), o.normalize(), "normalize mono 22050")
+    g, o = _pair(_rand(9600 * 2, 41), sr=48000, ch=2)
+    _same(g.normalize(), o.normalize(), "normalize stereo 48000")
+    g, o = _pair(_rand(8000, 42, full=False), sr=8000)
+    h, ho = _pair(_rand(3000, 43, full=False), sr=8000)
+    _same(g.copy().stereo_mix(h, "L", 0.7, 0.1), o.copy().stereo_mix(ho, "L", 0.7, 0.1), "stereo_mix L")
+    _same(g.copy().stereo().stereo_mix(h, "R", 1.3, 0.0), o.copy().stereo().stereo_mix(ho, "R", 1.3, 0.0), "stereo_mix R")
+
+
 def test_widths(cuda):
     g, o = _pair(_rand(10000, 21))
     g.make_32bit()
