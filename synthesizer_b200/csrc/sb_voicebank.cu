@@ -29,7 +29,13 @@
 namespace sb {
 
 constexpr int kItems = 8;
-constexpr int kSub = 32 * kItems;            // frames per warp step
+constexpr int kSub = 32 * kItems;            // frames per warp step (generic kernel; plan granularity)
+#ifndef FAST_ITEMS
+#define FAST_ITEMS 16          /* measured on B200: 8 frames per lane 2.95 ms, 16 frames per lane 2.63 ms */
+#endif
+constexpr int kFItems = FAST_ITEMS;          // fast kernels: consecutive frames per lane
+constexpr int kFSub = 32 * kFItems;          // fast kernels: frames per warp step (a multiple of kSub)
+static_assert(kFSub % kSub == 0, "the fast sub-tile must be a multiple of the plan granularity");
 constexpr int kMaxVoicesPerGroup = 64;
 
 constexpr int kGenWarps = 8;                 // generic kernel: warps per CTA
@@ -39,7 +45,16 @@ constexpr int kFastWarps = 4;                // fast kernel: warps per CTA
 #endif
 constexpr int kFastMaxSub = FAST_MAX_SUB;    // fast kernel: sub-tiles per span (anchors in smem)
 #ifndef FAST_MIN_BLOCKS
-#define FAST_MIN_BLOCKS 7      /* measured on B200: 3/4/5/6/7/8 CTAs per SM -> 3.84/3.84/3.50/3.21/3.13/3.29 ms */
+#define FAST_MIN_BLOCKS 5      /* CTAs per SM (register cap 96).  Measured on B200 with 8 frames per lane:
+                                  3/4/5/6/7/8 CTAs -> 3.84/3.84/3.50/3.21/3.13/3.29 ms; with 16 frames per lane:
+                                  4/5/6 CTAs -> 2.65/2.63/2.76 ms */
+#endif
+
+#ifndef FAST_ROTATE_MODULATOR
+#define FAST_ROTATE_MODULATOR 1
+#endif
+#ifndef FAST_PAIR_VOICES
+#define FAST_PAIR_VOICES 1     /* measured on B200 at 7 CTAs/SM: 3.12 ms without, 2.96 ms with */
 #endif
 
 enum : int {
@@ -68,13 +83,14 @@ struct alignas(16) FastVoice {
     float4 inc;              // wm, wm, wc, wc: fp32 phase steps per frame fm*inc_rad, f0b*inc_c (pairs for fp32x2)
     float4 g2;               // gdf, gdf, 4wm, 4wc: gd in fp32 (pair); phase steps of four frames
     float4 gain;             // aL, aL, aR, aR: c_amp*gain (as pairs for the packed fp32x2 FMAs)
+    float4 rot;              // cos(wm), cos(wm), sin(wm), sin(wm): one-frame rotation of the modulator phase
     long long n_a, n_d, n_s, n_r;
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
     float pw;                // Pulse carriers: the (clamped) pulse width
 };
-static_assert(sizeof(FastVoice) == 160, "FastVoice layout");
+static_assert(sizeof(FastVoice) == 176, "FastVoice layout");
 
 // Per-(voice, sub-tile) record precomputed at the start of a span, one 128-bit word:
 // the closed-form FM sum at the sub-tile's first frame and the ADSR line over the sub-tile
@@ -177,7 +193,11 @@ __global__ void bank_prepare_kernel(BankArgs a)
     F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
     const float wm = (float)(fm * inc_rad), wc = (float)(f0b * inc_c);
     F.inc = make_float4(wm, wm, wc, wc);
-    F.g2 = make_float4((float)F.gd, (float)F.gd, 4.0f * wm, 4.0f * wc);
+    F.g2 = make_float4((float)F.gd, (float)F.gd, (float)(kFItems / 2) * wm, (float)(kFItems / 2) * wc);
+    {
+        const double w = fm * inc_rad;
+        F.rot = make_float4((float)cos(w), (float)cos(w), (float)sin(w), (float)sin(w));
+    }
     F.bL = V.c_bias * V.gain_l;
     F.bR = V.c_bias * V.gain_r;
     F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_amp * V.gain_r);
@@ -327,10 +347,10 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
 template <bool MOD, int WAVE, bool RARE>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
                                                const double Tc0, const float lane8, const int64_t n,
-                                               const FastCtx ctx, float2 (&accL2)[kItems / 2],
-                                               float2 (&accR2)[kItems / 2])
+                                               const FastCtx ctx, float2 (&accL2)[kFItems / 2],
+                                               float2 (&accR2)[kFItems / 2])
 {
-    constexpr int H = kItems / 2;
+    constexpr int H = kFItems / 2;
     constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
     constexpr bool EDGES = (WAVE >= SB_WAVE_SQUARE);
     const double2 car = F.car;
@@ -347,6 +367,28 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
         // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
         const double2 mod = F.mod;
         const float th0 = (float)reduce_two_pi_fast(fma(mod.x, Tr0, mod.y));
+#if FAST_ROTATE_MODULATOR
+        // sin/cos of the two half-run start phases from the SFU, then the other frames by
+        // rotating (sin, cos) one modulator step at a time: 4 packed FMAs per frame pair and no
+        // SFU work, against 2 multiplies + 2 SFU sines (error ~1e-7 per step, as good as the SFU's)
+        const float th1 = th0 + g2.z;
+        float2 sn = make_float2(__sinf(th0), __sinf(th1));
+        float2 cs = make_float2(__cosf(th0), __cosf(th1));
+        const float4 rot = F.rot;
+        const float2 cw2 = make_float2(rot.x, rot.y), sw2 = make_float2(rot.z, rot.w);
+        const float2 nsw2 = make_float2(-rot.z, -rot.w);
+        float2 run = make_float2(0.0f, 0.0f);
+#pragma unroll
+        for (int q = 0; q < H; q++) {
+            ps[q] = run;
+            run = __fadd2_rn(run, sn);
+            if (q + 1 < H) {
+                const float2 sn1 = __ffma2_rn(cs, sw2, __fmul2_rn(sn, cw2));
+                cs = __ffma2_rn(sn, nsw2, __fmul2_rn(cs, cw2));
+                sn = sn1;
+            }
+        }
+#else
         float2 th = make_float2(th0, th0 + g2.z);
         const float2 step = make_float2(inc.x, inc.y);
         float2 run = make_float2(0.0f, 0.0f);
@@ -356,6 +398,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
             run = __fadd2_rn(run, make_float2(__sinf(th.x), __sinf(th.y)));
             th = __fadd2_rn(th, step);
         }
+#endif
         const float total = run.x + run.y;
         const float incl = warp_scan_incl_ptx(total);
         before = rec.anchor + (double)(incl - total);
@@ -376,7 +419,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
     const bool low = EDGES && !(B > 16.0);
     base = make_float2(b0, b0 + g2.w + half_gd);
     const float e0 = fmaf(lane8, rec.de, rec.e_sub);
-    float2 e = make_float2(e0, fmaf(4.0f, rec.de, e0));
+    float2 e = make_float2(e0, fmaf((float)H, rec.de, e0));
     const float2 cstep = make_float2(inc.z, inc.w), gd2 = make_float2(g2.x, g2.y);
     const float2 estep = make_float2(rec.de, rec.de);
     const float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
@@ -426,11 +469,26 @@ template <int KIND>
 __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const SubRec *s_rec, int begin, int end,
                                                 int s, const double Tr0, const double Tc0, const float lane8,
                                                 const int64_t n, const FastCtx ctx,
-                                                float2 (&accL2)[kItems / 2], float2 (&accR2)[kItems / 2])
+                                                float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
     constexpr bool MOD = (KIND & 1) != 0;
     constexpr int WAVE = KIND >> 1;
-    for (int v = begin; v < end; v++) {
+    int v = begin;
+#if FAST_PAIR_VOICES
+    // two voices per iteration in one basic block: their (independent) dependency chains give
+    // the scheduler twice the instruction-level parallelism to hide MUFU / shuffle latency
+    if (WAVE < SB_WAVE_SQUARE) {
+        for (; v + 1 < end; v += 2) {
+            const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
+            const SubRec r0 = s_rec[v * kFastMaxSub + s], r1 = s_rec[(v + 1) * kFastMaxSub + s];
+            const bool plain = r0.e_sub >= 0.0f && r1.e_sub >= 0.0f && !((F0.flags | F1.flags) & FV_BIAS);
+            if (!plain) break;                                                  // warp-uniform
+            fast_voice_run<MOD, WAVE, false>(F0, r0, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F1, r1, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+        }
+    }
+#endif
+    for (; v < end; v++) {
         const FastVoice &F = s_fv[v];
         const SubRec rec = s_rec[v * kFastMaxSub + s];
         if (rec.e_sub == kEnvSilent) continue;                                  // warp-uniform
@@ -449,7 +507,6 @@ template <bool EDGED>
 __global__ void __launch_bounds__(kFastWarps * 32, FAST_MIN_BLOCKS)
 bank_fast_kernel(BankArgs a)
 {
-    constexpr int kFirstKind = EDGED ? 4 : 0;          // kind = MOD | (waveform << 1); Square is waveform 2
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
     SubRec *s_rec_all = reinterpret_cast<SubRec *>(s_fv + a.voices_per_group);
@@ -511,14 +568,14 @@ bank_fast_kernel(BankArgs a)
     const int64_t span_begin = (int64_t)span * a.fast_span_len;
     int64_t span_end = span_begin + a.fast_span_len;
     if (span_end > a.frames) span_end = a.frames;
-    const int nsub = (int)((span_end - span_begin + kSub - 1) / kSub);
+    const int nsub = (int)((span_end - span_begin + kFSub - 1) / kFSub);
 
     // ---- per-(voice, sub-tile) records, all lanes busy: closed-form FM sum at the sub-tile
     //      start and the ADSR line across the sub-tile
     for (int idx = lane; idx < nv * nsub; idx += 32) {
         const int v = idx / nsub, s = idx - v * nsub;
         const FastVoice &F = s_fv[v];
-        const int64_t lo = a.n0 + span_begin + (int64_t)s * kSub, hi = lo + kSub;
+        const int64_t lo = a.n0 + span_begin + (int64_t)s * kFSub, hi = lo + kFSub;
         SubRec r;
         r.anchor = 0.0;
         r.e_sub = 1.0f;
@@ -544,10 +601,10 @@ bank_fast_kernel(BankArgs a)
     __syncwarp();
 
     float *out = a.out + (int64_t)group * a.out_stride;
-    const float lane8 = (float)(lane * kItems);
+    const float lane8 = (float)(lane * kFItems);
 
     for (int s = 0; s < nsub; s++) {
-        const int64_t i0 = span_begin + (int64_t)s * kSub + lane * kItems;
+        const int64_t i0 = span_begin + (int64_t)s * kFSub + lane * kFItems;
         const int64_t n = a.n0 + i0;
         // exact serial time at this lane's first frame in both bases (a fresh look-up per
         // sub-tile costs ~40 instructions per 64 voices and keeps no cursor state in registers)
@@ -564,9 +621,10 @@ bank_fast_kernel(BankArgs a)
         // keep both in registers for the voice loops (the compiler would otherwise recompute
         // the int64 -> fp64 conversion per voice)
         asm volatile("" : "+d"(Tr0), "+d"(Tc0));
-        float2 accL2[kItems / 2], accR2[kItems / 2];
+        constexpr int H = kFItems / 2;
+        float2 accL2[H], accR2[H];
 #pragma unroll
-        for (int q = 0; q < kItems / 2; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
+        for (int q = 0; q < H; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
         if (!EDGED) {
             fast_voice_loop<0>(s_fv, s_rec, 0, ke[0], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
@@ -582,34 +640,30 @@ bank_fast_kernel(BankArgs a)
             fast_voice_loop<9>(s_fv, s_rec, ke[8], ke[9], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
         }
 
-        // frame j of the run is accL2[j].x for j < 4 and accL2[j-4].y above; two frames per float4
-        if (i0 + kItems <= span_end) {
+        // frame j of the run is accL2[j].x for j < H and accL2[j-H].y above; two frames per float4
+        if (i0 + kFItems <= span_end) {
             float4 *dst = reinterpret_cast<float4 *>(out + i0 * 2);
-            float4 o0 = make_float4(accL2[0].x, accR2[0].x, accL2[1].x, accR2[1].x);
-            float4 o1 = make_float4(accL2[2].x, accR2[2].x, accL2[3].x, accR2[3].x);
-            float4 o2 = make_float4(accL2[0].y, accR2[0].y, accL2[1].y, accR2[1].y);
-            float4 o3 = make_float4(accL2[2].y, accR2[2].y, accL2[3].y, accR2[3].y);
-            if (EDGED) {                                // add to what the smooth-carrier kernel wrote
-                const float4 p0 = dst[0], p1 = dst[1], p2 = dst[2], p3 = dst[3];
-                o0 = make_float4(o0.x + p0.x, o0.y + p0.y, o0.z + p0.z, o0.w + p0.w);
-                o1 = make_float4(o1.x + p1.x, o1.y + p1.y, o1.z + p1.z, o1.w + p1.w);
-                o2 = make_float4(o2.x + p2.x, o2.y + p2.y, o2.z + p2.z, o2.w + p2.w);
-                o3 = make_float4(o3.x + p3.x, o3.y + p3.y, o3.z + p3.z, o3.w + p3.w);
+#pragma unroll
+            for (int k = 0; k < H; k++) {               // float4 k holds frames 2k, 2k+1
+                const int fa = 2 * k, fb = 2 * k + 1;
+                float4 o = make_float4(fa < H ? accL2[fa].x : accL2[fa - H].y, fa < H ? accR2[fa].x : accR2[fa - H].y,
+                                       fb < H ? accL2[fb].x : accL2[fb - H].y, fb < H ? accR2[fb].x : accR2[fb - H].y);
+                if (EDGED) {                            // add to what the smooth-carrier kernel wrote
+                    const float4 p = dst[k];
+                    o = make_float4(o.x + p.x, o.y + p.y, o.z + p.z, o.w + p.w);
+                }
+                dst[k] = o;
             }
-            dst[0] = o0;
-            dst[1] = o1;
-            dst[2] = o2;
-            dst[3] = o3;
         } else {
 #pragma unroll
-            for (int q = 0; q < kItems / 2; q++) {
+            for (int q = 0; q < H; q++) {
                 if (i0 + q < span_end) {
                     out[(i0 + q) * 2] = accL2[q].x + (EDGED ? out[(i0 + q) * 2] : 0.0f);
                     out[(i0 + q) * 2 + 1] = accR2[q].x + (EDGED ? out[(i0 + q) * 2 + 1] : 0.0f);
                 }
-                if (i0 + q + kItems / 2 < span_end) {
-                    out[(i0 + q + kItems / 2) * 2] = accL2[q].y + (EDGED ? out[(i0 + q + kItems / 2) * 2] : 0.0f);
-                    out[(i0 + q + kItems / 2) * 2 + 1] = accR2[q].y + (EDGED ? out[(i0 + q + kItems / 2) * 2 + 1] : 0.0f);
+                if (i0 + q + H < span_end) {
+                    out[(i0 + q + H) * 2] = accL2[q].y + (EDGED ? out[(i0 + q + H) * 2] : 0.0f);
+                    out[(i0 + q + H) * 2 + 1] = accR2[q].y + (EDGED ? out[(i0 + q + H) * 2 + 1] : 0.0f);
                 }
             }
         }
@@ -925,7 +979,7 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     int64_t span_len = ((nsub + nspans - 1) / nspans) * kSub;
     nspans = (frames + span_len - 1) / span_len;
     // fast path: spans of at most kFastMaxSub sub-tiles (their anchors sit in shared memory)
-    int64_t fast_sub = span_len / kSub;
+    int64_t fast_sub = span_len / kFSub;
     if (fast_sub > kFastMaxSub) fast_sub = kFastMaxSub;
     if (fast_sub < 1) fast_sub = 1;
     plan->nvoices = nvoices;
@@ -934,7 +988,7 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     plan->nspans = (int32_t)nspans;
     plan->frames = frames;
     plan->span_len = span_len;
-    plan->fast_span_len = fast_sub * kSub;
+    plan->fast_span_len = fast_sub * kFSub;
     plan->fast_nspans = (int32_t)((frames + plan->fast_span_len - 1) / plan->fast_span_len);
     plan->nsegs_rad = nsegs_rad;
     plan->generic_voices = -1;
@@ -963,7 +1017,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
                "sb_bank_render_f32: bad time base");
     SB_REQUIRE(plan->voices_per_group >= 1 && plan->voices_per_group <= kMaxVoicesPerGroup &&
                    plan->span_len % kSub == 0 && plan->nspans >= 1 && plan->ngroups >= 1 && n0 >= 0 &&
-                   plan->fast_span_len % kSub == 0 && plan->fast_span_len / kSub <= kFastMaxSub &&
+                   plan->fast_span_len % kFSub == 0 && plan->fast_span_len / kFSub <= kFastMaxSub &&
                    plan->fast_nspans >= 1,
                "sb_bank_render_f32: bad plan");
     SB_REQUIRE(plan->ngroups == 1 || partial_dev, "sb_bank_render_f32: partial scratch missing");
