@@ -117,6 +117,12 @@ def main():
     placed = [(when, h.copy().resample(sr)) for _, h, when in hits]
     torch.cuda.synchronize()
     resample_ms = (time.perf_counter() - t0) * 1e3
+    copies = [h.copy() for _, h, _ in hits]
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    sb.Sample.resample_many(copies, sr)
+    torch.cuda.synchronize()
+    resample_many_ms = (time.perf_counter() - t0) * 1e3
     base = sb.Sample.from_raw_frames(b"", 2, sr, 1).add_silence(600.0)
     span_samples = sum(len(h) for _, h in placed)
 
@@ -156,7 +162,8 @@ def main():
         dst.mix_at(when, h)
     torch.cuda.synchronize()
     loop_ms = (time.perf_counter() - t0) * 1e3 * 8
-    line("config4 through the Sample API", resample_4096_hits_ms=resample_ms, mix_at_many_ms=api_ms,
+    line("config4 through the Sample API", resample_4096_hits_ms=resample_ms, resample_many_ms=resample_many_ms,
+         mix_at_many_ms=api_ms,
          mix_at_loop_ms_extrapolated_from_512=loop_ms, msamples_per_s=total / api_ms / 1e3)
 
     # ---- config 2: FM sawtooth + ADSR + echo, 60 s stereo 48 kHz through the oscillator API -------

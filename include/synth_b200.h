@@ -288,6 +288,15 @@ int sb_pcm16_modulate(int16_t *buf_dev, const float *mod_dev, int64_t count, voi
 int64_t sb_pcm16_ratecv_frames(int64_t in_frames, int64_t inrate, int64_t outrate);
 int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nchannels, int64_t inrate,
                     int64_t outrate, int16_t *out_dev, void *stream);
+/* The same for many (short) samples in ONE launch: source s is in_pool[in_off[s] ..) with
+ * in_frames[s] frames at reduced rate inrate_red[s] -> outrate_red[s] (both divided by their
+ * gcd, below 2^21), written to out_pool[out_off[s] ..) with out_frames[s] =
+ * sb_pcm16_ratecv_frames(...) frames.  All arrays are device arrays of nsrc int64 (offsets in
+ * int16 units); max_out_frames = the largest out_frames[s]. */
+int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *in_off_dev, const int64_t *in_frames_dev,
+                         const int64_t *inrate_red_dev, const int64_t *outrate_red_dev,
+                         const int64_t *out_off_dev, const int64_t *out_frames_dev, int64_t nsrc,
+                         int nchannels, int64_t max_out_frames, int16_t *out_pool_dev, void *stream);
 /* Sample.mix_at for a list of sources applied IN ORDER: each step is audioop.add on the
  * overlapped span (saturation per step).  Source s is src_pool_dev[src_off[s] ..
  * src_off[s]+src_len[s]) (int16 sample units) mixed at dst sample index dst_off[s]; the

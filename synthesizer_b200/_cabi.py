@@ -115,6 +115,7 @@ _SIGNATURES = {
     "sb_pcm16_modulate": (c_int, [_P, _P, c_int64, _P]),
     "sb_pcm16_ratecv_frames": (c_int64, [c_int64, c_int64, c_int64]),
     "sb_pcm16_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
+    "sb_pcm16_ratecv_many": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int64, c_int, c_int64, _P, _P]),
     "sb_pcm16_mix_at_many_scratch_bytes": (c_int64, [c_int64, c_int64, c_int64]),
     "sb_pcm16_mix_at_many": (c_int, [_P, c_int64, _P, _P, _P, _P, c_int64, _P, c_int64, _P]),
     "sb_pcm32_add": (c_int, [_P, _P, c_int64, _P, _P]),

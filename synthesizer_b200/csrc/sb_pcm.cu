@@ -591,6 +591,63 @@ extern "C" int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nch
     return SB_OK;
 }
 
+// ---- many short samples resampled to one rate in ONE launch (config 4: thousands of drum hits).
+// Source s is in_pool[in_off[s] .. + in_frames[s]*nch) at rate inrate[s]; its output goes to
+// out_pool[out_off[s] .. + out_frames[s]*nch).  blockIdx.y walks the sources, blockIdx.x
+// (grid-stride) the output frames of a source.  Same arithmetic as pcm16_ratecv_kernel.
+__global__ void __launch_bounds__(kPBlock)
+pcm16_ratecv_many_kernel(const int16_t *__restrict__ in_pool, const int64_t *__restrict__ in_off,
+                         const int64_t *__restrict__ in_frames, const int64_t *__restrict__ inrate_red,
+                         const int64_t *__restrict__ outrate_red, const int64_t *__restrict__ out_off,
+                         const int64_t *__restrict__ out_frames, int64_t nsrc, int nch, int16_t *__restrict__ out_pool)
+{
+    for (int64_t s = blockIdx.y; s < nsrc; s += gridDim.y) {
+        const int16_t *in = in_pool + in_off[s];
+        int16_t *out = out_pool + out_off[s];
+        const int64_t nout = out_frames[s], inr = inrate_red[s], outr = outrate_red[s];
+        if (inr == outr) {                                  // same rate: audioop.ratecv copies
+            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nout * nch; i += (int64_t)gridDim.x * blockDim.x)
+                out[i] = in[i];
+            continue;
+        }
+        const double rcp = 1.0 / (double)outr;
+        for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nout; j += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t num = j * inr;
+            const int64_t c = (num + outr - 1) / outr;
+            const int64_t d = c * outr - num;
+            for (int ch = 0; ch < nch; ch++) {
+                const long long cur = (long long)(int)((uint32_t)(int32_t)in[c * nch + ch] << 16);
+                const long long prev = (c > 0) ? (long long)(int)((uint32_t)(int32_t)in[(c - 1) * nch + ch] << 16) : 0;
+                const long long sum = prev * d + cur * (outr - d);
+                const long long mag = sum < 0 ? -sum : sum;
+                long long q = (long long)__double2ll_rz(__dmul_rn((double)mag, rcp));
+                const long long rem = mag - q * outr;
+                if (rem < 0) q -= 1;
+                else if (rem >= outr) q += 1;
+                const int o = (int)(sum < 0 ? -q : q);
+                out[j * nch + ch] = (int16_t)(o >> 16);
+            }
+        }
+    }
+}
+
+extern "C" int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *in_off_dev, const int64_t *in_frames_dev,
+                                    const int64_t *inrate_red_dev, const int64_t *outrate_red_dev,
+                                    const int64_t *out_off_dev, const int64_t *out_frames_dev, int64_t nsrc,
+                                    int nchannels, int64_t max_out_frames, int16_t *out_pool_dev, void *stream)
+{
+    SB_REQUIRE(nsrc >= 0 && (nchannels == 1 || nchannels == 2) && max_out_frames >= 0, "sb_pcm16_ratecv_many: bad arguments");
+    if (!nsrc || !max_out_frames) return SB_OK;
+    SB_REQUIRE(in_pool_dev && in_off_dev && in_frames_dev && inrate_red_dev && outrate_red_dev && out_off_dev &&
+                   out_frames_dev && out_pool_dev, "sb_pcm16_ratecv_many: null pointer");
+    dim3 grid((unsigned)grid_for(max_out_frames, kPBlock, 64), (unsigned)(nsrc < 65535 ? nsrc : 65535));
+    pcm16_ratecv_many_kernel<<<grid, kPBlock, 0, (cudaStream_t)stream>>>(
+        in_pool_dev, in_off_dev, in_frames_dev, inrate_red_dev, outrate_red_dev, out_off_dev, out_frames_dev, nsrc,
+        nchannels, out_pool_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
 extern "C" int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t nsrc, int64_t total_src_samples)
 {
     if (dst_count <= 0 || nsrc <= 0) return 0;

@@ -251,6 +251,47 @@ class Sample:
         self.samplerate = samplerate
         return self
 
+    @staticmethod
+    def resample_many(samples, samplerate):
+        """Backend extension: ``s.resample(samplerate)`` for every sample of the list with ONE
+        kernel launch (16-bit samples with the same channel count; others fall back to their own
+        resample()).  Each sample is changed in place, exactly as its own resample() would."""
+        import math
+        todo = [s for s in samples if s.samplerate != samplerate and s._dev is not None]
+        for s in todo:
+            assert not s._locked
+        batch = [s for s in todo if s.samplewidth == 2 and s.nchannels == todo[0].nchannels]
+        in_batch = {id(s) for s in batch}
+        for s in todo:
+            if id(s) not in in_batch:
+                s.resample(samplerate)
+        if batch:
+            nch = batch[0].nchannels
+            in_frames = [len(s) for s in batch]
+            red = [(s.samplerate // math.gcd(s.samplerate, samplerate), samplerate // math.gcd(s.samplerate, samplerate))
+                   for s in batch]
+            for a, b in red:
+                if a >= (1 << 21) or b >= (1 << 21):
+                    raise ValueError("reduced sample rates must be below 2^21")
+            out_frames = [C.lib.sb_pcm16_ratecv_frames(n, a, b) for n, (a, b) in zip(in_frames, red)]
+            in_off, out_off, ai, ao = [], [], 0, 0
+            for n, m in zip(in_frames, out_frames):
+                in_off.append(ai)
+                out_off.append(ao)
+                ai += n * nch
+                ao += m * nch
+            pool = torch.cat([s._dev for s in batch])
+            out = D.empty(ao, torch.int16)
+            idx = torch.tensor([in_off, in_frames, [a for a, _ in red], [b for _, b in red], out_off, out_frames],
+                               dtype=torch.int64).to(D.device())
+            C.call("sb_pcm16_ratecv_many", D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]), D.ptr(idx[3]),
+                   D.ptr(idx[4]), D.ptr(idx[5]), len(batch), nch, max(out_frames), D.ptr(out), D.stream())
+            for s, o, m in zip(batch, out_off, out_frames):
+                s._dev = out[o:o + m * nch]
+        for s in samples:
+            s.samplerate = samplerate
+        return samples
+
     def speed(self, speed):
         assert not self._locked
         assert speed > 0

@@ -240,6 +240,22 @@ def test_config4_mix_at_4096_resampled_hits(cuda):
     got = np.frombuffer(dst.get_frames(), dtype="<i2")
     assert len(got) == total
     np.testing.assert_array_equal(got, want)
+    # the same through the batched resample (one launch for all 4096 hits)
+    rng = np.random.default_rng(4)
+    raw_hits, whens = [], []
+    for k in range(4096):
+        src_rate = int(rng.choice([22050, 44100, 32000]))
+        n = int(rng.integers(2000, 20000))
+        t = np.arange(n) / src_rate
+        hit = (rng.uniform(8000, 30000) * np.exp(-t * rng.uniform(8, 40)) *
+               np.sin(2 * np.pi * rng.uniform(60, 400) * t)).astype(np.int16)
+        raw_hits.append(sb.Sample.from_raw_frames(hit.astype("<i2").tobytes(), 2, src_rate, 1))
+        whens.append(float(rng.uniform(0, 599.0)))
+    sb.Sample.resample_many(raw_hits, sr)
+    assert all(h.samplerate == sr for h in raw_hits)
+    dst2 = sb.Sample.from_raw_frames(b"", 2, sr, 1).add_silence(600.0)
+    dst2.mix_at_many(list(zip(whens, raw_hits)))
+    np.testing.assert_array_equal(np.frombuffer(dst2.get_frames(), dtype="<i2"), want)
 
 
 def test_host_buffer_entry_points(cuda):
