@@ -262,6 +262,39 @@ def test_wavesynth_config1_sine_440(cuda):
     assert_within_lsb(got, want, 1, "config 1")
 
 
+def test_wavesynth_waveforms(cuda):
+    """WaveSynth folds the integer scale into the oscillator amplitude and truncates with int()."""
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    sr, dur = 22050, 0.5
+    n = int(sr * dur)
+    ws = sb.WaveSynth(samplerate=sr)
+    scale = 32767
+
+    def want(osc):
+        return np.trunc(np.array(so.render_floats(osc, n))).astype(np.int64)
+
+    def got(sample):
+        assert (sample.samplerate, sample.nchannels, sample.samplewidth, len(sample)) == (sr, 1, 2, n)
+        return np.frombuffer(sample.get_frames(), dtype="<i2")
+
+    lfo_g = sb.Sine(4.0, 0.02, samplerate=sr)
+    lfo_o = so.Sine(4.0, 0.02, samplerate=sr)
+    assert_within_lsb(got(ws.sine(330.0, dur, 0.8, 0.1, 0.05, fm_lfo=lfo_g)),
+                      want(so.Sine(330.0, 0.8 * scale, 0.1, 0.05 * scale, fm_lfo=lfo_o, samplerate=sr)), 1, "sine")
+    assert_within_lsb(got(ws.square(441.0, dur, 0.6)), want(so.Square(441.0, 0.6 * scale, samplerate=sr)), 1, "square")
+    assert_within_lsb(got(ws.triangle(200.0, dur, 0.9, 0.3)), want(so.Triangle(200.0, 0.9 * scale, 0.3, samplerate=sr)), 1, "triangle")
+    assert_within_lsb(got(ws.sawtooth(123.4, dur, 0.7)), want(so.Sawtooth(123.4, 0.7 * scale, samplerate=sr)), 1, "sawtooth")
+    assert_within_lsb(got(ws.pulse(220.5, dur, 0.7, pulsewidth=0.25)),
+                      want(so.Pulse(220.5, 0.7 * scale, pulsewidth=0.25, samplerate=sr)), 1, "pulse")
+    assert_within_lsb(got(ws.linear(dur, 0.1, 0.0001, -0.5, 0.5)),
+                      want(so.Linear(0.1 * scale, 0.0001 * scale, -0.5 * scale, 0.5 * scale, samplerate=sr)), 1, "linear")
+    u = np.random.default_rng(3).random(n)
+    assert_within_lsb(got(ws.white_noise(2205.0, dur, 0.9, noise_source=u)),
+                      want(so.WhiteNoise(2205.0, 0.9 * scale, samplerate=sr, noise_source=u)), 1, "white noise")
+    assert sb.synth.note_freq("A4") == 440.0 and abs(sb.synth.key_freq(40) - 261.6255653) < 1e-6
+
+
 def test_overflow_raises(cuda):
     import synthesizer_b200 as sb
     with pytest.raises(OverflowError):
