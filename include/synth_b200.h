@@ -210,8 +210,14 @@ typedef struct sb_voice {
     int32_t c_wave, m_wave;              /* m_wave = SB_WAVE_NONE: no FM */
     double c_freq, c_phase;              /* phase as passed upstream (fraction of a cycle) */
     double m_freq, m_phase;
-    float c_amp, c_bias, c_pw;
-    float m_amp, m_bias, m_pw;
+    /* Everything that decides WHERE an edge falls, or that is summed over the whole render,
+     * is fp64 as upstream has it: the modulator's amplitude and bias (they scale the FM sum) and
+     * both pulse widths (a float32 width moves an LFO edge by one sample whenever the phase
+     * hits the width exactly, e.g. 5.3 Hz, phase 0.1, width 0.4 at t = 1 s).  The carrier's
+     * amplitude, bias and the pan gains only scale the output value: float32. */
+    double m_amp, m_bias;
+    double c_pw, m_pw;
+    float c_amp, c_bias;
     float gain_l, gain_r;
     sb_envelope env;
 } sb_voice;

@@ -43,8 +43,9 @@ class Voice(Structure):
     _fields_ = [("c_wave", c_int32), ("m_wave", c_int32),
                 ("c_freq", c_double), ("c_phase", c_double),
                 ("m_freq", c_double), ("m_phase", c_double),
-                ("c_amp", c_float), ("c_bias", c_float), ("c_pw", c_float),
-                ("m_amp", c_float), ("m_bias", c_float), ("m_pw", c_float),
+                ("m_amp", c_double), ("m_bias", c_double),
+                ("c_pw", c_double), ("m_pw", c_double),
+                ("c_amp", c_float), ("c_bias", c_float),
                 ("gain_l", c_float), ("gain_r", c_float),
                 ("env", Envelope)]
 

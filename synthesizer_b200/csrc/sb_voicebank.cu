@@ -50,6 +50,15 @@ constexpr int kFastMaxSub = FAST_MAX_SUB;    // fast kernel: sub-tiles per span 
                                   4/5/6 CTAs -> 2.65/2.63/2.76 ms */
 #endif
 
+#ifndef FAST_LANE_ANCHOR
+#define FAST_LANE_ANCHOR 1
+#endif
+#ifndef FAST_SCAN_F64
+#define FAST_SCAN_F64 0
+#endif
+#ifndef FAST_MAX_FM_GAIN
+#define FAST_MAX_FM_GAIN 1.5
+#endif
 #ifndef FAST_ROTATE_MODULATOR
 #define FAST_ROTATE_MODULATOR 1
 #endif
@@ -66,7 +75,8 @@ enum : int {
     FV_BIAS = 32,
     FV_WAVE_SHIFT = 8,       // bits 8..10: the carrier's waveform id
 };
-constexpr int kFastKinds = 10;               // kind = MOD | (carrier waveform << 1)
+constexpr double kFastMaxFmGain = FAST_MAX_FM_GAIN;
+constexpr int kFastKinds = 10;              // kind = MOD | (carrier waveform << 1)
 constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer than this to a
                                              // discontinuity are re-evaluated exactly in fp64
 
@@ -84,13 +94,17 @@ struct alignas(16) FastVoice {
     float4 g2;               // gdf, gdf, 4wm, 4wc: gd in fp32 (pair); phase steps of four frames
     float4 gain;             // aL, aL, aR, aR: c_amp*gain (as pairs for the packed fp32x2 FMAs)
     float4 rot;              // cos(wm), cos(wm), sin(wm), sin(wm): one-frame rotation of the modulator phase
+    float2 rotH;             // cos(H*wm), sin(H*wm): rotation by half a run (H frames)
+    float2 pad2;
+    double half_w;           // half a modulator phase step, fm * inc_rad / 2 (radians)
+    double pw64;             // Pulse carriers: the (clamped) pulse width in fp64, for the exact re-evaluation
     long long n_a, n_d, n_s, n_r;
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
     float pw;                // Pulse carriers: the (clamped) pulse width
 };
-static_assert(sizeof(FastVoice) == 176, "FastVoice layout");
+static_assert(sizeof(FastVoice) == 208, "FastVoice layout");
 
 // Per-(voice, sub-tile) record precomputed at the start of a span, one 128-bit word:
 // the closed-form FM sum at the sub-tile's first frame and the ADSR line over the sub-tile
@@ -139,6 +153,14 @@ __host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplera
     const double w = V.m_freq * 6.283185307179586 / samplerate;      // modulator phase step
     if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return false;            // closed form needs sin(w/2) != 0
     if (!(fabs((double)V.m_amp) <= 4.0 && fabs((double)V.m_bias) <= 4.0)) return false;
+    // FM gain: carrier phase (radians) per unit of the modulator's running sum.  The fast path
+    // anchors that sum exactly (fp64 closed form) at the first frame of every 16-frame run and adds
+    // fp32 / SFU sines only inside the run; measured against the serial fp64 computation (tools/accuracy_sweep.py)
+    // the worst error is 0.28 LSB of full scale per radian of gain (it was 3.5 LSB per radian
+    // with a warp scan over the 512-frame sub-tile), so voices up to a gain of 1.5 are admitted;
+    // stronger FM takes the generic fp64 path.
+    const double gain_rad = fabs(V.c_freq) * (6.283185307179586 / samplerate) * fabs((double)V.m_amp);
+    if (!(gain_rad <= kFastMaxFmGain)) return false;
     return true;
 }
 
@@ -183,6 +205,8 @@ __global__ void bank_prepare_kernel(BankArgs a)
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
     F.pw = (float)clamp_pulsewidth((double)V.c_pw);
+    F.pw64 = clamp_pulsewidth((double)V.c_pw);
+    F.half_w = 0.0;
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
     const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
@@ -197,6 +221,11 @@ __global__ void bank_prepare_kernel(BankArgs a)
     {
         const double w = fm * inc_rad;
         F.rot = make_float4((float)cos(w), (float)cos(w), (float)sin(w), (float)sin(w));
+        const double wh = w * (double)(kFItems / 2);
+        F.rotH = make_float2((float)cos(wh), (float)sin(wh));
+        F.pad2 = make_float2(0.0f, 0.0f);
+        F.half_w = 0.5 * w;
+
     }
     F.bL = V.c_bias * V.gain_l;
     F.bR = V.c_bias * V.gain_r;
@@ -294,9 +323,23 @@ __device__ __forceinline__ float warp_scan_incl_ptx(float v)
     return v;
 }
 
+// the same for doubles (two 32-bit shuffles per step)
+__device__ __forceinline__ double warp_scan_incl_f64(double v)
+{
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const double o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += o;
+    }
+    return v;
+}
+
 struct FastCtx {
     const sb_time_seg *s_cyc;
     int nsegs_cyc;
+    const double2 *tab;      // [nvoices][nsegs_rad] closed-form FM table (A, C)
+    int nsegs_rad;
 };
 
 // Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
@@ -346,9 +389,9 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
 // every edge lands on the sample upstream puts it on.
 template <bool MOD, int WAVE, bool RARE>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
-                                               const double Tc0, const float lane8, const int64_t n,
-                                               const FastCtx ctx, float2 (&accL2)[kFItems / 2],
-                                               float2 (&accR2)[kFItems / 2])
+                                               const double Tc0, const int seg_r, const float lane8,
+                                               const int64_t n, const FastCtx ctx,
+                                               float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
     constexpr int H = kFItems / 2;
     constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
@@ -366,15 +409,27 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
     if (MOD) {
         // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
         const double2 mod = F.mod;
-        const float th0 = (float)reduce_two_pi_fast(fma(mod.x, Tr0, mod.y));
+        const double r0 = reduce_two_pi_fast(fma(mod.x, Tr0, mod.y));
+        const float th0 = (float)r0;
+#if FAST_LANE_ANCHOR
+        // FM sum ahead of this lane's first frame, exactly: the closed form A - C*cos(theta - w/2)
+        // of the modulator's time-base segment, evaluated in fp64 per lane.  No warp scan, no
+        // dependence between lanes, and fp32 / SFU error cannot build up over more than the
+        // 16 frames of the run.
+        const double2 ac = ctx.tab[(int64_t)F.pad0 * ctx.nsegs_rad + seg_r];
+        before = fma(-ac.y, cos_reduced(r0 - F.half_w), ac.x);
+#endif
 #if FAST_ROTATE_MODULATOR
         // sin/cos of the two half-run start phases from the SFU, then the other frames by
         // rotating (sin, cos) one modulator step at a time: 4 packed FMAs per frame pair and no
         // SFU work, against 2 multiplies + 2 SFU sines (error ~1e-7 per step, as good as the SFU's)
-        const float th1 = th0 + g2.z;
-        float2 sn = make_float2(__sinf(th0), __sinf(th1));
-        float2 cs = make_float2(__cosf(th0), __cosf(th1));
+        // (the second half-run's start is itself a rotation of the first by H steps, so the SFU
+        // only ever sees arguments inside [-pi, pi])
+        const float s0 = __sinf(th0), c0 = __cosf(th0);
         const float4 rot = F.rot;
+        const float2 rotH = F.rotH;
+        float2 sn = make_float2(s0, fmaf(c0, rotH.y, s0 * rotH.x));
+        float2 cs = make_float2(c0, fmaf(-s0, rotH.y, c0 * rotH.x));
         const float2 cw2 = make_float2(rot.x, rot.y), sw2 = make_float2(rot.z, rot.w);
         const float2 nsw2 = make_float2(-rot.z, -rot.w);
         float2 run = make_float2(0.0f, 0.0f);
@@ -399,9 +454,18 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
             th = __fadd2_rn(th, step);
         }
 #endif
+        // exclusive prefix over the lanes in fp64: the partial sums reach the hundreds when the
+        // LFO is slow against the 512-frame sub-tile, where an fp32 scan would lose ~3e-5 —
+        // times gd that was the dominant error of this path (tools/accuracy_sweep.py)
+#if FAST_LANE_ANCHOR
+        // (before was set above)
+#elif FAST_SCAN_F64
+        const double total = (double)run.x + (double)run.y;
+        before = rec.anchor + (warp_scan_incl_f64(total) - total);
+#else
         const float total = run.x + run.y;
-        const float incl = warp_scan_incl_ptx(total);
-        before = rec.anchor + (double)(incl - total);
+        before = rec.anchor + (double)(warp_scan_incl_ptx(total) - total);
+#endif
         B = fma(F.gd, before, B);
         half_gd = g2.x * run.x;
         half_sum = run.x;
@@ -441,10 +505,10 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
             w.y = guarded_shape<WAVE>(ph.y, pw, ny);
             if (nx || low)
                 w.x = exact_shape(WAVE, ctx, n + q, car.x, car.y, MOD ? F.gd * (before + (double)ps[q].x) : 0.0,
-                                  MOD, (double)pw);
+                                  MOD, F.pw64);
             if (ny || low)
                 w.y = exact_shape(WAVE, ctx, n + q + H, car.x, car.y,
-                                  MOD ? F.gd * (before + (double)half_sum + (double)ps[q].y) : 0.0, MOD, (double)pw);
+                                  MOD ? F.gd * (before + (double)half_sum + (double)ps[q].y) : 0.0, MOD, F.pw64);
         }
         float2 ee = e;
         if (RARE) {
@@ -467,8 +531,8 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
 // sorted by kind, so each loop is a branch-free run.
 template <int KIND>
 __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const SubRec *s_rec, int begin, int end,
-                                                int s, const double Tr0, const double Tc0, const float lane8,
-                                                const int64_t n, const FastCtx ctx,
+                                                int s, const double Tr0, const double Tc0, const int seg_r,
+                                                const float lane8, const int64_t n, const FastCtx ctx,
                                                 float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
     constexpr bool MOD = (KIND & 1) != 0;
@@ -483,8 +547,8 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const Sub
             const SubRec r0 = s_rec[v * kFastMaxSub + s], r1 = s_rec[(v + 1) * kFastMaxSub + s];
             const bool plain = r0.e_sub >= 0.0f && r1.e_sub >= 0.0f && !((F0.flags | F1.flags) & FV_BIAS);
             if (!plain) break;                                                  // warp-uniform
-            fast_voice_run<MOD, WAVE, false>(F0, r0, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_run<MOD, WAVE, false>(F1, r1, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F0, r0, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F1, r1, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
         }
     }
 #endif
@@ -493,9 +557,9 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const Sub
         const SubRec rec = s_rec[v * kFastMaxSub + s];
         if (rec.e_sub == kEnvSilent) continue;                                  // warp-uniform
         if (rec.e_sub == kEnvSlow || (F.flags & FV_BIAS))
-            fast_voice_run<MOD, WAVE, true>(F, rec, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, true>(F, rec, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
         else
-            fast_voice_run<MOD, WAVE, false>(F, rec, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F, rec, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
     }
 }
 
@@ -558,7 +622,7 @@ bank_fast_kernel(BankArgs a)
     nv = ke[kFastKinds - 1];                           // this kernel's voices only from here on
     if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
     const bool any_cyc = EDGED || nv > ke[1];
-    const FastCtx ctx = {s_cyc, a.nsegs_cyc};
+    const FastCtx ctx = {s_cyc, a.nsegs_cyc, a.tab, a.nsegs_rad};
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
@@ -580,7 +644,7 @@ bank_fast_kernel(BankArgs a)
         r.anchor = 0.0;
         r.e_sub = 1.0f;
         r.de = 0.0f;
-        if (F.flags & FV_HAS_MOD) {
+        if (!FAST_LANE_ANCHOR && (F.flags & FV_HAS_MOD)) {
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, lo);
             const double t = c.at(lo);
@@ -609,10 +673,12 @@ bank_fast_kernel(BankArgs a)
         // exact serial time at this lane's first frame in both bases (a fresh look-up per
         // sub-tile costs ~40 instructions per 64 voices and keeps no cursor state in registers)
         double Tr0, Tc0 = 0.0;
+        int seg_r;
         {
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, n);
             Tr0 = c.at(n);
+            seg_r = c.idx;
             if (any_cyc) {                              // carriers whose phase counts in cycles present
                 c.seek(s_cyc, a.nsegs_cyc, n);
                 Tc0 = c.at(n);
@@ -627,17 +693,17 @@ bank_fast_kernel(BankArgs a)
         for (int q = 0; q < H; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
         if (!EDGED) {
-            fast_voice_loop<0>(s_fv, s_rec, 0, ke[0], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<1>(s_fv, s_rec, ke[0], ke[1], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<2>(s_fv, s_rec, ke[1], ke[2], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<3>(s_fv, s_rec, ke[2], ke[3], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<0>(s_fv, s_rec, 0, ke[0], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<1>(s_fv, s_rec, ke[0], ke[1], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<2>(s_fv, s_rec, ke[1], ke[2], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<3>(s_fv, s_rec, ke[2], ke[3], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
         } else {
-            fast_voice_loop<4>(s_fv, s_rec, 0, ke[4], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<5>(s_fv, s_rec, ke[4], ke[5], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<6>(s_fv, s_rec, ke[5], ke[6], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<7>(s_fv, s_rec, ke[6], ke[7], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<8>(s_fv, s_rec, ke[7], ke[8], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<9>(s_fv, s_rec, ke[8], ke[9], s, Tr0, Tc0, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<4>(s_fv, s_rec, 0, ke[4], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<5>(s_fv, s_rec, ke[4], ke[5], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<6>(s_fv, s_rec, ke[5], ke[6], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<7>(s_fv, s_rec, ke[6], ke[7], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<8>(s_fv, s_rec, ke[7], ke[8], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<9>(s_fv, s_rec, ke[8], ke[9], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
         }
 
         // frame j of the run is accL2[j].x for j < H and accL2[j-H].y above; two frames per float4
@@ -711,13 +777,32 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-// modulator value at fp64 phase; amplitude/bias applied in fp32
-__device__ __forceinline__ float lfo_value(const sb_voice &V, double t)
+// Modulator value in fp64, as upstream computes it.  fp32 would not do here: the FM sum adds
+// these values over the whole render, and an fp32 sine's error is not zero-mean over a stretch
+// of a slow LFO — measured 87 LSB off on a 10 kHz carrier with a 0.1 Hz, depth-2 modulator
+// (tools/accuracy_sweep.py) before this was fp64.
+__device__ __forceinline__ double lfo_value(const sb_voice &V, double t)
 {
-    double ph = __dadd_rn(__dmul_rn(t, V.m_freq), phase0_of(V.m_wave, V.m_phase));
-    double pw = (V.m_wave == SB_WAVE_PULSE) ? clamp_pulsewidth((double)V.m_pw) : 0.0;
-    float s = wave_shape(V.m_wave, ph, pw);
-    return __fadd_rn(__fmul_rn(s, V.m_amp), V.m_bias);
+    const double ph = __dadd_rn(__dmul_rn(t, V.m_freq), phase0_of(V.m_wave, V.m_phase));
+    double s;
+    switch (V.m_wave) {
+    case SB_WAVE_SINE:
+        s = sin(ph);
+        break;
+    case SB_WAVE_TRIANGLE:
+        s = 4.0 * (fabs(py_mod1(__dadd_rn(ph, 0.75)) - 0.5) - 0.25);
+        break;
+    case SB_WAVE_SQUARE:
+        s = (((long long)__dmul_rn(ph, 2.0)) & 1) ? -1.0 : 1.0;
+        break;
+    case SB_WAVE_SAWTOOTH:
+        s = 2.0 * (ph - floor(__dadd_rn(0.5, ph)));
+        break;
+    default:
+        s = (py_mod1(ph) < clamp_pulsewidth((double)V.m_pw)) ? 1.0 : -1.0;
+        break;
+    }
+    return __dadd_rn(__dmul_rn(s, (double)V.m_amp), (double)V.m_bias);
 }
 
 // pre-pass: per-(voice, span) LFO sums of the generic FM voices
@@ -761,8 +846,7 @@ bank_carry_kernel(BankArgs a)
         for (int64_t n = begin + lane; n < end; n += 32) {
             double t_n = cc.at(n);                               // cursor only moves forward
             double step = __dadd_rn(cc.at(n + 1), -t_n);         // exact: both on the table
-            float m = lfo_value(V, mc.at(n));
-            acc += __dmul_rn((double)m, step);
+            acc += __dmul_rn(lfo_value(V, mc.at(n)), step);
         }
     }
     acc = warp_sum(acc);
@@ -867,8 +951,7 @@ bank_generic_kernel(BankArgs a)
                 for (int j = 0; j < kItems; j++) {
                     double t_next = run_at(cr, cs, cn, n, j + 1);
                     tc[j] = t_prev;
-                    float m = lfo_value(V, run_at(mr, ms, mn, n, j));
-                    w[j] = __dmul_rn((double)m, __dadd_rn(t_next, -t_prev));
+                    w[j] = __dmul_rn(lfo_value(V, run_at(mr, ms, mn, n, j)), __dadd_rn(t_next, -t_prev));
                     local += w[j];
                     t_prev = t_next;
                 }

@@ -151,7 +151,26 @@ class _WaveOscillator(Oscillator):
         while self._fm_pos < n0:
             self._fm_prefix(self._fm_pos, min(_FM_SEEK_CHUNK, n0 - self._fm_pos), tb)
 
+    def _as_single_voice(self):
+        """FM by a plain waveform oscillator is one voice of the fused bank kernel: the modulator
+        is then evaluated in fp64 (or in closed form) inside that kernel instead of passing
+        through a float32 node buffer, whose rounding does not average out over a slow LFO."""
+        lfo = self._fm_lfo
+        if lfo is None or self._pwm_lfo is not None or type(lfo)._render_range is not _WaveOscillator._render_range:
+            return None
+        from .voicebank import VoiceBank
+        try:
+            return VoiceBank(self._samplerate).add(self, 1.0, 0.0)
+        except ValueError:
+            return None
+
     def _render_range(self, n0, count):
+        bank = self._as_single_voice()
+        if bank is not None:
+            mix = bank.render(count, start=n0)
+            out = D.empty(count, torch.float32)
+            C.call("sb_channel_f32", D.ptr(mix), 2, 0, count, D.ptr(out), D.stream())
+            return out
         tb = self._timebase()
         fmsum = None
         if self._fm_lfo is not None:

@@ -36,7 +36,7 @@ def test_struct_sizes_match_the_c_side():
     # sizes the kernels assume (sb_voice is copied to shared memory word by word)
     assert ctypes.sizeof(C.TimeSeg) == 24
     assert ctypes.sizeof(C.Envelope) == 80
-    assert ctypes.sizeof(C.Voice) == 152
+    assert ctypes.sizeof(C.Voice) == 168
     assert ctypes.sizeof(C.OscParams) == 56
 
 

@@ -84,6 +84,28 @@ def test_fm(cuda, cwave, mwave):
         assert_within_lsb(got, want, 1, "FM %s by %s" % (WAVES[cwave], WAVES[mwave]))
 
 
+def test_fm_by_a_composite_lfo_uses_the_general_scan_path(cuda):
+    """An LFO that is itself FM'd, or a filter graph, cannot be a bank voice: its samples go
+    through a float32 node buffer and the fp64 prefix scan (sb_fm_prefix_f64)."""
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    sr, n = 48000, 40000
+
+    def build(m):
+        inner = m.Sine(0.7, 0.3, samplerate=sr)
+        lfo = m.Sine(6.0, 0.04, 0.2, fm_lfo=inner, samplerate=sr)                       # nested FM
+        a = m.Sine(330.0, 0.8, 0.1, fm_lfo=lfo, samplerate=sr)
+        lfo2 = m.AmpModulationFilter(m.Triangle(3.0, 0.05, samplerate=sr), m.Sine(0.5, 0.5, bias=0.5, samplerate=sr))
+        b = m.Triangle(220.0, 0.7, fm_lfo=lfo2, samplerate=sr)                          # LFO is a filter graph
+        return a, b
+
+    for g, o in zip(build(sb), build(so)):
+        assert g._as_single_voice() is None
+        got = dev_pcm16(g.render(n))
+        want = pcm16_of(so.render_floats(o, n))
+        assert_within_lsb(got, want, 1, type(g).__name__ + " with a composite LFO")
+
+
 def test_fm_chunked_equals_one_shot(cuda):
     """blocks() renders in chunks and carries the FM prefix sum across them."""
     import synthesizer_b200 as sb

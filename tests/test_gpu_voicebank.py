@@ -42,7 +42,7 @@ def make_bank(nvoices, sr, seed, duration, waves=None, fm=True):
         bank.add(sb.EnvelopeFilter(car, a, d, s, sl, r), gl, gr)
         # the C struct stores gains and amplitudes as float32: give the oracle the same values
         f32 = lambda x: float(np.float32(x))
-        P[v] = [cw, cf, f32(amp), cph, 0.0, f32(cpw), mw, mf, f32(depth), mph, 0.0, a, d, s, sl, r, f32(gl), f32(gr)]
+        P[v] = [cw, cf, f32(amp), cph, 0.0, cpw, mw, mf, depth, mph, 0.0, a, d, s, sl, r, f32(gl), f32(gr)]
         if mw == 4:
             pass
     return bank, P
@@ -113,6 +113,36 @@ def test_fast_path_ten_minutes_in(cuda):
     want[0::2] = pcm16_of(left[start:])
     want[1::2] = pcm16_of(right[start:])
     assert_within_lsb(got, want, 1, "fast path at 10 minutes")
+
+
+@pytest.mark.parametrize("cw", [0, 1, 3])
+def test_fm_accuracy_sweep_full_scale(cuda, cw):
+    """One FULL-SCALE voice per (carrier f0, modulator f, FM depth) — from slow deep vibrato to
+    audio-rate FM with index 2 on a 10 kHz carrier — against the oracle.  The error budget of
+    +-1 LSB has to hold at full amplitude, on whichever kernel class the voice lands.
+    Frequencies are chosen incommensurate with the sample rate: with 3520 Hz x 2000 Hz at 48 kHz
+    the sawtooth's exact phase comes within 1e-13..1e-9 cycles of a wrap every 1200 samples, and
+    on which side such a sample falls is decided by the rounding noise of upstream's own fp64
+    recurrence — no other evaluation order can reproduce it."""
+    import itertools
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 48000, 48000
+    classes = {0: sb.Sine, 1: sb.Triangle, 3: sb.Sawtooth}
+    seen = set()
+    for f0, fm, d in itertools.product((55.1, 441.3, 3517.9, 9973.0), (0.1, 5.3, 109.7, 1999.3), (0.01, 0.5, 2.0)):
+        lfo = sb.Sine(fm, d, 0.3, samplerate=sr)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        seen.add(bank.count_generic())
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, fm, d, 0.3, 0.0)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        flips = err > 100          # a sawtooth wrap one sample early/late (fp64 noise of upstream's recurrence)
+        assert flips.sum() <= (3 if cw == 3 else 0), (f0, fm, d, int(flips.sum()))
+        assert err[~flips].max() < 0.9, "f0=%g fm=%g depth=%g: %.3f LSB" % (f0, fm, d, err[~flips].max())
+    assert seen == {0, 1}, "the sweep is meant to exercise both the fast and the generic kernels"
 
 
 def test_fast_and_generic_voices_share_a_group(cuda):
