@@ -73,19 +73,19 @@ __global__ void pcm16_bias_kernel(const int16_t *a, int64_t count, int bias, int
 
 __global__ void pcm16_fadeout_kernel(int16_t *buf, int64_t nsamples, double decrease)
 {
-    const double numsamples = (double)nsamples;
+    const double numsamples = (double)nsamples, rcp_n = __drcp_rn(numsamples);
     map16(buf, nullptr, buf, nsamples, [=](int64_t k, int x, int) {
         // int(sample * (1.0 - k*decrease/numsamples)), every operation rounded like CPython's
-        double f = __dsub_rn(1.0, __ddiv_rn(__dmul_rn((double)k, decrease), numsamples));
+        double f = __dsub_rn(1.0, div_by_known(__dmul_rn((double)k, decrease), numsamples, rcp_n));
         return __double2int_rz(__dmul_rn((double)x, f));
     });
 }
 
 __global__ void pcm16_fadein_kernel(int16_t *buf, int64_t nsamples, double increase, double start_volume)
 {
-    const double numsamples = (double)nsamples;
+    const double numsamples = (double)nsamples, rcp_n = __drcp_rn(numsamples);
     map16(buf, nullptr, buf, nsamples, [=](int64_t k, int x, int) {
-        double f = __dadd_rn(__ddiv_rn(__dmul_rn((double)k, increase), numsamples), start_volume);
+        double f = __dadd_rn(div_by_known(__dmul_rn((double)k, increase), numsamples, rcp_n), start_volume);
         return __double2int_rz(__dmul_rn((double)x, f));
     });
 }
@@ -160,61 +160,149 @@ __global__ void pcm32_to_16_kernel(const int32_t *__restrict__ in, int64_t count
 //   c = ceil(j*inrate/outrate) is the newest input frame read when j is emitted,
 //   d = c*outrate - j*inrate in [0, outrate) the interpolation counter,
 //   out = (int)((prev*d + cur*(outrate-d)) / outrate) on samples widened to 32 bits (<<16),
-//   then >>16.  The fp64 expression is evaluated exactly as audioop.c writes it.
-constexpr int kRcvIters = 16;            // a warp owns 32*kRcvIters consecutive output frames
+//   then >>16.
+//
+// The per-sample arithmetic in 32-bit integers.  With p, q the 16-bit samples and M = p*d +
+// q*(outrate-d) = q*outrate + (p-q)*d, audioop's numerator is 65536*M: below 2^53 for reduced
+// rates under 2^21, so its two fp64 products and their sum are exact, and the correctly rounded
+// quotient truncates like the exact one (a non-integer quotient is at least 1/outrate from the
+// next integer, far more than half an ulp).  Hence the value stored is
+//   trunc(65536*M / outrate) >> 16  =  floor(M / outrate)                       for M >= 0
+//                                   =  floor(M / outrate) + [0 < outrate - rem < outrate/65536]   for M < 0
+// (rem = M mod outrate; the second case is C's truncation toward zero followed by an arithmetic
+// shift), and floor(M / outrate) = q + floor((p-q)*d / outrate), a 17-bit quotient: one fp32
+// estimate (error < 0.02) and a remainder correction in wrapping 32-bit arithmetic.
+// tools/ratecv_formula_check.py replays exactly this against CPython's audioop.
+struct RcvRate {
+    uint32_t outr;       // reduced output rate (< 2^21)
+    uint32_t Qk, Rk;     // 32*inrate = Qk*outr + Rk: what 32 output frames advance (c, d) by
+    uint32_t lim;        // outr - ceil(outr/65536): remainders above it trigger the negative fix-up
+    float rcp;           // 1/outr
+};
 
-__global__ void pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t in_frames, int nch, int64_t inrate,
-                                    int64_t outrate, int64_t out_frames, int16_t *__restrict__ out)
+__device__ __forceinline__ RcvRate rcv_rate(int64_t inrate, int64_t outrate)
 {
-    // One 64-bit division locates the first frame of a warp's chunk; every other frame is placed
-    // relative to it with 32-bit arithmetic (the reduced rates are below 2^21, so lane*inrate
-    // fits easily).  Lanes map to consecutive output frames: coalesced stores, near-coalesced loads.
-    const int lane = threadIdx.x & 31;
-    const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const uint32_t inr = (uint32_t)inrate, outr32 = (uint32_t)outrate;
-    const double rcp_outr = 1.0 / (double)outrate;
-    const int64_t chunk = 32 * kRcvIters;
-    for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk) {
-        const int64_t num0 = jc * inrate;
-        int64_t c0 = (num0 + outrate - 1) / outrate;
-        uint32_t d0 = (uint32_t)(c0 * outrate - num0);
-        for (int it = 0; it < kRcvIters; it++) {
-            const int64_t j = jc + it * 32 + lane;
-            // this lane's frame: num = num_base + lane*inrate
-            const uint32_t k = (uint32_t)lane * inr;
-            const uint32_t adv = (k > d0) ? (k - d0 + outr32 - 1) / outr32 : 0u;
-            const int64_t c = c0 + adv;
-            const uint32_t d = d0 + adv * outr32 - k;
-            if (j < out_frames) {
-                for (int ch = 0; ch < nch; ch++) {
-                    int cur = (int)((uint32_t)(int32_t)in[c * nch + ch] << 16);
-                    int prev = (c > 0) ? (int)((uint32_t)(int32_t)in[(c - 1) * nch + ch] << 16) : 0;
-                    // prev*d + cur*(outrate-d) is below 2^52 in magnitude: audioop's two fp64
-                    // products and their sum are exact, so the integer sum converted once is the
-                    // same double; the division is the IEEE one audioop performs
-                    // same double; and because |quotient| < 2^31 while outrate < 2^21, the correctly
-                    // rounded fp64 quotient truncates to the same integer as the exact quotient
-                    // does (a non-integer quotient is at least 1/outrate > half an ulp away from
-                    // the next integer).  So: exact integer division, via a reciprocal estimate
-                    // and one correction step instead of the ~60-instruction fp64 divide.
-                    const long long num = (long long)prev * (long long)d + (long long)cur * (long long)(outr32 - d);
-                    const long long mag = num < 0 ? -num : num;
-                    long long q = (long long)__double2int_rz(__dmul_rn((double)mag, rcp_outr));
-                    const long long rem = mag - q * (long long)outr32;
-                    if (rem < 0) q -= 1;
-                    else if (rem >= (long long)outr32) q += 1;
-                    int o = (int)(num < 0 ? -q : q);
-                    out[j * nch + ch] = (int16_t)(o >> 16);
-                }
+    RcvRate rt;
+    rt.outr = (uint32_t)outrate;
+    const uint32_t K = 32u * (uint32_t)inrate;
+    rt.Qk = K / rt.outr;
+    rt.Rk = K - rt.Qk * rt.outr;
+    rt.lim = rt.outr - ((rt.outr + 65535u) >> 16);
+    rt.rcp = __frcp_rn((float)rt.outr);
+    return rt;
+}
+
+__device__ __forceinline__ int rcv_sample(int prev, int cur, uint32_t d, float w, const RcvRate &rt)
+{
+    const int diff = prev - cur;
+    // w = d/outr; the estimate is biased down by more than its error, so it is floor or floor-1
+    int est = __float2int_rd(__fmaf_rn((float)diff, w, -0.015625f));
+    uint32_t r = (uint32_t)diff * d - (uint32_t)est * rt.outr;       // in [0, 2*outr)
+    const bool hi = r >= rt.outr;
+    est += hi ? 1 : 0;
+    r -= hi ? rt.outr : 0u;
+    const int qf = cur + est;
+    return qf + ((qf < 0 && r > rt.lim) ? 1 : 0);
+}
+
+// A lane's ITERS frames j0, j0+32, ...: all loads first (2*ITERS in flight per lane), then the
+// arithmetic and the stores.  `pin` points at the lane's newest input frame for j0, `pout` at
+// output frame j0; everything inside is 32-bit offsets from those.  FULL = every frame exists.
+template <int NCH, bool VEC, int ITERS, bool FULL>
+__device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16_t *__restrict__ pout, int nleft,
+                                          bool first_is_frame0, uint32_t &crel, uint32_t &d, const RcvRate &rt)
+{
+    uint32_t dd[ITERS];
+    uint32_t wc[ITERS], wp[ITERS];              // raw current / previous frames (one or two int16)
+#pragma unroll
+    for (int it = 0; it < ITERS; it++) {
+        dd[it] = d;
+        wc[it] = wp[it] = 0;
+        if (FULL || it * 32 < nleft) {
+            // frame 0 of the output has no previous frame; its weight d is 0 there, any value does
+            const int back = (it == 0 && first_is_frame0) ? 0 : 1;
+            if (NCH == 1) {
+                wc[it] = (uint16_t)pin[crel];
+                wp[it] = (uint16_t)pin[(int)crel - back];
+            } else if (VEC) {
+                wc[it] = reinterpret_cast<const uint32_t *>(pin)[crel];
+                wp[it] = reinterpret_cast<const uint32_t *>(pin)[(int)crel - back];
+            } else {
+                wc[it] = (uint32_t)(uint16_t)pin[2 * crel] | ((uint32_t)(uint16_t)pin[2 * crel + 1] << 16);
+                const int pb = 2 * ((int)crel - back);
+                wp[it] = (uint32_t)(uint16_t)pin[pb] | ((uint32_t)(uint16_t)pin[pb + 1] << 16);
             }
-            // advance the base by 32 frames
-            const uint32_t kk = 32u * inr;
-            const uint32_t adv0 = (kk > d0) ? (kk - d0 + outr32 - 1) / outr32 : 0u;
-            c0 += adv0;
-            d0 = d0 + adv0 * outr32 - kk;
+        }
+        const bool inc = rt.Rk > d;
+        crel += rt.Qk + (inc ? 1u : 0u);
+        d = d - rt.Rk + (inc ? rt.outr : 0u);
+    }
+#pragma unroll
+    for (int it = 0; it < ITERS; it++) {
+        if (FULL || it * 32 < nleft) {
+            const float w = __fmul_rn((float)dd[it], rt.rcp);
+            const int o0 = rcv_sample((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], w, rt);
+            if (NCH == 1) {
+                pout[it * 32] = (int16_t)o0;
+            } else {
+                const int o1 = rcv_sample((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], w, rt);
+                if (VEC) reinterpret_cast<uint32_t *>(pout)[it * 32] = ((uint32_t)o0 & 0xffffu) | ((uint32_t)o1 << 16);
+                else pout[it * 64] = (int16_t)o0, pout[it * 64 + 1] = (int16_t)o1;
+            }
         }
     }
+}
+
+// A warp renders the 32*ITERS*BATCHES consecutive output frames starting at jc; lane l owns
+// frames jc + l + 32*k.  A lane's first frame is placed by one 64-bit division (fp64 estimate
+// plus correction); each further frame is 32 outputs on, which moves (c, d) by constants.
+// Lanes map to consecutive output frames: coalesced stores, near-coalesced loads.
+template <int NCH, bool VEC, int ITERS, int BATCHES>
+__device__ __forceinline__ void rcv_chunk(const int16_t *__restrict__ in, int16_t *__restrict__ out, int64_t jc,
+                                          int64_t out_frames, int64_t inrate, int64_t outrate, const RcvRate &rt,
+                                          double rcp64)
+{
+    const int64_t j0 = jc + (threadIdx.x & 31);
+    if (j0 >= out_frames) return;
+    const int64_t num = j0 * inrate;
+    int64_t q = __double2ll_rd(__dmul_rn((double)num, rcp64));     // floor(num/outrate) +-1
+    int64_t r = num - q * outrate;
+    if (r < 0) { q -= 1; r += outrate; }
+    else if (r >= outrate) { q += 1; r -= outrate; }
+    const int64_t c = q + (r > 0 ? 1 : 0);                         // ceil
+    uint32_t d = r > 0 ? (uint32_t)(outrate - r) : 0u;
+    const int16_t *pin = in + c * NCH;
+    int16_t *pout = out + j0 * NCH;
+    uint32_t crel = 0;
+    const bool full = jc + 32 * ITERS * BATCHES <= out_frames;     // warp-uniform
+    if (full) {
+#pragma unroll 1
+        for (int b = 0; b < BATCHES; b++)
+            rcv_batch<NCH, VEC, ITERS, true>(pin, pout + (int64_t)b * 32 * ITERS * NCH, 0, b == 0 && j0 == 0, crel, d, rt);
+    } else {
+        const int64_t left = out_frames - j0;
+        for (int b = 0; b < BATCHES && (int64_t)b * 32 * ITERS < left; b++)
+            rcv_batch<NCH, VEC, ITERS, false>(pin, pout + (int64_t)b * 32 * ITERS * NCH,
+                                              (int)min(left - (int64_t)b * 32 * ITERS, (int64_t)(32 * ITERS)),
+                                              b == 0 && j0 == 0, crel, d, rt);
+    }
+}
+
+constexpr int kRcvIters = 8;             // frames a lane has in flight
+constexpr int kRcvBatches = 4;           // a warp owns 32*kRcvIters*kRcvBatches consecutive output frames
+
+template <int NCH, bool VEC>
+__global__ void __launch_bounds__(kPBlock)
+pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t inrate, int64_t outrate, int64_t out_frames,
+                    int16_t *__restrict__ out)
+{
+    const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const RcvRate rt = rcv_rate(inrate, outrate);
+    const double rcp64 = 1.0 / (double)outrate;
+    const int64_t chunk = 32 * kRcvIters * kRcvBatches;
+    for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
+        rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
 }
 
 // Sample.mix_at for many sources, in order.  Thread <-> destination sample; the sources that
@@ -585,8 +673,16 @@ extern "C" int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nch
     // prev*d + cur*(outrate-d) must stay exact in fp64: |sample<<16| < 2^31, so outrate < 2^21
     SB_REQUIRE(outrate < (1 << 21) && inrate < (1 << 21), "sb_pcm16_ratecv: reduced rates must be below 2^21");
     int64_t out_frames = ((in_frames - 1) * outrate) / inrate + 1;
-    pcm16_ratecv_kernel<<<grid_for((out_frames + kRcvIters - 1) / kRcvIters, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
-        in_dev, in_frames, nchannels, inrate, outrate, out_frames, out_dev);
+    const int per_lane = kRcvIters * kRcvBatches;
+    const int grid = grid_for((out_frames + per_lane - 1) / per_lane, kPBlock, kPMaxBlocks);
+    const bool vec = (((uintptr_t)in_dev | (uintptr_t)out_dev) & 3) == 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nchannels == 1)
+        pcm16_ratecv_kernel<1, false><<<grid, kPBlock, 0, st>>>(in_dev, inrate, outrate, out_frames, out_dev);
+    else if (vec)
+        pcm16_ratecv_kernel<2, true><<<grid, kPBlock, 0, st>>>(in_dev, inrate, outrate, out_frames, out_dev);
+    else
+        pcm16_ratecv_kernel<2, false><<<grid, kPBlock, 0, st>>>(in_dev, inrate, outrate, out_frames, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -595,12 +691,15 @@ extern "C" int sb_pcm16_ratecv(const int16_t *in_dev, int64_t in_frames, int nch
 // Source s is in_pool[in_off[s] .. + in_frames[s]*nch) at rate inrate[s]; its output goes to
 // out_pool[out_off[s] .. + out_frames[s]*nch).  blockIdx.y walks the sources, blockIdx.x
 // (grid-stride) the output frames of a source.  Same arithmetic as pcm16_ratecv_kernel.
+constexpr int kRcvManyIters = 4;
+
 __global__ void __launch_bounds__(kPBlock)
 pcm16_ratecv_many_kernel(const int16_t *__restrict__ in_pool, const int64_t *__restrict__ in_off,
                          const int64_t *__restrict__ in_frames, const int64_t *__restrict__ inrate_red,
                          const int64_t *__restrict__ outrate_red, const int64_t *__restrict__ out_off,
                          const int64_t *__restrict__ out_frames, int64_t nsrc, int nch, int16_t *__restrict__ out_pool)
 {
+    const bool pools_aligned = (((uintptr_t)in_pool | (uintptr_t)out_pool) & 3) == 0;
     for (int64_t s = blockIdx.y; s < nsrc; s += gridDim.y) {
         const int16_t *in = in_pool + in_off[s];
         int16_t *out = out_pool + out_off[s];
@@ -610,23 +709,17 @@ pcm16_ratecv_many_kernel(const int16_t *__restrict__ in_pool, const int64_t *__r
                 out[i] = in[i];
             continue;
         }
-        const double rcp = 1.0 / (double)outr;
-        for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nout; j += (int64_t)gridDim.x * blockDim.x) {
-            const int64_t num = j * inr;
-            const int64_t c = (num + outr - 1) / outr;
-            const int64_t d = c * outr - num;
-            for (int ch = 0; ch < nch; ch++) {
-                const long long cur = (long long)(int)((uint32_t)(int32_t)in[c * nch + ch] << 16);
-                const long long prev = (c > 0) ? (long long)(int)((uint32_t)(int32_t)in[(c - 1) * nch + ch] << 16) : 0;
-                const long long sum = prev * d + cur * (outr - d);
-                const long long mag = sum < 0 ? -sum : sum;
-                long long q = (long long)__double2ll_rz(__dmul_rn((double)mag, rcp));
-                const long long rem = mag - q * outr;
-                if (rem < 0) q -= 1;
-                else if (rem >= outr) q += 1;
-                const int o = (int)(sum < 0 ? -q : q);
-                out[j * nch + ch] = (int16_t)(o >> 16);
-            }
+        // the block's warps take 32*kRcvManyIters-frame chunks of this source in turn
+        const RcvRate rt = rcv_rate(inr, outr);
+        const double rcp64 = 1.0 / (double)outr;
+        const int64_t chunk = 32 * kRcvManyIters;
+        const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+        const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+        const bool vec = ((in_off[s] | out_off[s]) & 1) == 0 && pools_aligned;
+        for (int64_t jc = warp_id * chunk; jc < nout; jc += nwarps * chunk) {
+            if (nch == 1) rcv_chunk<1, false, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else if (vec) rcv_chunk<2, true, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else rcv_chunk<2, false, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
         }
     }
 }
@@ -640,7 +733,7 @@ extern "C" int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *i
     if (!nsrc || !max_out_frames) return SB_OK;
     SB_REQUIRE(in_pool_dev && in_off_dev && in_frames_dev && inrate_red_dev && outrate_red_dev && out_off_dev &&
                    out_frames_dev && out_pool_dev, "sb_pcm16_ratecv_many: null pointer");
-    dim3 grid((unsigned)grid_for(max_out_frames, kPBlock, 64), (unsigned)(nsrc < 65535 ? nsrc : 65535));
+    dim3 grid((unsigned)grid_for((max_out_frames + kRcvManyIters - 1) / kRcvManyIters, kPBlock, 64), (unsigned)(nsrc < 65535 ? nsrc : 65535));
     pcm16_ratecv_many_kernel<<<grid, kPBlock, 0, (cudaStream_t)stream>>>(
         in_pool_dev, in_off_dev, in_frames_dev, inrate_red_dev, outrate_red_dev, out_off_dev, out_frames_dev, nsrc,
         nchannels, out_pool_dev);

@@ -142,10 +142,10 @@ extern "C" int sb_pcm32_fadeout(int32_t *buf_dev, int64_t nsamples, double targe
 {
     SB_REQUIRE(buf_dev && nsamples >= 0, "sb_pcm32_fadeout: bad arguments");
     if (!nsamples) return SB_OK;
-    const double decrease = 1.0 - target_volume, numsamples = (double)nsamples;
+    const double decrease = 1.0 - target_volume, numsamples = (double)nsamples, rcp_n = 1.0 / numsamples;
     LAUNCH_MAP32((const int32_t *)buf_dev, (const int32_t *)nullptr, buf_dev, nsamples, stream,
                  [=] __device__(int64_t k, int x, int) {
-                     const double f = __dsub_rn(1.0, __ddiv_rn(__dmul_rn((double)k, decrease), numsamples));
+                     const double f = __dsub_rn(1.0, div_by_known(__dmul_rn((double)k, decrease), numsamples, rcp_n));
                      return __double2int_rz(__dmul_rn((double)x, f));
                  });
     return SB_OK;
@@ -155,10 +155,10 @@ extern "C" int sb_pcm32_fadein(int32_t *buf_dev, int64_t nsamples, double start_
 {
     SB_REQUIRE(buf_dev && nsamples >= 0, "sb_pcm32_fadein: bad arguments");
     if (!nsamples) return SB_OK;
-    const double increase = 1.0 - start_volume, numsamples = (double)nsamples;
+    const double increase = 1.0 - start_volume, numsamples = (double)nsamples, rcp_n = 1.0 / numsamples;
     LAUNCH_MAP32((const int32_t *)buf_dev, (const int32_t *)nullptr, buf_dev, nsamples, stream,
                  [=] __device__(int64_t k, int x, int) {
-                     const double f = __dadd_rn(__ddiv_rn(__dmul_rn((double)k, increase), numsamples), start_volume);
+                     const double f = __dadd_rn(div_by_known(__dmul_rn((double)k, increase), numsamples, rcp_n), start_volume);
                      return __double2int_rz(__dmul_rn((double)x, f));
                  });
     return SB_OK;

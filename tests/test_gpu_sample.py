@@ -99,11 +99,39 @@ def test_mix_at_many_equals_sequential_with_saturation(cuda):
 
 
 @pytest.mark.parametrize("rates", [(44100, 48000), (48000, 44100), (22050, 48000), (48000, 8000),
-                                   (44100, 44101), (8000, 96000), (11025, 44100)])
+                                   (44100, 44101), (8000, 96000), (11025, 44100), (96000, 44100),
+                                   (1999999, 2000000), (2000000, 1999999), (48000, 16), (16, 1600),
+                                   (65537, 65536), (1048573, 1048576)])
 @pytest.mark.parametrize("ch", [1, 2])
 def test_resample(cuda, rates, ch):
     g, o = _pair(_rand(20011 * ch, 12), sr=rates[0], ch=ch)
     _same(g.resample(rates[1]), o.resample(rates[1]), "resample %s" % (rates,))
+    # small and extreme values: negative sums a hair below an integer, where C's truncation
+    # toward zero followed by >>16 differs from a plain floor
+    rng = np.random.default_rng(5)
+    for data in (rng.integers(-3, 4, 20011 * ch), rng.choice([-32768, 32767, -1, 0, 1], 20011 * ch)):
+        g, o = _pair(data.astype(np.int16), sr=rates[0], ch=ch)
+        _same(g.resample(rates[1]), o.resample(rates[1]), "resample %s small/extreme values" % (rates,))
+
+
+@pytest.mark.parametrize("in_off,out_off", [(0, 0), (1, 0), (0, 1), (1, 1), (3, 2)])
+def test_ratecv_views_at_odd_offsets(cuda, in_off, out_off):
+    """Stereo frames that start on a 2-byte (not 4-byte) boundary take the scalar load/store
+    path; lengths that end inside a warp's chunk take the guarded path.  Straight through the C ABI."""
+    import torch
+    from oracle import coracle as co
+    from synthesizer_b200 import _cabi as C, _device as D
+    for nin in (1, 2, 31, 257, 8191, 8192 * 3 + 5):
+        src = _rand(2 * nin + 8, 50 + nin)
+        dsrc = torch.from_numpy(src).cuda()
+        want = co.pcm16_ratecv(src[in_off:in_off + 2 * nin], 2, 44100, 48000)
+        nout = C.lib.sb_pcm16_ratecv_frames(nin, 44100, 48000)
+        assert want.size == 2 * nout
+        out = torch.full((2 * nout + 8,), 12345, dtype=torch.int16, device="cuda")
+        C.call("sb_pcm16_ratecv", D.ptr(dsrc[in_off:]), nin, 2, 44100, 48000, D.ptr(out[out_off:]), D.stream())
+        got = out.cpu().numpy()
+        assert np.array_equal(got[out_off:out_off + 2 * nout], want), (nin, in_off, out_off)
+        assert (got[:out_off] == 12345).all() and (got[out_off + 2 * nout:] == 12345).all(), "wrote outside"
 
 
 def test_speed(cuda):
