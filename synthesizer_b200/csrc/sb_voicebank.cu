@@ -1,29 +1,34 @@
 // The fused hot path: a bank of FM voices with ADSR, mixed to stereo.
 //
 // Decomposition: work unit = (group of voices) x (span of consecutive frames), one WARP per
-// unit; warps never synchronise with each other.  A warp walks its span in sub-tiles of 256
-// frames (8 consecutive frames per lane) and, for every voice of its group, evaluates
+// unit; warps never synchronise with each other.  A warp walks its span in sub-tiles of 512
+// frames (16 consecutive frames per lane) and, for every voice of its group, evaluates
 // modulator -> FM prefix sum -> carrier -> ADSR -> pan, accumulating the voice sum in
-// registers; one coalesced 128-bit store per lane pair of frames writes the group's partial
-// mix, and a fold kernel sums the groups.
+// registers; coalesced 128-bit stores write the group's partial mix, and a fold kernel sums
+// the groups.
 //
 // Two voice classes share that decomposition:
 //
-//  FAST    continuous carrier (Sine, Triangle) with no FM or a Sine modulator.  Everything
-//          that needs fp64 is done once per lane per sub-tile (exact time base, phase base
-//          reduced mod one turn); the 8 samples of the run advance in fp32 from that base and
-//          use the SFU sine.  The FM prefix sum has a closed form for a Sine modulator
-//          (sum of sin over an arithmetic progression), evaluated in fp64 at every sub-tile
-//          start ("anchor") from a per-(voice, time-base segment) table; inside the sub-tile
-//          an fp32 warp scan supplies the rest.  No pre-pass over the samples, no running
-//          carry, and float error cannot build up over more than 256 frames.
+//  FAST    any of the five carriers with no FM or a Sine modulator of moderate gain.
+//          Everything that needs fp64 is done once per lane per 16-frame run: the exact time
+//          base, the carrier's phase base reduced mod one turn, and the FM sum ahead of the
+//          run, which has a closed form for a Sine modulator (sum of sin over an arithmetic
+//          progression).  That closed form needs cos/sin of the modulator's phase at the
+//          run's first frame; they come from a per-(voice, sub-tile) fp64 anchor rotated by
+//          a per-(voice, lane) fp64 table, four fp64 multiply-adds instead of a range
+//          reduction and a polynomial.  The 16 samples of the run then advance in fp32: the
+//          modulator by the two-term recurrence s += d, d -= k*s (no SFU work), the carrier
+//          by the SFU sine, in packed fp32x2 over frame pairs (q, q+8).  No pre-pass over
+//          the samples, no running carry, and fp32 error cannot build up over more than 16
+//          frames.  Square / Sawtooth / Pulse carriers re-evaluate the few samples within a
+//          guard band of an edge exactly in fp64.
 //
-//  GENERIC anything else (Square/Sawtooth/Pulse carriers, whose edges must fall on exactly
-//          the sample upstream's fp64 arithmetic puts them on; non-sine modulators).  Phase
-//          arithmetic per sample in explicitly rounded fp64, FM prefix by fp64 warp scan with
-//          a running carry that starts from per-(voice, span) sums computed by a pre-pass.
+//  GENERIC anything else (non-sine modulators, FM gain above kFastMaxFmGain, carriers with a
+//          negative start phase).  Phase arithmetic per sample in explicitly rounded fp64,
+//          FM prefix by fp64 warp scan with a running carry that starts from per-(voice,
+//          span) sums computed by a pre-pass.
 //
-// The generic kernel runs after the fast one and adds into the same partial mixes.
+// The generic kernel runs after the fast ones and adds into the same partial mixes.
 #include "sb_common.cuh"
 
 namespace sb {
@@ -49,18 +54,8 @@ constexpr int kFastMaxSub = FAST_MAX_SUB;    // fast kernel: sub-tiles per span 
                                   3/4/5/6/7/8 CTAs -> 3.84/3.84/3.50/3.21/3.13/3.29 ms; with 16 frames per lane:
                                   4/5/6 CTAs -> 2.65/2.63/2.76 ms */
 #endif
-
-#ifndef FAST_LANE_ANCHOR
-#define FAST_LANE_ANCHOR 1
-#endif
-#ifndef FAST_SCAN_F64
-#define FAST_SCAN_F64 0
-#endif
 #ifndef FAST_MAX_FM_GAIN
 #define FAST_MAX_FM_GAIN 1.5
-#endif
-#ifndef FAST_ROTATE_MODULATOR
-#define FAST_ROTATE_MODULATOR 1
 #endif
 #ifndef FAST_PAIR_VOICES
 #define FAST_PAIR_VOICES 1     /* measured on B200 at 7 CTAs/SM: 3.12 ms without, 2.96 ms with */
@@ -81,38 +76,44 @@ constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer t
                                              // discontinuity are re-evaluated exactly in fp64
 
 // Per-voice constants of the fast path, derived once per render by bank_prepare_kernel.
-// The first five 128-bit words are everything the per-sample loop needs and are read with five
-// vector loads per (voice, sub-tile); the rest is the envelope description, used by the
-// per-span precompute and by the rare sub-tile that straddles an envelope segment.
+// The first six 128-bit words are everything the per-run set-up and the per-sample loop need
+// (values used by packed fp32x2 instructions are stored as pairs); the rest is used by the
+// per-span precompute and by the rare sub-tile that straddles an envelope corner.
+// H = kFItems/2 frames is half a run; w the modulator's phase step per frame; "scaled" means
+// multiplied by gd, the carrier phase per unit of the modulator's running sum.
 struct alignas(16) FastVoice {
-    double2 mod;             // fm, pcm: modulator frequency and start phase (radians)
     double2 car;             // f0b, pc0: carrier frequency * (1 + modulator bias), start phase
-    double gd;               // carrier phase per unit of sum(sin(theta_k)): f0 * inc_c * depth
     int flags;
-    int pad0;
-    float4 inc;              // wm, wm, wc, wc: fp32 phase steps per frame fm*inc_rad, f0b*inc_c (pairs for fp32x2)
-    float4 g2;               // gdf, gdf, 4wm, 4wc: gd in fp32 (pair); phase steps of four frames
-    float4 gain;             // aL, aL, aR, aR: c_amp*gain (as pairs for the packed fp32x2 FMAs)
-    float4 rot;              // cos(wm), cos(wm), sin(wm), sin(wm): one-frame rotation of the modulator phase
-    float2 rotH;             // cos(H*wm), sin(H*wm): rotation by half a run (H frames)
-    float2 pad2;
-    double half_w;           // half a modulator phase step, fm * inc_rad / 2 (radians)
+    int vidx;                // the voice's index in the bank (rows of the FM tables)
+    float Hwc;               // H carrier steps
+    float pw;                // Pulse carriers: the (clamped) pulse width
+    float4 stepk;            // wc, wc, -k, -k: carrier phase step; k = 4 sin^2(w/2)
+    float4 gain;             // aL, aL, aR, aR: c_amp*gain
+    float4 ini;              // k/2, k/2, sin w, sin w: first backward difference of the modulator recurrence
+    float4 half;             // cos(H w), sin(H w), P, Q: second half-run start; sum of the first H sines = s0*P + c0*Q
+    double2 mod;             // fm, pcm: modulator frequency and start phase (radians)
+    double gd;               // carrier phase per unit of sum(sin(theta_k)): f0 * inc_c * depth
     double pw64;             // Pulse carriers: the (clamped) pulse width in fp64, for the exact re-evaluation
     long long n_a, n_d, n_s, n_r;
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
-    float pw;                // Pulse carriers: the (clamped) pulse width
+    float pad;
 };
-static_assert(sizeof(FastVoice) == 208, "FastVoice layout");
+static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
 
-// Per-(voice, sub-tile) record precomputed at the start of a span, one 128-bit word:
-// the closed-form FM sum at the sub-tile's first frame and the ADSR line over the sub-tile
-// (e(i) = e_sub + i*de), or e_sub = kEnvSilent / kEnvSlow.
-struct alignas(16) SubRec {
-    double anchor;
-    float e_sub, de;
+// Closed-form FM table entry per (voice, modulator time-base segment b), step w_b = fm*step_b:
+//   gd * sum_{k<n} sin(theta_k) = A - Cc*(gd cos theta_n) - (gd sin theta_n)/2      (n in segment b)
+// with Cc = cot(w_b/2)/2 and A = gd*(sum over earlier segments + C_b cos(theta_b - w_b/2)),
+// C_b = 1/(2 sin(w_b/2)).  dw = w_b - w: how far the segment's phase step is from the nominal
+// one the lane table is built with (|dw/w| < 1e-8; first-order correction in the kernel).
+struct alignas(16) FmSeg {
+    double A, Cc, dw, pad;
 };
+
+// Per-(voice, sub-tile) records precomputed at the start of a span:
+//   anchor = gd * (cos, sin)(theta) at the sub-tile's first frame, fp64;
+//   env    = the ADSR line over the sub-tile (e(i) = e_sub + i*de), or e_sub = kEnvSilent / kEnvSlow.
 constexpr float kEnvSilent = -1.0f;          // after the release: the voice adds nothing here
 constexpr float kEnvSlow = -2.0f;            // an envelope corner falls inside: per-sample ADSR
 
@@ -128,7 +129,8 @@ struct BankArgs {
     double *carry;        // [nvoices][nprefix + nspans] per-span LFO sums of generic voices (pre-pass), or null
     int nprefix;          // spans of span_len frames covering [0, n0): the FM sum before this render
     FastVoice *fastv;     // [nvoices]
-    double2 *tab;         // [nvoices][nsegs_rad]: closed-form table (A, C) per modulator segment
+    FmSeg *tab;           // [nvoices][nsegs_rad]: closed-form FM table per modulator segment
+    double2 *lanetab;     // [nvoices][32]: (cos, sin)(lane * kFItems * w), the rotation from a sub-tile's anchor
     int fast_nspans;
     int64_t fast_span_len;
     float *out;           // [ngroups][stride] partial mixes (or the mix itself if ngroups==1)
@@ -184,6 +186,26 @@ __device__ __forceinline__ double cos_reduced(double r)
     return fma(p, x, 1.0);
 }
 
+// sin(r) for |r| <= pi + small, fp64 Taylor to r^27 (error < 1e-13)
+__device__ __forceinline__ double sin_reduced(double r)
+{
+    const double x = r * r;
+    double p = -1.0 / 10888869450418352160768000000.0;         // -1/27!
+    p = fma(p, x, 1.0 / 15511210043330985984000000.0);         // 1/25!
+    p = fma(p, x, -1.0 / 25852016738884976640000.0);           // -1/23!
+    p = fma(p, x, 1.0 / 51090942171709440000.0);               // 1/21!
+    p = fma(p, x, -1.0 / 121645100408832000.0);                // -1/19!
+    p = fma(p, x, 1.0 / 355687428096000.0);                    // 1/17!
+    p = fma(p, x, -1.0 / 1307674368000.0);                     // -1/15!
+    p = fma(p, x, 1.0 / 6227020800.0);                         // 1/13!
+    p = fma(p, x, -1.0 / 39916800.0);                          // -1/11!
+    p = fma(p, x, 1.0 / 362880.0);                             // 1/9!
+    p = fma(p, x, -1.0 / 5040.0);                              // -1/7!
+    p = fma(p, x, 1.0 / 120.0);                                // 1/5!
+    p = fma(p, x, -1.0 / 6.0);
+    return fma(p * x, r, r);
+}
+
 __device__ __forceinline__ double reduce_two_pi(double x)
 {
     double k = rint(x * kInvTwoPi);
@@ -197,16 +219,17 @@ __global__ void bank_prepare_kernel(BankArgs a)
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= a.nvoices) return;
     const sb_voice V = a.voices[v];
+    constexpr int H = kFItems / 2;
     FastVoice F;
     F.flags = 0;
-    F.pad0 = 0;
+    F.vidx = v;
+    F.pad = 0.0f;
     const bool fast = voice_is_fast(V, a.samplerate);
     const bool tri = (V.c_wave != SB_WAVE_SINE);         // phase counted in cycles (all but Sine)
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
     F.pw = (float)clamp_pulsewidth((double)V.c_pw);
     F.pw64 = clamp_pulsewidth((double)V.c_pw);
-    F.half_w = 0.0;
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
     const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
@@ -215,17 +238,19 @@ __global__ void bank_prepare_kernel(BankArgs a)
     F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
     F.gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
     F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
-    const float wm = (float)(fm * inc_rad), wc = (float)(f0b * inc_c);
-    F.inc = make_float4(wm, wm, wc, wc);
-    F.g2 = make_float4((float)F.gd, (float)F.gd, (float)(kFItems / 2) * wm, (float)(kFItems / 2) * wc);
+    const double w = fm * inc_rad;                        // nominal modulator phase step
     {
-        const double w = fm * inc_rad;
-        F.rot = make_float4((float)cos(w), (float)cos(w), (float)sin(w), (float)sin(w));
-        const double wh = w * (double)(kFItems / 2);
-        F.rotH = make_float2((float)cos(wh), (float)sin(wh));
-        F.pad2 = make_float2(0.0f, 0.0f);
-        F.half_w = 0.5 * w;
-
+        const float wc = (float)(f0b * inc_c);
+        const double sh = sin(0.5 * w);
+        const float k = (float)(4.0 * sh * sh);
+        F.stepk = make_float4(wc, wc, -k, -k);
+        F.Hwc = (float)((double)H * f0b * inc_c);
+        const float hk = (float)(2.0 * sh * sh), sw = (float)sin(w);
+        F.ini = make_float4(hk, hk, sw, sw);
+        // sum_{j<H} sin(theta + j w) = sin(theta + (H-1) w/2) * sin(H w/2)/sin(w/2)
+        const double R = (fabs(sh) > 1e-300) ? sin(0.5 * (double)H * w) / sh : (double)H;
+        const double mid = 0.5 * (double)(H - 1) * w;
+        F.half = make_float4((float)cos((double)H * w), (float)sin((double)H * w), (float)(cos(mid) * R), (float)(sin(mid) * R));
     }
     F.bL = V.c_bias * V.gain_l;
     F.bR = V.c_bias * V.gain_r;
@@ -244,25 +269,37 @@ __global__ void bank_prepare_kernel(BankArgs a)
     if (fast && has_mod) {
         // Closed form of sum_{k<n} sin(theta_k), theta_k = fm*t(k) + pcm, t piecewise linear:
         // inside segment b (start n_b, t_b, step_b): theta_k = theta_b + (k-n_b)*w_b and
-        //   sum_{k=n_b}^{n-1} sin(theta_k) = [cos(theta_b - w_b/2) - cos(theta_b + (n-n_b-1/2) w_b)] / (2 sin(w_b/2)).
-        // tab[b] = (A_b, C_b) with C_b = 1/(2 sin(w_b/2)) and A_b = (sum over earlier segments)
-        // + C_b cos(theta_b - w_b/2), so the sum up to n in segment b is A_b - C_b cos(fm*(t(n) - step_b/2) + pcm).
-        double2 *row = a.tab + (int64_t)v * a.nsegs_rad;
+        //   sum_{k=n_b}^{n-1} sin(theta_k) = [cos(theta_b - w_b/2) - cos(theta_n - w_b/2)] / (2 sin(w_b/2)),
+        // so with C_b = 1/(2 sin(w_b/2)) and S_b = (sum over earlier segments) + C_b cos(theta_b - w_b/2)
+        // the sum up to n in segment b is S_b - C_b cos(theta_n - w_b/2)
+        //                               = S_b - C_b cos(w_b/2) cos(theta_n) - sin(theta_n)/2.
+        FmSeg *row = a.tab + (int64_t)v * a.nsegs_rad;
         double before = 0.0;
         for (int b = 0; b < a.nsegs_rad; b++) {
             const sb_time_seg s = a.tb_rad[b];
-            const double w = fm * s.step;
-            const double half = 0.5 * w;
+            const double wb = fm * s.step;
+            const double half = 0.5 * wb;
             const double sh = sin(half);
-            double C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
+            const double C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
             const double th_lo = fm * (s.t_start - 0.5 * s.step) + pcm;
-            double A = before + C * cos(th_lo);
-            row[b] = make_double2(A, C);
+            const double S = before + C * cos(th_lo);
+            FmSeg e;
+            e.A = F.gd * S;
+            e.Cc = C * cos(half);
+            e.dw = fm * (s.step - inc_rad);
+            e.pad = 0.0;
+            row[b] = e;
             if (b + 1 < a.nsegs_rad) {
                 const double len = (double)(a.tb_rad[b + 1].n_start - s.n_start);
                 const double th_hi = fm * (s.t_start + (len - 0.5) * s.step) + pcm;
-                before = (C != 0.0) ? A - C * cos(th_hi) : before + len * sin(fm * s.t_start + pcm);
+                before = (C != 0.0) ? S - C * cos(th_hi) : before + len * sin(fm * s.t_start + pcm);
             }
+        }
+        // rotation from a sub-tile's first frame to each lane's first frame, at the nominal step
+        double2 *lt = a.lanetab + (int64_t)v * 32;
+        for (int l = 0; l < 32; l++) {
+            const double ang = reduce_two_pi((double)(l * kFItems) * w);
+            lt[l] = make_double2(cos(ang), sin(ang));
         }
     }
 }
@@ -338,7 +375,8 @@ __device__ __forceinline__ double warp_scan_incl_f64(double v)
 struct FastCtx {
     const sb_time_seg *s_cyc;
     int nsegs_cyc;
-    const double2 *tab;      // [nvoices][nsegs_rad] closed-form FM table (A, C)
+    const FmSeg *tab;        // [nvoices][nsegs_rad] closed-form FM table
+    const double2 *lanetab;  // [nvoices][32] anchor -> lane rotations
     int nsegs_rad;
 };
 
@@ -376,99 +414,66 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
     return f < pw ? 1.0f : -1.0f;                          // tt % 1.0 < pulsewidth
 }
 
-// One voice over one lane's run of kItems frames.  MOD: Sine modulator present.  WAVE: the
+// One voice over one lane's run of kFItems frames.  MOD: Sine modulator present.  WAVE: the
 // carrier.  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
+//
 // Frame pairing: the packed fp32x2 operations (Blackwell FFMA2/FADD2/FMUL2) work on frames
-// (q, q+4) of the lane's run of 8, so that the exclusive sums of the modulator advance through
-// both halves of the run in one dependent chain of 4 packed adds (the second half's offset
-// joins the carrier phase later).  accL2[q] = left-channel sums of frames (q, q+4), accR2[q]
-// the right-channel ones.
+// (q, q+H) of the lane's run, H = kFItems/2.  accL2[q] = left-channel sums of frames (q, q+H),
+// accR2[q] the right-channel ones.
+//
+// Per pair and step, with P the carrier phase (within a turn, fp32), s = gd*sin(theta) the FM
+// increment and d its backward difference:
+//     value = shape(P);   acc += value * e * gain;
+//     P += wc + s;        d -= k*s;   s += d;        e += de
+// The recurrence for s is sin(theta+w) = 2cos(w) sin(theta) - sin(theta-w) written with
+// k = 2 - 2cos(w) = 4 sin^2(w/2) so that slow modulators lose nothing to cancellation.
+//
+// Set-up (fp64, once per run): gd*(cos, sin)(theta) at the lane's first frame by rotating the
+// sub-tile's anchor with the lane table (plus the first-order term for the time-base segment's
+// own step); the FM sum ahead of the run from the closed form; the carrier phase base.
+//
 // Square / Sawtooth / Pulse carriers: their value is evaluated in fp32 like the others, which
 // is exact (+-1, or a continuous ramp) unless the phase sits within kEdgeGuard cycles of a
 // discontinuity; those few samples are redone in fp64 exactly as upstream forms the phase, so
 // every edge lands on the sample upstream puts it on.
 template <bool MOD, int WAVE, bool RARE>
-__device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec rec, const double Tr0,
-                                               const double Tc0, const int seg_r, const float lane8,
-                                               const int64_t n, const FastCtx ctx,
-                                               float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
+__device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2 anc, const float2 env,
+                                               const double Tr0, const double Tc0, const int seg_r,
+                                               const double lane16d, const float lane8, const int64_t n,
+                                               const FastCtx ctx, float2 (&accL2)[kFItems / 2],
+                                               float2 (&accR2)[kFItems / 2])
 {
     constexpr int H = kFItems / 2;
     constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
     constexpr bool EDGES = (WAVE >= SB_WAVE_SQUARE);
     const double2 car = F.car;
-    const float4 inc = F.inc;               // wm, wm, wc, wc
-    const float4 g2 = F.g2;                 // gdf, gdf, 4wm, 4wc
+    const float4 stepk = F.stepk;           // wc, wc, -k, -k
     const float4 gain = F.gain;             // aL, aL, aR, aR
-    float2 ps[H];                           // exclusive sums within each half: (frames q, q+4)
-    float2 base;                            // carrier phase of frames (q, q+4), fp32, within a turn
     double B = fma(car.x, CYC ? Tc0 : Tr0, car.y);
-    float half_gd = 0.0f;                   // gd * (sum of the first half's sines)
-    double before = 0.0;                    // FM sum ahead of this lane's run
-    float half_sum = 0.0f;
+    double gbefore = 0.0;                   // gd * (FM sum ahead of this lane's run)
+    float2 sn = make_float2(0.0f, 0.0f), dl = make_float2(0.0f, 0.0f);
+    float half_sum = 0.0f;                  // gd * (sum of the first half-run's sines)
     if (MOD) {
-        // modulator: 8 sines from one fp64 phase base; exclusive sums feed the FM prefix
-        const double2 mod = F.mod;
-        const double r0 = reduce_two_pi_fast(fma(mod.x, Tr0, mod.y));
-        const float th0 = (float)r0;
-#if FAST_LANE_ANCHOR
-        // FM sum ahead of this lane's first frame, exactly: the closed form A - C*cos(theta - w/2)
-        // of the modulator's time-base segment, evaluated in fp64 per lane.  No warp scan, no
-        // dependence between lanes, and fp32 / SFU error cannot build up over more than the
-        // 16 frames of the run.
-        const double2 ac = ctx.tab[(int64_t)F.pad0 * ctx.nsegs_rad + seg_r];
-        before = fma(-ac.y, cos_reduced(r0 - F.half_w), ac.x);
-#endif
-#if FAST_ROTATE_MODULATOR
-        // sin/cos of the two half-run start phases from the SFU, then the other frames by
-        // rotating (sin, cos) one modulator step at a time: 4 packed FMAs per frame pair and no
-        // SFU work, against 2 multiplies + 2 SFU sines (error ~1e-7 per step, as good as the SFU's)
-        // (the second half-run's start is itself a rotation of the first by H steps, so the SFU
-        // only ever sees arguments inside [-pi, pi])
-        const float s0 = __sinf(th0), c0 = __cosf(th0);
-        const float4 rot = F.rot;
-        const float2 rotH = F.rotH;
-        float2 sn = make_float2(s0, fmaf(c0, rotH.y, s0 * rotH.x));
-        float2 cs = make_float2(c0, fmaf(-s0, rotH.y, c0 * rotH.x));
-        const float2 cw2 = make_float2(rot.x, rot.y), sw2 = make_float2(rot.z, rot.w);
-        const float2 nsw2 = make_float2(-rot.z, -rot.w);
-        float2 run = make_float2(0.0f, 0.0f);
-#pragma unroll
-        for (int q = 0; q < H; q++) {
-            ps[q] = run;
-            run = __fadd2_rn(run, sn);
-            if (q + 1 < H) {
-                const float2 sn1 = __ffma2_rn(cs, sw2, __fmul2_rn(sn, cw2));
-                cs = __ffma2_rn(sn, nsw2, __fmul2_rn(cs, cw2));
-                sn = sn1;
-            }
-        }
-#else
-        float2 th = make_float2(th0, th0 + g2.z);
-        const float2 step = make_float2(inc.x, inc.y);
-        float2 run = make_float2(0.0f, 0.0f);
-#pragma unroll
-        for (int q = 0; q < H; q++) {
-            ps[q] = run;
-            run = __fadd2_rn(run, make_float2(__sinf(th.x), __sinf(th.y)));
-            th = __fadd2_rn(th, step);
-        }
-#endif
-        // exclusive prefix over the lanes in fp64: the partial sums reach the hundreds when the
-        // LFO is slow against the 512-frame sub-tile, where an fp32 scan would lose ~3e-5 —
-        // times gd that was the dominant error of this path (tools/accuracy_sweep.py)
-#if FAST_LANE_ANCHOR
-        // (before was set above)
-#elif FAST_SCAN_F64
-        const double total = (double)run.x + (double)run.y;
-        before = rec.anchor + (warp_scan_incl_f64(total) - total);
-#else
-        const float total = run.x + run.y;
-        before = rec.anchor + (double)(warp_scan_incl_ptx(total) - total);
-#endif
-        B = fma(F.gd, before, B);
-        half_gd = g2.x * run.x;
-        half_sum = run.x;
+        const int lane = threadIdx.x & 31;
+        const double2 L = ctx.lanetab[(int64_t)F.vidx * 32 + lane];
+        const FmSeg fs = ctx.tab[(int64_t)F.vidx * ctx.nsegs_rad + seg_r];
+        // gd*(cos, sin) of the modulator phase at this lane's first frame
+        const double cl = fma(-anc.y, L.y, anc.x * L.x);
+        const double sl = fma(anc.x, L.y, anc.y * L.x);
+        // closed form, with theta advanced by the small angle lane16*dw to first order
+        double u = fma(-fs.Cc, cl, fs.A);
+        u = fma(-0.5, sl, u);
+        const double vv = fma(fs.Cc, sl, -0.5 * cl);
+        gbefore = fma(lane16d * fs.dw, vv, u);
+        B += gbefore;
+        const float s0 = (float)sl, c0 = (float)cl;
+        const float4 hf = F.half;           // cos(H w), sin(H w), P, Q
+        const float4 ini = F.ini;           // k/2, k/2, sin w, sin w
+        const float sH = fmaf(c0, hf.y, s0 * hf.x);
+        const float cH = fmaf(-s0, hf.y, c0 * hf.x);
+        sn = make_float2(s0, sH);
+        dl = __ffma2_rn(make_float2(c0, cH), make_float2(ini.z, ini.w), __fmul2_rn(sn, make_float2(ini.x, ini.y)));
+        half_sum = fmaf(s0, hf.z, c0 * hf.w);
     }
     // carrier: phase base reduced to one turn in fp64, fp32 from there
     float b0;
@@ -481,38 +486,36 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
     // while the (unreduced) phase may still be negative, Square's int() truncation is not the
     // periodic rule: take the exact path for the whole run (only the first cycles of a voice)
     const bool low = EDGES && !(B > 16.0);
-    base = make_float2(b0, b0 + g2.w + half_gd);
-    const float e0 = fmaf(lane8, rec.de, rec.e_sub);
-    float2 e = make_float2(e0, fmaf((float)H, rec.de, e0));
-    const float2 cstep = make_float2(inc.z, inc.w), gd2 = make_float2(g2.x, g2.y);
-    const float2 estep = make_float2(rec.de, rec.de);
+    float2 P = make_float2(b0, b0 + F.Hwc + half_sum);
+    float2 run = make_float2(0.0f, 0.0f);   // EDGES only: gd * (sines summed so far in each half)
+    const float e0 = fmaf(lane8, env.y, env.x);
+    float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
+    const float2 cstep = make_float2(stepk.x, stepk.y), nk2 = make_float2(stepk.z, stepk.w);
+    const float2 estep = make_float2(env.y, env.y);
     const float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
     const float pw = (WAVE == SB_WAVE_PULSE) ? F.pw : 0.0f;
 #pragma unroll
     for (int q = 0; q < H; q++) {
-        float2 ph = base;
-        if (MOD) ph = __ffma2_rn(gd2, ps[q], base);
         float2 w;
         if (WAVE == SB_WAVE_SINE) {
-            w.x = __sinf(ph.x);
-            w.y = __sinf(ph.y);
+            w.x = __sinf(P.x);
+            w.y = __sinf(P.y);
         } else if (WAVE == SB_WAVE_TRIANGLE) {
-            w.x = tri_shape(ph.x);
-            w.y = tri_shape(ph.y);
+            w.x = tri_shape(P.x);
+            w.y = tri_shape(P.y);
         } else {
             bool nx, ny;
-            w.x = guarded_shape<WAVE>(ph.x, pw, nx);
-            w.y = guarded_shape<WAVE>(ph.y, pw, ny);
+            w.x = guarded_shape<WAVE>(P.x, pw, nx);
+            w.y = guarded_shape<WAVE>(P.y, pw, ny);
             if (nx || low)
-                w.x = exact_shape(WAVE, ctx, n + q, car.x, car.y, MOD ? F.gd * (before + (double)ps[q].x) : 0.0,
-                                  MOD, F.pw64);
+                w.x = exact_shape(WAVE, ctx, n + q, car.x, car.y, MOD ? gbefore + (double)run.x : 0.0, MOD, F.pw64);
             if (ny || low)
                 w.y = exact_shape(WAVE, ctx, n + q + H, car.x, car.y,
-                                  MOD ? F.gd * (before + (double)half_sum + (double)ps[q].y) : 0.0, MOD, F.pw64);
+                                  MOD ? gbefore + (double)half_sum + (double)run.y : 0.0, MOD, F.pw64);
         }
         float2 ee = e;
         if (RARE) {
-            if (rec.e_sub == kEnvSlow) {
+            if (env.x == kEnvSlow) {
                 ee.x = fast_env_at(F, n + q);
                 ee.y = fast_env_at(F, n + q + H);
             }
@@ -522,44 +525,57 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const SubRec 
         const float2 we = __fmul2_rn(w, ee);
         accL2[q] = __ffma2_rn(we, aL2, accL2[q]);
         accR2[q] = __ffma2_rn(we, aR2, accR2[q]);
-        base = __fadd2_rn(base, cstep);
-        e = __fadd2_rn(e, estep);
+        if (q + 1 < H) {
+            P = __fadd2_rn(P, cstep);
+            if (MOD) {
+                P = __fadd2_rn(P, sn);
+                if (EDGES) run = __fadd2_rn(run, sn);
+                dl = __ffma2_rn(nk2, sn, dl);
+                sn = __fadd2_rn(sn, dl);
+            }
+            e = __fadd2_rn(e, estep);
+        }
     }
 }
 
 // One instantiation per kind (bit0 = MOD, bits 1.. = carrier waveform); voices are stored
 // sorted by kind, so each loop is a branch-free run.
 template <int KIND>
-__device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const SubRec *s_rec, int begin, int end,
-                                                int s, const double Tr0, const double Tc0, const int seg_r,
-                                                const float lane8, const int64_t n, const FastCtx ctx,
+__device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const double2 *s_anc, const float2 *s_env,
+                                                int begin, int end, int s, const double Tr0, const double Tc0,
+                                                const int seg_r, const double lane16d, const float lane8,
+                                                const int64_t n, const FastCtx ctx,
                                                 float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
     constexpr bool MOD = (KIND & 1) != 0;
     constexpr int WAVE = KIND >> 1;
+    const double2 none = make_double2(0.0, 0.0);
     int v = begin;
 #if FAST_PAIR_VOICES
     // two voices per iteration in one basic block: their (independent) dependency chains give
-    // the scheduler twice the instruction-level parallelism to hide MUFU / shuffle latency
+    // the scheduler twice the instruction-level parallelism to hide MUFU / fp64 latency
     if (WAVE < SB_WAVE_SQUARE) {
         for (; v + 1 < end; v += 2) {
             const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
-            const SubRec r0 = s_rec[v * kFastMaxSub + s], r1 = s_rec[(v + 1) * kFastMaxSub + s];
-            const bool plain = r0.e_sub >= 0.0f && r1.e_sub >= 0.0f && !((F0.flags | F1.flags) & FV_BIAS);
+            const float2 e0 = s_env[v * kFastMaxSub + s], e1 = s_env[(v + 1) * kFastMaxSub + s];
+            const bool plain = e0.x >= 0.0f && e1.x >= 0.0f && !((F0.flags | F1.flags) & FV_BIAS);
             if (!plain) break;                                                  // warp-uniform
-            fast_voice_run<MOD, WAVE, false>(F0, r0, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_run<MOD, WAVE, false>(F1, r1, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            const double2 a0 = MOD ? s_anc[v * kFastMaxSub + s] : none;
+            const double2 a1 = MOD ? s_anc[(v + 1) * kFastMaxSub + s] : none;
+            fast_voice_run<MOD, WAVE, false>(F0, a0, e0, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F1, a1, e1, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
         }
     }
 #endif
     for (; v < end; v++) {
         const FastVoice &F = s_fv[v];
-        const SubRec rec = s_rec[v * kFastMaxSub + s];
-        if (rec.e_sub == kEnvSilent) continue;                                  // warp-uniform
-        if (rec.e_sub == kEnvSlow || (F.flags & FV_BIAS))
-            fast_voice_run<MOD, WAVE, true>(F, rec, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+        const float2 env = s_env[v * kFastMaxSub + s];
+        if (env.x == kEnvSilent) continue;                                      // warp-uniform
+        const double2 anc = MOD ? s_anc[v * kFastMaxSub + s] : none;
+        if (env.x == kEnvSlow || (F.flags & FV_BIAS))
+            fast_voice_run<MOD, WAVE, true>(F, anc, env, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
         else
-            fast_voice_run<MOD, WAVE, false>(F, rec, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false>(F, anc, env, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
     }
 }
 
@@ -573,8 +589,10 @@ bank_fast_kernel(BankArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
-    SubRec *s_rec_all = reinterpret_cast<SubRec *>(s_fv + a.voices_per_group);
-    sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(s_rec_all + (size_t)kFastWarps * a.voices_per_group * kFastMaxSub);
+    const size_t nrec = (size_t)kFastWarps * a.voices_per_group * kFastMaxSub;
+    double2 *s_anc_all = reinterpret_cast<double2 *>(s_fv + a.voices_per_group);
+    float2 *s_env_all = reinterpret_cast<float2 *>(s_anc_all + nrec);
+    sb_time_seg *s_rad = reinterpret_cast<sb_time_seg *>(s_env_all + nrec);
     sb_time_seg *s_cyc = s_rad + a.nsegs_rad;
     __shared__ int s_kind_end[kFastKinds];     // voices are stored sorted by kind; end index of each kind
 
@@ -603,8 +621,6 @@ bank_fast_kernel(BankArgs a)
             int4 *dst = reinterpret_cast<int4 *>(s_fv + pos);
 #pragma unroll
             for (int i = 0; i < (int)(sizeof(FastVoice) / 16); i++) dst[i] = w[i];
-            // s_fv[pos].pad0 remembers the voice's index in the bank (for its FM table row)
-            s_fv[pos].pad0 = v_begin + v;
         }
     }
     if (threadIdx.x < kFastKinds) {
@@ -622,50 +638,49 @@ bank_fast_kernel(BankArgs a)
     nv = ke[kFastKinds - 1];                           // this kernel's voices only from here on
     if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
     const bool any_cyc = EDGED || nv > ke[1];
-    const FastCtx ctx = {s_cyc, a.nsegs_cyc, a.tab, a.nsegs_rad};
+    const FastCtx ctx = {s_cyc, a.nsegs_cyc, a.tab, a.lanetab, a.nsegs_rad};
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
     if (span >= a.fast_nspans) return;                 // no block-wide sync after this point
-    SubRec *s_rec = s_rec_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
+    double2 *s_anc = s_anc_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
+    float2 *s_env = s_env_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
 
     const int64_t span_begin = (int64_t)span * a.fast_span_len;
     int64_t span_end = span_begin + a.fast_span_len;
     if (span_end > a.frames) span_end = a.frames;
     const int nsub = (int)((span_end - span_begin + kFSub - 1) / kFSub);
 
-    // ---- per-(voice, sub-tile) records, all lanes busy: closed-form FM sum at the sub-tile
-    //      start and the ADSR line across the sub-tile
+    // ---- per-(voice, sub-tile) records, all lanes busy: the modulator's (cos, sin) at the
+    //      sub-tile's first frame, scaled by gd, and the ADSR line across the sub-tile
     for (int idx = lane; idx < nv * nsub; idx += 32) {
         const int v = idx / nsub, s = idx - v * nsub;
         const FastVoice &F = s_fv[v];
         const int64_t lo = a.n0 + span_begin + (int64_t)s * kFSub, hi = lo + kFSub;
-        SubRec r;
-        r.anchor = 0.0;
-        r.e_sub = 1.0f;
-        r.de = 0.0f;
-        if (!FAST_LANE_ANCHOR && (F.flags & FV_HAS_MOD)) {
+        double2 anc = make_double2(0.0, 0.0);
+        float2 r = make_float2(1.0f, 0.0f);                 // e_sub, de
+        if (F.flags & FV_HAS_MOD) {
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, lo);
-            const double t = c.at(lo);
-            const double arg = fma(F.mod.x, t - 0.5 * c.step, F.mod.y);
-            const double2 ac = a.tab[(int64_t)F.pad0 * a.nsegs_rad + c.idx];
-            r.anchor = ac.x - ac.y * cos_reduced(reduce_two_pi(arg));
+            const double th = reduce_two_pi(fma(F.mod.x, c.at(lo), F.mod.y));
+            anc = make_double2(F.gd * cos_reduced(th), F.gd * sin_reduced(th));
         }
         if (F.flags & FV_ENV) {
-            if (lo > F.n_r) r.e_sub = kEnvSilent;
-            else if (hi <= F.n_a) { r.e_sub = (float)lo * F.a_slope; r.de = F.a_slope; }
-            else if (lo >= F.n_a && hi <= F.n_d) { r.e_sub = 1.0f + (float)(lo - F.n_a) * F.d_slope; r.de = F.d_slope; }
-            else if (lo >= F.n_d && hi <= F.n_s) { r.e_sub = F.sl; }
-            else if (lo >= F.n_s && hi <= F.n_r) { r.e_sub = F.sl + (float)(lo - F.n_s) * F.r_slope; r.de = F.r_slope; }
-            else r.e_sub = kEnvSlow;
+            if (lo > F.n_r) r.x = kEnvSilent;
+            else if (hi <= F.n_a) { r.x = (float)lo * F.a_slope; r.y = F.a_slope; }
+            else if (lo >= F.n_a && hi <= F.n_d) { r.x = 1.0f + (float)(lo - F.n_a) * F.d_slope; r.y = F.d_slope; }
+            else if (lo >= F.n_d && hi <= F.n_s) { r.x = F.sl; }
+            else if (lo >= F.n_s && hi <= F.n_r) { r.x = F.sl + (float)(lo - F.n_s) * F.r_slope; r.y = F.r_slope; }
+            else r.x = kEnvSlow;
         }
-        s_rec[v * kFastMaxSub + s] = r;
+        s_anc[v * kFastMaxSub + s] = anc;
+        s_env[v * kFastMaxSub + s] = r;
     }
     __syncwarp();
 
     float *out = a.out + (int64_t)group * a.out_stride;
     const float lane8 = (float)(lane * kFItems);
+    const double lane16d = (double)(lane * kFItems);
 
     for (int s = 0; s < nsub; s++) {
         const int64_t i0 = span_begin + (int64_t)s * kFSub + lane * kFItems;
@@ -693,17 +708,17 @@ bank_fast_kernel(BankArgs a)
         for (int q = 0; q < H; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
         if (!EDGED) {
-            fast_voice_loop<0>(s_fv, s_rec, 0, ke[0], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<1>(s_fv, s_rec, ke[0], ke[1], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<2>(s_fv, s_rec, ke[1], ke[2], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<3>(s_fv, s_rec, ke[2], ke[3], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<0>(s_fv, s_anc, s_env, 0, ke[0], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<1>(s_fv, s_anc, s_env, ke[0], ke[1], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<2>(s_fv, s_anc, s_env, ke[1], ke[2], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<3>(s_fv, s_anc, s_env, ke[2], ke[3], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
         } else {
-            fast_voice_loop<4>(s_fv, s_rec, 0, ke[4], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<5>(s_fv, s_rec, ke[4], ke[5], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<6>(s_fv, s_rec, ke[5], ke[6], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<7>(s_fv, s_rec, ke[6], ke[7], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<8>(s_fv, s_rec, ke[7], ke[8], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<9>(s_fv, s_rec, ke[8], ke[9], s, Tr0, Tc0, seg_r, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<4>(s_fv, s_anc, s_env, 0, ke[4], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<5>(s_fv, s_anc, s_env, ke[4], ke[5], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<6>(s_fv, s_anc, s_env, ke[5], ke[6], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<7>(s_fv, s_anc, s_env, ke[6], ke[7], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<8>(s_fv, s_anc, s_env, ke[7], ke[8], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<9>(s_fv, s_anc, s_env, ke[8], ke[9], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
         }
 
         // frame j of the run is accL2[j].x for j < H and accL2[j-H].y above; two frames per float4
@@ -1082,7 +1097,9 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     plan->nprefix = (int32_t)nprefix;
     plan->off_fastv = align_up((int64_t)nvoices * (nprefix + nspans) * (int64_t)sizeof(double), 256);
     plan->off_tab = align_up(plan->off_fastv + (int64_t)nvoices * (int64_t)sizeof(FastVoice), 256);
-    plan->carry_bytes = align_up(plan->off_tab + (int64_t)nvoices * nsegs_rad * (int64_t)sizeof(double2), 256);
+    // the closed-form FM table, then the lane rotation table [nvoices][32]
+    plan->carry_bytes = align_up(plan->off_tab + (int64_t)nvoices * nsegs_rad * (int64_t)sizeof(FmSeg), 256) +
+                        align_up((int64_t)nvoices * 32 * (int64_t)sizeof(double2), 256);
     plan->partial_bytes = (ngroups > 1) ? (int64_t)ngroups * ((frames * 2 + 3) / 4 * 4) * (int64_t)sizeof(float) : 0;
     return SB_OK;
 }
@@ -1125,7 +1142,8 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.nprefix = plan->nprefix;
     a.carry = (plan->nspans + plan->nprefix > 1) ? (double *)scratch : nullptr;
     a.fastv = (FastVoice *)(scratch + plan->off_fastv);
-    a.tab = (double2 *)(scratch + plan->off_tab);
+    a.tab = (FmSeg *)(scratch + plan->off_tab);
+    a.lanetab = (double2 *)(scratch + align_up(plan->off_tab + (int64_t)plan->nvoices * nsegs_rad * (int64_t)sizeof(FmSeg), 256));
     a.fast_nspans = plan->fast_nspans;
     a.fast_span_len = plan->fast_span_len;
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
@@ -1137,7 +1155,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     const size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);
     {
         size_t smem = tb_bytes + (size_t)a.voices_per_group * sizeof(FastVoice) +
-                      (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * sizeof(SubRec);
+                      (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * (sizeof(double2) + sizeof(float2));
         if (smem > 48 * 1024)
         {
             SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
