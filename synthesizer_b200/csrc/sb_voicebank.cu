@@ -84,31 +84,30 @@ constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer t
 struct alignas(16) FastVoice {
     double2 car;             // f0b, pc0: carrier frequency * (1 + modulator bias), start phase
     int flags;
-    int vidx;                // the voice's index in the bank (rows of the FM tables)
+    int tab_row;             // voice index * nsegs_rad: the voice's row of the closed-form FM table
+    int lt_row;              // voice index * 32: the voice's row of the lane rotation table
     float Hwc;               // H carrier steps
-    float pw;                // Pulse carriers: the (clamped) pulse width
     float4 stepk;            // wc, wc, -k, -k: carrier phase step; k = 4 sin^2(w/2)
     float4 gain;             // aL, aL, aR, aR: c_amp*gain
     float4 ini;              // k/2, k/2, sin w, sin w: first backward difference of the modulator recurrence
     float4 half;             // cos(H w), sin(H w), P, Q: second half-run start; sum of the first H sines = s0*P + c0*Q
-    double2 mod;             // fm, pcm: modulator frequency and start phase (radians)
+    double2 mod;             // fm, pcm: modulator frequency and start phase (radians); fm is read per run
     double gd;               // carrier phase per unit of sum(sin(theta_k)): f0 * inc_c * depth
     double pw64;             // Pulse carriers: the (clamped) pulse width in fp64, for the exact re-evaluation
     long long n_a, n_d, n_s, n_r;
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
-    float pad;
+    float pw;                // Pulse carriers: the (clamped) pulse width
 };
 static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
 
 // Closed-form FM table entry per (voice, modulator time-base segment b), step w_b = fm*step_b:
 //   gd * sum_{k<n} sin(theta_k) = A - Cc*(gd cos theta_n) - (gd sin theta_n)/2      (n in segment b)
 // with Cc = cot(w_b/2)/2 and A = gd*(sum over earlier segments + C_b cos(theta_b - w_b/2)),
-// C_b = 1/(2 sin(w_b/2)).  dw = w_b - w: how far the segment's phase step is from the nominal
-// one the lane table is built with (|dw/w| < 1e-8; first-order correction in the kernel).
+// C_b = 1/(2 sin(w_b/2)).
 struct alignas(16) FmSeg {
-    double A, Cc, dw, pad;
+    double A, Cc;
 };
 
 // Per-(voice, sub-tile) records precomputed at the start of a span:
@@ -222,8 +221,8 @@ __global__ void bank_prepare_kernel(BankArgs a)
     constexpr int H = kFItems / 2;
     FastVoice F;
     F.flags = 0;
-    F.vidx = v;
-    F.pad = 0.0f;
+    F.tab_row = v * a.nsegs_rad;
+    F.lt_row = v * 32;
     const bool fast = voice_is_fast(V, a.samplerate);
     const bool tri = (V.c_wave != SB_WAVE_SINE);         // phase counted in cycles (all but Sine)
     const double inc_rad = 6.283185307179586 / a.samplerate;
@@ -286,8 +285,6 @@ __global__ void bank_prepare_kernel(BankArgs a)
             FmSeg e;
             e.A = F.gd * S;
             e.Cc = C * cos(half);
-            e.dw = fm * (s.step - inc_rad);
-            e.pad = 0.0;
             row[b] = e;
             if (b + 1 < a.nsegs_rad) {
                 const double len = (double)(a.tb_rad[b + 1].n_start - s.n_start);
@@ -375,9 +372,8 @@ __device__ __forceinline__ double warp_scan_incl_f64(double v)
 struct FastCtx {
     const sb_time_seg *s_cyc;
     int nsegs_cyc;
-    const FmSeg *tab;        // [nvoices][nsegs_rad] closed-form FM table
-    const double2 *lanetab;  // [nvoices][32] anchor -> lane rotations
-    int nsegs_rad;
+    const FmSeg *tab_seg;    // closed-form FM table, offset to this lane's time-base segment: row stride nsegs_rad
+    const double2 *lt_lane;  // anchor -> lane rotation table, offset to this lane: row stride 32
 };
 
 // Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
@@ -428,18 +424,21 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
 // The recurrence for s is sin(theta+w) = 2cos(w) sin(theta) - sin(theta-w) written with
 // k = 2 - 2cos(w) = 4 sin^2(w/2) so that slow modulators lose nothing to cancellation.
 //
+// FLAT: the envelope is constant over the sub-tile (sustain, or no envelope): it is folded
+// into the pan gains once per run, which takes two packed operations out of every step.
+//
 // Set-up (fp64, once per run): gd*(cos, sin)(theta) at the lane's first frame by rotating the
 // sub-tile's anchor with the lane table (plus the first-order term for the time-base segment's
-// own step); the FM sum ahead of the run from the closed form; the carrier phase base.
+// own step: dstep = (frames from the sub-tile start) * (segment step - nominal step)); the FM sum ahead of the run from the closed form; the carrier phase base.
 //
 // Square / Sawtooth / Pulse carriers: their value is evaluated in fp32 like the others, which
 // is exact (+-1, or a continuous ramp) unless the phase sits within kEdgeGuard cycles of a
 // discontinuity; those few samples are redone in fp64 exactly as upstream forms the phase, so
 // every edge lands on the sample upstream puts it on.
-template <bool MOD, int WAVE, bool RARE>
+template <bool MOD, int WAVE, bool RARE, bool FLAT>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2 anc, const float2 env,
-                                               const double Tr0, const double Tc0, const int seg_r,
-                                               const double lane16d, const float lane8, const int64_t n,
+                                               const double Tr0, const double Tc0, const double dstep,
+                                               const float lane8, const int64_t n,
                                                const FastCtx ctx, float2 (&accL2)[kFItems / 2],
                                                float2 (&accR2)[kFItems / 2])
 {
@@ -454,17 +453,17 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     float2 sn = make_float2(0.0f, 0.0f), dl = make_float2(0.0f, 0.0f);
     float half_sum = 0.0f;                  // gd * (sum of the first half-run's sines)
     if (MOD) {
-        const int lane = threadIdx.x & 31;
-        const double2 L = ctx.lanetab[(int64_t)F.vidx * 32 + lane];
-        const FmSeg fs = ctx.tab[(int64_t)F.vidx * ctx.nsegs_rad + seg_r];
+        const double2 L = ctx.lt_lane[F.lt_row];
+        const FmSeg fs = ctx.tab_seg[F.tab_row];
         // gd*(cos, sin) of the modulator phase at this lane's first frame
         const double cl = fma(-anc.y, L.y, anc.x * L.x);
         const double sl = fma(anc.x, L.y, anc.y * L.x);
-        // closed form, with theta advanced by the small angle lane16*dw to first order
+        // closed form, with theta advanced to first order by the small angle fm*dstep: how far
+        // this segment's time step has carried the lane from where the nominal step would have
         double u = fma(-fs.Cc, cl, fs.A);
         u = fma(-0.5, sl, u);
         const double vv = fma(fs.Cc, sl, -0.5 * cl);
-        gbefore = fma(lane16d * fs.dw, vv, u);
+        gbefore = fma(F.mod.x * dstep, vv, u);
         B += gbefore;
         const float s0 = (float)sl, c0 = (float)cl;
         const float4 hf = F.half;           // cos(H w), sin(H w), P, Q
@@ -492,7 +491,12 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
     const float2 cstep = make_float2(stepk.x, stepk.y), nk2 = make_float2(stepk.z, stepk.w);
     const float2 estep = make_float2(env.y, env.y);
-    const float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
+    float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
+    if (FLAT) {
+        const float2 ec = make_float2(env.x, env.x);
+        aL2 = __fmul2_rn(aL2, ec);
+        aR2 = __fmul2_rn(aR2, ec);
+    }
     const float pw = (WAVE == SB_WAVE_PULSE) ? F.pw : 0.0f;
 #pragma unroll
     for (int q = 0; q < H; q++) {
@@ -522,7 +526,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
             accL2[q] = __ffma2_rn(ee, make_float2(F.bL, F.bL), accL2[q]);
             accR2[q] = __ffma2_rn(ee, make_float2(F.bR, F.bR), accR2[q]);
         }
-        const float2 we = __fmul2_rn(w, ee);
+        const float2 we = FLAT ? w : __fmul2_rn(w, ee);
         accL2[q] = __ffma2_rn(we, aL2, accL2[q]);
         accR2[q] = __ffma2_rn(we, aR2, accR2[q]);
         if (q + 1 < H) {
@@ -533,7 +537,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
                 dl = __ffma2_rn(nk2, sn, dl);
                 sn = __fadd2_rn(sn, dl);
             }
-            e = __fadd2_rn(e, estep);
+            if (!FLAT) e = __fadd2_rn(e, estep);
         }
     }
 }
@@ -543,7 +547,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
 template <int KIND>
 __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const double2 *s_anc, const float2 *s_env,
                                                 int begin, int end, int s, const double Tr0, const double Tc0,
-                                                const int seg_r, const double lane16d, const float lane8,
+                                                const double dstep, const float lane8,
                                                 const int64_t n, const FastCtx ctx,
                                                 float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
@@ -558,12 +562,18 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
         for (; v + 1 < end; v += 2) {
             const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
             const float2 e0 = s_env[v * kFastMaxSub + s], e1 = s_env[(v + 1) * kFastMaxSub + s];
-            const bool plain = e0.x >= 0.0f && e1.x >= 0.0f && !((F0.flags | F1.flags) & FV_BIAS);
+            // both envelopes plain lines (sign bits clear: not kEnvSilent / kEnvSlow), no carrier bias
+            const bool plain = (__float_as_int(e0.x) | __float_as_int(e1.x)) >= 0 && !((F0.flags | F1.flags) & FV_BIAS);
             if (!plain) break;                                                  // warp-uniform
             const double2 a0 = MOD ? s_anc[v * kFastMaxSub + s] : none;
             const double2 a1 = MOD ? s_anc[(v + 1) * kFastMaxSub + s] : none;
-            fast_voice_run<MOD, WAVE, false>(F0, a0, e0, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_run<MOD, WAVE, false>(F1, a1, e1, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            if (((__float_as_int(e0.y) | __float_as_int(e1.y)) << 1) == 0) {     // both slopes +-0: warp-uniform
+                fast_voice_run<MOD, WAVE, false, true>(F0, a0, e0, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+                fast_voice_run<MOD, WAVE, false, true>(F1, a1, e1, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            } else {
+                fast_voice_run<MOD, WAVE, false, false>(F0, a0, e0, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+                fast_voice_run<MOD, WAVE, false, false>(F1, a1, e1, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            }
         }
     }
 #endif
@@ -573,9 +583,9 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
         if (env.x == kEnvSilent) continue;                                      // warp-uniform
         const double2 anc = MOD ? s_anc[v * kFastMaxSub + s] : none;
         if (env.x == kEnvSlow || (F.flags & FV_BIAS))
-            fast_voice_run<MOD, WAVE, true>(F, anc, env, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, true, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         else
-            fast_voice_run<MOD, WAVE, false>(F, anc, env, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_run<MOD, WAVE, false, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
     }
 }
 
@@ -638,7 +648,6 @@ bank_fast_kernel(BankArgs a)
     nv = ke[kFastKinds - 1];                           // this kernel's voices only from here on
     if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
     const bool any_cyc = EDGED || nv > ke[1];
-    const FastCtx ctx = {s_cyc, a.nsegs_cyc, a.tab, a.lanetab, a.nsegs_rad};
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
@@ -680,20 +689,24 @@ bank_fast_kernel(BankArgs a)
 
     float *out = a.out + (int64_t)group * a.out_stride;
     const float lane8 = (float)(lane * kFItems);
-    const double lane16d = (double)(lane * kFItems);
+    const double inc_rad = 6.283185307179586 / a.samplerate;
 
     for (int s = 0; s < nsub; s++) {
         const int64_t i0 = span_begin + (int64_t)s * kFSub + lane * kFItems;
         const int64_t n = a.n0 + i0;
         // exact serial time at this lane's first frame in both bases (a fresh look-up per
         // sub-tile costs ~40 instructions per 64 voices and keeps no cursor state in registers)
-        double Tr0, Tc0 = 0.0;
-        int seg_r;
+        double Tr0, Tc0 = 0.0, dstep;
+        FastCtx ctx;
+        ctx.s_cyc = s_cyc;
+        ctx.nsegs_cyc = a.nsegs_cyc;
+        ctx.lt_lane = a.lanetab + lane;
         {
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, n);
             Tr0 = c.at(n);
-            seg_r = c.idx;
+            ctx.tab_seg = a.tab + c.idx;
+            dstep = (double)(lane * kFItems) * (c.step - inc_rad);
             if (any_cyc) {                              // carriers whose phase counts in cycles present
                 c.seek(s_cyc, a.nsegs_cyc, n);
                 Tc0 = c.at(n);
@@ -701,24 +714,24 @@ bank_fast_kernel(BankArgs a)
         }
         // keep both in registers for the voice loops (the compiler would otherwise recompute
         // the int64 -> fp64 conversion per voice)
-        asm volatile("" : "+d"(Tr0), "+d"(Tc0));
+        asm volatile("" : "+d"(Tr0), "+d"(Tc0), "+d"(dstep));
         constexpr int H = kFItems / 2;
         float2 accL2[H], accR2[H];
 #pragma unroll
         for (int q = 0; q < H; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
         if (!EDGED) {
-            fast_voice_loop<0>(s_fv, s_anc, s_env, 0, ke[0], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<1>(s_fv, s_anc, s_env, ke[0], ke[1], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<2>(s_fv, s_anc, s_env, ke[1], ke[2], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<3>(s_fv, s_anc, s_env, ke[2], ke[3], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<0>(s_fv, s_anc, s_env, 0, ke[0], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<1>(s_fv, s_anc, s_env, ke[0], ke[1], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<2>(s_fv, s_anc, s_env, ke[1], ke[2], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<3>(s_fv, s_anc, s_env, ke[2], ke[3], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         } else {
-            fast_voice_loop<4>(s_fv, s_anc, s_env, 0, ke[4], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<5>(s_fv, s_anc, s_env, ke[4], ke[5], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<6>(s_fv, s_anc, s_env, ke[5], ke[6], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<7>(s_fv, s_anc, s_env, ke[6], ke[7], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<8>(s_fv, s_anc, s_env, ke[7], ke[8], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
-            fast_voice_loop<9>(s_fv, s_anc, s_env, ke[8], ke[9], s, Tr0, Tc0, seg_r, lane16d, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<4>(s_fv, s_anc, s_env, 0, ke[4], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<5>(s_fv, s_anc, s_env, ke[4], ke[5], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<6>(s_fv, s_anc, s_env, ke[5], ke[6], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<7>(s_fv, s_anc, s_env, ke[6], ke[7], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<8>(s_fv, s_anc, s_env, ke[7], ke[8], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<9>(s_fv, s_anc, s_env, ke[8], ke[9], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         }
 
         // frame j of the run is accL2[j].x for j < H and accL2[j-H].y above; two frames per float4
