@@ -50,15 +50,16 @@ constexpr int kFastWarps = 4;                // fast kernel: warps per CTA
 #endif
 constexpr int kFastMaxSub = FAST_MAX_SUB;    // fast kernel: sub-tiles per span (anchors in smem)
 #ifndef FAST_MIN_BLOCKS
-#define FAST_MIN_BLOCKS 5      /* CTAs per SM (register cap 96).  Measured on B200 with 8 frames per lane:
-                                  3/4/5/6/7/8 CTAs -> 3.84/3.84/3.50/3.21/3.13/3.29 ms; with 16 frames per lane:
-                                  4/5/6 CTAs -> 2.65/2.63/2.76 ms */
+#define FAST_MIN_BLOCKS 5      /* CTAs per SM (register cap 96; 39 KB of shared memory each).  Measured on B200:
+                                  4/5 CTAs -> 2.20/2.19 ms; 6 needs 80 registers (spills) and a shorter span: 2.56 ms */
 #endif
 #ifndef FAST_MAX_FM_GAIN
 #define FAST_MAX_FM_GAIN 1.5
 #endif
 #ifndef FAST_PAIR_VOICES
-#define FAST_PAIR_VOICES 1     /* measured on B200 at 7 CTAs/SM: 3.12 ms without, 2.96 ms with */
+#define FAST_PAIR_VOICES 1     /* measured on B200: 2.42 ms without, 2.19 ms with; three per iteration 2.22 ms (4 CTAs/SM,
+                                  126 registers) or 2.37 ms (5 CTAs/SM, spills); separate code per (flat, ramp) mix
+                                  of a pair 2.29 ms (instruction cache) */
 #endif
 
 enum : int {
@@ -212,33 +213,37 @@ __device__ __forceinline__ double reduce_two_pi(double x)
     return fma(-k, kTwoPiLo, r);
 }
 
-// ------------------------------------------------------------------ prepare (one thread per voice)
+// ------------------------------------------------------------------ prepare (one warp per voice)
+// Lane 0 derives the voice's constants; all lanes share the trigonometry of the FM tables
+// (one time-base segment and one lane-table entry each).
 __global__ void bank_prepare_kernel(BankArgs a)
 {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= a.nvoices) return;
+    const int v = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (v >= a.nvoices) return;                          // the whole warp leaves
     const sb_voice V = a.voices[v];
     constexpr int H = kFItems / 2;
-    FastVoice F;
-    F.flags = 0;
-    F.tab_row = v * a.nsegs_rad;
-    F.lt_row = v * 32;
     const bool fast = voice_is_fast(V, a.samplerate);
     const bool tri = (V.c_wave != SB_WAVE_SINE);         // phase counted in cycles (all but Sine)
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
-    F.pw = (float)clamp_pulsewidth((double)V.c_pw);
-    F.pw64 = clamp_pulsewidth((double)V.c_pw);
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
     const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
     const double f0b = V.c_freq * (1.0 + mbias);
-    F.mod = make_double2(fm, pcm);
-    F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
-    F.gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
-    F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
+    const double gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
     const double w = fm * inc_rad;                        // nominal modulator phase step
-    {
+    if (lane == 0) {
+        FastVoice F;
+        F.flags = 0;
+        F.tab_row = v * a.nsegs_rad;
+        F.lt_row = v * 32;
+        F.pw = (float)clamp_pulsewidth((double)V.c_pw);
+        F.pw64 = clamp_pulsewidth((double)V.c_pw);
+        F.mod = make_double2(fm, pcm);
+        F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
+        F.gd = gd;
+        F.n_a = V.env.n_a; F.n_d = V.env.n_d; F.n_s = V.env.n_s; F.n_r = V.env.n_r;
         const float wc = (float)(f0b * inc_c);
         const double sh = sin(0.5 * w);
         const float k = (float)(4.0 * sh * sh);
@@ -250,65 +255,63 @@ __global__ void bank_prepare_kernel(BankArgs a)
         const double R = (fabs(sh) > 1e-300) ? sin(0.5 * (double)H * w) / sh : (double)H;
         const double mid = 0.5 * (double)(H - 1) * w;
         F.half = make_float4((float)cos((double)H * w), (float)sin((double)H * w), (float)(cos(mid) * R), (float)(sin(mid) * R));
+        F.bL = V.c_bias * V.gain_l;
+        F.bR = V.c_bias * V.gain_r;
+        F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_amp * V.gain_r);
+        F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
+        F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
+        if (fast) F.flags |= FV_FAST;
+        if (has_mod) F.flags |= FV_HAS_MOD;
+        if (tri) F.flags |= FV_TRIANGLE;
+        F.flags |= (V.c_wave & 7) << FV_WAVE_SHIFT;
+        if (V.env.enabled) F.flags |= FV_ENV;
+        if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
+        if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
+        a.fastv[v] = F;
     }
-    F.bL = V.c_bias * V.gain_l;
-    F.bR = V.c_bias * V.gain_r;
-    F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_amp * V.gain_r);
-    F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
-    F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
-    if (fast) F.flags |= FV_FAST;
-    if (has_mod) F.flags |= FV_HAS_MOD;
-    if (tri) F.flags |= FV_TRIANGLE;
-    F.flags |= (V.c_wave & 7) << FV_WAVE_SHIFT;
-    if (V.env.enabled) F.flags |= FV_ENV;
-    if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
-    if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
-    a.fastv[v] = F;
+    if (!(fast && has_mod)) return;
 
-    if (fast && has_mod) {
-        // Closed form of sum_{k<n} sin(theta_k), theta_k = fm*t(k) + pcm, t piecewise linear:
-        // inside segment b (start n_b, t_b, step_b): theta_k = theta_b + (k-n_b)*w_b and
-        //   sum_{k=n_b}^{n-1} sin(theta_k) = [cos(theta_b - w_b/2) - cos(theta_n - w_b/2)] / (2 sin(w_b/2)),
-        // so with C_b = 1/(2 sin(w_b/2)) and S_b = (sum over earlier segments) + C_b cos(theta_b - w_b/2)
-        // the sum up to n in segment b is S_b - C_b cos(theta_n - w_b/2)
-        //                               = S_b - C_b cos(w_b/2) cos(theta_n) - sin(theta_n)/2.
-        FmSeg *row = a.tab + (int64_t)v * a.nsegs_rad;
-        double before = 0.0;
-        for (int b = 0; b < a.nsegs_rad; b++) {
+    // Closed form of sum_{k<n} sin(theta_k), theta_k = fm*t(k) + pcm, t piecewise linear:
+    // inside segment b (start n_b, t_b, step_b): theta_k = theta_b + (k-n_b)*w_b and
+    //   sum_{k=n_b}^{n-1} sin(theta_k) = [cos(theta_b - w_b/2) - cos(theta_n - w_b/2)] / (2 sin(w_b/2)),
+    // so with C_b = 1/(2 sin(w_b/2)) and S_b = (sum over earlier segments) + C_b cos(theta_b - w_b/2)
+    // the sum up to n in segment b is S_b - C_b cos(theta_n - w_b/2)
+    //                               = S_b - C_b cos(w_b/2) cos(theta_n) - sin(theta_n)/2.
+    // A lane takes one segment; the sums over earlier segments come from a warp scan.
+    FmSeg *row = a.tab + (int64_t)v * a.nsegs_rad;
+    double carry = 0.0;
+    for (int b0 = 0; b0 < a.nsegs_rad; b0 += 32) {
+        const int b = b0 + lane;
+        double whole = 0.0, C = 0.0, c_lo = 0.0, half = 0.0;
+        if (b < a.nsegs_rad) {
             const sb_time_seg s = a.tb_rad[b];
-            const double wb = fm * s.step;
-            const double half = 0.5 * wb;
+            half = 0.5 * fm * s.step;
             const double sh = sin(half);
-            const double C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
-            const double th_lo = fm * (s.t_start - 0.5 * s.step) + pcm;
-            const double S = before + C * cos(th_lo);
-            FmSeg e;
-            e.A = F.gd * S;
-            e.Cc = C * cos(half);
-            row[b] = e;
-            if (b + 1 < a.nsegs_rad) {
+            C = (fabs(sh) > 1e-300) ? 0.5 / sh : 0.0;
+            c_lo = cos(fm * (s.t_start - 0.5 * s.step) + pcm);
+            if (b + 1 < a.nsegs_rad) {                    // this segment's whole sum, for the ones after it
                 const double len = (double)(a.tb_rad[b + 1].n_start - s.n_start);
                 const double th_hi = fm * (s.t_start + (len - 0.5) * s.step) + pcm;
-                before = (C != 0.0) ? S - C * cos(th_hi) : before + len * sin(fm * s.t_start + pcm);
+                whole = (C != 0.0) ? C * (c_lo - cos(th_hi)) : len * sin(fm * s.t_start + pcm);
             }
         }
-        // rotation from a sub-tile's first frame to each lane's first frame, at the nominal step
-        double2 *lt = a.lanetab + (int64_t)v * 32;
-        for (int l = 0; l < 32; l++) {
-            const double ang = reduce_two_pi((double)(l * kFItems) * w);
-            lt[l] = make_double2(cos(ang), sin(ang));
-        }
-    }
-}
-
-__device__ __forceinline__ float warp_scan_incl_f(float v, int lane)
-{
+        double incl = whole;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        float o = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d) v += o;
+        for (int d = 1; d < 32; d <<= 1) {
+            const double o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        if (b < a.nsegs_rad) {
+            FmSeg e;
+            e.A = gd * (carry + (incl - whole) + C * c_lo);
+            e.Cc = C * cos(half);
+            row[b] = e;
+        }
+        carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    return v;
+    // rotation from a sub-tile's first frame to each lane's first frame, at the nominal step
+    const double ang = reduce_two_pi((double)(lane * kFItems) * w);
+    a.lanetab[(int64_t)v * 32 + lane] = make_double2(cos(ang), sin(ang));
 }
 
 __device__ __forceinline__ float tri_shape(float cycles)
@@ -338,35 +341,6 @@ __device__ __forceinline__ double reduce_two_pi_fast(double x)
     const double k = __dadd_rn(__fma_rn(x, kInvTwoPi, M), -M);
     const double r = fma(-k, kTwoPiHi, x);
     return fma(-k, kTwoPiLo, r);
-}
-
-// Inclusive warp scan, two instructions per step: shfl.up reports through a predicate whether
-// the source lane exists, and the add is predicated on it.
-__device__ __forceinline__ float warp_scan_incl_ptx(float v)
-{
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        asm volatile("{\n\t"
-                     ".reg .pred p;\n\t"
-                     ".reg .f32 t;\n\t"
-                     "shfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t"
-                     "@p add.f32 %0, %0, t;\n\t"
-                     "}"
-                     : "+f"(v) : "r"(d));
-    }
-    return v;
-}
-
-// the same for doubles (two 32-bit shuffles per step)
-__device__ __forceinline__ double warp_scan_incl_f64(double v)
-{
-    const int lane = threadIdx.x & 31;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const double o = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d) v += o;
-    }
-    return v;
 }
 
 struct FastCtx {
@@ -1036,7 +1010,16 @@ __global__ void bank_fold_kernel(const float *__restrict__ partial, int ngroups,
     int64_t nvec = nfloats / 4;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
         float4 acc = reinterpret_cast<const float4 *>(partial)[i];
-        for (int g = 1; g < ngroups; g++) {
+        int g = 1;
+        // eight groups' loads in flight per thread; the additions stay in group order
+        for (; g + 8 <= ngroups; g += 8) {
+            float4 p[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) p[k] = __ldcs(reinterpret_cast<const float4 *>(partial + (int64_t)(g + k) * gstride) + i);
+#pragma unroll
+            for (int k = 0; k < 8; k++) { acc.x += p[k].x; acc.y += p[k].y; acc.z += p[k].z; acc.w += p[k].w; }
+        }
+        for (; g < ngroups; g++) {
             float4 p = reinterpret_cast<const float4 *>(partial + (int64_t)g * gstride)[i];
             acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
         }
@@ -1162,7 +1145,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
     a.out_stride = (plan->frames * 2 + 3) / 4 * 4;
 
-    bank_prepare_kernel<<<(a.nvoices + 127) / 128, 128, 0, s>>>(a);
+    bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
 
     const size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);

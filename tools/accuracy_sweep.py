@@ -34,3 +34,6 @@ for r in rows:
     print("%d %8.1f %7.1f %5.2f %d %8.4f %8.4f %d" % r)
 worst = max(r[6] for r in rows if r[4])
 print("worst non-edge error on the fast path: %.4f LSB" % worst)
+per_rad = max(r[6] / (r[1] * 2 * np.pi / sr * r[3]) for r in rows if r[4] and r[1] * 2 * np.pi / sr * r[3] > 0.2)
+print("worst error per radian of FM gain (fast voices with gain > 0.2 rad): %.3f LSB/rad" % per_rad)
+print("worst non-edge error on the generic path: %.4f LSB" % max([r[6] for r in rows if not r[4]] or [0.0]))
