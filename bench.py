@@ -251,6 +251,8 @@ def run_ours(args):
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL's own banner ("NCCL version ...") goes to stdout by default: keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     frames = int(SR * SECONDS)
     total_voices = VOICES_PER_GPU * world
@@ -358,13 +360,13 @@ def run_ours(args):
         peak_gsin = 16 * sms * sm_mhz * 1e6 / 1e9
         achieved_gsin = 2 * (hi - lo) * frames / (render_ms / 1e3) / 1e9
         # DRAM traffic of the dominant kernel from the committed ncu capture
-        # (profiles/r1h_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
-        # of bank_fast_kernel on this workload): 4.8 MB read + 438.1 MB written
-        ncu_traffic = 4762112 + 438083072 if (hi - lo) == VOICES_PER_GPU else None
+        # (profiles/r1j_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
+        # of bank_fast_kernel on this workload): 9.6 MB read + 440.2 MB written
+        ncu_traffic = 9648384 + 440207872 if (hi - lo) == VOICES_PER_GPU else None
         # "achieved" counts ALGORITHMIC sines (2 per voice-sample: modulator + carrier), like
         # algorithmic bytes on an HBM roofline; the kernel issues fewer SFU operations than that
-        # (the modulator's sines come from a rotation recurrence: 20 MUFU per 16 frames, not 32).
-        roofline = {"bound": "sfu", "kernel": "bank_fast_kernel (+ bank_prepare, bank_fold: 94/1/4 % of the step)",
+        # (the modulator's sines come from a two-term recurrence: 16 MUFU per 16 frames, not 32).
+        roofline = {"bound": "sfu", "kernel": "bank_fast_kernel (+ bank_prepare, bank_fold: 94/1/5 % of the step)",
                     "achieved": achieved_gsin, "peak": peak_gsin, "unit": "Gsin/s",
                     "frac": achieved_gsin / peak_gsin, "traffic": ncu_traffic,
                     "peak_source": "16 MUFU lanes/clk/SM x %d SMs x %d MHz (clock sampled under load)" % (sms, sm_mhz),

@@ -91,12 +91,13 @@ def main():
     # float -> PCM and the float filter kernels (4 B in, 2 or 4 B out)
     nf = 600 * 48000
     x = torch.rand(nf, device="cuda") * 1.6 - 0.8
+    x2 = torch.rand(nf, device="cuda")
     y = torch.empty_like(x)
     p16 = torch.empty(nf, dtype=torch.int16, device="cuda")
     ovf = torch.zeros(1, dtype=torch.int64, device="cuda")
     for name, nbytes, fn in [
         ("f32_to_pcm16", 6 * nf, lambda: C.call("sb_f32_to_pcm16", D.ptr(x), nf, 32767.0, D.ptr(p16), D.ptr(ovf), D.stream())),
-        ("mul_f32 (AmpModulationFilter)", 12 * nf, lambda: C.call("sb_mul_f32", D.ptr(x), D.ptr(x), nf, D.ptr(y), D.stream())),
+        ("mul_f32 (AmpModulationFilter)", 12 * nf, lambda: C.call("sb_mul_f32", D.ptr(x), D.ptr(x2), nf, D.ptr(y), D.stream())),
         ("clip_f32 (ClipFilter)", 8 * nf, lambda: C.call("sb_clip_f32", D.ptr(x), -0.5, 0.5, nf, D.ptr(y), D.stream())),
     ]:
         ms = timed(fn, args.reps, flush)
