@@ -214,6 +214,28 @@ def main():
     line("config3 128-voice chord bank, mixed waveforms + ADSR, 10 s stereo 48 kHz", ms=ms,
          generic_voices=bank.count_generic(), msamples_per_s=128 * nfr / ms / 1e3)
 
+    # ---- one kernel class at a time: 8192 voices x 10 s of a single (carrier, modulator) kind -------
+    def class_bank(cw, mw, nv=8192):
+        b = sb.VoiceBank(sr)
+        r = np.random.default_rng(11)
+        for v in range(nv):
+            lfo = None
+            if mw is not None:
+                lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr)
+            car = classes[cw](float(r.uniform(55, 1760)), 0.9 / nv, fm_lfo=lfo, samplerate=sr)
+            pan = float(r.uniform(-1, 1))
+            b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
+        return b
+    for name, cw, mw, nv in [("Sine x Sine (fast, smooth)", 0, 0, 8192), ("Triangle, no FM (fast, smooth)", 1, None, 8192),
+                             ("Sawtooth x Sine (fast, edged)", 3, 0, 8192), ("Square, no FM (fast, edged)", 2, None, 8192),
+                             ("Sine x Triangle LFO (generic)", 0, 1, 1024), ("Sawtooth x Square LFO (generic)", 3, 2, 1024)]:
+        b = class_bank(cw, mw, nv)
+        vd, _ = b._upload(0, None)                       # voice parameters resident, as in bench.py
+        g, e = b.count_generic(), b.count_edged()
+        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e), max(2, args.reps // 4))
+        line("bank class: %s, %d voices x 10 s" % (name, nv), ms=ms, generic_voices=g, edged_voices=e,
+             msamples_per_s=nv * nfr / ms / 1e3)
+
 
 if __name__ == "__main__":
     main()

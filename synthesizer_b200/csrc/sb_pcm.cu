@@ -383,89 +383,80 @@ pcm16_mix_at_many_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int
     }
 }
 
-// ---- indexed variant: per-tile source lists built on the device (count, scan, fill), so that a
+// ---- indexed variant: per-tile source lists built on the device (count, allocate, fill), so that a
 // tile only visits the sources that touch it.  The lists come out of the atomics unordered;
 // the apply kernel rank-sorts each (short) list in shared memory to restore source order.
+// (a warp per source, a lane per tile it touches: the atomics of one source are all in flight at once)
 __global__ void mix_count_kernel(const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
                                  int64_t nsrc, int64_t dst_count, int *__restrict__ tile_count)
 {
-    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t s = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (s >= nsrc) return;
-    int64_t o = dst_off[s], l = src_len[s];
+    const int64_t o = dst_off[s], l = src_len[s];
     if (l <= 0 || o >= dst_count) return;
-    int64_t last = min(o + l, dst_count) - 1;
-    for (int64_t t = o / kMixTile; t <= last / kMixTile; t++) atomicAdd(&tile_count[t], 1);
+    const int64_t last = min(o + l, dst_count) - 1;
+    for (int64_t t = o / kMixTile + (threadIdx.x & 31); t <= last / kMixTile; t += 32) atomicAdd(&tile_count[t], 1);
 }
 
-__global__ void __launch_bounds__(1024)
-mix_scan_kernel(const int *__restrict__ tile_count, int64_t ntiles, int *__restrict__ tile_start, int *__restrict__ tile_fill)
+// Gives every tile a private range of the list: ranges need not be in tile order (each list is
+// rank-sorted when it is used), so a warp-aggregated atomic on one cursor replaces a scan.
+__global__ void mix_alloc_kernel(const int *__restrict__ tile_count, int64_t ntiles, int *__restrict__ cursor,
+                                 int *__restrict__ tile_start, int *__restrict__ tile_fill)
 {
-    __shared__ int s_warp[32];
-    __shared__ int s_running;
-    if (threadIdx.x == 0) s_running = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = 0; base < ntiles; base += 1024) {
-        int64_t i = base + threadIdx.x;
-        int v = (i < ntiles) ? tile_count[i] : 0;
-        int inc = v;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int v = (t < ntiles) ? tile_count[t] : 0;
+    int inc = v;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-        }
-        if (lane == 31) s_warp[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            int w = s_warp[lane], winc = w;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int o = __shfl_up_sync(0xffffffffu, winc, d);
-                if (lane >= d) winc += o;
-            }
-            s_warp[lane] = winc - w;
-        }
-        __syncthreads();
-        int ex = s_running + s_warp[warp] + inc - v;
-        if (i < ntiles) { tile_start[i] = ex; tile_fill[i] = 0; }
-        __syncthreads();
-        if (threadIdx.x == 1023) s_running = ex + v;
-        __syncthreads();
+    for (int d = 1; d < 32; d <<= 1) {
+        int o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
     }
-    if (threadIdx.x == 0) tile_start[ntiles] = s_running;
+    int base = 0;
+    if (lane == 31 && inc) base = atomicAdd(cursor, inc);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    if (t < ntiles) {
+        tile_start[t] = base + inc - v;
+        tile_fill[t] = 0;
+    }
 }
 
 __global__ void mix_fill_kernel(const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
                                 int64_t nsrc, int64_t dst_count, const int *__restrict__ tile_start,
                                 int *__restrict__ tile_fill, int *__restrict__ list)
 {
-    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t s = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (s >= nsrc) return;
-    int64_t o = dst_off[s], l = src_len[s];
+    const int64_t o = dst_off[s], l = src_len[s];
     if (l <= 0 || o >= dst_count) return;
-    int64_t last = min(o + l, dst_count) - 1;
-    for (int64_t t = o / kMixTile; t <= last / kMixTile; t++)
+    const int64_t last = min(o + l, dst_count) - 1;
+    for (int64_t t = o / kMixTile + (threadIdx.x & 31); t <= last / kMixTile; t += 32)
         list[tile_start[t] + atomicAdd(&tile_fill[t], 1)] = (int)s;
 }
 
-__global__ void __launch_bounds__(kPBlock)
+constexpr int kMixMeta = 128;            // sources per list chunk whose placement is staged in shared memory
+__global__ void __launch_bounds__(kPBlock, 8)
 mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__restrict__ pool,
                  const int64_t *__restrict__ src_off, const int64_t *__restrict__ src_len,
-                 const int64_t *__restrict__ dst_off, const int *__restrict__ tile_start,
-                 const int *__restrict__ list)
+                 const int64_t *__restrict__ dst_off, const int *__restrict__ tile_count,
+                 const int *__restrict__ tile_start, const int *__restrict__ list)
 {
     __shared__ int s_raw[kMixList];
     __shared__ int s_sorted[kMixList];
+    __shared__ int64_t s_o[kMixMeta], s_l[kMixMeta];
+    __shared__ const int16_t *s_p[kMixMeta];
     const int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
     constexpr int kPer = kMixTile / kPBlock;           // 8 consecutive destination samples per thread
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int begin = tile_start[tile], n = tile_start[tile + 1] - begin;
+        const int n = tile_count[tile];
         if (n == 0) continue;                          // block-uniform: nothing mixes into this tile
+        const int begin = tile_start[tile];
         const int64_t t0 = tile * kMixTile;
         const int64_t t1 = min(t0 + (int64_t)kMixTile, dst_count);
         const int64_t i0 = t0 + (int64_t)threadIdx.x * kPer;
+        const int live = (int)max((int64_t)0, min((int64_t)kPer, t1 - i0));    // this thread's samples inside the buffer
         int acc[kPer];
-        const bool full = (i0 + kPer <= t1) && ((((uintptr_t)(dst + i0)) & 15) == 0);
+        const bool full = (live == kPer) && ((((uintptr_t)(dst + i0)) & 15) == 0);
         if (full) {
             Vec8 v;
             v.v = *reinterpret_cast<const int4 *>(dst + i0);
@@ -473,7 +464,7 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
             for (int k = 0; k < kPer; k++) acc[k] = v.s[k];
         } else {
 #pragma unroll
-            for (int k = 0; k < kPer; k++) acc[k] = (i0 + k < t1) ? dst[i0 + k] : 0;
+            for (int k = 0; k < kPer; k++) acc[k] = (k < live) ? dst[i0 + k] : 0;
         }
         // the list in chunks of kMixList, each rank-sorted so that sources apply in index order;
         // chunks themselves are ordered by splitting on the source index range
@@ -500,16 +491,31 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
                 }
             }
             __syncthreads();
-            for (int q = 0; q < m; q++) {
-                const int64_t s = s_sorted[q];
-                const int64_t o = dst_off[s], l = src_len[s];
-                const int16_t *src = pool + src_off[s];
-                const int64_t r0 = i0 - o;
-                if (r0 + kPer <= 0 || r0 >= l) continue;            // this thread's run is outside
+            // Stage the placements of the chunk's sources with one round trip (instead of three
+            // dependent loads per source), then apply the sources in order.  All per-sample index
+            // arithmetic is 32-bit: the 64-bit part is done once per (thread, source).
+            // (Loading several sources' samples before adding any was tried and is slower: the
+            // kernel is bound by instruction issue, and empty batch slots cost instructions.)
+            for (int mb = 0; mb < m; mb += kMixMeta) {
+                const int mm = min(kMixMeta, m - mb);
+                if (mb) __syncthreads();
+                for (int i = threadIdx.x; i < mm; i += kPBlock) {
+                    const int64_t s = s_sorted[mb + i];
+                    s_o[i] = dst_off[s];
+                    s_l[i] = src_len[s];
+                    s_p[i] = pool + src_off[s];
+                }
+                __syncthreads();
+                for (int q = 0; q < mm; q++) {
+                    const int64_t r0 = i0 - s_o[q];                 // source index of this thread's first sample
+                    // samples k in [klo, khi) of the run are covered by the source (none if khi <= klo)
+                    const int klo = (int)max((int64_t)0, min((int64_t)kPer, -r0));
+                    const int khi = (int)max((int64_t)0, min((int64_t)live, s_l[q] - r0));
+                    if (khi <= klo) continue;
+                    const int16_t *p0 = s_p[q] + r0;
 #pragma unroll
-                for (int k = 0; k < kPer; k++) {
-                    const int64_t r = r0 + k;
-                    if (r >= 0 && r < l && i0 + k < t1) acc[k] = sat16(acc[k] + (int)src[r]);
+                    for (int k = 0; k < kPer; k++)
+                        if (k >= klo && k < khi) acc[k] = sat16(acc[k] + (int)p0[k]);
                 }
             }
         }
@@ -521,7 +527,7 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
         } else {
 #pragma unroll
             for (int k = 0; k < kPer; k++)
-                if (i0 + k < t1) dst[i0 + k] = (int16_t)acc[k];
+                if (k < live) dst[i0 + k] = (int16_t)acc[k];
         }
     }
 }
@@ -746,7 +752,7 @@ extern "C" int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t
     if (dst_count <= 0 || nsrc <= 0) return 0;
     int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
     int64_t cap = total_src_samples / kMixTile + 2 * nsrc + 1;     // every source touches <= len/tile + 2 tiles
-    return (3 * ntiles + 2 + cap) * (int64_t)sizeof(int);
+    return (3 * ntiles + 4 + cap) * (int64_t)sizeof(int);
 }
 
 extern "C" int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
@@ -767,22 +773,24 @@ extern "C" int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const i
         SB_LAUNCH_CHECK();
         return SB_OK;
     }
-    SB_REQUIRE(scratch_bytes >= (3 * ntiles + 2) * (int64_t)sizeof(int) + (int64_t)sizeof(int),
+    SB_REQUIRE(scratch_bytes >= (3 * ntiles + 4) * (int64_t)sizeof(int) + (int64_t)sizeof(int),
                "sb_pcm16_mix_at_many: scratch too small");
-    int *tile_count = (int *)scratch_dev;
+    // layout: cursor (4 ints), tile_count, tile_start, tile_fill, list
+    int *cursor = (int *)scratch_dev;
+    int *tile_count = cursor + 4;
     int *tile_start = tile_count + ntiles;
-    int *tile_fill = tile_start + ntiles + 1;
-    int *list = tile_fill + ntiles + 1;
-    SB_CUDA_CHECK(cudaMemsetAsync(tile_count, 0, (size_t)ntiles * sizeof(int), s));
-    int sgrid = (int)((nsrc + 255) / 256);
+    int *tile_fill = tile_start + ntiles;
+    int *list = tile_fill + ntiles;
+    SB_CUDA_CHECK(cudaMemsetAsync(cursor, 0, (size_t)(ntiles + 4) * sizeof(int), s));
+    int sgrid = (int)((nsrc * 32 + 255) / 256);             // a warp per source
     mix_count_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_count);
     SB_LAUNCH_CHECK();
-    mix_scan_kernel<<<1, 1024, 0, s>>>(tile_count, ntiles, tile_start, tile_fill);
+    mix_alloc_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, s>>>(tile_count, ntiles, cursor, tile_start, tile_fill);
     SB_LAUNCH_CHECK();
     mix_fill_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_start, tile_fill, list);
     SB_LAUNCH_CHECK();
     mix_apply_kernel<<<grid_for(ntiles, 1, kPMaxBlocks * 4), kPBlock, 0, s>>>(
-        dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, tile_start, list);
+        dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, tile_count, tile_start, list);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
