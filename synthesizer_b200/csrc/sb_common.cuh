@@ -165,6 +165,25 @@ __device__ __forceinline__ float envelope_at(const sb_envelope &e, int64_t n)
     return 0.0f;
 }
 
+// int <-> fp64 without conversion instructions (I2F / F2I / FRND run on the 16-lane XU pipe and
+// bound the integer PCM kernels; these are one integer and one fp64-pipe operation each):
+// exact for |x| < 2^31, and for |v| < 2^31 respectively.
+__device__ __forceinline__ double i32_to_f64(int x)
+{
+    // bits of 2^52 + 2^31 + x, minus that offset
+    return __dadd_rn(__hiloint2double(0x43300000, (int)((unsigned)x ^ 0x80000000u)), -4503601774854144.0);
+}
+__device__ __forceinline__ int f64_floor_to_i32(double v)
+{
+    // v + 1.5*2^52 rounded toward -inf: the low word holds floor(v) in two's complement
+    return __double2loint(__dadd_rd(v, 6755399441055744.0));
+}
+__device__ __forceinline__ int f64_trunc_to_i32(double v)
+{
+    const int m = __double2loint(__dadd_rd(fabs(v), 6755399441055744.0));      // floor(|v|)
+    return (__double2hiint(v) < 0) ? -m : m;
+}
+
 // IEEE a/b for a divisor known in advance: rcp_b = RN(1/b) once, then a product and two fused
 // correction steps per quotient (Markstein) instead of the ~40-instruction fp64 divide.  The
 // result is the correctly rounded quotient for normal a/b (b's significand not all ones, which

@@ -19,6 +19,12 @@ __device__ __forceinline__ int fbound16(double val)
     return (int)floor(val);
 }
 
+// the same for |val| < 2^31 (callers check their factors on the host): no conversion instructions
+__device__ __forceinline__ int fbound16_small(double val)
+{
+    return max(-32768, min(32767, f64_floor_to_i32(val)));
+}
+
 union Vec8 {
     int4 v;
     short s[8];
@@ -60,9 +66,13 @@ __global__ void pcm16_add_kernel(const int16_t *a, const int16_t *b, int64_t cou
     map16(a, b, out, count, [](int64_t, int x, int y) { return sat16(x + y); });
 }
 
+// SMALL: |factor| <= 16384 (checked on the host), so every product is below 2^31 in magnitude
+template <bool SMALL>
 __global__ void pcm16_mul_kernel(const int16_t *a, int64_t count, double factor, int16_t *out)
 {
-    map16(a, nullptr, out, count, [factor](int64_t, int x, int) { return fbound16(__dmul_rn((double)x, factor)); });
+    map16(a, nullptr, out, count, [factor](int64_t, int x, int) {
+        return SMALL ? fbound16_small(__dmul_rn(i32_to_f64(x), factor)) : fbound16(__dmul_rn((double)x, factor));
+    });
 }
 
 __global__ void pcm16_bias_kernel(const int16_t *a, int64_t count, int bias, int16_t *out)
@@ -71,22 +81,27 @@ __global__ void pcm16_bias_kernel(const int16_t *a, int64_t count, int bias, int
           [bias](int64_t, int x, int) { return (int)(int16_t)(uint16_t)((uint32_t)(uint16_t)x + (uint32_t)bias); });
 }
 
+// SMALL: fewer than 2^31 samples and volumes of at most 16384 in magnitude (checked on the host)
+template <bool SMALL>
 __global__ void pcm16_fadeout_kernel(int16_t *buf, int64_t nsamples, double decrease)
 {
     const double numsamples = (double)nsamples, rcp_n = __drcp_rn(numsamples);
     map16(buf, nullptr, buf, nsamples, [=](int64_t k, int x, int) {
         // int(sample * (1.0 - k*decrease/numsamples)), every operation rounded like CPython's
-        double f = __dsub_rn(1.0, div_by_known(__dmul_rn((double)k, decrease), numsamples, rcp_n));
-        return __double2int_rz(__dmul_rn((double)x, f));
+        const double kd = SMALL ? i32_to_f64((int)k) : (double)k;
+        double f = __dsub_rn(1.0, div_by_known(__dmul_rn(kd, decrease), numsamples, rcp_n));
+        return SMALL ? f64_trunc_to_i32(__dmul_rn(i32_to_f64(x), f)) : __double2int_rz(__dmul_rn((double)x, f));
     });
 }
 
+template <bool SMALL>
 __global__ void pcm16_fadein_kernel(int16_t *buf, int64_t nsamples, double increase, double start_volume)
 {
     const double numsamples = (double)nsamples, rcp_n = __drcp_rn(numsamples);
     map16(buf, nullptr, buf, nsamples, [=](int64_t k, int x, int) {
-        double f = __dadd_rn(div_by_known(__dmul_rn((double)k, increase), numsamples, rcp_n), start_volume);
-        return __double2int_rz(__dmul_rn((double)x, f));
+        const double kd = SMALL ? i32_to_f64((int)k) : (double)k;
+        double f = __dadd_rn(div_by_known(__dmul_rn(kd, increase), numsamples, rcp_n), start_volume);
+        return SMALL ? f64_trunc_to_i32(__dmul_rn(i32_to_f64(x), f)) : __double2int_rz(__dmul_rn((double)x, f));
     });
 }
 
@@ -118,27 +133,73 @@ __global__ void pcm16_maxabs_kernel(const int16_t *__restrict__ in, int64_t coun
     if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
+// SMALL: |lf|, |rf| <= 16384 (checked on the host)
+template <bool SMALL>
+__device__ __forceinline__ int mono_of(int l, int r, double lf, double rf)
+{
+    if (SMALL) return fbound16_small(__dadd_rn(__dmul_rn(i32_to_f64(l), lf), __dmul_rn(i32_to_f64(r), rf)));
+    return fbound16(__dadd_rn(__dmul_rn((double)l, lf), __dmul_rn((double)r, rf)));
+}
+
+// four frames per thread over the aligned bulk: 16 B in, 8 B out
+template <bool SMALL>
 __global__ void pcm16_tomono_kernel(const int16_t *__restrict__ in, int64_t frames, double lf, double rf,
                                     int16_t *__restrict__ out)
 {
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < frames; i += stride) {
-        short2 v = reinterpret_cast<const short2 *>(in)[i];
-        double val = __dadd_rn(__dmul_rn((double)v.x, lf), __dmul_rn((double)v.y, rf));
-        out[i] = (int16_t)fbound16(val);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+    const bool aligned = ((((uintptr_t)in) & 15) | (((uintptr_t)out) & 7)) == 0;
+    const int64_t nvec = aligned ? frames / 4 : 0;
+    for (int64_t v = tid; v < nvec; v += stride) {
+        Vec8 x;
+        x.v = reinterpret_cast<const int4 *>(in)[v];
+        short4 o;
+        o.x = (short)mono_of<SMALL>(x.s[0], x.s[1], lf, rf);
+        o.y = (short)mono_of<SMALL>(x.s[2], x.s[3], lf, rf);
+        o.z = (short)mono_of<SMALL>(x.s[4], x.s[5], lf, rf);
+        o.w = (short)mono_of<SMALL>(x.s[6], x.s[7], lf, rf);
+        reinterpret_cast<short4 *>(out)[v] = o;
     }
+    for (int64_t i = nvec * 4 + tid; i < frames; i += stride)
+        out[i] = (int16_t)mono_of<SMALL>(in[2 * i], in[2 * i + 1], lf, rf);
 }
 
+template <bool SMALL>
+__device__ __forceinline__ short2 stereo_of(int x, double lf, double rf)
+{
+    short2 o;
+    if (SMALL) {
+        const double v = i32_to_f64(x);
+        o.x = (short)fbound16_small(__dmul_rn(v, lf));
+        o.y = (short)fbound16_small(__dmul_rn(v, rf));
+    } else {
+        const double v = (double)x;
+        o.x = (short)fbound16(__dmul_rn(v, lf));
+        o.y = (short)fbound16(__dmul_rn(v, rf));
+    }
+    return o;
+}
+
+// four frames per thread over the aligned bulk: 8 B in, 16 B out
+template <bool SMALL>
 __global__ void pcm16_tostereo_kernel(const int16_t *__restrict__ in, int64_t frames, double lf, double rf,
                                       int16_t *__restrict__ out)
 {
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < frames; i += stride) {
-        double v = (double)in[i];
-        short2 o;
-        o.x = (short)fbound16(__dmul_rn(v, lf));
-        o.y = (short)fbound16(__dmul_rn(v, rf));
-        reinterpret_cast<short2 *>(out)[i] = o;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+    const bool aligned = ((((uintptr_t)in) & 7) | (((uintptr_t)out) & 15)) == 0;
+    const int64_t nvec = aligned ? frames / 4 : 0;
+    for (int64_t v = tid; v < nvec; v += stride) {
+        const short4 x = reinterpret_cast<const short4 *>(in)[v];
+        const short2 a = stereo_of<SMALL>(x.x, lf, rf), b = stereo_of<SMALL>(x.y, lf, rf);
+        const short2 c = stereo_of<SMALL>(x.z, lf, rf), d = stereo_of<SMALL>(x.w, lf, rf);
+        Vec8 o;
+        o.s[0] = a.x, o.s[1] = a.y, o.s[2] = b.x, o.s[3] = b.y;
+        o.s[4] = c.x, o.s[5] = c.y, o.s[6] = d.x, o.s[7] = d.y;
+        reinterpret_cast<int4 *>(out)[v] = o.v;
+    }
+    for (int64_t i = nvec * 4 + tid; i < frames; i += stride) {
+        const short2 o = stereo_of<SMALL>(in[i], lf, rf);
+        out[2 * i] = o.x;
+        out[2 * i + 1] = o.y;
     }
 }
 
@@ -551,7 +612,10 @@ extern "C" int sb_pcm16_mul(const int16_t *in_dev, int64_t count, double factor,
 {
     SB_REQUIRE(count >= 0 && (count == 0 || (in_dev && out_dev)), "sb_pcm16_mul: bad arguments");
     if (!count) return SB_OK;
-    pcm16_mul_kernel<<<PCM_GRID(count), kPBlock, 0, (cudaStream_t)stream>>>(in_dev, count, factor, out_dev);
+    if (fabs(factor) <= 16384.0)
+        pcm16_mul_kernel<true><<<PCM_GRID(count), kPBlock, 0, (cudaStream_t)stream>>>(in_dev, count, factor, out_dev);
+    else
+        pcm16_mul_kernel<false><<<PCM_GRID(count), kPBlock, 0, (cudaStream_t)stream>>>(in_dev, count, factor, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -589,8 +653,11 @@ extern "C" int sb_pcm16_tomono(const int16_t *in_dev, int64_t frames, double lfa
 {
     SB_REQUIRE(in_dev && out_dev && frames >= 0, "sb_pcm16_tomono: bad arguments");
     if (!frames) return SB_OK;
-    pcm16_tomono_kernel<<<grid_for(frames, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
-        in_dev, frames, lfactor, rfactor, out_dev);
+    const int grid = grid_for(frames / 4 + 1, kPBlock, kPMaxBlocks);
+    if (fabs(lfactor) <= 16384.0 && fabs(rfactor) <= 16384.0)
+        pcm16_tomono_kernel<true><<<grid, kPBlock, 0, (cudaStream_t)stream>>>(in_dev, frames, lfactor, rfactor, out_dev);
+    else
+        pcm16_tomono_kernel<false><<<grid, kPBlock, 0, (cudaStream_t)stream>>>(in_dev, frames, lfactor, rfactor, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -600,8 +667,11 @@ extern "C" int sb_pcm16_tostereo(const int16_t *in_dev, int64_t frames, double l
 {
     SB_REQUIRE(in_dev && out_dev && frames >= 0, "sb_pcm16_tostereo: bad arguments");
     if (!frames) return SB_OK;
-    pcm16_tostereo_kernel<<<grid_for(frames, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
-        in_dev, frames, lfactor, rfactor, out_dev);
+    const int grid = grid_for(frames / 4 + 1, kPBlock, kPMaxBlocks);
+    if (fabs(lfactor) <= 16384.0 && fabs(rfactor) <= 16384.0)
+        pcm16_tostereo_kernel<true><<<grid, kPBlock, 0, (cudaStream_t)stream>>>(in_dev, frames, lfactor, rfactor, out_dev);
+    else
+        pcm16_tostereo_kernel<false><<<grid, kPBlock, 0, (cudaStream_t)stream>>>(in_dev, frames, lfactor, rfactor, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -628,7 +698,10 @@ extern "C" int sb_pcm16_fadeout(int16_t *buf_dev, int64_t nsamples, double targe
 {
     SB_REQUIRE(nsamples >= 0 && (nsamples == 0 || buf_dev), "sb_pcm16_fadeout: bad arguments");
     if (!nsamples) return SB_OK;
-    pcm16_fadeout_kernel<<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - target_volume);
+    if (nsamples < (1LL << 31) && fabs(target_volume) <= 16384.0)
+        pcm16_fadeout_kernel<true><<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - target_volume);
+    else
+        pcm16_fadeout_kernel<false><<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - target_volume);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -637,8 +710,12 @@ extern "C" int sb_pcm16_fadein(int16_t *buf_dev, int64_t nsamples, double start_
 {
     SB_REQUIRE(buf_dev && nsamples >= 0, "sb_pcm16_fadein: bad arguments");
     if (!nsamples) return SB_OK;
-    pcm16_fadein_kernel<<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - start_volume,
-                                                                                   start_volume);
+    if (nsamples < (1LL << 31) && fabs(start_volume) <= 16384.0)
+        pcm16_fadein_kernel<true><<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - start_volume,
+                                                                                          start_volume);
+    else
+        pcm16_fadein_kernel<false><<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - start_volume,
+                                                                                           start_volume);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }

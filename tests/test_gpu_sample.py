@@ -162,6 +162,25 @@ def test_echo(cuda):
     _same(g.echo(0.3, 4, 0.11, 0.6), o.echo(0.3, 4, 0.11, 0.6), "echo")
 
 
+def test_huge_factors_and_ragged_lengths(cuda):
+    """Factors above 16384 take the kernels' general (converting) path, small ones the
+    conversion-free one; frame counts that are not a multiple of 4 exercise the scalar tails of
+    the vectorised mono / stereo kernels.  Both must equal audioop."""
+    for nfr in (1, 2, 3, 5, 4099):
+        g, o = _pair(_rand(2 * nfr, 40 + nfr), ch=2)
+        for lf, rf in ((0.5, 0.5), (1.0, -1.0), (16384.0, 1.0), (30000.0, -29999.5), (-1e6, 1e-6)):
+            _same(g.copy().mono(lf, rf), o.copy().mono(lf, rf), "mono %r %r n=%d" % (lf, rf, nfr))
+        m, mo = _pair(_rand(nfr, 41 + nfr))
+        for lf, rf in ((1.0, 1.0), (0.7, 1.4), (-16384.0, 16384.0), (1e5, -1e5)):
+            _same(m.copy().stereo(lf, rf), mo.copy().stereo(lf, rf), "stereo %r %r n=%d" % (lf, rf, nfr))
+        for f in (16384.0, -16384.0, 16384.5, 70000.25, -1e9, 1e300):
+            _same(m.copy().amplify(f), mo.copy().amplify(f), "amplify %r n=%d" % (f, nfr))
+    g, o = _pair(_rand(30011, 42))
+    for target in (0.0, 0.25, -0.5, 1.0):          # above 1 upstream's array('h') raises OverflowError
+        _same(g.copy().fadeout(0.3, target), o.copy().fadeout(0.3, target), "fadeout to %r" % target)
+        _same(g.copy().fadein(0.3, target), o.copy().fadein(0.3, target), "fadein from %r" % target)
+
+
 def test_channels(cuda):
     g, o = _pair(_rand(20000, 19), ch=2)
     _same(g.copy().mono(), o.copy().mono(), "mono")
