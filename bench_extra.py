@@ -78,7 +78,7 @@ def main():
     ]
     for name, nbytes, fn in cases:
         if fn is None:
-            nin = 44100 * 300
+            nin = 44100 * 600
             src_t = a[: nin * 2]
             nout = C.lib.sb_pcm16_ratecv_frames(nin, 44100, 48000)
             dst_t = torch.empty(nout * 2, dtype=torch.int16, device="cuda")

@@ -253,23 +253,38 @@ __device__ __forceinline__ RcvRate rcv_rate(int64_t inrate, int64_t outrate)
     return rt;
 }
 
+// int -> float and floor(float) -> int for magnitudes below 2^22, by adding 1.5*2^23: one integer
+// and one FMA-pipe operation each instead of a conversion on the 16-lane XU pipe
+__device__ __forceinline__ float small_int_to_float(int x)
+{
+    return __fadd_rn(__int_as_float(0x4B400000 + x), -12582912.0f);
+}
+__device__ __forceinline__ int small_floor_to_int(float x)
+{
+    return __float_as_int(__fadd_rd(x, 12582912.0f)) - 0x4B400000;
+}
+
+// FIXUP = false for outr <= 65536 (every real sample-rate pair): then ceil(outr/65536) = 1, a
+// remainder can never exceed outr - 1 = lim, and the negative fix-up above never applies.
+template <bool FIXUP>
 __device__ __forceinline__ int rcv_sample(int prev, int cur, uint32_t d, float w, const RcvRate &rt)
 {
     const int diff = prev - cur;
     // w = d/outr; the estimate is biased down by more than its error, so it is floor or floor-1
-    int est = __float2int_rd(__fmaf_rn((float)diff, w, -0.015625f));
+    int est = small_floor_to_int(__fmaf_rn(small_int_to_float(diff), w, -0.015625f));
     uint32_t r = (uint32_t)diff * d - (uint32_t)est * rt.outr;       // in [0, 2*outr)
     const bool hi = r >= rt.outr;
     est += hi ? 1 : 0;
-    r -= hi ? rt.outr : 0u;
     const int qf = cur + est;
+    if (!FIXUP) return qf;
+    r -= hi ? rt.outr : 0u;
     return qf + ((qf < 0 && r > rt.lim) ? 1 : 0);
 }
 
 // A lane's ITERS frames j0, j0+32, ...: all loads first (2*ITERS in flight per lane), then the
 // arithmetic and the stores.  `pin` points at the lane's newest input frame for j0, `pout` at
 // output frame j0; everything inside is 32-bit offsets from those.  FULL = every frame exists.
-template <int NCH, bool VEC, int ITERS, bool FULL>
+template <int NCH, bool VEC, int ITERS, bool FULL, bool FIXUP>
 __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16_t *__restrict__ pout, int nleft,
                                           bool first_is_frame0, uint32_t &crel, uint32_t &d, const RcvRate &rt)
 {
@@ -301,12 +316,12 @@ __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16
 #pragma unroll
     for (int it = 0; it < ITERS; it++) {
         if (FULL || it * 32 < nleft) {
-            const float w = __fmul_rn((float)dd[it], rt.rcp);
-            const int o0 = rcv_sample((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], w, rt);
+            const float w = __fmul_rn(small_int_to_float((int)dd[it]), rt.rcp);
+            const int o0 = rcv_sample<FIXUP>((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], w, rt);
             if (NCH == 1) {
                 pout[it * 32] = (int16_t)o0;
             } else {
-                const int o1 = rcv_sample((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], w, rt);
+                const int o1 = rcv_sample<FIXUP>((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], w, rt);
                 if (VEC) reinterpret_cast<uint32_t *>(pout)[it * 32] = ((uint32_t)o0 & 0xffffu) | ((uint32_t)o1 << 16);
                 else pout[it * 64] = (int16_t)o0, pout[it * 64 + 1] = (int16_t)o1;
             }
@@ -318,7 +333,7 @@ __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16
 // frames jc + l + 32*k.  A lane's first frame is placed by one 64-bit division (fp64 estimate
 // plus correction); each further frame is 32 outputs on, which moves (c, d) by constants.
 // Lanes map to consecutive output frames: coalesced stores, near-coalesced loads.
-template <int NCH, bool VEC, int ITERS, int BATCHES>
+template <int NCH, bool VEC, int ITERS, int BATCHES, bool FIXUP>
 __device__ __forceinline__ void rcv_chunk(const int16_t *__restrict__ in, int16_t *__restrict__ out, int64_t jc,
                                           int64_t out_frames, int64_t inrate, int64_t outrate, const RcvRate &rt,
                                           double rcp64)
@@ -339,21 +354,30 @@ __device__ __forceinline__ void rcv_chunk(const int16_t *__restrict__ in, int16_
     if (full) {
 #pragma unroll 1
         for (int b = 0; b < BATCHES; b++)
-            rcv_batch<NCH, VEC, ITERS, true>(pin, pout + (int64_t)b * 32 * ITERS * NCH, 0, b == 0 && j0 == 0, crel, d, rt);
+            rcv_batch<NCH, VEC, ITERS, true, FIXUP>(pin, pout + (int64_t)b * 32 * ITERS * NCH, 0, b == 0 && j0 == 0, crel, d, rt);
     } else {
         const int64_t left = out_frames - j0;
         for (int b = 0; b < BATCHES && (int64_t)b * 32 * ITERS < left; b++)
-            rcv_batch<NCH, VEC, ITERS, false>(pin, pout + (int64_t)b * 32 * ITERS * NCH,
+            rcv_batch<NCH, VEC, ITERS, false, FIXUP>(pin, pout + (int64_t)b * 32 * ITERS * NCH,
                                               (int)min(left - (int64_t)b * 32 * ITERS, (int64_t)(32 * ITERS)),
                                               b == 0 && j0 == 0, crel, d, rt);
     }
 }
 
-constexpr int kRcvIters = 8;             // frames a lane has in flight
-constexpr int kRcvBatches = 4;           // a warp owns 32*kRcvIters*kRcvBatches consecutive output frames
+#ifndef RCV_ITERS
+#define RCV_ITERS 8
+#endif
+#ifndef RCV_BATCHES
+#define RCV_BATCHES 4
+#endif
+#ifndef RCV_MIN_BLOCKS
+#define RCV_MIN_BLOCKS 4
+#endif
+constexpr int kRcvIters = RCV_ITERS;     // frames a lane has in flight
+constexpr int kRcvBatches = RCV_BATCHES; // a warp owns 32*kRcvIters*kRcvBatches consecutive output frames
 
 template <int NCH, bool VEC>
-__global__ void __launch_bounds__(kPBlock)
+__global__ void __launch_bounds__(kPBlock, RCV_MIN_BLOCKS)
 pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t inrate, int64_t outrate, int64_t out_frames,
                     int16_t *__restrict__ out)
 {
@@ -362,8 +386,13 @@ pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t inrate, int64_t outr
     const RcvRate rt = rcv_rate(inrate, outrate);
     const double rcp64 = 1.0 / (double)outrate;
     const int64_t chunk = 32 * kRcvIters * kRcvBatches;
-    for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
-        rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+    if (outrate <= 65536) {
+        for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
+            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, false>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+    } else {
+        for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
+            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, true>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+    }
 }
 
 // Sample.mix_at for many sources, in order.  Thread <-> destination sample; the sources that
@@ -800,9 +829,9 @@ pcm16_ratecv_many_kernel(const int16_t *__restrict__ in_pool, const int64_t *__r
         const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
         const bool vec = ((in_off[s] | out_off[s]) & 1) == 0 && pools_aligned;
         for (int64_t jc = warp_id * chunk; jc < nout; jc += nwarps * chunk) {
-            if (nch == 1) rcv_chunk<1, false, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
-            else if (vec) rcv_chunk<2, true, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
-            else rcv_chunk<2, false, kRcvManyIters, 1>(in, out, jc, nout, inr, outr, rt, rcp64);
+            if (nch == 1) rcv_chunk<1, false, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else if (vec) rcv_chunk<2, true, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else rcv_chunk<2, false, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
         }
     }
 }
