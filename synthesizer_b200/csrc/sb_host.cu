@@ -58,6 +58,9 @@ static int host_timebases(double samplerate, int64_t max_n)
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// one pinned word for the overflow counter, so that its device->host copy is asynchronous too
+static unsigned long long *g_pinned_ovf = nullptr;
+
 }  // namespace sb
 
 using namespace sb;
@@ -77,12 +80,7 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     sb_bank_plan plan;
     rc = sb_bank_plan_make(nvoices, frames, 0, sms, (int)g_tb.rad.size(), &plan);
     if (rc) return rc;
-    plan.generic_voices = 0;
-    plan.edged_voices = 0;
-    for (int v = 0; v < nvoices; v++) {
-        if (!sb_voice_is_fast(&voices[v], samplerate)) plan.generic_voices++;
-        else if (voices[v].c_wave >= SB_WAVE_SQUARE) plan.edged_voices++;
-    }
+    if (!g_pinned_ovf) SB_CUDA_CHECK(cudaHostAlloc((void **)&g_pinned_ovf, sizeof(unsigned long long), cudaHostAllocDefault));
 
     const size_t b_voices = align256((size_t)nvoices * sizeof(sb_voice));
     const size_t b_rad = align256(g_tb.rad.size() * sizeof(sb_time_seg));
@@ -106,6 +104,13 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
 
     cudaStream_t s = 0;
     SB_CUDA_CHECK(cudaMemcpyAsync(d_voices, voices, (size_t)nvoices * sizeof(sb_voice), cudaMemcpyHostToDevice, s));
+    // which kernels the bank needs: counted on the host while the voices are on their way
+    plan.generic_voices = 0;
+    plan.edged_voices = 0;
+    for (int v = 0; v < nvoices; v++) {
+        if (!sb_voice_is_fast(&voices[v], samplerate)) plan.generic_voices++;
+        else if (voices[v].c_wave >= SB_WAVE_SQUARE) plan.edged_voices++;
+    }
     SB_CUDA_CHECK(cudaMemcpyAsync(d_rad, g_tb.rad.data(), g_tb.rad.size() * sizeof(sb_time_seg), cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_cyc, g_tb.cyc.data(), g_tb.cyc.size() * sizeof(sb_time_seg), cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemsetAsync(d_ovf, 0, sizeof(unsigned long long), s));
@@ -115,10 +120,9 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     rc = sb_f32_to_pcm16(d_mix, frames * 2, scale, d_pcm, d_ovf, s);
     if (rc) return rc;
     SB_CUDA_CHECK(cudaMemcpyAsync(out_stereo, d_pcm, (size_t)frames * 2 * sizeof(int16_t), cudaMemcpyDeviceToHost, s));
-    unsigned long long ovf = 0;
-    SB_CUDA_CHECK(cudaMemcpyAsync(&ovf, d_ovf, sizeof(ovf), cudaMemcpyDeviceToHost, s));
+    SB_CUDA_CHECK(cudaMemcpyAsync(g_pinned_ovf, d_ovf, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     SB_CUDA_CHECK(cudaStreamSynchronize(s));
-    if (overflow) *overflow = ovf;
+    if (overflow) *overflow = *g_pinned_ovf;
     return SB_OK;
 }
 
