@@ -274,7 +274,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step_resident():
-        mix = bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0)
+        mix = bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0, scan_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -291,7 +291,7 @@ def run_ours(args):
                    e2e_out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(e2e_ovf))
             return
         vd = host_voices.to(D.device(), non_blocking=True)       # H2D of this step's inputs
-        mix = bank.render(frames, voices_dev=vd, generic_voices=0, edged_voices=0)
+        mix = bank.render(frames, voices_dev=vd, generic_voices=0, edged_voices=0, scan_voices=0)
         if world > 1:
             dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -343,7 +343,7 @@ def run_ours(args):
         l0 = D.launch_count()
         ev[0].record()
         for _ in range(reps):
-            bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0)
+            bank.render(frames, voices_dev=voices_dev, generic_voices=0, edged_voices=0, scan_voices=0)
         ev[1].record()
         torch.cuda.synchronize()
         render_ms = ev[0].elapsed_time(ev[1]) / reps

@@ -198,7 +198,7 @@ def main():
     bank = sb.VoiceBank(sr)
     for v in range(128):
         # mixed carrier waveforms; half of the voices have a sine vibrato, an eighth an LFO of
-        # another waveform (those take the generic per-sample fp64 kernel)
+        # another waveform (those take the tile-scan variant of the fast kernel)
         cw = int(rng.integers(0, 5))
         r = rng.random()
         lfo = None
@@ -220,20 +220,26 @@ def main():
         r = np.random.default_rng(11)
         for v in range(nv):
             lfo = None
-            if mw is not None:
+            f0 = float(r.uniform(55, 1760))
+            if mw == 5:          # a Sine modulator too strong for the fast path: 3.9 x 2 pi f0 / sr > 1.5 rad
+                lfo = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=sr)
+                f0 = float(r.uniform(3000, 5000))
+            elif mw is not None:
                 lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr)
-            car = classes[cw](float(r.uniform(55, 1760)), 0.9 / nv, fm_lfo=lfo, samplerate=sr)
+            car = classes[cw](f0, 0.9 / nv, fm_lfo=lfo, samplerate=sr)
             pan = float(r.uniform(-1, 1))
             b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
         return b
     for name, cw, mw, nv in [("Sine x Sine (fast, smooth)", 0, 0, 8192), ("Triangle, no FM (fast, smooth)", 1, None, 8192),
                              ("Sawtooth x Sine (fast, edged)", 3, 0, 8192), ("Square, no FM (fast, edged)", 2, None, 8192),
-                             ("Sine x Triangle LFO (generic)", 0, 1, 1024), ("Sawtooth x Square LFO (generic)", 3, 2, 1024)]:
+                             ("Sine x Triangle LFO (fast, tile scan)", 0, 1, 8192), ("Sawtooth x Square LFO (fast, tile scan)", 3, 2, 8192),
+                             ("Sine x Sine, FM gain 3 rad (generic)", 0, 5, 1024)]:
         b = class_bank(cw, mw, nv)
         vd, _ = b._upload(0, None)                       # voice parameters resident, as in bench.py
-        g, e = b.count_generic(), b.count_edged()
-        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e), max(2, args.reps // 4))
-        line("bank class: %s, %d voices x 10 s" % (name, nv), ms=ms, generic_voices=g, edged_voices=e,
+        g, e, sc = b.count_generic(), b.count_edged(), b.count_scan()
+        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc),
+                   max(2, args.reps // 4))
+        line("bank class: %s, %d voices x 10 s" % (name, nv), ms=ms, generic_voices=g, edged_voices=e, scan_voices=sc,
              msamples_per_s=nv * nfr / ms / 1e3)
 
 

@@ -233,7 +233,8 @@ typedef struct sb_bank_plan {
     int32_t nprefix;                     /* generic path: spans covering [0, n0), see below */
     int32_t edged_voices;                /* hint: 0 = no fast voice has a Square/Sawtooth/Pulse carrier
                                             (skip that kernel), -1 = unknown */
-    int32_t reserved;
+    int32_t scan_voices;                 /* hint: 0 = no voice has a Triangle/Square/Sawtooth/Pulse modulator on the
+                                            fast path (skip their pre-pass), -1 = unknown (run it over every voice) */
     int64_t n0;                          /* first frame of the render the plan was made for */
     int64_t off_fastv, off_tab;          /* layout of the scratch buffer */
     int64_t carry_bytes;                 /* size of scratch_dev: span sums + per-voice constants + FM tables */
@@ -247,12 +248,24 @@ typedef struct sb_bank_plan {
  * [0, n0) (cost proportional to n0 for those voices only). */
 int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan);
 
-/* 1 when the voice takes the fast path (any of the five carriers, with no FM or a Sine
- * modulator): fp32 per-sample arithmetic off one fp64 base per 8 samples, SFU sine, closed-form
- * FM sums; Square/Sawtooth/Pulse carriers re-evaluate in exact fp64 the few samples whose
- * phase is within 2e-5 cycles of an edge, so edges fall where upstream puts them.
- * Other voices (non-sine modulators, negative phases or frequencies on edged carriers) take
- * the generic path (per-sample fp64 phase). */
+/* Optional, between sb_bank_plan_make and allocating scratch_dev: how many voices of the bank
+ * are generic (sb_voice_is_fast == 0), have a Square/Sawtooth/Pulse carrier, and are of class 2
+ * (sb_voice_is_fast == 2); -1 = unknown.  Kernels no voice needs are not launched, and
+ * plan->carry_bytes shrinks to what the class-2 voices need (without the hint it is sized as if
+ * every voice were one: nvoices * (n0+frames)/512 * 8 bytes).  Counts must not be too small:
+ * a class-2 voice beyond scan_voices is handed to the generic kernels, which a generic_voices
+ * of 0 would have skipped. */
+int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int edged_voices, int scan_voices);
+
+/* Which path the voice takes:
+ *   1  fast: any of the five carriers, with no FM or a Sine modulator of moderate gain: fp32
+ *      per-sample arithmetic off one fp64 base per 16 samples, SFU sine, closed-form FM sums;
+ *      Square/Sawtooth/Pulse carriers re-evaluate in exact fp64 the few samples whose phase is
+ *      within 2e-5 cycles of an edge, so edges fall where upstream puts them;
+ *   2  fast with a Triangle/Square/Sawtooth/Pulse modulator: the same, with the FM sum taken
+ *      from a pre-pass (exact fp64 sums per 512 frames) plus a warp scan inside them;
+ *   0  generic (stronger FM, negative phases or frequencies on edged carriers or modulators):
+ *      per-sample fp64 phase. */
 int sb_voice_is_fast(const sb_voice *voice, double samplerate);
 
 /* Renders frames [n0, n0+plan->frames) of all voices.  tb_rad_dev / tb_cyc_dev: time bases

@@ -82,7 +82,24 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     if (rc) return rc;
     if (!g_pinned_ovf) SB_CUDA_CHECK(cudaHostAlloc((void **)&g_pinned_ovf, sizeof(unsigned long long), cudaHostAllocDefault));
 
+    // the voices go to their own workspace first, so that their copy can run while the host
+    // counts which kernels the bank needs (the count decides how much scratch the render takes)
     const size_t b_voices = align256((size_t)nvoices * sizeof(sb_voice));
+    rc = g_ws[2].ensure(b_voices);
+    if (rc) return rc;
+    sb_voice *d_voices = (sb_voice *)g_ws[2].ptr;
+    cudaStream_t s = 0;
+    SB_CUDA_CHECK(cudaMemcpyAsync(d_voices, voices, (size_t)nvoices * sizeof(sb_voice), cudaMemcpyHostToDevice, s));
+    int n_generic = 0, n_edged = 0, n_scan = 0;
+    for (int v = 0; v < nvoices; v++) {
+        const int cls = sb_voice_is_fast(&voices[v], samplerate);
+        if (!cls) n_generic++;
+        else if (voices[v].c_wave >= SB_WAVE_SQUARE) n_edged++;
+        if (cls == 2) n_scan++;
+    }
+    rc = sb_bank_plan_hint(&plan, n_generic, n_edged, n_scan);
+    if (rc) return rc;
+
     const size_t b_rad = align256(g_tb.rad.size() * sizeof(sb_time_seg));
     const size_t b_cyc = align256(g_tb.cyc.size() * sizeof(sb_time_seg));
     const size_t b_carry = align256((size_t)plan.carry_bytes);
@@ -90,10 +107,9 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     const size_t b_mix = align256((size_t)frames * 2 * sizeof(float));
     const size_t b_pcm = align256((size_t)frames * 2 * sizeof(int16_t));
     const size_t b_ovf = 256;
-    rc = g_ws[0].ensure(b_voices + b_rad + b_cyc + b_carry + b_partial + b_mix + b_pcm + b_ovf);
+    rc = g_ws[0].ensure(b_rad + b_cyc + b_carry + b_partial + b_mix + b_pcm + b_ovf);
     if (rc) return rc;
     unsigned char *p = (unsigned char *)g_ws[0].ptr;
-    sb_voice *d_voices = (sb_voice *)p; p += b_voices;
     sb_time_seg *d_rad = (sb_time_seg *)p; p += b_rad;
     sb_time_seg *d_cyc = (sb_time_seg *)p; p += b_cyc;
     void *d_carry = (void *)p; p += b_carry;
@@ -102,15 +118,6 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     int16_t *d_pcm = (int16_t *)p; p += b_pcm;
     unsigned long long *d_ovf = (unsigned long long *)p;
 
-    cudaStream_t s = 0;
-    SB_CUDA_CHECK(cudaMemcpyAsync(d_voices, voices, (size_t)nvoices * sizeof(sb_voice), cudaMemcpyHostToDevice, s));
-    // which kernels the bank needs: counted on the host while the voices are on their way
-    plan.generic_voices = 0;
-    plan.edged_voices = 0;
-    for (int v = 0; v < nvoices; v++) {
-        if (!sb_voice_is_fast(&voices[v], samplerate)) plan.generic_voices++;
-        else if (voices[v].c_wave >= SB_WAVE_SQUARE) plan.edged_voices++;
-    }
     SB_CUDA_CHECK(cudaMemcpyAsync(d_rad, g_tb.rad.data(), g_tb.rad.size() * sizeof(sb_time_seg), cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemcpyAsync(d_cyc, g_tb.cyc.data(), g_tb.cyc.size() * sizeof(sb_time_seg), cudaMemcpyHostToDevice, s));
     SB_CUDA_CHECK(cudaMemsetAsync(d_ovf, 0, sizeof(unsigned long long), s));

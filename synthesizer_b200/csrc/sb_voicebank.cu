@@ -69,10 +69,21 @@ enum : int {
     FV_ENV = 8,
     FV_ENV_EXTRA = 16,
     FV_BIAS = 32,
+    FV_SCAN = 64,            // Triangle/Square/Sawtooth/Pulse modulator: FM sum from the tile pre-pass + warp scan
     FV_WAVE_SHIFT = 8,       // bits 8..10: the carrier's waveform id
+    FV_MWAVE_SHIFT = 12,     // bits 12..14: the modulator's waveform id (FV_SCAN voices)
 };
 constexpr double kFastMaxFmGain = FAST_MAX_FM_GAIN;
-constexpr int kFastKinds = 10;              // kind = MOD | (carrier waveform << 1)
+constexpr int kFastKinds = 15;              // kind = MOD | (carrier waveform << 1) for no / Sine modulators,
+                                             // 10 + carrier waveform for the other modulators
+__host__ __device__ inline int fast_kind_of(int flags)
+{
+    const int wave = (flags >> FV_WAVE_SHIFT) & 7;
+    return (flags & FV_SCAN) ? 10 + wave : (((flags & FV_HAS_MOD) ? 1 : 0) | (wave << 1));
+}
+// kinds 0..3 (Sine / Triangle carrier, no or Sine modulator) run in bank_fast_kernel<0>, 4..9
+// (Square / Sawtooth / Pulse carrier) in <1>, 10..14 (piecewise-linear modulators) in <2>
+__host__ __device__ inline int fast_kind_part(int kind) { return kind >= 10 ? 2 : (kind >= 4 ? 1 : 0); }
 constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer than this to a
                                              // discontinuity are re-evaluated exactly in fp64
 
@@ -102,6 +113,9 @@ struct alignas(16) FastVoice {
     float pw;                // Pulse carriers: the (clamped) pulse width
 };
 static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
+// FV_SCAN voices have no use for `ini` and `half`; a Pulse modulator's (clamped) pulse width is
+// kept there in fp64
+__host__ __device__ inline double scan_m_pw64(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.half); }
 
 // Closed-form FM table entry per (voice, modulator time-base segment b), step w_b = fm*step_b:
 //   gd * sum_{k<n} sin(theta_k) = A - Cc*(gd cos theta_n) - (gd sin theta_n)/2      (n in segment b)
@@ -131,6 +145,11 @@ struct BankArgs {
     FastVoice *fastv;     // [nvoices]
     FmSeg *tab;           // [nvoices][nsegs_rad]: closed-form FM table per modulator segment
     double2 *lanetab;     // [nvoices][32]: (cos, sin)(lane * kFItems * w), the rotation from a sub-tile's anchor
+    double *lfo_prefix;   // [nvoices][lfo_rows]: FV_SCAN voices: sum of the modulator's shape over all frames
+                          // before tile `row` (tiles of kFSub frames: lfo_nprefix over [0, n0), then the render's)
+    int lfo_rows, lfo_nprefix;
+    int *scan_list;       // [1 + nvoices]: count, then the indices of the FV_SCAN voices (any order)
+    int scan_cap;         // rows of the pre-pass grid: how many list entries the launch covers
     int fast_nspans;
     int64_t fast_span_len;
     float *out;           // [ngroups][stride] partial mixes (or the mix itself if ngroups==1)
@@ -138,32 +157,44 @@ struct BankArgs {
 };
 
 // ------------------------------------------------------------------ classification
-__host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplerate)
+// 0 = generic, 1 = fast (no FM, or a Sine modulator: closed-form FM sum), 2 = fast with a
+// Triangle / Square / Sawtooth / Pulse modulator (FM sum from the tile pre-pass + a warp scan)
+__host__ __device__ inline int voice_class(const sb_voice &V, double samplerate)
 {
-    if (V.c_wave < SB_WAVE_SINE || V.c_wave > SB_WAVE_PULSE) return false;
+    if (V.c_wave < SB_WAVE_SINE || V.c_wave > SB_WAVE_PULSE) return 0;
     const double inc_c = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0) / samplerate;
     const double turns = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0);
     // carrier advance per 8-sample run must stay small enough for fp32 increments
-    if (!(fabs(V.c_freq) * inc_c * 8.0 < 64.0 * turns)) return false;
+    if (!(fabs(V.c_freq) * inc_c * 8.0 < 64.0 * turns)) return 0;
     if (V.c_wave >= SB_WAVE_SQUARE) {
         // discontinuous carriers: the fp32 run must resolve the phase to ~1e-6 cycles so that only
         // samples in a narrow guard band around an edge need the exact fp64 evaluation
-        if (!(V.c_freq >= 0.0 && V.c_freq * 2.0 <= samplerate && V.c_phase >= 0.0)) return false;
+        if (!(V.c_freq >= 0.0 && V.c_freq * 2.0 <= samplerate && V.c_phase >= 0.0)) return 0;
     }
-    if (V.m_wave == SB_WAVE_NONE) return true;
-    if (V.m_wave != SB_WAVE_SINE) return false;
-    const double w = V.m_freq * 6.283185307179586 / samplerate;      // modulator phase step
-    if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return false;            // closed form needs sin(w/2) != 0
-    if (!(fabs((double)V.m_amp) <= 4.0 && fabs((double)V.m_bias) <= 4.0)) return false;
+    if (V.m_wave == SB_WAVE_NONE) return 1;
+    if (V.m_wave < SB_WAVE_SINE || V.m_wave > SB_WAVE_PULSE) return 0;
+    if (!(fabs((double)V.m_amp) <= 4.0 && fabs((double)V.m_bias) <= 4.0)) return 0;
     // FM gain: carrier phase (radians) per unit of the modulator's running sum.  The fast path
-    // anchors that sum exactly (fp64 closed form) at the first frame of every 16-frame run and adds
-    // fp32 / SFU sines only inside the run; measured against the serial fp64 computation (tools/accuracy_sweep.py)
-    // the worst error is 0.28 LSB of full scale per radian of gain (it was 3.5 LSB per radian
-    // with a warp scan over the 512-frame sub-tile), so voices up to a gain of 1.5 are admitted;
+    // anchors that sum exactly (fp64) at the first frame of every 16-frame run and adds fp32
+    // values only inside the run; measured against the serial fp64 computation
+    // (tools/accuracy_sweep.py) the error stays below half an LSB of full scale up to a gain
+    // of 1.5 (it was 3.5 LSB per radian with an fp32 warp scan over the 512-frame sub-tile);
     // stronger FM takes the generic fp64 path.
     const double gain_rad = fabs(V.c_freq) * (6.283185307179586 / samplerate) * fabs((double)V.m_amp);
-    if (!(gain_rad <= kFastMaxFmGain)) return false;
-    return true;
+    if (!(gain_rad <= kFastMaxFmGain)) return 0;
+    if (V.m_wave == SB_WAVE_SINE) {
+        const double w = V.m_freq * 6.283185307179586 / samplerate;  // modulator phase step
+        if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return 0;            // closed form needs sin(w/2) != 0
+        return 1;
+    }
+    // piecewise-linear modulators: the periodic rules below hold for non-negative phases, and the
+    // fp32 run must resolve the modulator phase like an edged carrier's
+    if (!(V.m_freq >= 0.0 && V.m_freq * 2.0 <= samplerate && V.m_phase >= 0.0)) return 0;
+    return 2;
+}
+__host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplerate)
+{
+    return voice_class(V, samplerate) != 0;
 }
 
 // cos(r) for |r| <= pi + small, fp64 Taylor to r^26 (error < 1e-13)
@@ -223,13 +254,14 @@ __global__ void bank_prepare_kernel(BankArgs a)
     if (v >= a.nvoices) return;                          // the whole warp leaves
     const sb_voice V = a.voices[v];
     constexpr int H = kFItems / 2;
-    const bool fast = voice_is_fast(V, a.samplerate);
+    const int cls = voice_class(V, a.samplerate);
+    const bool fast = cls != 0, scan = cls == 2;
     const bool tri = (V.c_wave != SB_WAVE_SINE);         // phase counted in cycles (all but Sine)
     const double inc_rad = 6.283185307179586 / a.samplerate;
     const double inc_c = tri ? 1.0 / a.samplerate : inc_rad;
     const bool has_mod = (V.m_wave != SB_WAVE_NONE);
     const double mbias = has_mod ? (double)V.m_bias : 0.0;
-    const double fm = V.m_freq, pcm = phase0_of(SB_WAVE_SINE, V.m_phase);
+    const double fm = V.m_freq, pcm = scan ? V.m_phase : phase0_of(SB_WAVE_SINE, V.m_phase);
     const double f0b = V.c_freq * (1.0 + mbias);
     const double gd = has_mod ? V.c_freq * inc_c * (double)V.m_amp : 0.0;
     const double w = fm * inc_rad;                        // nominal modulator phase step
@@ -255,12 +287,27 @@ __global__ void bank_prepare_kernel(BankArgs a)
         const double R = (fabs(sh) > 1e-300) ? sin(0.5 * (double)H * w) / sh : (double)H;
         const double mid = 0.5 * (double)(H - 1) * w;
         F.half = make_float4((float)cos((double)H * w), (float)sin((double)H * w), (float)(cos(mid) * R), (float)(sin(mid) * R));
+        bool demote = false;
+        if (scan) {
+            // slot in the list = row block of the modulator prefix table (kept in tab_row, unused
+            // here).  A voice beyond the capacity the caller's scan_voices hint allowed for is
+            // left to the generic kernels.
+            const int slot = a.scan_cap > 0 ? atomicAdd(a.scan_list, 1) : 0;
+            if (slot < a.scan_cap) {
+                a.scan_list[1 + slot] = v;
+                F.tab_row = slot;
+                *reinterpret_cast<double *>(&F.half) = clamp_pulsewidth((double)V.m_pw);
+                F.flags |= FV_SCAN | ((V.m_wave & 7) << FV_MWAVE_SHIFT);
+            } else {
+                demote = true;
+            }
+        }
         F.bL = V.c_bias * V.gain_l;
         F.bR = V.c_bias * V.gain_r;
         F.gain = make_float4(V.c_amp * V.gain_l, V.c_amp * V.gain_l, V.c_amp * V.gain_r, V.c_amp * V.gain_r);
         F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
         F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
-        if (fast) F.flags |= FV_FAST;
+        if (fast && !demote) F.flags |= FV_FAST;
         if (has_mod) F.flags |= FV_HAS_MOD;
         if (tri) F.flags |= FV_TRIANGLE;
         F.flags |= (V.c_wave & 7) << FV_WAVE_SHIFT;
@@ -269,7 +316,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
         if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
         a.fastv[v] = F;
     }
-    if (!(fast && has_mod)) return;
+    if (!(cls == 1 && has_mod)) return;
 
     // Closed form of sum_{k<n} sin(theta_k), theta_k = fm*t(k) + pcm, t piecewise linear:
     // inside segment b (start n_b, t_b, step_b): theta_k = theta_b + (k-n_b)*w_b and
@@ -343,12 +390,73 @@ __device__ __forceinline__ double reduce_two_pi_fast(double x)
     return fma(-k, kTwoPiLo, r);
 }
 
+// Exact unit-amplitude value of a Triangle / Square / Sawtooth / Pulse modulator at time t
+// (cycles time base), operation for operation what upstream's oscillator computes.  The phase
+// is non-negative here (voice_class admits only such modulators), so Python's int() and % 1.0
+// are floors, taken with one round-down add of 1.5*2^52 instead of a conversion.
+__device__ __forceinline__ double floor_nonneg(double x)
+{
+    return __dadd_rn(__dadd_rd(x, 6755399441055744.0), -6755399441055744.0);
+}
+__device__ __forceinline__ double lfo_shape_exact(int mwave, double t, double fm, double phm, double pw)
+{
+    const double ph = __dadd_rn(__dmul_rn(t, fm), phm);
+    switch (mwave) {
+    case SB_WAVE_TRIANGLE: {
+        const double x = __dadd_rn(ph, 0.75);
+        return 4.0 * (fabs((x - floor_nonneg(x)) - 0.5) - 0.25);
+    }
+    case SB_WAVE_SQUARE:
+        return (__double2loint(__dadd_rd(__dmul_rn(ph, 2.0), 6755399441055744.0)) & 1) ? -1.0 : 1.0;
+    case SB_WAVE_SAWTOOTH:
+        return 2.0 * (ph - floor_nonneg(__dadd_rn(0.5, ph)));
+    default:
+        return ((ph - floor_nonneg(ph)) < pw) ? 1.0 : -1.0;
+    }
+}
+
+struct FastCtx;
+template <int MW>
+__device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t n, double fm, double phm, double mpw,
+                                        double gd, float2 (&sv)[kFItems / 2], double &tot);
+
 struct FastCtx {
     const sb_time_seg *s_cyc;
     int nsegs_cyc;
+    double cstep;            // cycles time base: step of the segment holding this lane's first frame
+    bool cstraddle;          // ... and whether the lane's run crosses into the next segment
+    const double *lfo_row;   // FV_SCAN voices: modulator sums before this sub-tile, row stride lfo_rows
+    int64_t lfo_rows;
     const FmSeg *tab_seg;    // closed-form FM table, offset to this lane's time-base segment: row stride nsegs_rad
     const double2 *lt_lane;  // anchor -> lane rotation table, offset to this lane: row stride 32
 };
+
+// The 16 values of a piecewise-linear modulator over a lane's run, exactly as upstream computes
+// them; sv = the FM increments gd*value in fp32 (frame pairs (q, q+H)), tot = the sum of the values.
+// Square / Pulse values are +-1: their increments need no fp64 -> fp32 conversion.
+template <int MW>
+__device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t n, double fm, double phm, double mpw,
+                                        double gd, float2 (&sv)[kFItems / 2], double &tot)
+{
+    constexpr int H = kFItems / 2;
+    const float gdf = (float)gd;
+    tot = 0.0;
+#pragma unroll
+    for (int j = 0; j < kFItems; j++) {
+        double t;
+        if (!ctx.cstraddle) {
+            t = __dadd_rn(Tc0, __dmul_rn((double)j, ctx.cstep));          // exact inside a time-base segment
+        } else {
+            TimeCursor c;
+            c.seek(ctx.s_cyc, ctx.nsegs_cyc, n + j);
+            t = c.at(n + j);
+        }
+        const double v = lfo_shape_exact(MW, t, fm, phm, mpw);
+        tot += v;
+        const float inc = (MW == SB_WAVE_SQUARE || MW == SB_WAVE_PULSE) ? (v > 0.0 ? gdf : -gdf) : (float)(gd * v);
+        if (j < H) sv[j].x = inc; else sv[j - H].y = inc;
+    }
+}
 
 // Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
 // way upstream forms it (no FM: fl(fl(t*f) + phase), bit for bit).  Called only for samples
@@ -409,7 +517,11 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
 // is exact (+-1, or a continuous ramp) unless the phase sits within kEdgeGuard cycles of a
 // discontinuity; those few samples are redone in fp64 exactly as upstream forms the phase, so
 // every edge lands on the sample upstream puts it on.
-template <bool MOD, int WAVE, bool RARE, bool FLAT>
+// MODC: 0 = no modulator, 1 = Sine modulator (closed form + recurrence), 2 = Triangle / Square /
+// Sawtooth / Pulse modulator: its 16 values are evaluated exactly (fp64, as upstream does) and
+// the FM sum ahead of the run is the tile pre-pass's prefix plus an fp64 warp scan of the lanes'
+// run totals.
+template <int MODC, int WAVE, bool RARE, bool FLAT>
 __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2 anc, const float2 env,
                                                const double Tr0, const double Tc0, const double dstep,
                                                const float lane8, const int64_t n,
@@ -417,6 +529,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
                                                float2 (&accR2)[kFItems / 2])
 {
     constexpr int H = kFItems / 2;
+    constexpr bool MOD = MODC != 0;
     constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
     constexpr bool EDGES = (WAVE >= SB_WAVE_SQUARE);
     const double2 car = F.car;
@@ -426,7 +539,30 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     double gbefore = 0.0;                   // gd * (FM sum ahead of this lane's run)
     float2 sn = make_float2(0.0f, 0.0f), dl = make_float2(0.0f, 0.0f);
     float half_sum = 0.0f;                  // gd * (sum of the first half-run's sines)
-    if (MOD) {
+    float2 sv[kFItems / 2];                 // MODC 2: the FM increments gd*lfo of frames (q, q+H)
+    if (MODC == 2) {
+        const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+        const double fm = F.mod.x, phm = F.mod.y, gd = F.gd, mpw = scan_m_pw64(F);
+        double tot;
+        switch (mwave) {                                // warp-uniform
+        case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
+        case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
+        case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
+        default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
+        }
+        const int lane = threadIdx.x & 31;
+        double incl = tot;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const double o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        gbefore = gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + (incl - tot));
+        B += gbefore;
+#pragma unroll
+        for (int q = 0; q < H; q++) half_sum += sv[q].x;
+    }
+    if (MODC == 1) {
         const double2 L = ctx.lt_lane[F.lt_row];
         const FmSeg fs = ctx.tab_seg[F.tab_row];
         // gd*(cos, sin) of the modulator phase at this lane's first frame
@@ -505,9 +641,12 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
         accR2[q] = __ffma2_rn(we, aR2, accR2[q]);
         if (q + 1 < H) {
             P = __fadd2_rn(P, cstep);
+            if (MODC == 2) sn = sv[q];
             if (MOD) {
                 P = __fadd2_rn(P, sn);
                 if (EDGES) run = __fadd2_rn(run, sn);
+            }
+            if (MODC == 1) {
                 dl = __ffma2_rn(nk2, sn, dl);
                 sn = __fadd2_rn(sn, dl);
             }
@@ -525,22 +664,22 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
                                                 const int64_t n, const FastCtx ctx,
                                                 float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
 {
-    constexpr bool MOD = (KIND & 1) != 0;
-    constexpr int WAVE = KIND >> 1;
+    constexpr int MOD = KIND >= 10 ? 2 : (KIND & 1);         // modulator class (see fast_voice_run)
+    constexpr int WAVE = KIND >= 10 ? KIND - 10 : (KIND >> 1);
     const double2 none = make_double2(0.0, 0.0);
     int v = begin;
 #if FAST_PAIR_VOICES
     // two voices per iteration in one basic block: their (independent) dependency chains give
     // the scheduler twice the instruction-level parallelism to hide MUFU / fp64 latency
-    if (WAVE < SB_WAVE_SQUARE) {
+    if (WAVE < SB_WAVE_SQUARE && MOD != 2) {
         for (; v + 1 < end; v += 2) {
             const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
             const float2 e0 = s_env[v * kFastMaxSub + s], e1 = s_env[(v + 1) * kFastMaxSub + s];
             // both envelopes plain lines (sign bits clear: not kEnvSilent / kEnvSlow), no carrier bias
             const bool plain = (__float_as_int(e0.x) | __float_as_int(e1.x)) >= 0 && !((F0.flags | F1.flags) & FV_BIAS);
             if (!plain) break;                                                  // warp-uniform
-            const double2 a0 = MOD ? s_anc[v * kFastMaxSub + s] : none;
-            const double2 a1 = MOD ? s_anc[(v + 1) * kFastMaxSub + s] : none;
+            const double2 a0 = MOD == 1 ? s_anc[v * kFastMaxSub + s] : none;
+            const double2 a1 = MOD == 1 ? s_anc[(v + 1) * kFastMaxSub + s] : none;
             if (((__float_as_int(e0.y) | __float_as_int(e1.y)) << 1) == 0) {     // both slopes +-0: warp-uniform
                 fast_voice_run<MOD, WAVE, false, true>(F0, a0, e0, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
                 fast_voice_run<MOD, WAVE, false, true>(F1, a1, e1, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
@@ -555,7 +694,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
         const FastVoice &F = s_fv[v];
         const float2 env = s_env[v * kFastMaxSub + s];
         if (env.x == kEnvSilent) continue;                                      // warp-uniform
-        const double2 anc = MOD ? s_anc[v * kFastMaxSub + s] : none;
+        const double2 anc = MOD == 1 ? s_anc[v * kFastMaxSub + s] : none;
         if (env.x == kEnvSlow || (F.flags & FV_BIAS))
             fast_voice_run<MOD, WAVE, true, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         else
@@ -563,14 +702,17 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
     }
 }
 
-// EDGED = false: Sine / Triangle carriers; writes the group's partial mix (zeros included).
-// EDGED = true : Square / Sawtooth / Pulse carriers; runs afterwards and adds into it.  Two
+// PART 0: Sine / Triangle carriers with no or a Sine modulator; writes the group's partial mix
+//         (zeros included).
+// PART 1: Square / Sawtooth / Pulse carriers with no or a Sine modulator; adds into it.
+// PART 2: any carrier with a Triangle / Square / Sawtooth / Pulse modulator; adds into it.  Separate
 // kernels rather than one so that the exact-fallback call and its register needs stay out of
 // the smooth carriers' loop (the headline path).
-template <bool EDGED>
-__global__ void __launch_bounds__(kFastWarps * 32, FAST_MIN_BLOCKS)
+template <int PART>
+__global__ void __launch_bounds__(kFastWarps * 32, PART == 2 ? 4 : FAST_MIN_BLOCKS)   // part 2: 128 registers for its fp64 run
 bank_fast_kernel(BankArgs a)
 {
+    constexpr bool EDGED = PART != 0;                  // adds into what part 0 wrote
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
     const size_t nrec = (size_t)kFastWarps * a.voices_per_group * kFastMaxSub;
@@ -592,13 +734,13 @@ bank_fast_kernel(BankArgs a)
     for (int v = threadIdx.x; v < nv; v += blockDim.x) {
         const FastVoice *src = a.fastv + v_begin;
         const int fl = src[v].flags;
-        const int kind = ((fl & FV_HAS_MOD) ? 1 : 0) | (((fl >> FV_WAVE_SHIFT) & 7) << 1);
-        if ((fl & FV_FAST) && (kind >= 4) == EDGED) {
+        const int kind = fast_kind_of(fl);
+        if ((fl & FV_FAST) && fast_kind_part(kind) == PART) {
             int pos = 0;
             for (int u = 0; u < nv; u++) {
                 const int fu = src[u].flags;
-                const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | (((fu >> FV_WAVE_SHIFT) & 7) << 1);
-                if (!(fu & FV_FAST) || (ku >= 4) != EDGED) continue;
+                const int ku = fast_kind_of(fu);
+                if (!(fu & FV_FAST) || fast_kind_part(ku) != PART) continue;
                 pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
             }
             const int4 *w = reinterpret_cast<const int4 *>(src + v);
@@ -611,8 +753,8 @@ bank_fast_kernel(BankArgs a)
         int c = 0;
         for (int u = 0; u < nv; u++) {
             const int fu = a.fastv[v_begin + u].flags;
-            const int ku = ((fu & FV_HAS_MOD) ? 1 : 0) | (((fu >> FV_WAVE_SHIFT) & 7) << 1);
-            if (!(fu & FV_FAST) || (ku >= 4) != EDGED) continue;
+            const int ku = fast_kind_of(fu);
+            if (!(fu & FV_FAST) || fast_kind_part(ku) != PART) continue;
             c += (ku <= (int)threadIdx.x) ? 1 : 0;
         }
         s_kind_end[threadIdx.x] = c;
@@ -642,7 +784,7 @@ bank_fast_kernel(BankArgs a)
         const int64_t lo = a.n0 + span_begin + (int64_t)s * kFSub, hi = lo + kFSub;
         double2 anc = make_double2(0.0, 0.0);
         float2 r = make_float2(1.0f, 0.0f);                 // e_sub, de
-        if (F.flags & FV_HAS_MOD) {
+        if ((F.flags & (FV_HAS_MOD | FV_SCAN)) == FV_HAS_MOD) {     // Sine modulators only
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, lo);
             const double th = reduce_two_pi(fma(F.mod.x, c.at(lo), F.mod.y));
@@ -681,9 +823,21 @@ bank_fast_kernel(BankArgs a)
             Tr0 = c.at(n);
             ctx.tab_seg = a.tab + c.idx;
             dstep = (double)(lane * kFItems) * (c.step - inc_rad);
+            ctx.cstep = 0.0;
+            ctx.cstraddle = false;
             if (any_cyc) {                              // carriers whose phase counts in cycles present
                 c.seek(s_cyc, a.nsegs_cyc, n);
                 Tc0 = c.at(n);
+                if (PART == 2) {                        // (modulators evaluated per sample live in this part only)
+                    ctx.cstep = c.step;
+                    ctx.cstraddle = (n + kFItems >= c.next_start);
+                }
+            }
+            ctx.lfo_rows = 0;
+            ctx.lfo_row = nullptr;
+            if (PART == 2) {                            // tile row of this sub-tile in the modulator prefix table
+                ctx.lfo_rows = a.lfo_rows;
+                ctx.lfo_row = a.lfo_prefix + a.lfo_nprefix + (span_begin + (int64_t)s * kFSub) / kFSub;
             }
         }
         // keep both in registers for the voice loops (the compiler would otherwise recompute
@@ -694,18 +848,24 @@ bank_fast_kernel(BankArgs a)
 #pragma unroll
         for (int q = 0; q < H; q++) accL2[q] = accR2[q] = make_float2(0.0f, 0.0f);
 
-        if (!EDGED) {
+        if (PART == 0) {
             fast_voice_loop<0>(s_fv, s_anc, s_env, 0, ke[0], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<1>(s_fv, s_anc, s_env, ke[0], ke[1], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<2>(s_fv, s_anc, s_env, ke[1], ke[2], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<3>(s_fv, s_anc, s_env, ke[2], ke[3], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
-        } else {
+        } else if (PART == 1) {
             fast_voice_loop<4>(s_fv, s_anc, s_env, 0, ke[4], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<5>(s_fv, s_anc, s_env, ke[4], ke[5], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<6>(s_fv, s_anc, s_env, ke[5], ke[6], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<7>(s_fv, s_anc, s_env, ke[6], ke[7], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<8>(s_fv, s_anc, s_env, ke[7], ke[8], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             fast_voice_loop<9>(s_fv, s_anc, s_env, ke[8], ke[9], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+        } else {
+            fast_voice_loop<10>(s_fv, s_anc, s_env, 0, ke[10], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<11>(s_fv, s_anc, s_env, ke[10], ke[11], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<12>(s_fv, s_anc, s_env, ke[11], ke[12], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<13>(s_fv, s_anc, s_env, ke[12], ke[13], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            fast_voice_loop<14>(s_fv, s_anc, s_env, ke[13], ke[14], s, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         }
 
         // frame j of the run is accL2[j].x for j < H and accL2[j-H].y above; two frames per float4
@@ -738,6 +898,91 @@ bank_fast_kernel(BankArgs a)
     }
 }
 
+__device__ __forceinline__ double warp_scan_incl(double v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        double o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += o;
+    }
+    return v;
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// ------------------------------------------------------------------ modulator tile pre-pass
+// FV_SCAN voices (Triangle / Square / Sawtooth / Pulse modulators): the sum of the modulator's
+// unit-amplitude values over every tile of kFSub frames, evaluated exactly (the same function
+// the fast kernel uses per sample), then turned into an exclusive prefix per voice.  Rows:
+// lfo_nprefix tiles over [0, n0) (the FM sum accumulated before this render starts; the last
+// one may be short), then the render's own tiles from n0.  One warp per (voice, tile).
+__global__ void __launch_bounds__(kGenWarps * 32)
+bank_lfo_tile_kernel(BankArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    sb_time_seg *s_cyc = reinterpret_cast<sb_time_seg *>(smem);
+    for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * kGenWarps + (threadIdx.x >> 5);
+    if (row >= a.lfo_rows) return;
+    int64_t begin, end;
+    if (row < a.lfo_nprefix) {
+        begin = (int64_t)row * kFSub;
+        end = min(begin + kFSub, a.n0);
+    } else {
+        begin = a.n0 + (int64_t)(row - a.lfo_nprefix) * kFSub;
+        end = min(begin + kFSub, a.n0 + a.frames);
+    }
+    // the times of this lane's frames (lane, lane+32, ...) are the same for every voice
+    double t[kFItems];
+    {
+        TimeCursor c;
+        c.seek(s_cyc, a.nsegs_cyc, begin + lane);
+#pragma unroll
+        for (int j = 0; j < kFItems; j++) {
+            const int64_t k = begin + lane + 32 * j;
+            t[j] = (k < end) ? c.at(k) : -1.0;
+        }
+    }
+    const int nscan = min(a.scan_list[0], a.scan_cap);
+    for (int e = blockIdx.y; e < nscan; e += gridDim.y) {
+        const FastVoice &F = a.fastv[a.scan_list[1 + e]];
+        const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+        const double fm = F.mod.x, phm = F.mod.y, mpw = scan_m_pw64(F);
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < kFItems; j++)
+            if (t[j] >= 0.0) acc += lfo_shape_exact(mwave, t[j], fm, phm, mpw);
+        acc = warp_sum(acc);
+        if (lane == 0) a.lfo_prefix[(int64_t)e * a.lfo_rows + row] = acc;
+    }
+}
+
+// in-place exclusive prefix over the rows of each FV_SCAN voice: one warp per voice
+__global__ void __launch_bounds__(kGenWarps * 32)
+bank_lfo_prefix_kernel(BankArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const int nscan = min(a.scan_list[0], a.scan_cap);
+    for (int e = blockIdx.x * kGenWarps + (threadIdx.x >> 5); e < nscan; e += gridDim.x * kGenWarps) {
+        double *rowp = a.lfo_prefix + (int64_t)e * a.lfo_rows;
+        double carry = 0.0;
+        for (int r0 = 0; r0 < a.lfo_rows; r0 += 32) {
+            const int r = r0 + lane;
+            const double v = (r < a.lfo_rows) ? rowp[r] : 0.0;
+            const double incl = warp_scan_incl(v, lane);
+            if (r < a.lfo_rows) rowp[r] = carry + (incl - v);
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+    }
+}
+
 // ------------------------------------------------------------------ generic path
 // Base value and step of a time base for a run of kItems+1 consecutive indices.
 struct TimeRun {
@@ -760,23 +1005,6 @@ __device__ __forceinline__ double run_at(const TimeRun &r, const sb_time_seg *se
     TimeCursor c;
     c.seek(segs, nsegs, n + j);
     return c.at(n + j);
-}
-
-__device__ __forceinline__ double warp_scan_incl(double v, int lane)
-{
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        double o = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d) v += o;
-    }
-    return v;
-}
-
-__device__ __forceinline__ double warp_sum(double v)
-{
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-    return v;
 }
 
 // Modulator value in fp64, as upstream computes it.  fp32 would not do here: the FM sum adds
@@ -1034,6 +1262,29 @@ __global__ void bank_fold_kernel(const float *__restrict__ partial, int ngroups,
 
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
+// Scratch layout after the span sums and FastVoice array (plan->off_tab onwards): closed-form FM
+// table, lane rotation table, list of FV_SCAN voices, and last - so that its size can follow
+// the scan_voices hint - the modulator tile prefix table [scan slots][rows].
+static inline int64_t bank_off_lanetab(const sb_bank_plan *p)
+{
+    return align_up(p->off_tab + (int64_t)p->nvoices * p->nsegs_rad * (int64_t)sizeof(FmSeg), 256);
+}
+static inline int64_t bank_off_scanlist(const sb_bank_plan *p)
+{
+    return bank_off_lanetab(p) + align_up((int64_t)p->nvoices * 32 * (int64_t)sizeof(double2), 256);
+}
+static inline int64_t bank_off_lfo(const sb_bank_plan *p)
+{
+    return bank_off_scanlist(p) + align_up((int64_t)(p->nvoices + 1) * (int64_t)sizeof(int), 256);
+}
+static inline int64_t bank_lfo_nprefix(const sb_bank_plan *p) { return (p->n0 + kFSub - 1) / kFSub; }
+static inline int64_t bank_lfo_rows(const sb_bank_plan *p) { return bank_lfo_nprefix(p) + (p->frames + kFSub - 1) / kFSub; }
+static inline int64_t bank_scratch_bytes(const sb_bank_plan *p)
+{
+    const int64_t slots = p->scan_voices < 0 ? p->nvoices : p->scan_voices;
+    return bank_off_lfo(p) + align_up(slots * bank_lfo_rows(p) * (int64_t)sizeof(double), 256);
+}
+
 }  // namespace sb
 
 using namespace sb;
@@ -1041,7 +1292,7 @@ using namespace sb;
 extern "C" int sb_voice_is_fast(const sb_voice *voice, double samplerate)
 {
     if (!voice || !(samplerate > 1)) return 0;
-    return voice_is_fast(*voice, samplerate) ? 1 : 0;
+    return voice_class(*voice, samplerate);
 }
 
 extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan)
@@ -1087,16 +1338,28 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     plan->nsegs_rad = nsegs_rad;
     plan->generic_voices = -1;
     plan->edged_voices = -1;
+    plan->scan_voices = -1;
     plan->n0 = n0;
     const int64_t nprefix = (n0 + span_len - 1) / span_len;
     SB_REQUIRE(nprefix < 0x7fffffff, "sb_bank_plan_make: start offset too large");
     plan->nprefix = (int32_t)nprefix;
     plan->off_fastv = align_up((int64_t)nvoices * (nprefix + nspans) * (int64_t)sizeof(double), 256);
     plan->off_tab = align_up(plan->off_fastv + (int64_t)nvoices * (int64_t)sizeof(FastVoice), 256);
-    // the closed-form FM table, then the lane rotation table [nvoices][32]
-    plan->carry_bytes = align_up(plan->off_tab + (int64_t)nvoices * nsegs_rad * (int64_t)sizeof(FmSeg), 256) +
-                        align_up((int64_t)nvoices * 32 * (int64_t)sizeof(double2), 256);
+    SB_REQUIRE(bank_lfo_rows(plan) < 0x7fffffff, "sb_bank_plan_make: too many frames");
+    plan->carry_bytes = bank_scratch_bytes(plan);          // worst case until sb_bank_plan_hint() says otherwise
     plan->partial_bytes = (ngroups > 1) ? (int64_t)ngroups * ((frames * 2 + 3) / 4 * 4) * (int64_t)sizeof(float) : 0;
+    return SB_OK;
+}
+
+extern "C" int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int edged_voices, int scan_voices)
+{
+    SB_REQUIRE(plan && plan->nvoices >= 1 && generic_voices >= -1 && edged_voices >= -1 && scan_voices >= -1 &&
+                   generic_voices <= plan->nvoices && edged_voices <= plan->nvoices && scan_voices <= plan->nvoices,
+               "sb_bank_plan_hint: bad arguments");
+    plan->generic_voices = generic_voices;
+    plan->edged_voices = edged_voices;
+    plan->scan_voices = scan_voices;
+    plan->carry_bytes = bank_scratch_bytes(plan);
     return SB_OK;
 }
 
@@ -1139,7 +1402,13 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.carry = (plan->nspans + plan->nprefix > 1) ? (double *)scratch : nullptr;
     a.fastv = (FastVoice *)(scratch + plan->off_fastv);
     a.tab = (FmSeg *)(scratch + plan->off_tab);
-    a.lanetab = (double2 *)(scratch + align_up(plan->off_tab + (int64_t)plan->nvoices * nsegs_rad * (int64_t)sizeof(FmSeg), 256));
+    a.lanetab = (double2 *)(scratch + bank_off_lanetab(plan));
+    a.scan_list = (int *)(scratch + bank_off_scanlist(plan));
+    a.lfo_prefix = (double *)(scratch + bank_off_lfo(plan));
+    a.lfo_nprefix = (int)bank_lfo_nprefix(plan);
+    a.lfo_rows = (int)bank_lfo_rows(plan);
+    a.scan_cap = plan->scan_voices < 0 ? plan->nvoices : plan->scan_voices;
+    if (plan->scan_voices != 0) SB_CUDA_CHECK(cudaMemsetAsync(a.scan_list, 0, sizeof(int), s));
     a.fast_nspans = plan->fast_nspans;
     a.fast_span_len = plan->fast_span_len;
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
@@ -1147,6 +1416,20 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
+    if (plan->scan_voices != 0) {
+        // modulator tile sums of the FV_SCAN voices, then their prefix (the fast kernel reads it)
+        // a CTA keeps its frames' times in registers and walks the voices in steps of grid.y
+        const int64_t tx = (a.lfo_rows + kGenWarps - 1) / kGenWarps;
+        int64_t ty = (1184 * 4 + tx - 1) / tx;
+        if (ty > a.scan_cap) ty = a.scan_cap;
+        if (ty < 1) ty = 1;
+        dim3 tgrid((unsigned)tx, (unsigned)ty);
+        bank_lfo_tile_kernel<<<tgrid, kGenWarps * 32, (size_t)nsegs_cyc * sizeof(sb_time_seg), s>>>(a);
+        SB_LAUNCH_CHECK();
+        const int pgrid = (a.scan_cap + kGenWarps - 1) / kGenWarps;
+        bank_lfo_prefix_kernel<<<pgrid < 1184 ? pgrid : 1184, kGenWarps * 32, 0, s>>>(a);
+        SB_LAUNCH_CHECK();
+    }
 
     const size_t tb_bytes = (size_t)(nsegs_rad + nsegs_cyc) * sizeof(sb_time_seg);
     {
@@ -1154,14 +1437,19 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
                       (size_t)kFastWarps * a.voices_per_group * kFastMaxSub * (sizeof(double2) + sizeof(float2));
         if (smem > 48 * 1024)
         {
-            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         }
         dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
-        bank_fast_kernel<false><<<grid, kFastWarps * 32, smem, s>>>(a);
+        bank_fast_kernel<0><<<grid, kFastWarps * 32, smem, s>>>(a);
         SB_LAUNCH_CHECK();
         if (plan->edged_voices != 0) {
-            bank_fast_kernel<true><<<grid, kFastWarps * 32, smem, s>>>(a);
+            bank_fast_kernel<1><<<grid, kFastWarps * 32, smem, s>>>(a);
+            SB_LAUNCH_CHECK();
+        }
+        if (plan->scan_voices != 0) {
+            bank_fast_kernel<2><<<grid, kFastWarps * 32, smem, s>>>(a);
             SB_LAUNCH_CHECK();
         }
     }

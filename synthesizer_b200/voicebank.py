@@ -108,12 +108,18 @@ class VoiceBank:
         return sum(1 for v in self._voices[begin:end]
                    if not C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)))
 
+    def count_scan(self, begin=0, end=None):
+        """Voices of [begin, end) on the fast path with a Triangle / Square / Sawtooth / Pulse
+        modulator (class 2: their FM sum comes from a tile pre-pass)."""
+        return sum(1 for v in self._voices[begin:end]
+                   if C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)) == 2)
+
     def count_edged(self, begin=0, end=None):
         """Voices of [begin, end) with a Square / Sawtooth / Pulse carrier (the second fast kernel)."""
         return sum(1 for v in self._voices[begin:end] if v.c_wave >= C.WAVE_SQUARE)
 
     def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None,
-               edged_voices=None):
+               edged_voices=None, scan_voices=None):
         """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
@@ -121,6 +127,7 @@ class VoiceBank:
             voices_dev, nv = self._upload(begin, end)
             generic_voices = self.count_generic(begin, end)
             edged_voices = self.count_edged(begin, end)
+            scan_voices = self.count_scan(begin, end)
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
         mix = D.empty(2 * nframes, torch.float32)
@@ -130,10 +137,9 @@ class VoiceBank:
         sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
         tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
         C.call("sb_bank_plan_make", nv, nframes, start, sms, tr.nsegs, ctypes.byref(plan))
-        if generic_voices is not None:
-            plan.generic_voices = generic_voices
-        if edged_voices is not None:
-            plan.edged_voices = edged_voices
+        unknown = lambda x: -1 if x is None else x
+        C.call("sb_bank_plan_hint", ctypes.byref(plan), unknown(generic_voices), unknown(edged_voices),
+               unknown(scan_voices))
         carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
         partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,

@@ -48,6 +48,19 @@ def make_bank(nvoices, sr, seed, duration, waves=None, fm=True):
     return bank, P
 
 
+def force_some_generic(bank, P):
+    """Gives every other voice with a non-sine modulator a negative modulator start phase: the
+    fast path's periodic rules need it non-negative, so those voices take the generic kernel
+    (negative phases are legal upstream: Python's % and int() define the waveform there)."""
+    k = 0
+    for i, v in enumerate(bank._voices):
+        if v.m_wave > 0:
+            k += 1
+            if k % 2:
+                v.m_phase = P[i, 9] = -0.3 - 0.01 * i
+    bank._dev = None
+
+
 def oracle_bank_pcm(P, nframes, sr, mpw=None):
     from oracle import coracle as co
     left, right = co.voice_bank(P, nframes, sr)
@@ -145,6 +158,36 @@ def test_fm_accuracy_sweep_full_scale(cuda, cw):
     assert seen == {0, 1}, "the sweep is meant to exercise both the fast and the generic kernels"
 
 
+@pytest.mark.parametrize("mw", [1, 2, 3, 4])
+def test_piecewise_modulators_full_scale(cuda, mw):
+    """Triangle / Square / Sawtooth / Pulse modulators on the fast path (class 2: exact fp64
+    modulator values per run, tile pre-pass + warp scan for the FM sum): one FULL-SCALE voice per
+    (carrier, f0, modulator f, depth) against the oracle, 3 s so that the sum runs over many
+    tiles, and a second render started mid-way that must continue the same sum."""
+    import itertools
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n, cut = 48000, 144000, 70001
+    classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    for cw, f0, fm, d in itertools.product((0, 3), (110.3, 2217.7), (0.37, 6.1, 331.3), (0.02, 0.4)):
+        mkw = dict(pulsewidth=0.37) if mw == 4 else {}
+        lfo = classes[mw](fm, d, 0.3, 0.05, samplerate=sr, **mkw)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 2, (cw, f0, fm, d)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(mw, n, sr, fm, d, 0.3, 0.05, pulsewidth=0.37)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        flips = err > 100          # a sawtooth carrier's wrap one sample early/late
+        assert flips.sum() <= (3 if cw == 3 else 0), (cw, f0, fm, d, int(flips.sum()))
+        assert err[~flips].max() < 0.9, "cw=%d f0=%g fm=%g depth=%g: %.3f LSB" % (cw, f0, fm, d, err[~flips].max())
+        tail = bank.render(n - cut, start=cut).cpu().numpy()[0::2].astype(np.float64)
+        terr = np.abs(tail - want[cut:]) * 32767.0
+        assert (terr > 100).sum() <= (3 if cw == 3 else 0) and terr[terr <= 100].max() < 0.9, (cw, f0, fm, d)
+
+
 def test_fast_and_generic_voices_share_a_group(cuda):
     """A group holding both classes: the generic kernel adds into what the fast one wrote."""
     import synthesizer_b200 as sb
@@ -154,9 +197,10 @@ def test_fast_and_generic_voices_share_a_group(cuda):
     for v in bank._voices:
         if v.m_wave == 4:
             v.m_pw = 0.1
+    force_some_generic(bank, P)
     kinds = [C.lib.sb_voice_is_fast(ctypes.byref(v), float(sr)) for v in bank._voices]
-    assert 0 < sum(kinds) < len(kinds)
-    assert bank.count_generic() == len(kinds) - sum(kinds)
+    assert set(kinds) == {0, 1, 2}, "the bank is meant to hold generic, closed-form and tile-scan voices"
+    assert bank.count_generic() == kinds.count(0) and bank.count_scan() == kinds.count(2)
     got = dev_pcm16(bank.render(n))
     bad = np.abs(got.astype(np.int64) - oracle_bank_pcm(P, n, sr)) > 1
     assert bad.mean() < 2e-5
@@ -177,13 +221,14 @@ def test_bank_chunked_start_offsets(cuda):
 
 def test_bank_start_offset_with_fm_voices_of_both_classes(cuda):
     """A render that starts at n0 > 0 must continue every voice's FM sum from frame 0: fast
-    voices by closed form, generic ones through the pre-pass over [0, n0)."""
+    voices by closed form, tile-scan and generic ones through their pre-passes over [0, n0)."""
     sr, n, cut = 48000, 40000, 23456
     bank, P = make_bank(20, sr, 123, 0.8, fm=True)
     for v in bank._voices:
         if v.m_wave == 4:
             v.m_pw = 0.1
-    assert 0 < bank.count_generic() < 20
+    force_some_generic(bank, P)
+    assert bank.count_generic() > 0 and bank.count_scan() > 0 and bank.count_generic() + bank.count_scan() < 20
     whole = bank.render(n).cpu().numpy()
     tail = bank.render(n - cut, start=cut).cpu().numpy()
     off = np.abs(tail - whole[2 * cut:]) > 1e-6
