@@ -138,6 +138,57 @@ def test_bank_plan_covers_the_work():
         assert 1 <= plan.voices_per_group <= 64
 
 
+def test_bank_plan_hint_sizes_the_scratch():
+    """Without a hint the scratch is sized as if every voice needed the modulator tile table;
+    the hint shrinks it to the class-2 voices and records which kernels can be skipped."""
+    nv, frames = 1000, 480_000
+    plan = C.BankPlan()
+    C.call("sb_bank_plan_make", nv, frames, 0, 148, 40, ctypes.byref(plan))
+    assert (plan.generic_voices, plan.edged_voices, plan.scan_voices) == (-1, -1, -1)
+    worst = plan.carry_bytes
+    rows = (frames + 511) // 512
+    assert worst >= nv * rows * 8
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, 0)
+    none = plan.carry_bytes
+    assert none <= worst - nv * rows * 8 and (plan.generic_voices, plan.edged_voices, plan.scan_voices) == (0, 0, 0)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 3, 10, 7)
+    assert none + 7 * rows * 8 <= plan.carry_bytes <= none + 7 * rows * 8 + 256
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), -1, -1, -1)
+    assert plan.carry_bytes == worst
+    with pytest.raises(C.SbError):
+        C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, nv + 1)
+    # a start offset adds the tiles over [0, n0)
+    shifted = C.BankPlan()
+    C.call("sb_bank_plan_make", nv, frames, 512 * 10 + 1, 148, 40, ctypes.byref(shifted))
+    C.call("sb_bank_plan_hint", ctypes.byref(shifted), 0, 0, 7)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, 7)
+    assert shifted.carry_bytes - plan.carry_bytes >= 7 * 11 * 8 - 256
+
+
+def test_voice_classes_on_the_host():
+    """sb_voice_is_fast: 1 = closed-form fast path, 2 = tile-scan fast path, 0 = generic."""
+    v = C.Voice()
+    v.c_wave, v.c_freq, v.c_amp, v.c_pw = C.WAVE_SINE, 440.0, 0.5, 0.1
+    v.m_wave = C.WAVE_NONE
+    cls = lambda: C.lib.sb_voice_is_fast(ctypes.byref(v), 48000.0)
+    assert cls() == 1
+    v.m_wave, v.m_freq, v.m_amp, v.m_pw = C.WAVE_SINE, 5.0, 0.05, 0.1
+    assert cls() == 1
+    for w in (C.WAVE_TRIANGLE, C.WAVE_SQUARE, C.WAVE_SAWTOOTH, C.WAVE_PULSE):
+        v.m_wave = w
+        assert cls() == 2
+    v.m_phase = -0.25
+    assert cls() == 0                       # negative modulator phase: periodic rules do not hold
+    v.m_phase, v.m_amp = 0.0, 30.0          # 2*pi*440/48000 * 30 = 1.7 rad per unit of modulator output
+    assert cls() == 0
+    v.m_amp, v.c_wave, v.c_phase = 0.05, C.WAVE_SQUARE, -0.1
+    assert cls() == 0                       # edged carrier starting at a negative phase
+    v.c_phase = 0.3
+    assert cls() == 2
+    v.m_wave = C.WAVE_SINE
+    assert cls() == 1
+
+
 def test_no_gpu_means_loud_failure_not_fallback():
     import torch
     if torch.cuda.is_available():
