@@ -360,9 +360,9 @@ def run_ours(args):
         peak_gsin = 16 * sms * sm_mhz * 1e6 / 1e9
         achieved_gsin = 2 * (hi - lo) * frames / (render_ms / 1e3) / 1e9
         # DRAM traffic of the dominant kernel from the committed ncu capture
-        # (profiles/r1j_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
-        # of bank_fast_kernel on this workload): 9.6 MB read + 440.2 MB written
-        ncu_traffic = 9648384 + 440207872 if (hi - lo) == VOICES_PER_GPU else None
+        # (profiles/r1k_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
+        # of bank_fast_kernel on this workload): 8.8 MB read + 440.2 MB written
+        ncu_traffic = 8760064 + 440221696 if (hi - lo) == VOICES_PER_GPU else None
         # "achieved" counts ALGORITHMIC sines (2 per voice-sample: modulator + carrier), like
         # algorithmic bytes on an HBM roofline; the kernel issues fewer SFU operations than that
         # (the modulator's sines come from a two-term recurrence: 16 MUFU per 16 frames, not 32).
