@@ -251,9 +251,20 @@ def run_ours(args):
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
     torch.cuda.set_device(local)
     if world > 1:
-        # NCCL's own banner ("NCCL version ...") goes to stdout by default: keep stdout to the one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL prints its banner ("NCCL version ...") on stdout when the communicator is created
+        # (NCCL_DEBUG_FILE does not move it): point fd 1 at stderr until that has happened, so
+        # that stdout carries the one JSON line and nothing else
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     frames = int(SR * SECONDS)
     total_voices = VOICES_PER_GPU * world
     p = voice_params(total_voices)
