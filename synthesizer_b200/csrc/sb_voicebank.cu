@@ -84,8 +84,6 @@ __host__ __device__ inline int fast_kind_of(int flags)
 // kinds 0..3 (Sine / Triangle carrier, no or Sine modulator) run in bank_fast_kernel<0>, 4..9
 // (Square / Sawtooth / Pulse carrier) in <1>, 10..14 (piecewise-linear modulators) in <2>
 __host__ __device__ inline int fast_kind_part(int kind) { return kind >= 10 ? 2 : (kind >= 4 ? 1 : 0); }
-constexpr float kEdgeGuard = 2e-5f;          // cycles: fp32 run phases closer than this to a
-                                             // discontinuity are re-evaluated exactly in fp64
 
 // Per-voice constants of the fast path, derived once per render by bank_prepare_kernel.
 // The first six 128-bit words are everything the per-run set-up and the per-sample loop need
@@ -280,6 +278,14 @@ __global__ void bank_prepare_kernel(BankArgs a)
         const double sh = sin(0.5 * w);
         const float k = (float)(4.0 * sh * sh);
         F.stepk = make_float4(wc, wc, -k, -k);
+        if (V.c_wave >= SB_WAVE_SQUARE) {
+            // edged carriers walk an integer phase (2^32 = one cycle): the step and the pulse
+            // width as such integers, in the slots of the fp32 step
+            const double cyc = f0b * inc_c;
+            const double wfrac = cyc - floor(cyc);
+            F.stepk.x = __uint_as_float((uint32_t)(unsigned long long)llrint(wfrac * 4294967296.0));
+            F.stepk.y = __uint_as_float((uint32_t)(unsigned long long)llrint(clamp_pulsewidth((double)V.c_pw) * 4294967296.0));
+        }
         F.Hwc = (float)((double)H * f0b * inc_c);
         const float hk = (float)(2.0 * sh * sh), sw = (float)sin(w);
         F.ini = make_float4(hk, hk, sw, sw);
@@ -460,7 +466,7 @@ __device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t 
 
 // Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
 // way upstream forms it (no FM: fl(fl(t*f) + phase), bit for bit).  Called only for samples
-// whose fp32 run phase is within kEdgeGuard of an edge, or while the phase may still be negative.
+// whose run phase is within the guard band of an edge, or while the phase may still be negative.
 __device__ __noinline__ float exact_shape(int wave, FastCtx ctx, int64_t k, double f0b, double pc0,
                                           double fm_term, int has_mod, double pw)
 {
@@ -472,28 +478,7 @@ __device__ __noinline__ float exact_shape(int wave, FastCtx ctx, int64_t k, doub
     return wave_shape(wave, tt, pw);
 }
 
-// fp32 shape of a discontinuous waveform from a phase in cycles, plus whether that phase is
-// too close to an edge for fp32 to be trusted
-template <int WAVE>
-__device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
-{
-    if (WAVE == SB_WAVE_SAWTOOTH) {
-        const float g = ph + 0.5f;
-        const float f = g - floorf(g);                     // jumps where 0.5 + tt crosses an integer
-        near = fminf(f, 1.0f - f) < kEdgeGuard;
-        return fmaf(2.0f, f, -1.0f);                       // 2*(tt - floor(0.5 + tt))
-    }
-    const float f = ph - floorf(ph);
-    if (WAVE == SB_WAVE_SQUARE) {
-        near = fminf(fminf(f, 1.0f - f), fabsf(f - 0.5f)) < kEdgeGuard;
-        return f < 0.5f ? 1.0f : -1.0f;                    // int(tt*2) % 2
-    }
-    near = fminf(fminf(f, 1.0f - f), fabsf(f - pw)) < kEdgeGuard;
-    return f < pw ? 1.0f : -1.0f;                          // tt % 1.0 < pulsewidth
-}
-
-// One voice over one lane's run of kFItems frames.  MOD: Sine modulator present.  WAVE: the
-// carrier.  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
+// One voice over one lane's run of kFItems frames.  WAVE: the carrier (Sine or Triangle).  RARE: per-sample envelope and/or carrier bias (warp-uniform, uncommon).
 //
 // Frame pairing: the packed fp32x2 operations (Blackwell FFMA2/FADD2/FMUL2) work on frames
 // (q, q+H) of the lane's run, H = kFItems/2.  accL2[q] = left-channel sums of frames (q, q+H),
@@ -513,10 +498,7 @@ __device__ __forceinline__ float guarded_shape(float ph, float pw, bool &near)
 // sub-tile's anchor with the lane table (plus the first-order term for the time-base segment's
 // own step: dstep = (frames from the sub-tile start) * (segment step - nominal step)); the FM sum ahead of the run from the closed form; the carrier phase base.
 //
-// Square / Sawtooth / Pulse carriers: their value is evaluated in fp32 like the others, which
-// is exact (+-1, or a continuous ramp) unless the phase sits within kEdgeGuard cycles of a
-// discontinuity; those few samples are redone in fp64 exactly as upstream forms the phase, so
-// every edge lands on the sample upstream puts it on.
+// (Square / Sawtooth / Pulse carriers: edged_voice_run below.)
 // MODC: 0 = no modulator, 1 = Sine modulator (closed form + recurrence), 2 = Triangle / Square /
 // Sawtooth / Pulse modulator: its 16 values are evaluated exactly (fp64, as upstream does) and
 // the FM sum ahead of the run is the tile pre-pass's prefix plus an fp64 warp scan of the lanes'
@@ -531,7 +513,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     constexpr int H = kFItems / 2;
     constexpr bool MOD = MODC != 0;
     constexpr bool CYC = (WAVE != SB_WAVE_SINE);            // phase counted in cycles
-    constexpr bool EDGES = (WAVE >= SB_WAVE_SQUARE);
+    static_assert(WAVE == SB_WAVE_SINE || WAVE == SB_WAVE_TRIANGLE, "edged carriers go through edged_voice_run");
     const double2 car = F.car;
     const float4 stepk = F.stepk;           // wc, wc, -k, -k
     const float4 gain = F.gain;             // aL, aL, aR, aR
@@ -592,11 +574,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     } else {
         b0 = (float)reduce_two_pi_fast(B);
     }
-    // while the (unreduced) phase may still be negative, Square's int() truncation is not the
-    // periodic rule: take the exact path for the whole run (only the first cycles of a voice)
-    const bool low = EDGES && !(B > 16.0);
     float2 P = make_float2(b0, b0 + F.Hwc + half_sum);
-    float2 run = make_float2(0.0f, 0.0f);   // EDGES only: gd * (sines summed so far in each half)
     const float e0 = fmaf(lane8, env.y, env.x);
     float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
     const float2 cstep = make_float2(stepk.x, stepk.y), nk2 = make_float2(stepk.z, stepk.w);
@@ -607,25 +585,15 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
         aL2 = __fmul2_rn(aL2, ec);
         aR2 = __fmul2_rn(aR2, ec);
     }
-    const float pw = (WAVE == SB_WAVE_PULSE) ? F.pw : 0.0f;
 #pragma unroll
     for (int q = 0; q < H; q++) {
         float2 w;
         if (WAVE == SB_WAVE_SINE) {
             w.x = __sinf(P.x);
             w.y = __sinf(P.y);
-        } else if (WAVE == SB_WAVE_TRIANGLE) {
+        } else {
             w.x = tri_shape(P.x);
             w.y = tri_shape(P.y);
-        } else {
-            bool nx, ny;
-            w.x = guarded_shape<WAVE>(P.x, pw, nx);
-            w.y = guarded_shape<WAVE>(P.y, pw, ny);
-            if (nx || low)
-                w.x = exact_shape(WAVE, ctx, n + q, car.x, car.y, MOD ? gbefore + (double)run.x : 0.0, MOD, F.pw64);
-            if (ny || low)
-                w.y = exact_shape(WAVE, ctx, n + q + H, car.x, car.y,
-                                  MOD ? gbefore + (double)half_sum + (double)run.y : 0.0, MOD, F.pw64);
         }
         float2 ee = e;
         if (RARE) {
@@ -642,15 +610,214 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
         if (q + 1 < H) {
             P = __fadd2_rn(P, cstep);
             if (MODC == 2) sn = sv[q];
-            if (MOD) {
-                P = __fadd2_rn(P, sn);
-                if (EDGES) run = __fadd2_rn(run, sn);
-            }
+            if (MOD) P = __fadd2_rn(P, sn);
             if (MODC == 1) {
                 dl = __ffma2_rn(nk2, sn, dl);
                 sn = __fadd2_rn(sn, dl);
             }
             if (!FLAT) e = __fadd2_rn(e, estep);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ edged carriers, integer phase
+// Square / Sawtooth / Pulse carriers: their value is exact (+-1, or a continuous ramp) unless the
+// phase sits within a guard band of a discontinuity; those few samples are redone in fp64
+// exactly as upstream forms the phase, so every edge lands on the sample upstream puts it on.
+// They keep their phase as a 32-bit fraction of a cycle (2^32 = one
+// cycle): the carrier step is an integer add that wraps for free, the waveform value and the
+// "within the guard band of an edge" test are two or three integer operations each, and the
+// resolution (2^-32 cycles, against fp32's 6e-8) lets the guard band shrink to 5e-7 cycles for
+// voices without FM.  The FM part of the phase stays an fp32 sum of the increments (cycles),
+// converted per sample at 2^-20 cycles resolution by a magic-number add.
+constexpr uint32_t kGuardIntFm = 85899u;     // 2e-5 cycles: fp32 FM sum + its 2^-20 quantisation
+constexpr uint32_t kGuardIntPlain = 2048u;   // 4.8e-7 cycles: 16 steps of a 2^-33-rounded step
+
+__device__ __forceinline__ uint32_t cycles_to_phase(float phi)          // |phi| < 4 cycles
+{
+    return (uint32_t)(__float_as_int(__fmaf_rn(phi, 1048576.0f, 12582912.0f)) - 0x4B400000) << 12;
+}
+
+template <int WAVE>
+__device__ __forceinline__ float edged_value(uint32_t p, uint32_t pwi, uint32_t g, bool &near)
+{
+    if (WAVE == SB_WAVE_SQUARE) {                          // int(tt*2) % 2: +1 on the first half cycle
+        near = ((p + g) << 1) < (g << 2);                  // edges at 0 and 2^31
+        return __uint_as_float(0x3f800000u | (p & 0x80000000u));
+    }
+    if (WAVE == SB_WAVE_SAWTOOTH) {                        // 2*(tt - floor(0.5 + tt)) = 2*frac(tt + 0.5) - 1
+        const uint32_t q = p + 0x80000000u;
+        near = (q + g) < (g << 1);                         // wraps where 0.5 + tt crosses an integer
+        return fmaf(__uint_as_float(0x3f800000u | (q >> 9)), 2.0f, -3.0f);
+    }
+    near = ((p + g) < (g << 1)) | ((p - pwi + g) < (g << 1));          // tt % 1.0 < pulsewidth: edges at 0 and pw
+    return p < pwi ? 1.0f : -1.0f;
+}
+
+// One pass over a lane's run.  FIX = false: the values from the integer phase, returns whether
+// any sample sat in a guard band.  FIX = true (rare, per lane): the same walk, adding for every
+// such sample the difference between the exact fp64 value (phase formed as upstream forms it)
+// and the value the first pass used.
+struct RunIncrements {                      // MODC 2: the FM increments gd*lfo of frames (q, q+H), by value
+    float2 v[kFItems / 2];
+};
+
+template <int MODC, int WAVE, bool RARE, bool FLAT, bool FIX>
+__device__ __forceinline__ bool edged_pass(const FastVoice &F, const float2 env, const float lane8, const int64_t n,
+                                           const FastCtx ctx, const uint32_t p0, const double gbefore,
+                                           float2 sn, float2 dl, const RunIncrements sv, const float half_sum,
+                                           const bool low, float2 (&accL2)[kFItems / 2], float2 (&accR2)[kFItems / 2])
+{
+    constexpr int H = kFItems / 2;
+    constexpr bool MOD = MODC != 0;
+    constexpr uint32_t g = MOD ? kGuardIntFm : kGuardIntPlain;
+    const float4 stepk = F.stepk;           // carrier step and pulse width as phase integers, -k, -k
+    const float4 gain = F.gain;
+    const uint32_t wci = __float_as_uint(stepk.x), pwi = __float_as_uint(stepk.y);
+    const float2 nk2 = make_float2(stepk.z, stepk.w);
+    uint32_t bx = p0, by = p0 + (uint32_t)H * wci;
+    float2 run = make_float2(0.0f, half_sum);               // FM phase (cycles) ahead of frames (q, q+H)
+    const float e0 = fmaf(lane8, env.y, env.x);
+    float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
+    const float2 estep = make_float2(env.y, env.y);
+    float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
+    if (FLAT) {                                             // constant envelope: folded into the gains
+        const float2 ec = make_float2(env.x, env.x);
+        aL2 = __fmul2_rn(aL2, ec);
+        aR2 = __fmul2_rn(aR2, ec);
+    }
+    bool any = false;
+#pragma unroll
+    for (int q = 0; q < H; q++) {
+        if (MODC == 2) sn = sv.v[q];
+        const uint32_t px = MOD ? bx + cycles_to_phase(run.x) : bx;
+        const uint32_t py = MOD ? by + cycles_to_phase(run.y) : by;
+        bool nx, ny;
+        float2 w = make_float2(edged_value<WAVE>(px, pwi, g, nx), edged_value<WAVE>(py, pwi, g, ny));
+        if (!FIX) {
+            any |= nx | ny;
+        } else {
+            float2 d = make_float2(0.0f, 0.0f);
+            if (nx || low)
+                d.x = exact_shape(WAVE, ctx, n + q, F.car.x, F.car.y, MOD ? gbefore + (double)run.x : 0.0, MOD, F.pw64) - w.x;
+            if (ny || low)
+                d.y = exact_shape(WAVE, ctx, n + q + H, F.car.x, F.car.y, MOD ? gbefore + (double)run.y : 0.0, MOD, F.pw64) - w.y;
+            w = d;
+        }
+        float2 ee = e;
+        if (RARE) {
+            if (env.x == kEnvSlow) {
+                ee.x = fast_env_at(F, n + q);
+                ee.y = fast_env_at(F, n + q + H);
+            }
+            if (!FIX) {
+                accL2[q] = __ffma2_rn(ee, make_float2(F.bL, F.bL), accL2[q]);
+                accR2[q] = __ffma2_rn(ee, make_float2(F.bR, F.bR), accR2[q]);
+            }
+        }
+        const float2 we = FLAT ? w : __fmul2_rn(w, ee);
+        accL2[q] = __ffma2_rn(we, aL2, accL2[q]);
+        accR2[q] = __ffma2_rn(we, aR2, accR2[q]);
+        if (q + 1 < H) {
+            bx += wci;
+            by += wci;
+            if (MOD) run = __fadd2_rn(run, sn);
+            if (MODC == 1) {
+                dl = __ffma2_rn(nk2, sn, dl);
+                sn = __fadd2_rn(sn, dl);
+            }
+            if (!FLAT) e = __fadd2_rn(e, estep);
+        }
+    }
+    return any;
+}
+
+// The fix-up pass as a real call: it is rare (a sample in a guard band, or the first cycles of a
+// voice), it contains the calls of the exact evaluation, and kept inline it makes the compiler
+// spill the accumulators around every one of them on the main path too.  It returns the
+// corrections of the run's 16 frames through local memory.
+struct RunFix {
+    float2 L[kFItems / 2], R[kFItems / 2];
+};
+
+template <int MODC, int WAVE, bool RARE, bool FLAT>
+__device__ __noinline__ RunFix edged_fix(const FastVoice *Fp, const float2 env, const float lane8, const int64_t n,
+                                         const FastCtx ctx, const uint32_t p0, const double gbefore, const float2 sn,
+                                         const float2 dl, const RunIncrements sv, const float half_sum, const bool low)
+{
+    RunFix r = {};
+    edged_pass<MODC, WAVE, RARE, FLAT, true>(*Fp, env, lane8, n, ctx, p0, gbefore, sn, dl, sv, half_sum, low, r.L, r.R);
+    return r;
+}
+
+template <int MODC, int WAVE, bool RARE, bool FLAT>
+__device__ __forceinline__ void edged_voice_run(const FastVoice &F, const double2 anc, const float2 env,
+                                                const double Tc0, const double dstep,
+                                                const float lane8, const int64_t n,
+                                                const FastCtx ctx, float2 (&accL2)[kFItems / 2],
+                                                float2 (&accR2)[kFItems / 2])
+{
+    constexpr int H = kFItems / 2;
+    double B = fma(F.car.x, Tc0, F.car.y);
+    double gbefore = 0.0;
+    float2 sn = make_float2(0.0f, 0.0f), dl = make_float2(0.0f, 0.0f);
+    float half_sum = 0.0f;
+    RunIncrements sv = {};
+    if (MODC == 2) {
+        const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+        const double fm = F.mod.x, phm = F.mod.y, gd = F.gd, mpw = scan_m_pw64(F);
+        double tot;
+        switch (mwave) {                                // warp-uniform
+        case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
+        case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
+        case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
+        default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
+        }
+        const int lane = threadIdx.x & 31;
+        double incl = tot;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const double o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        gbefore = gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + (incl - tot));
+        B += gbefore;
+#pragma unroll
+        for (int q = 0; q < H; q++) half_sum += sv.v[q].x;
+    }
+    if (MODC == 1) {
+        const double2 L = ctx.lt_lane[F.lt_row];
+        const FmSeg fs = ctx.tab_seg[F.tab_row];
+        const double cl = fma(-anc.y, L.y, anc.x * L.x);
+        const double sl = fma(anc.x, L.y, anc.y * L.x);
+        double u = fma(-fs.Cc, cl, fs.A);
+        u = fma(-0.5, sl, u);
+        const double vv = fma(fs.Cc, sl, -0.5 * cl);
+        gbefore = fma(F.mod.x * dstep, vv, u);
+        B += gbefore;
+        const float s0 = (float)sl, c0 = (float)cl;
+        const float4 hf = F.half;           // cos(H w), sin(H w), P, Q
+        const float4 ini = F.ini;           // k/2, k/2, sin w, sin w
+        const float sH = fmaf(c0, hf.y, s0 * hf.x);
+        const float cH = fmaf(-s0, hf.y, c0 * hf.x);
+        sn = make_float2(s0, sH);
+        dl = __ffma2_rn(make_float2(c0, cH), make_float2(ini.z, ini.w), __fmul2_rn(sn, make_float2(ini.x, ini.y)));
+        half_sum = fmaf(s0, hf.z, c0 * hf.w);
+    }
+    // phase base: its fraction of a cycle as a 32-bit integer (two magic-number adds, no conversion)
+    const double M = 6755399441055744.0;
+    const double fr = B - __dadd_rn(__dadd_rn(B, M), -M);                      // [-0.5, 0.5]
+    const uint32_t p0 = (uint32_t)__double2loint(__dadd_rn(fr * 4294967296.0, M));
+    // while the (unreduced) phase may still be negative, Square's int() truncation is not the
+    // periodic rule: take the exact path for the whole run (only the first cycles of a voice)
+    const bool low = !(B > 16.0);
+    const bool any = edged_pass<MODC, WAVE, RARE, FLAT, false>(F, env, lane8, n, ctx, p0, gbefore, sn, dl, sv, half_sum, low, accL2, accR2);
+    if (any || low) {
+        const RunFix r = edged_fix<MODC, WAVE, RARE, FLAT>(&F, env, lane8, n, ctx, p0, gbefore, sn, dl, sv, half_sum, low);
+#pragma unroll
+        for (int q = 0; q < H; q++) {
+            accL2[q] = __fadd2_rn(accL2[q], r.L[q]);
+            accR2[q] = __fadd2_rn(accR2[q], r.R[q]);
         }
     }
 }
@@ -671,7 +838,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
 #if FAST_PAIR_VOICES
     // two voices per iteration in one basic block: their (independent) dependency chains give
     // the scheduler twice the instruction-level parallelism to hide MUFU / fp64 latency
-    if (WAVE < SB_WAVE_SQUARE && MOD != 2) {
+    if constexpr (WAVE < SB_WAVE_SQUARE && MOD != 2) {      // (pairing edged carriers was measured slower)
         for (; v + 1 < end; v += 2) {
             const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
             const float2 e0 = s_env[v * kFastMaxSub + s], e1 = s_env[(v + 1) * kFastMaxSub + s];
@@ -695,10 +862,19 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
         const float2 env = s_env[v * kFastMaxSub + s];
         if (env.x == kEnvSilent) continue;                                      // warp-uniform
         const double2 anc = MOD == 1 ? s_anc[v * kFastMaxSub + s] : none;
-        if (env.x == kEnvSlow || (F.flags & FV_BIAS))
-            fast_voice_run<MOD, WAVE, true, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
-        else
-            fast_voice_run<MOD, WAVE, false, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+        if constexpr (WAVE >= SB_WAVE_SQUARE) {
+            if (env.x == kEnvSlow || (F.flags & FV_BIAS))
+                edged_voice_run<MOD, WAVE, true, false>(F, anc, env, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            else if (MOD != 2 && (__float_as_int(env.y) << 1) == 0)              // slope +-0: warp-uniform
+                edged_voice_run<MOD, WAVE, false, MOD != 2>(F, anc, env, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            else
+                edged_voice_run<MOD, WAVE, false, false>(F, anc, env, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+        } else {
+            if (env.x == kEnvSlow || (F.flags & FV_BIAS))
+                fast_voice_run<MOD, WAVE, true, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+            else
+                fast_voice_run<MOD, WAVE, false, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
+        }
     }
 }
 
@@ -709,7 +885,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
 // kernels rather than one so that the exact-fallback call and its register needs stay out of
 // the smooth carriers' loop (the headline path).
 template <int PART>
-__global__ void __launch_bounds__(kFastWarps * 32, PART == 2 ? 4 : FAST_MIN_BLOCKS)   // part 2: 128 registers for its fp64 run
+__global__ void __launch_bounds__(kFastWarps * 32, PART != 0 ? 4 : FAST_MIN_BLOCKS)   // parts 1, 2: 128 registers
 bank_fast_kernel(BankArgs a)
 {
     constexpr bool EDGED = PART != 0;                  // adds into what part 0 wrote
