@@ -627,11 +627,12 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
 // They keep their phase as a 32-bit fraction of a cycle (2^32 = one
 // cycle): the carrier step is an integer add that wraps for free, the waveform value and the
 // "within the guard band of an edge" test are two or three integer operations each, and the
-// resolution (2^-32 cycles, against fp32's 6e-8) lets the guard band shrink to 5e-7 cycles for
+// resolution (2^-32 cycles, against fp32's 6e-8) lets the guard band shrink to 2e-6 cycles for
 // voices without FM.  The FM part of the phase stays an fp32 sum of the increments (cycles),
 // converted per sample at 2^-20 cycles resolution by a magic-number add.
 constexpr uint32_t kGuardIntFm = 85899u;     // 2e-5 cycles: fp32 FM sum + its 2^-20 quantisation
-constexpr uint32_t kGuardIntPlain = 2048u;   // 4.8e-7 cycles: 16 steps of a 2^-33-rounded step
+constexpr uint32_t kGuardIntPlain = 8192u;   // 1.9e-6 cycles: 16 steps of a 2^-33-rounded step, plus the drift of the
+                                             // time base's step from the nominal one (1e-8 relative an hour into a render)
 
 __device__ __forceinline__ uint32_t cycles_to_phase(float phi)          // |phi| < 4 cycles
 {

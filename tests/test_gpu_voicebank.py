@@ -128,6 +128,30 @@ def test_fast_path_ten_minutes_in(cuda):
     assert_within_lsb(got, want, 1, "fast path at 10 minutes")
 
 
+def test_edged_carriers_ten_minutes_in(cuda):
+    """Square / Sawtooth / Pulse carriers without FM, 10 minutes into a render, one voice at a
+    time at full scale: every edge must still fall on the sample upstream puts it on — also at
+    frequencies that divide the sample rate, where all edges sit on sample boundaries and the
+    side is decided by the rounding of the accumulated t, and at a high frequency, where the
+    16-sample integer-phase run drifts furthest from the time base's own step."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr = 44100
+    start, n = 600 * sr - 20000, 20000
+    classes = {2: sb.Square, 3: sb.Sawtooth, 4: sb.Pulse}
+    for cw, f0, ph in [(2, 2205.0, 0.0), (2, 441.0, 0.25), (2, 9973.3, 0.1), (3, 1102.5, 0.5), (3, 15011.7, 0.3),
+                       (4, 4410.0, 0.0), (4, 733.1, 0.9)]:
+        kw = dict(pulsewidth=0.3) if cw == 4 else {}
+        car = classes[cw](f0, 0.99, ph, 0.0, samplerate=sr, **kw)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert bank.count_generic() == 0 and bank.count_edged() == 1
+        got = bank.render(n, start=start).cpu().numpy()[0::2].astype(np.float64)
+        want = co.osc(cw, start + n, sr, f0, float(np.float32(0.99)), ph, 0.0, pulsewidth=0.3)[start:]
+        err = np.abs(got - want)
+        assert err.max() < 1e-6, "wave %d f0 %g: %d samples differ, first at %d" % (
+            cw, f0, int((err >= 1e-6).sum()), int(np.argmax(err >= 1e-6)))
+
+
 @pytest.mark.parametrize("cw", [0, 1, 3])
 def test_fm_accuracy_sweep_full_scale(cuda, cw):
     """One FULL-SCALE voice per (carrier f0, modulator f, FM depth) — from slow deep vibrato to
