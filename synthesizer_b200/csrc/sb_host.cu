@@ -29,6 +29,8 @@ struct Workspace {
     }
 };
 
+void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *edged, int *scan);
+
 static std::mutex g_mu;
 static Workspace g_ws[8];
 
@@ -91,12 +93,7 @@ extern "C" int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, in
     cudaStream_t s = 0;
     SB_CUDA_CHECK(cudaMemcpyAsync(d_voices, voices, (size_t)nvoices * sizeof(sb_voice), cudaMemcpyHostToDevice, s));
     int n_generic = 0, n_edged = 0, n_scan = 0;
-    for (int v = 0; v < nvoices; v++) {
-        const int cls = sb_voice_is_fast(&voices[v], samplerate);
-        if (!cls) n_generic++;
-        else if (voices[v].c_wave >= SB_WAVE_SQUARE) n_edged++;
-        if (cls == 2) n_scan++;
-    }
+    bank_count_classes(voices, nvoices, samplerate, &n_generic, &n_edged, &n_scan);
     rc = sb_bank_plan_hint(&plan, n_generic, n_edged, n_scan);
     if (rc) return rc;
 

@@ -157,10 +157,13 @@ struct BankArgs {
 // ------------------------------------------------------------------ classification
 // 0 = generic, 1 = fast (no FM, or a Sine modulator: closed-form FM sum), 2 = fast with a
 // Triangle / Square / Sawtooth / Pulse modulator (FM sum from the tile pre-pass + a warp scan)
-__host__ __device__ inline int voice_class(const sb_voice &V, double samplerate)
+// (inv_sr = 1/samplerate and w1 = 2*pi/samplerate are passed in: a caller classifying a whole
+// bank on the host - sb_host_bank_render_pcm16, inside its end-to-end time - pays the two
+// divisions once; host and device evaluate the same expressions, so they always agree)
+__host__ __device__ inline int voice_class(const sb_voice &V, double samplerate, double inv_sr, double w1)
 {
     if (V.c_wave < SB_WAVE_SINE || V.c_wave > SB_WAVE_PULSE) return 0;
-    const double inc_c = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0) / samplerate;
+    const double inc_c = (V.c_wave == SB_WAVE_SINE ? w1 : inv_sr);
     const double turns = (V.c_wave == SB_WAVE_SINE ? 6.283185307179586 : 1.0);
     // carrier advance per 8-sample run must stay small enough for fp32 increments
     if (!(fabs(V.c_freq) * inc_c * 8.0 < 64.0 * turns)) return 0;
@@ -178,10 +181,10 @@ __host__ __device__ inline int voice_class(const sb_voice &V, double samplerate)
     // (tools/accuracy_sweep.py) the error stays below half an LSB of full scale up to a gain
     // of 1.5 (it was 3.5 LSB per radian with an fp32 warp scan over the 512-frame sub-tile);
     // stronger FM takes the generic fp64 path.
-    const double gain_rad = fabs(V.c_freq) * (6.283185307179586 / samplerate) * fabs((double)V.m_amp);
+    const double gain_rad = fabs(V.c_freq) * w1 * fabs((double)V.m_amp);
     if (!(gain_rad <= kFastMaxFmGain)) return 0;
     if (V.m_wave == SB_WAVE_SINE) {
-        const double w = V.m_freq * 6.283185307179586 / samplerate;  // modulator phase step
+        const double w = V.m_freq * w1;                              // modulator phase step
         if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return 0;            // closed form needs sin(w/2) != 0
         return 1;
     }
@@ -190,9 +193,9 @@ __host__ __device__ inline int voice_class(const sb_voice &V, double samplerate)
     if (!(V.m_freq >= 0.0 && V.m_freq * 2.0 <= samplerate && V.m_phase >= 0.0)) return 0;
     return 2;
 }
-__host__ __device__ inline bool voice_is_fast(const sb_voice &V, double samplerate)
+__host__ __device__ inline int voice_class(const sb_voice &V, double samplerate)
 {
-    return voice_class(V, samplerate) != 0;
+    return voice_class(V, samplerate, 1.0 / samplerate, 6.283185307179586 / samplerate);
 }
 
 // cos(r) for |r| <= pi + small, fp64 Taylor to r^26 (error < 1e-13)
@@ -1465,6 +1468,24 @@ static inline int64_t bank_scratch_bytes(const sb_bank_plan *p)
 }  // namespace sb
 
 using namespace sb;
+
+namespace sb {
+// the hint counts of a whole bank, for host-side callers (one pass, divisions hoisted)
+void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *edged, int *scan)
+{
+    const double inv_sr = 1.0 / samplerate, w1 = 6.283185307179586 / samplerate;
+    int g = 0, e = 0, sc = 0;
+    for (int v = 0; v < nvoices; v++) {
+        const int cls = voice_class(voices[v], samplerate, inv_sr, w1);
+        if (!cls) g++;
+        else if (voices[v].c_wave >= SB_WAVE_SQUARE) e++;
+        if (cls == 2) sc++;
+    }
+    *generic = g;
+    *edged = e;
+    *scan = sc;
+}
+}  // namespace sb
 
 extern "C" int sb_voice_is_fast(const sb_voice *voice, double samplerate)
 {
