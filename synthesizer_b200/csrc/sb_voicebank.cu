@@ -146,6 +146,9 @@ struct BankArgs {
     double *lfo_prefix;   // [nvoices][lfo_rows]: FV_SCAN voices: sum of the modulator's shape over all frames
                           // before tile `row` (tiles of kFSub frames: lfo_nprefix over [0, n0), then the render's)
     int lfo_rows, lfo_nprefix;
+    int *order;           // [3][nvoices]: per kernel part, each group's voices of that part sorted by kind
+                          // (bank_sort_kernel); entry = voice index, the group's slice starts at its first voice
+    int *kind_end;        // [ngroups][3][kFastKinds]: end position of each kind in the group's sorted slice
     int *scan_list;       // [1 + nvoices]: count, then the indices of the FV_SCAN voices (any order)
     int scan_cap;         // rows of the pre-pass grid: how many list entries the launch covers
     int fast_nspans;
@@ -882,6 +885,49 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
     }
 }
 
+// One CTA per voice group, once per render: for each of the three kernel parts, the group's
+// voices of that part sorted by kind (stable), and where each kind ends.  The fast kernels'
+// CTAs - there are thousands per render - then stage their voices with a plain indexed copy
+// instead of each repeating this O(n^2) ranking against flags in global memory.
+__global__ void __launch_bounds__(kMaxVoicesPerGroup)
+bank_sort_kernel(BankArgs a)
+{
+    __shared__ int s_flags[kMaxVoicesPerGroup];
+    const int group = blockIdx.x;
+    const int v_begin = group * a.voices_per_group;
+    int nv = a.nvoices - v_begin;
+    if (nv > a.voices_per_group) nv = a.voices_per_group;
+    const int v = threadIdx.x;
+    if (v < nv) s_flags[v] = a.fastv[v_begin + v].flags;
+    __syncthreads();
+    for (int part = 0; part < 3; part++) {
+        if (v < nv) {
+            const int fl = s_flags[v];
+            const int kind = fast_kind_of(fl);
+            if ((fl & FV_FAST) && fast_kind_part(kind) == part) {
+                int pos = 0;
+                for (int u = 0; u < nv; u++) {
+                    const int fu = s_flags[u];
+                    const int ku = fast_kind_of(fu);
+                    if (!(fu & FV_FAST) || fast_kind_part(ku) != part) continue;
+                    pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
+                }
+                a.order[(int64_t)part * a.nvoices + v_begin + pos] = v_begin + v;
+            }
+        }
+        if (v < kFastKinds) {
+            int c = 0;
+            for (int u = 0; u < nv; u++) {
+                const int fu = s_flags[u];
+                const int ku = fast_kind_of(fu);
+                if (!(fu & FV_FAST) || fast_kind_part(ku) != part) continue;
+                c += (ku <= v) ? 1 : 0;
+            }
+            a.kind_end[((int64_t)group * 3 + part) * kFastKinds + v] = c;
+        }
+    }
+}
+
 // PART 0: Sine / Triangle carriers with no or a Sine modulator; writes the group's partial mix
 //         (zeros included).
 // PART 1: Square / Sawtooth / Pulse carriers with no or a Sine modulator; adds into it.
@@ -907,42 +953,25 @@ bank_fast_kernel(BankArgs a)
     int nv = a.nvoices - v_begin;
     if (nv > a.voices_per_group) nv = a.voices_per_group;
 
+    // this part's voices of the group, already ranked by kind (bank_sort_kernel): where each kind ends
+    const int *kend = a.kind_end + ((int64_t)group * 3 + PART) * kFastKinds;
+    nv = kend[kFastKinds - 1];
+    if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
+    if (threadIdx.x < kFastKinds) s_kind_end[threadIdx.x] = kend[threadIdx.x];
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
-    // Copy this group's fast voices into shared memory sorted by kind (no FM / FM x sine /
-    // triangle), so that the inner loops are branch-free runs of one instantiation each.
-    for (int v = threadIdx.x; v < nv; v += blockDim.x) {
-        const FastVoice *src = a.fastv + v_begin;
-        const int fl = src[v].flags;
-        const int kind = fast_kind_of(fl);
-        if ((fl & FV_FAST) && fast_kind_part(kind) == PART) {
-            int pos = 0;
-            for (int u = 0; u < nv; u++) {
-                const int fu = src[u].flags;
-                const int ku = fast_kind_of(fu);
-                if (!(fu & FV_FAST) || fast_kind_part(ku) != PART) continue;
-                pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
-            }
-            const int4 *w = reinterpret_cast<const int4 *>(src + v);
-            int4 *dst = reinterpret_cast<int4 *>(s_fv + pos);
-#pragma unroll
-            for (int i = 0; i < (int)(sizeof(FastVoice) / 16); i++) dst[i] = w[i];
+    // stage them in shared memory in that order, so that the inner loops are branch-free runs
+    // of one instantiation each
+    {
+        constexpr int kWords = (int)(sizeof(FastVoice) / 16);
+        const int *ord = a.order + (int64_t)PART * a.nvoices + v_begin;
+        for (int i = threadIdx.x; i < nv * kWords; i += blockDim.x) {
+            const int pos = i / kWords, w = i - pos * kWords;
+            reinterpret_cast<int4 *>(s_fv + pos)[w] = reinterpret_cast<const int4 *>(a.fastv + ord[pos])[w];
         }
-    }
-    if (threadIdx.x < kFastKinds) {
-        int c = 0;
-        for (int u = 0; u < nv; u++) {
-            const int fu = a.fastv[v_begin + u].flags;
-            const int ku = fast_kind_of(fu);
-            if (!(fu & FV_FAST) || fast_kind_part(ku) != PART) continue;
-            c += (ku <= (int)threadIdx.x) ? 1 : 0;
-        }
-        s_kind_end[threadIdx.x] = c;
     }
     __syncthreads();
     const int *ke = s_kind_end;                        // read from shared memory where needed: no registers held
-    nv = ke[kFastKinds - 1];                           // this kernel's voices only from here on
-    if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
     const bool any_cyc = EDGED || nv > ke[1];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1443,7 +1472,7 @@ __global__ void bank_fold_kernel(const float *__restrict__ partial, int ngroups,
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
 // Scratch layout after the span sums and FastVoice array (plan->off_tab onwards): closed-form FM
-// table, lane rotation table, list of FV_SCAN voices, and last - so that its size can follow
+// table, lane rotation table, list of FV_SCAN voices, the per-part voice order and kind ends, and last - so that its size can follow
 // the scan_voices hint - the modulator tile prefix table [scan slots][rows].
 static inline int64_t bank_off_lanetab(const sb_bank_plan *p)
 {
@@ -1453,9 +1482,17 @@ static inline int64_t bank_off_scanlist(const sb_bank_plan *p)
 {
     return bank_off_lanetab(p) + align_up((int64_t)p->nvoices * 32 * (int64_t)sizeof(double2), 256);
 }
-static inline int64_t bank_off_lfo(const sb_bank_plan *p)
+static inline int64_t bank_off_order(const sb_bank_plan *p)
 {
     return bank_off_scanlist(p) + align_up((int64_t)(p->nvoices + 1) * (int64_t)sizeof(int), 256);
+}
+static inline int64_t bank_off_kindend(const sb_bank_plan *p)
+{
+    return bank_off_order(p) + align_up(3 * (int64_t)p->nvoices * (int64_t)sizeof(int), 256);
+}
+static inline int64_t bank_off_lfo(const sb_bank_plan *p)
+{
+    return bank_off_kindend(p) + align_up((int64_t)p->ngroups * 3 * kFastKinds * (int64_t)sizeof(int), 256);
 }
 static inline int64_t bank_lfo_nprefix(const sb_bank_plan *p) { return (p->n0 + kFSub - 1) / kFSub; }
 static inline int64_t bank_lfo_rows(const sb_bank_plan *p) { return bank_lfo_nprefix(p) + (p->frames + kFSub - 1) / kFSub; }
@@ -1602,6 +1639,8 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.tab = (FmSeg *)(scratch + plan->off_tab);
     a.lanetab = (double2 *)(scratch + bank_off_lanetab(plan));
     a.scan_list = (int *)(scratch + bank_off_scanlist(plan));
+    a.order = (int *)(scratch + bank_off_order(plan));
+    a.kind_end = (int *)(scratch + bank_off_kindend(plan));
     a.lfo_prefix = (double *)(scratch + bank_off_lfo(plan));
     a.lfo_nprefix = (int)bank_lfo_nprefix(plan);
     a.lfo_rows = (int)bank_lfo_rows(plan);
@@ -1613,6 +1652,8 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.out_stride = (plan->frames * 2 + 3) / 4 * 4;
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
+    SB_LAUNCH_CHECK();
+    bank_sort_kernel<<<a.ngroups, kMaxVoicesPerGroup, 0, s>>>(a);     // one CTA per voice group
     SB_LAUNCH_CHECK();
     if (plan->scan_voices != 0) {
         // modulator tile sums of the FV_SCAN voices, then their prefix (the fast kernel reads it)
