@@ -95,7 +95,7 @@ struct alignas(16) FastVoice {
     double2 car;             // f0b, pc0: carrier frequency * (1 + modulator bias), start phase
     int flags;
     int tab_row;             // voice index * nsegs_rad: the voice's row of the closed-form FM table
-    int lt_row;              // voice index * 32: the voice's row of the lane rotation table
+    int lt_row;              // voice index * kLaneTab: the voice's row of the lane rotation table
     float Hwc;               // H carrier steps
     float4 stepk;            // wc, wc, -k, -k: carrier phase step; k = 4 sin^2(w/2)
     float4 gain;             // aL, aL, aR, aR: c_amp*gain
@@ -129,6 +129,8 @@ struct alignas(16) FmSeg {
 constexpr float kEnvSilent = -1.0f;          // after the release: the voice adds nothing here
 constexpr float kEnvSlow = -2.0f;            // an envelope corner falls inside: per-sample ADSR
 
+constexpr int kLaneTab = 33;     // entries per voice of the lane rotation table: lanes 0..31, then one whole sub-tile
+
 struct BankArgs {
     const sb_voice *voices;
     int nvoices, voices_per_group, ngroups, nspans;
@@ -142,7 +144,8 @@ struct BankArgs {
     int nprefix;          // spans of span_len frames covering [0, n0): the FM sum before this render
     FastVoice *fastv;     // [nvoices]
     FmSeg *tab;           // [nvoices][nsegs_rad]: closed-form FM table per modulator segment
-    double2 *lanetab;     // [nvoices][32]: (cos, sin)(lane * kFItems * w), the rotation from a sub-tile's anchor
+    double2 *lanetab;     // [nvoices][kLaneTab]: (cos, sin)(l * kFItems * w), l = 0..32: the rotation from a
+                          // sub-tile's anchor to lane l's first frame; l = 32 is the next sub-tile's anchor
     double *lfo_prefix;   // [nvoices][lfo_rows]: FV_SCAN voices: sum of the modulator's shape over all frames
                           // before tile `row` (tiles of kFSub frames: lfo_nprefix over [0, n0), then the render's)
     int lfo_rows, lfo_nprefix;
@@ -273,7 +276,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
         FastVoice F;
         F.flags = 0;
         F.tab_row = v * a.nsegs_rad;
-        F.lt_row = v * 32;
+        F.lt_row = v * kLaneTab;
         F.pw = (float)clamp_pulsewidth((double)V.c_pw);
         F.pw64 = clamp_pulsewidth((double)V.c_pw);
         F.mod = make_double2(fm, pcm);
@@ -370,7 +373,11 @@ __global__ void bank_prepare_kernel(BankArgs a)
     }
     // rotation from a sub-tile's first frame to each lane's first frame, at the nominal step
     const double ang = reduce_two_pi((double)(lane * kFItems) * w);
-    a.lanetab[(int64_t)v * 32 + lane] = make_double2(cos(ang), sin(ang));
+    a.lanetab[(int64_t)v * kLaneTab + lane] = make_double2(cos(ang), sin(ang));
+    if (lane == 0) {
+        const double ang32 = reduce_two_pi((double)(32 * kFItems) * w);
+        a.lanetab[(int64_t)v * kLaneTab + 32] = make_double2(cos(ang32), sin(ang32));
+    }
 }
 
 __device__ __forceinline__ float tri_shape(float cycles)
@@ -502,7 +509,7 @@ __device__ __noinline__ float exact_shape(int wave, FastCtx ctx, int64_t k, doub
 //
 // Set-up (fp64, once per run): gd*(cos, sin)(theta) at the lane's first frame by rotating the
 // sub-tile's anchor with the lane table (plus the first-order term for the time-base segment's
-// own step: dstep = (frames from the sub-tile start) * (segment step - nominal step)); the FM sum ahead of the run from the closed form; the carrier phase base.
+// own step: dstep = (frames from the span start) * (segment step - nominal step)); the FM sum ahead of the run from the closed form; the carrier phase base.
 //
 // (Square / Sawtooth / Pulse carriers: edged_voice_run below.)
 // MODC: 0 = no modulator, 1 = Sine modulator (closed form + recurrence), 2 = Triangle / Square /
@@ -985,30 +992,39 @@ bank_fast_kernel(BankArgs a)
     if (span_end > a.frames) span_end = a.frames;
     const int nsub = (int)((span_end - span_begin + kFSub - 1) / kFSub);
 
-    // ---- per-(voice, sub-tile) records, all lanes busy: the modulator's (cos, sin) at the
-    //      sub-tile's first frame, scaled by gd, and the ADSR line across the sub-tile
-    for (int idx = lane; idx < nv * nsub; idx += 32) {
-        const int v = idx / nsub, s = idx - v * nsub;
+    // ---- per-(voice, sub-tile) records: the modulator's (cos, sin) at the sub-tile's first
+    //      frame, scaled by gd, and the ADSR line across the sub-tile.  The anchor of the span's
+    //      first sub-tile is evaluated exactly (range reduction + fp64 polynomials); those of the
+    //      following ones are that anchor rotated by one sub-tile's worth of modulator steps
+    //      (four fp64 multiply-adds; the lanes' first-order step correction counts from the
+    //      span's first frame, so it covers the rotation too).
+    for (int v = lane; v < nv; v += 32) {
         const FastVoice &F = s_fv[v];
-        const int64_t lo = a.n0 + span_begin + (int64_t)s * kFSub, hi = lo + kFSub;
-        double2 anc = make_double2(0.0, 0.0);
-        float2 r = make_float2(1.0f, 0.0f);                 // e_sub, de
-        if ((F.flags & (FV_HAS_MOD | FV_SCAN)) == FV_HAS_MOD) {     // Sine modulators only
+        const bool sine_mod = (F.flags & (FV_HAS_MOD | FV_SCAN)) == FV_HAS_MOD;
+        double2 anc = make_double2(0.0, 0.0), rot = make_double2(1.0, 0.0);
+        if (sine_mod) {
+            const int64_t lo = a.n0 + span_begin;
             TimeCursor c;
             c.seek(s_rad, a.nsegs_rad, lo);
             const double th = reduce_two_pi(fma(F.mod.x, c.at(lo), F.mod.y));
             anc = make_double2(F.gd * cos_reduced(th), F.gd * sin_reduced(th));
+            rot = a.lanetab[F.lt_row + 32];
         }
-        if (F.flags & FV_ENV) {
-            if (lo > F.n_r) r.x = kEnvSilent;
-            else if (hi <= F.n_a) { r.x = (float)lo * F.a_slope; r.y = F.a_slope; }
-            else if (lo >= F.n_a && hi <= F.n_d) { r.x = 1.0f + (float)(lo - F.n_a) * F.d_slope; r.y = F.d_slope; }
-            else if (lo >= F.n_d && hi <= F.n_s) { r.x = F.sl; }
-            else if (lo >= F.n_s && hi <= F.n_r) { r.x = F.sl + (float)(lo - F.n_s) * F.r_slope; r.y = F.r_slope; }
-            else r.x = kEnvSlow;
+        for (int s = 0; s < nsub; s++) {
+            const int64_t lo = a.n0 + span_begin + (int64_t)s * kFSub, hi = lo + kFSub;
+            float2 r = make_float2(1.0f, 0.0f);                 // e_sub, de
+            if (F.flags & FV_ENV) {
+                if (lo > F.n_r) r.x = kEnvSilent;
+                else if (hi <= F.n_a) { r.x = (float)lo * F.a_slope; r.y = F.a_slope; }
+                else if (lo >= F.n_a && hi <= F.n_d) { r.x = 1.0f + (float)(lo - F.n_a) * F.d_slope; r.y = F.d_slope; }
+                else if (lo >= F.n_d && hi <= F.n_s) { r.x = F.sl; }
+                else if (lo >= F.n_s && hi <= F.n_r) { r.x = F.sl + (float)(lo - F.n_s) * F.r_slope; r.y = F.r_slope; }
+                else r.x = kEnvSlow;
+            }
+            s_anc[v * kFastMaxSub + s] = anc;
+            s_env[v * kFastMaxSub + s] = r;
+            if (sine_mod) anc = make_double2(fma(-anc.y, rot.y, anc.x * rot.x), fma(anc.x, rot.y, anc.y * rot.x));
         }
-        s_anc[v * kFastMaxSub + s] = anc;
-        s_env[v * kFastMaxSub + s] = r;
     }
     __syncwarp();
 
@@ -1031,7 +1047,7 @@ bank_fast_kernel(BankArgs a)
             c.seek(s_rad, a.nsegs_rad, n);
             Tr0 = c.at(n);
             ctx.tab_seg = a.tab + c.idx;
-            dstep = (double)(lane * kFItems) * (c.step - inc_rad);
+            dstep = (double)(s * kFSub + lane * kFItems) * (c.step - inc_rad);      // frames from the span's first one
             ctx.cstep = 0.0;
             ctx.cstraddle = false;
             if (any_cyc) {                              // carriers whose phase counts in cycles present
@@ -1480,7 +1496,7 @@ static inline int64_t bank_off_lanetab(const sb_bank_plan *p)
 }
 static inline int64_t bank_off_scanlist(const sb_bank_plan *p)
 {
-    return bank_off_lanetab(p) + align_up((int64_t)p->nvoices * 32 * (int64_t)sizeof(double2), 256);
+    return bank_off_lanetab(p) + align_up((int64_t)p->nvoices * kLaneTab * (int64_t)sizeof(double2), 256);
 }
 static inline int64_t bank_off_order(const sb_bank_plan *p)
 {
