@@ -371,13 +371,13 @@ def run_ours(args):
         peak_gsin = 16 * sms * sm_mhz * 1e6 / 1e9
         achieved_gsin = 2 * (hi - lo) * frames / (render_ms / 1e3) / 1e9
         # DRAM traffic of the dominant kernel from the committed ncu capture
-        # (profiles/r1k_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
-        # of bank_fast_kernel on this workload): 8.8 MB read + 440.2 MB written
-        ncu_traffic = 8760064 + 440221696 if (hi - lo) == VOICES_PER_GPU else None
+        # (profiles/r1m_bank_fast_ncu_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum, one launch
+        # of bank_fast_kernel on this workload): 9.0 MB read + 440.8 MB written
+        ncu_traffic = 8987136 + 440818688 if (hi - lo) == VOICES_PER_GPU else None
         # "achieved" counts ALGORITHMIC sines (2 per voice-sample: modulator + carrier), like
         # algorithmic bytes on an HBM roofline; the kernel issues fewer SFU operations than that
         # (the modulator's sines come from a two-term recurrence: 16 MUFU per 16 frames, not 32).
-        roofline = {"bound": "sfu", "kernel": "bank_fast_kernel (+ bank_prepare, bank_fold: 94/1/5 % of the step)",
+        roofline = {"bound": "sfu", "kernel": "bank_fast_kernel (+ bank_prepare, bank_sort, bank_fold: 94/1/0.5/4.5 % of the step)",
                     "achieved": achieved_gsin, "peak": peak_gsin, "unit": "Gsin/s",
                     "frac": achieved_gsin / peak_gsin, "traffic": ncu_traffic,
                     "peak_source": "16 MUFU lanes/clk/SM x %d SMs x %d MHz (clock sampled under load)" % (sms, sm_mhz),
