@@ -291,15 +291,18 @@ def run_ours(args):
         if rank == 0:
             C.call("sb_f32_to_pcm16", D.ptr(mix), 2 * frames, 32767.0, D.ptr(pcm), D.ptr(ovf), D.stream())
 
-    e2e_out = np.empty(2 * frames, dtype=np.int16)
     e2e_ovf = ctypes.c_ulonglong(0)
+    # both host buffers of the C-ABI call are pinned (page-locked): its copies are then DMA
+    # transfers instead of staged pageable copies
+    e2e_in = ctypes.cast(ctypes.c_void_p(host_voices.data_ptr()), ctypes.POINTER(C.Voice))
+    e2e_out = ctypes.c_void_p(host_pcm.data_ptr())
 
     def step_e2e():
         if world == 1:
             # the reference-facing C-ABI call with HOST buffers: voice parameters in host memory
             # -> interleaved int16 PCM in host memory; copies, render and conversion inside
-            C.call("sb_host_bank_render_pcm16", arr, len(arr), frames, float(SR), 32767.0,
-                   e2e_out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(e2e_ovf))
+            C.call("sb_host_bank_render_pcm16", e2e_in, len(arr), frames, float(SR), 32767.0,
+                   e2e_out, ctypes.byref(e2e_ovf))
             return
         vd = host_voices.to(D.device(), non_blocking=True)       # H2D of this step's inputs
         mix = bank.render(frames, voices_dev=vd, generic_voices=0, edged_voices=0, scan_voices=0)
@@ -408,7 +411,7 @@ def run_ours(args):
             "config": workload_config(world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_voices,
                     "d2h_bytes_per_step": 2 * frames * 2, "ms_per_step": ms_e2e / args.steps,
-                    "api": "sb_host_bank_render_pcm16 (C ABI, host buffers in and out)" if world == 1 else
+                    "api": "sb_host_bank_render_pcm16 (C ABI, pinned host buffers in and out)" if world == 1 else
                            "pinned voice parameters H2D + VoiceBank.render + NCCL reduce + PCM D2H to pinned memory"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "parity": "unpinned (reference source absent offline; oracle = restatement)", **extra,
