@@ -260,34 +260,37 @@ class Sample:
         todo = [s for s in samples if s.samplerate != samplerate and s._dev is not None]
         for s in todo:
             assert not s._locked
-        batch = [s for s in todo if s.samplewidth == 2 and s.nchannels == todo[0].nchannels]
+        batch = [s for s in todo if s.samplewidth == 2 and s.nchannels == todo[0].nchannels and s._dev.numel() > 0]
         in_batch = {id(s) for s in batch}
         for s in todo:
             if id(s) not in in_batch:
                 s.resample(samplerate)
         if batch:
+            import numpy as np
             nch = batch[0].nchannels
-            in_frames = [len(s) for s in batch]
-            red = [(s.samplerate // math.gcd(s.samplerate, samplerate), samplerate // math.gcd(s.samplerate, samplerate))
-                   for s in batch]
-            for a, b in red:
-                if a >= (1 << 21) or b >= (1 << 21):
-                    raise ValueError("reduced sample rates must be below 2^21")
-            out_frames = [C.lib.sb_pcm16_ratecv_frames(n, a, b) for n, (a, b) in zip(in_frames, red)]
-            in_off, out_off, ai, ao = [], [], 0, 0
-            for n, m in zip(in_frames, out_frames):
-                in_off.append(ai)
-                out_off.append(ao)
-                ai += n * nch
-                ao += m * nch
-            pool = torch.cat([s._dev for s in batch])
-            out = D.empty(ao, torch.int16)
-            idx = torch.tensor([in_off, in_frames, [a for a, _ in red], [b for _, b in red], out_off, out_frames],
-                               dtype=torch.int64).to(D.device())
-            C.call("sb_pcm16_ratecv_many", D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]), D.ptr(idx[3]),
-                   D.ptr(idx[4]), D.ptr(idx[5]), len(batch), nch, max(out_frames), D.ptr(out), D.stream())
-            for s, o, m in zip(batch, out_off, out_frames):
-                s._dev = out[o:o + m * nch]
+            # per-sample bookkeeping in numpy (thousands of short samples: Python loops would
+            # cost more than the kernel); audioop.ratecv's output length, on the reduced rates
+            in_frames = np.array([s._dev.numel() for s in batch], dtype=np.int64) // nch
+            rates = np.array([s.samplerate for s in batch], dtype=np.int64)
+            g = np.gcd(rates, np.int64(samplerate))
+            red_in, red_out = rates // g, np.int64(samplerate) // g
+            if red_in.max() >= (1 << 21) or red_out.max() >= (1 << 21):
+                raise ValueError("reduced sample rates must be below 2^21")
+            out_frames = np.where(in_frames > 0, ((in_frames - 1) * red_out) // red_in + 1, 0)
+            out_off = np.concatenate([[0], np.cumsum(out_frames * nch)[:-1]])
+            # the sources stay where they are: the kernel takes element offsets from a base
+            # pointer, here the lowest address among them (no concatenated copy)
+            ptrs = np.array([s._dev.data_ptr() for s in batch], dtype=np.int64)
+            base = int(ptrs.min())
+            in_off = (ptrs - base) // 2
+            out = D.empty(int((out_frames * nch).sum()), torch.int16)
+            idx = torch.from_numpy(np.stack([in_off, in_frames, red_in, red_out, out_off, out_frames])).to(D.device())
+            C.call("sb_pcm16_ratecv_many", ctypes.c_void_p(base), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]),
+                   D.ptr(idx[3]), D.ptr(idx[4]), D.ptr(idx[5]), len(batch), nch, int(out_frames.max()), D.ptr(out),
+                   D.stream())
+            pieces = torch.split(out, (out_frames * nch).tolist())      # views into `out`; keeps the sources
+            for s, piece in zip(batch, pieces):                          # alive until here
+                s._dev = piece
         for s in samples:
             s.samplerate = samplerate
         return samples
@@ -618,17 +621,23 @@ class Sample:
             srcs.append(other._dev)
         if not srcs:
             return self
-        lens = [s.numel() for s in srcs]
-        self._grow(max(a + n for a, n in zip(starts, lens)))
-        pool = torch.cat(srcs) if len(srcs) > 1 else srcs[0]
-        offs = [0]
-        for n in lens[:-1]:
-            offs.append(offs[-1] + n)
-        idx = torch.tensor([offs, lens, starts], dtype=torch.int64).to(D.device())
-        nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), len(srcs), sum(lens))
+        import numpy as np
+        lens = np.array([s.numel() for s in srcs], dtype=np.int64)
+        starts = np.array(starts, dtype=np.int64)
+        self._grow(int((starts + lens).max()))
+        keep = lens > 0                                 # an empty sample only extends the destination
+        if not keep.any():
+            return self
+        # the sources stay where they are: the kernel takes element offsets from a base pointer,
+        # here the lowest address among them (no concatenated copy of thousands of tensors)
+        ptrs = np.array([s.data_ptr() for s in srcs], dtype=np.int64)[keep]
+        lens, starts = lens[keep], starts[keep]
+        base = int(ptrs.min())
+        idx = torch.from_numpy(np.stack([(ptrs - base) // 2, lens, starts])).to(D.device())
+        nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), len(lens), int(lens.sum()))
         scratch = D.empty(nscratch, torch.uint8)
-        C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), D.ptr(pool), D.ptr(idx[0]),
-               D.ptr(idx[1]), D.ptr(idx[2]), len(srcs), D.ptr(scratch), nscratch, D.stream())
+        C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), ctypes.c_void_p(base), D.ptr(idx[0]),
+               D.ptr(idx[1]), D.ptr(idx[2]), len(lens), D.ptr(scratch), nscratch, D.stream())
         return self
 
     def echo(self, length, amount, delay, decay):
