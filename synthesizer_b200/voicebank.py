@@ -94,6 +94,10 @@ class VoiceBank:
         bank._voices = list(voices)
         return bank
 
+    def invalidate(self):
+        """Forget the uploaded copy of the voices (call after changing a voice in place)."""
+        self._dev = None
+
     def voice_array(self, begin=0, end=None):
         sel = self._voices[begin:end]
         return (C.Voice * len(sel))(*sel)
@@ -124,10 +128,15 @@ class VoiceBank:
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
         if voices_dev is None:
-            voices_dev, nv = self._upload(begin, end)
-            generic_voices = self.count_generic(begin, end)
-            edged_voices = self.count_edged(begin, end)
-            scan_voices = self.count_scan(begin, end)
+            # the uploaded voices and their class counts are kept until a voice is added
+            # (chunked renders - blocks(), PcmStreamer - come back here for every chunk)
+            if self._dev is None:
+                self._dev = {}
+            key = (begin, end)
+            if key not in self._dev:
+                self._dev[key] = self._upload(begin, end) + (self.count_generic(begin, end),
+                                                             self.count_edged(begin, end), self.count_scan(begin, end))
+            voices_dev, nv, generic_voices, edged_voices, scan_voices = self._dev[key]
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
         mix = D.empty(2 * nframes, torch.float32)
