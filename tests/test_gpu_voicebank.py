@@ -228,6 +228,17 @@ def test_fast_and_generic_voices_share_a_group(cuda):
     got = dev_pcm16(bank.render(n))
     bad = np.abs(got.astype(np.int64) - oracle_bank_pcm(P, n, sr)) > 1
     assert bad.mean() < 2e-5
+    # the counts are hints: without them (-1 = unknown: every kernel runs, scratch sized for the
+    # worst case) the render is the same, bit for bit
+    hinted = bank.render(n).cpu().numpy()
+    vd, _ = bank._upload(0, None)
+    unknown = bank.render(n, voices_dev=vd).cpu().numpy()
+    assert np.array_equal(hinted, unknown)
+    # ... and a scan_voices hint that is too small hands the surplus tile-scan voices to the
+    # generic kernels (which must then be allowed to run): still within tolerance of the oracle
+    short = bank.render(n, voices_dev=vd, generic_voices=len(kinds), edged_voices=len(kinds), scan_voices=1)
+    bad = np.abs(dev_pcm16(short).astype(np.int64) - oracle_bank_pcm(P, n, sr)) > 1
+    assert bad.mean() < 2e-5
 
 
 def test_bank_chunked_start_offsets(cuda):
