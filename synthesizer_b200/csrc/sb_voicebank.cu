@@ -7,9 +7,9 @@
 // registers; coalesced 128-bit stores write the group's partial mix, and a fold kernel sums
 // the groups.
 //
-// Two voice classes share that decomposition:
+// Voice classes (voice_class / sb_voice_is_fast) share that decomposition:
 //
-//  FAST    any of the five carriers with no FM or a Sine modulator of moderate gain.
+//  FAST (1) any of the five carriers with no FM or a Sine modulator of moderate gain.
 //          Everything that needs fp64 is done once per lane per 16-frame run: the exact time
 //          base, the carrier's phase base reduced mod one turn, and the FM sum ahead of the
 //          run, which has a closed form for a Sine modulator (sum of sin over an arithmetic
@@ -20,15 +20,23 @@
 //          modulator by the two-term recurrence s += d, d -= k*s (no SFU work), the carrier
 //          by the SFU sine, in packed fp32x2 over frame pairs (q, q+8).  No pre-pass over
 //          the samples, no running carry, and fp32 error cannot build up over more than 16
-//          frames.  Square / Sawtooth / Pulse carriers re-evaluate the few samples within a
-//          guard band of an edge exactly in fp64.
+//          frames.  Square / Sawtooth / Pulse carriers (bank_fast_kernel<1>) walk an integer
+//          phase and re-evaluate the few samples within a guard band of an edge exactly in fp64.
 //
-//  GENERIC anything else (non-sine modulators, FM gain above kFastMaxFmGain, carriers with a
-//          negative start phase).  Phase arithmetic per sample in explicitly rounded fp64,
-//          FM prefix by fp64 warp scan with a running carry that starts from per-(voice,
-//          span) sums computed by a pre-pass.
+//  FAST (2) the same carriers with a Triangle / Square / Sawtooth / Pulse modulator
+//          (bank_fast_kernel<2>): the modulator's values are evaluated exactly per sample; the
+//          FM sum ahead of a run is a per-512-frame tile prefix from a pre-pass
+//          (bank_lfo_tile_kernel, bank_lfo_prefix_kernel) plus an fp64 warp scan.
 //
-// The generic kernel runs after the fast ones and adds into the same partial mixes.
+//  GENERIC (0) anything else (FM gain above kFastMaxFmGain, carriers or modulators with a
+//          negative start phase or frequency).  Phase arithmetic per sample in explicitly
+//          rounded fp64, FM prefix by fp64 warp scan with a running carry that starts from
+//          per-(voice, span) sums computed by a pre-pass.
+//
+// Order of kernels in a render: bank_prepare_kernel (per-voice constants and tables),
+// bank_sort_kernel (each group's voices by kind), the tile pre-pass if any class-2 voice,
+// bank_fast_kernel<0> (writes the partial mixes), <1>, <2> and the generic kernels (add into
+// them) as far as the bank has such voices, bank_fold_kernel.
 #include "sb_common.cuh"
 
 namespace sb {
