@@ -188,7 +188,8 @@ __host__ __device__ inline int voice_class(const sb_voice &V, double samplerate,
     }
     if (V.m_wave == SB_WAVE_NONE) return 1;
     if (V.m_wave < SB_WAVE_SINE || V.m_wave > SB_WAVE_PULSE) return 0;
-    if (!(fabs((double)V.m_amp) <= 4.0 && fabs((double)V.m_bias) <= 4.0)) return 0;
+    // (depth and bias only need to be sane numbers: what bounds the fp32 run is the FM gain below)
+    if (!(fabs((double)V.m_amp) <= 64.0 && fabs((double)V.m_bias) <= 64.0)) return 0;
     // FM gain: carrier phase (radians) per unit of the modulator's running sum.  The fast path
     // anchors that sum exactly (fp64) at the first frame of every 16-frame run and adds fp32
     // values only inside the run; measured against the serial fp64 computation

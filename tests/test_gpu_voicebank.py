@@ -182,6 +182,30 @@ def test_fm_accuracy_sweep_full_scale(cuda, cw):
     assert seen == {0, 1}, "the sweep is meant to exercise both the fast and the generic kernels"
 
 
+@pytest.mark.parametrize("cw", [0, 1, 3])
+def test_deep_fm_on_low_carriers(cuda, cw):
+    """Depths well above 1 (the instantaneous frequency goes negative, the phase runs backwards
+    for part of every modulator cycle) stay on the fast path as long as the FM gain
+    2*pi*f0*depth/sr is at most 1.5 rad: full-scale voices against the oracle."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n = 48000, 96000
+    classes = {0: sb.Sine, 1: sb.Triangle, 3: sb.Sawtooth}
+    for f0, fm, d in [(55.1, 5.3, 20.0), (110.3, 109.7, 12.0), (441.3, 0.13, 6.0), (27.5, 880.3, 60.0)]:
+        lfo = sb.Sine(fm, d, 0.3, samplerate=sr)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 1, (f0, fm, d)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, fm, d, 0.3, 0.0)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        flips = err > 100
+        assert flips.sum() <= (3 if cw == 3 else 0), (f0, fm, d, int(flips.sum()))
+        assert err[~flips].max() < 0.9, "cw=%d f0=%g fm=%g depth=%g: %.3f LSB" % (cw, f0, fm, d, err[~flips].max())
+
+
 @pytest.mark.parametrize("mw", [1, 2, 3, 4])
 def test_piecewise_modulators_full_scale(cuda, mw):
     """Triangle / Square / Sawtooth / Pulse modulators on the fast path (class 2: exact fp64
