@@ -302,7 +302,9 @@ __global__ void bank_prepare_kernel(BankArgs a)
             const double cyc = f0b * inc_c;
             const double wfrac = cyc - floor(cyc);
             F.stepk.x = __uint_as_float((uint32_t)(unsigned long long)llrint(wfrac * 4294967296.0));
-            F.stepk.y = __uint_as_float((uint32_t)(unsigned long long)llrint(clamp_pulsewidth((double)V.c_pw) * 4294967296.0));
+            // (a pulse width clamped to just below 1 rounds to 2^32: keep it in 32 bits)
+            const unsigned long long pwll = (unsigned long long)llrint(clamp_pulsewidth((double)V.c_pw) * 4294967296.0);
+            F.stepk.y = __uint_as_float(pwll > 0xffffffffull ? 0xffffffffu : (uint32_t)pwll);
         }
         F.Hwc = (float)((double)H * f0b * inc_c);
         const float hk = (float)(2.0 * sh * sh), sw = (float)sin(w);

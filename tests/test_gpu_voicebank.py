@@ -182,6 +182,24 @@ def test_fm_accuracy_sweep_full_scale(cuda, cw):
     assert seen == {0, 1}, "the sweep is meant to exercise both the fast and the generic kernels"
 
 
+@pytest.mark.parametrize("pw", [0.0, 1.0, 1e-12, 1.0 - 1e-12, 0.5, 0.999999])
+def test_pulse_carrier_extreme_widths(cuda, pw):
+    """Pulse widths at and beyond the ends of (0, 1) — upstream clamps them to one ulp inside —
+    on the integer-phase path, where a width of almost 1 rounds to 2^32."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 44100, 30000
+    for f0, fmlfo in ((441.0, None), (997.3, sb.Sine(5.0, 0.03, samplerate=sr))):
+        car = sb.Pulse(f0, 0.99, 0.2, 0.0, pulsewidth=pw, fm_lfo=fmlfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert bank.count_generic() == 0
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, 5.0, 0.03, 0.0, 0.0) if fmlfo is not None else None
+        want = co.osc(4, n, sr, f0, float(np.float32(0.99)), 0.2, 0.0, fm=m, pulsewidth=pw)
+        flips = np.abs(got - want) > 1e-6
+        assert flips.sum() <= (2 if fmlfo is not None else 0), (pw, f0, int(flips.sum()))
+
+
 @pytest.mark.parametrize("cw", [0, 1, 3])
 def test_deep_fm_on_low_carriers(cuda, cw):
     """Depths well above 1 (the instantaneous frequency goes negative, the phase runs backwards
