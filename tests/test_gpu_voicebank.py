@@ -200,6 +200,31 @@ def test_pulse_carrier_extreme_widths(cuda, pw):
         assert flips.sum() <= (2 if fmlfo is not None else 0), (pw, f0, int(flips.sum()))
 
 
+@pytest.mark.parametrize("cw", [2, 3, 4])
+def test_edged_carriers_with_modulator_bias(cuda, cw):
+    """A modulator bias scales the carrier frequency (f0*(1+bias)): also above Nyquist, where the
+    integer phase wraps more than once per sample, and below zero, where the phase runs
+    backwards and the periodic rules for the edges no longer hold (exact path)."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 48000, 48000
+    classes = {2: sb.Square, 3: sb.Sawtooth, 4: sb.Pulse}
+    for f0, bias in ((441.3, 0.3), (2217.7, 20.5), (661.1, -1.5), (97.3, -0.999)):
+        lfo = sb.Sine(3.1, 0.02, 0.1, bias, samplerate=sr)
+        kw = dict(pulsewidth=0.3) if cw == 4 else {}
+        car = classes[cw](f0, 0.99, 0.2, 0.0, fm_lfo=lfo, samplerate=sr, **kw)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, 3.1, 0.02, 0.1, bias)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.2, 0.0, fm=m, pulsewidth=0.3)
+        err = np.abs(got - want)
+        flips = err > 1e-3
+        # (a sawtooth far above Nyquist steps by most of its range per sample: its fp32 ramp
+        # value carries the phase error of the run, 2e-5 cycles at worst)
+        assert flips.sum() <= 3, (cw, f0, bias, int(flips.sum()), bank.count_generic())
+        assert err[~flips].max() < 1e-4, (cw, f0, bias, float(err[~flips].max()))
+
+
 @pytest.mark.parametrize("cw", [0, 1, 3])
 def test_deep_fm_on_low_carriers(cuda, cw):
     """Depths well above 1 (the instantaneous frequency goes negative, the phase runs backwards
