@@ -200,6 +200,29 @@ def test_pulse_carrier_extreme_widths(cuda, pw):
         assert flips.sum() <= (2 if fmlfo is not None else 0), (pw, f0, int(flips.sum()))
 
 
+def test_piecewise_modulator_corner_cases(cuda):
+    """Tile-scan class at its edges: a modulator that never moves (0 Hz), one at Nyquist, zero
+    depth, and Pulse modulators whose width is clamped at either end."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n = 48000, 40000
+    classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    cases = [(1, 0.0, 0.3, 0.1), (2, 24000.0, 0.2, 0.1), (3, 7.7, 0.0, 0.1), (4, 3.3, 0.25, 0.0), (4, 3.3, 0.25, 1.0),
+             (2, 0.0, 0.5, 0.1), (4, 12000.0, 0.1, 0.5)]
+    for mw, fm, d, mpw in cases:
+        kw = dict(pulsewidth=mpw) if mw == 4 else {}
+        lfo = classes[mw](fm, d, 0.6, 0.0, samplerate=sr, **kw)
+        car = sb.Sine(523.3, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 2, (mw, fm, d, mpw)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(mw, n, sr, fm, d, 0.6, 0.0, pulsewidth=mpw)
+        want = co.osc(0, n, sr, 523.3, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.9, "modulator %d f=%g depth=%g pw=%g: %.3f LSB" % (mw, fm, d, mpw, err.max())
+
+
 @pytest.mark.parametrize("cw", [2, 3, 4])
 def test_edged_carriers_with_modulator_bias(cuda, cw):
     """A modulator bias scales the carrier frequency (f0*(1+bias)): also above Nyquist, where the
