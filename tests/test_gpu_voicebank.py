@@ -200,6 +200,27 @@ def test_pulse_carrier_extreme_widths(cuda, pw):
         assert flips.sum() <= (2 if fmlfo is not None else 0), (pw, f0, int(flips.sum()))
 
 
+def test_sine_modulator_corner_cases(cuda):
+    """Closed-form class at its edges: modulator steps close to the bounds the classifier
+    admits (1e-7 < |w| < 3 rad per sample), a negative modulator frequency, a modulator at a
+    start phase above one cycle; and just outside them, where the generic kernel takes over."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n = 48000, 60000
+    for fm, d, mph, want_cls in [(0.002, 0.4, 0.25, 1), (22000.0, 0.3, 0.0, 1), (-6.3, 0.2, 0.7, 1), (5.1, 0.3, 3.75, 1),
+                                 (0.0005, 0.4, 0.25, 0), (23500.0, 0.3, 0.0, 0)]:
+        lfo = sb.Sine(fm, d, mph, 0.0, samplerate=sr)
+        car = sb.Sine(1318.5, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == want_cls, (fm, d)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, fm, d, mph, 0.0)
+        want = co.osc(0, n, sr, 1318.5, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.9, "modulator f=%g depth=%g phase=%g: %.3f LSB" % (fm, d, mph, err.max())
+
+
 def test_piecewise_modulator_corner_cases(cuda):
     """Tile-scan class at its edges: a modulator that never moves (0 Hz), one at Nyquist, zero
     depth, and Pulse modulators whose width is clamped at either end."""
