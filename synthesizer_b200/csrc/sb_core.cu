@@ -4,6 +4,7 @@
 #include <string.h>
 #include <math.h>
 #include <atomic>
+#include <cmath>
 #include "sb_common.cuh"
 
 namespace sb {
@@ -134,6 +135,48 @@ extern "C" int64_t sb_timebase_first_ge(const sb_time_seg *segs, int nsegs, int6
     return hi;
 }
 
+// x after `count` serial fp64 additions of c (x = x + c, rounded each time), without doing them
+// one by one.  While x stays inside one binade every addition rounds on the same grid, so the
+// step actually taken, RN(x + c) - x, is the same each time (a tie of round-half-even settles
+// after one step): two real additions establish it, then the remaining steps inside the
+// binade are one exact multiply-add; a step that leaves the binade (or touches zero) is taken
+// for real.  A 10 s release at 48 kHz is ~50 iterations instead of 480 000 additions.
+static double serial_add_repeat(double x, double c, int64_t count)
+{
+    while (count > 0) {
+        volatile double a1v = x + c;
+        const double a1 = a1v;
+        count -= 1;
+        if (count == 0 || a1 == 0.0 || x == 0.0 || !std::isfinite(a1) || std::ilogb(a1) != std::ilogb(x) ||
+            std::signbit(a1) != std::signbit(x)) {
+            x = a1;
+            continue;
+        }
+        volatile double a2v = a1 + c;
+        const double a2 = a2v;
+        const double s1 = a1 - x, s2 = a2 - a1;          // exact: neighbours in one binade
+        if (s1 != s2 || s2 == 0.0 || a2 == 0.0 || std::ilogb(a2) != std::ilogb(a1) ||
+            std::signbit(a2) != std::signbit(a1)) {
+            x = a1;                                       // not settled, or about to leave: single steps
+            if (s2 == 0.0 && s1 == 0.0) return x;        // c vanishes against x: nothing changes any more
+            continue;
+        }
+        // from a1, how many more steps of s2 stay inside the binade [2^e, 2^(e+1)) of |a1|
+        const int e = std::ilogb(a1);
+        const double lo = std::ldexp(1.0, e), mag = std::fabs(a1), step = std::fabs(s2);
+        const bool away = (std::signbit(s2) == std::signbit(a1));          // magnitude grows
+        double room = away ? (std::ldexp(1.0, e + 1) - mag) : (mag - lo);  // exact
+        int64_t k = (int64_t)std::floor(room / step);
+        if (away && (double)k * step >= room && k > 0) k -= 1;             // stay strictly below 2^(e+1)
+        if (k > count) k = count;
+        if (k > 1) k -= 1;                                                  // (one step of slack for the quotient's rounding)
+        else k = 0;
+        x = a1 + (double)k * s2;                                            // exact: all values on the binade's grid
+        count -= k;
+    }
+    return x;
+}
+
 extern "C" int sb_envelope_build(double samplerate, double attack, double decay, double sustain,
                                  double sustain_level, double release, sb_envelope *out)
 {
@@ -171,9 +214,7 @@ extern "C" int sb_envelope_build(double samplerate, double attack, double decay,
         out->r_slope = (-sustain_level) / release * increment;
         n = sb_timebase_first_ge(segs, ns, n, end_time_release);
         // the serially accumulated release amplitude decides whether one more sample follows
-        volatile double amp = sustain_level;
-        double amp_change = out->r_slope;
-        for (int64_t k = out->n_s; k < n; k++) amp = amp + amp_change;
+        const double amp = serial_add_repeat(sustain_level, out->r_slope, n - out->n_s);
         if (amp > 0.0) {
             out->extra = 1;
             out->amp_extra = amp;

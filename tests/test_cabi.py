@@ -105,6 +105,26 @@ def test_envelope_boundaries_match_the_serial_generator(adsr):
     assert np.array_equal(model != 0, shape != 0)
 
 
+def test_release_replay_equals_the_serial_accumulation():
+    """sb_envelope_build decides the "one more sample" of the release from the amplitude that
+    upstream's loop has accumulated by then (amp += step, once per sample).  The library jumps
+    through that accumulation one binade at a time; here it is replayed addition by addition."""
+    rng = np.random.default_rng(8)
+    cases = [(0.05, 0.1, 0.3, 0.6, 0.2), (0.0, 0.0, 0.0, 1.0, 3.0), (0.01, 0.02, 0.0, 1e-9, 0.5), (0.2, 0.1, 0.1, 0.333, 1e-4)]
+    cases += [tuple(float(x) for x in (rng.uniform(0, 0.3), rng.uniform(0, 0.3), rng.uniform(0, 0.5),
+                                        rng.uniform(0, 1), rng.uniform(1e-3, 2.5))) for _ in range(24)]
+    for sr in (44100.0, 48000.0):
+        for adsr in cases:
+            env = C.Envelope()
+            C.call("sb_envelope_build", sr, *adsr, ctypes.byref(env))
+            amp, step = adsr[3], env.r_slope
+            for _ in range(env.n_r - env.n_s):
+                amp = amp + step
+            assert env.extra == (1 if amp > 0.0 else 0), (sr, adsr, amp)
+            if env.extra:
+                assert env.amp_extra == amp, (sr, adsr, amp, env.amp_extra)
+
+
 def test_bad_arguments_fail_loudly():
     segs = (C.TimeSeg * 4)()
     assert C.lib.sb_timebase_build(-1.0, 10, segs, 4) < 0
