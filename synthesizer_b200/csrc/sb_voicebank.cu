@@ -471,6 +471,25 @@ __device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t 
     constexpr int H = kFItems / 2;
     const float gdf = (float)gd;
     tot = 0.0;
+    if (MW == SB_WAVE_TRIANGLE && !ctx.cstraddle) {
+        // A triangle has no edges: its value does not hinge on the last bits of the phase, so
+        // only the run's first phase is formed the way upstream forms it and the other 15 step
+        // from it (phase fraction += step, wrapped), which halves the fp64 work per sample.
+        // The difference from upstream's own rounding of each phase is ~1e-16 of the value.
+        const double x0 = __dadd_rn(__dadd_rn(__dmul_rn(Tc0, fm), phm), 0.75);
+        double f = x0 - floor_nonneg(x0);                                   // in [0, 1)
+        const double w = fm * ctx.cstep;                                    // cycles per frame (< 1)
+#pragma unroll
+        for (int j = 0; j < kFItems; j++) {
+            const double v = fma(4.0, fabs(f - 0.5), -1.0);
+            tot += v;
+            const float inc = (float)(gd * v);
+            if (j < H) sv[j].x = inc; else sv[j - H].y = inc;
+            f += w;
+            if (f >= 1.0) f -= 1.0;
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < kFItems; j++) {
         double t;
@@ -1176,10 +1195,11 @@ bank_lfo_tile_kernel(BankArgs a)
         end = min(begin + kFSub, a.n0 + a.frames);
     }
     // the times of this lane's frames (lane, lane+32, ...) are the same for every voice
-    double t[kFItems];
+    double t[kFItems], tstep;
     {
         TimeCursor c;
         c.seek(s_cyc, a.nsegs_cyc, begin + lane);
+        tstep = c.step;
 #pragma unroll
         for (int j = 0; j < kFItems; j++) {
             const int64_t k = begin + lane + 32 * j;
@@ -1192,9 +1212,25 @@ bank_lfo_tile_kernel(BankArgs a)
         const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
         const double fm = F.mod.x, phm = F.mod.y, mpw = scan_m_pw64(F);
         double acc = 0.0;
+        if (mwave == SB_WAVE_TRIANGLE) {
+            // (see lfo_run: no edges, so the lane's frames step from its first phase; the frames
+            // of a lane are 32 apart, and a tile that crosses a time-base segment is not special
+            // at this accuracy: the step changes by parts in 1e9)
+            const double x0 = __dadd_rn(__dadd_rn(__dmul_rn(t[0] >= 0.0 ? t[0] : 0.0, fm), phm), 0.75);
+            double f = x0 - floor_nonneg(x0);
+            const double w32 = 32.0 * fm * tstep;
+            const double wf = w32 - floor_nonneg(w32);
 #pragma unroll
-        for (int j = 0; j < kFItems; j++)
-            if (t[j] >= 0.0) acc += lfo_shape_exact(mwave, t[j], fm, phm, mpw);
+            for (int j = 0; j < kFItems; j++) {
+                if (t[j] >= 0.0) acc += fma(4.0, fabs(f - 0.5), -1.0);
+                f += wf;
+                if (f >= 1.0) f -= 1.0;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < kFItems; j++)
+                if (t[j] >= 0.0) acc += lfo_shape_exact(mwave, t[j], fm, phm, mpw);
+        }
         acc = warp_sum(acc);
         if (lane == 0) a.lfo_prefix[(int64_t)e * a.lfo_rows + row] = acc;
     }
