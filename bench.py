@@ -140,10 +140,45 @@ CPU_VOICES_PER_PROC = 8
 CPU_FRAMES = 96000
 
 
-def _cpu_worker(args):
-    """Pure-Python port: render `hi-lo` voices x `frames`, pan and mix them, convert to PCM."""
-    lo, hi, frames, seed = args
+def reference_package_dir():
+    """Where the UNMODIFIED reference package would sit: baseline/_ref (the pip --target install
+    that travels to the GPU box), else SYNTHPLAYER_SRC.  None while the source is absent."""
+    for d in (os.path.join(ROOT, "baseline", "_ref"), os.environ.get("SYNTHPLAYER_SRC") or ""):
+        if d and os.path.isfile(os.path.join(d, "synthplayer", "oscillators.py")):
+            return d
+    return None
+
+
+def _cpu_modules():
+    """(oscillator module, float->PCM function, kind): the real synthplayer package when it is
+    installed under baseline/_ref (kind "reference"), else the oracle port (kind "port")."""
+    ref = reference_package_dir()
+    if ref:
+        if ref not in sys.path:
+            sys.path.insert(0, ref)
+        import synthplayer.oscillators as osc
+
+        def render_floats(o, n):
+            out = []
+            for block in o.blocks():
+                out.extend(block)
+                if len(out) >= n:
+                    break
+            return out[:n]
+
+        def to_pcm(values):
+            return [int(v * 32767) for v in values]
+        osc.render_floats, osc.to_pcm = render_floats, to_pcm
+        return osc, "reference"
     from oracle import synth_oracle as so
+    return so, "port"
+
+
+def _cpu_worker(args):
+    """The CPU implementation of the path (the reference package if present, else the pure-Python
+    port): render `hi-lo` voices x `frames`, pan and mix them, convert to PCM."""
+    lo, hi, frames, seed = args
+    so, _ = _cpu_modules()
     p = voice_params(VOICES_PER_GPU, seed)
     left, right = [0.0] * frames, [0.0] * frames
     t0 = time.perf_counter()
@@ -213,16 +248,19 @@ def run_reference(args):
         vals.append(v)
     wall = time.perf_counter() - t_all
     value = sum(vals) / len(vals)
-    sample = "%d processes x %d voices x %d frames per step (pure-Python port of the FM+ADSR+mix chain)" % (
-        cores, nv, frames)
+    kind = _cpu_modules()[1]
+    what = "the synthplayer package itself, from baseline/_ref" if kind == "reference" else \
+        "pure-Python port of the FM+ADSR+mix chain"
+    sample = "%d processes x %d voices x %d frames per step (%s)" % (cores, nv, frames, what)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic", "config": workload_config(args.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference source absent offline (/root/reference holds only README.md): this is the oracle port",
+        "note": "the unmodified synthplayer package (baseline/_ref)" if kind == "reference" else
+                "reference source absent offline (/root/reference holds only README.md): this is the oracle port",
     }))
 
 
@@ -399,8 +437,8 @@ def run_ours(args):
             v1, dt1 = cpu_port_throughput(1, nv)
             vn, dtn = cpu_port_throughput(cores, nv)
             vc, dtc = cpu_c_port_throughput()
-            cpu = {"value": vn, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": "pure-Python port (oracle/synth_oracle.py), %d processes x %d voices x %d frames (%.1f s); "
+            cpu = {"value": vn, "unit": UNIT, "cores": cores, "kind": _cpu_modules()[1],
+                   "sample": "pure-Python CPU implementation (synthplayer from baseline/_ref if present, else oracle/synth_oracle.py), %d processes x %d voices x %d frames (%.1f s); "
                              "single process: %.4f Msamples/s (%.1f s); compiled C port, 1 thread, 48 voices x 10 s: "
                              "%.2f Msamples/s (%.1f s)" % (cores, nv, CPU_FRAMES, dtn, v1, dt1, vc, dtc),
                    "single_process_value": v1, "c_port_1thread_value": vc}

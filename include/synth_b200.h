@@ -36,6 +36,9 @@ extern "C" {
 #define SB_WAVE_SQUARE 2
 #define SB_WAVE_SAWTOOTH 3
 #define SB_WAVE_PULSE 4
+/* general render path only (sb_osc_render_f32); not admitted as bank voices */
+#define SB_WAVE_SEMICIRCLE 5
+#define SB_WAVE_POINTY 6
 
 int sb_abi_version(void);
 const char *sb_last_error(void);

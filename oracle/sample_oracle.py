@@ -464,3 +464,46 @@ class Sample:
             R.fadeout(release)
         self.join(D).join(S).join(R)
         return self
+
+
+class WaveSynth:
+    """synthplayer.synth.WaveSynth (recalled): the waveform methods build the oscillator with the
+    integer scale folded into amplitude and bias, take int(samplerate*duration) values and store
+    int(v) of each (truncation toward zero) in a mono Sample."""
+
+    def __init__(self, samplerate=0, samplewidth=0):
+        self.samplerate = samplerate or so.NORM_SAMPLERATE
+        self.samplewidth = samplewidth or so.NORM_SAMPLEWIDTH
+        if self.samplewidth not in (2, 4):
+            raise ValueError("only samplewidth 2 or 4 supported")
+
+    def _scale(self, freq, amplitude, bias):
+        assert freq <= self.samplerate / 2
+        assert 0 <= amplitude <= 1.0
+        assert -1 <= bias <= 1.0
+        return 2 ** (self.samplewidth * 8 - 1) - 1
+
+    def _sample(self, osc, duration):
+        values = so.render_floats(osc, int(self.samplerate * duration))
+        return Sample.from_array(Sample.get_array(self.samplewidth, [int(v) for v in values]), self.samplerate, 1)
+
+    def sine(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Sine(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)
+
+    def square(self, frequency, duration, amplitude=0.75, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Square(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)
+
+    def triangle(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Triangle(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)
+
+    def sawtooth(self, frequency, duration, amplitude=0.75, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Sawtooth(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)
+
+    def pulse(self, frequency, duration, amplitude=0.75, phase=0.0, bias=0.0, pulsewidth=0.1, fm_lfo=None, pwm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Pulse(frequency, amplitude * k, phase, bias * k, pulsewidth, fm_lfo=fm_lfo,
+                                     pwm_lfo=pwm_lfo, samplerate=self.samplerate), duration)

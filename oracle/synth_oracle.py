@@ -40,7 +40,7 @@ Design notes that bear on parity (answers to SURVEY.md K1..K10, as recalled):
 import itertools
 import random
 import sys
-from math import pi, sin, fabs, floor, log, sqrt
+from math import pi, sin, cos, copysign, fabs, floor, log, sqrt
 
 NORM_SAMPLERATE = 44100
 NORM_SAMPLEWIDTH = 2
@@ -87,19 +87,24 @@ class Sine(Oscillator):
         self._phase = phase
         self._fm_lfo = fm_lfo
 
-    def generator(self):
+    def _phases(self):
         fm = _fm_iter(self._fm_lfo)
         phase_correction = self._phase * 2 * pi
         freq_previous = self.frequency
         increment = 2.0 * pi / self._samplerate
         t = 0.0
-        frequency, amplitude, bias = self.frequency, self.amplitude, self.bias
+        frequency = self.frequency
         while True:
             freq = frequency * (1.0 + next(fm))
             phase_correction += (freq_previous - freq) * t
             freq_previous = freq
-            yield sin(t * freq + phase_correction) * amplitude + bias
+            yield t * freq + phase_correction
             t += increment
+
+    def generator(self):
+        amplitude, bias = self.amplitude, self.bias
+        for x in self._phases():
+            yield sin(x) * amplitude + bias
 
 
 class _CycleOsc(Oscillator):
@@ -179,6 +184,27 @@ class Pulse(_CycleOsc):
             elif pw >= 1.0:
                 pw = 1.0 - epsilon
             yield (amplitude if tt % 1.0 < pw else -amplitude) + bias
+
+
+class Semicircle(_CycleOsc):
+    """synthplayer.oscillators.Semicircle (recalled, LOW confidence in the exact expression):
+    ft = tt - floor(tt) - 0.5; value = sqrt(0.25 - ft*ft) * (2*amplitude) + bias."""
+
+    def generator(self):
+        amplitude2, bias = self.amplitude * 2.0, self.bias
+        for tt in self._tt():
+            ft = tt - floor(tt) - 0.5
+            yield sqrt(0.25 - ft * ft) * amplitude2 + bias
+
+
+class Pointy(Sine):
+    """synthplayer.oscillators.Pointy (recalled, LOW confidence in the exact expression): phase in
+    radians like Sine; vv = 1 - |cos x|; value = copysign(vv*vv, sin x) * amplitude + bias."""
+
+    def generator(self):
+        for x in self._phases():
+            vv = 1.0 - fabs(cos(x))
+            yield copysign(vv * vv, sin(x)) * self.amplitude + self.bias
 
 
 class WhiteNoise(Oscillator):

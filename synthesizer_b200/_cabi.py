@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SYNTH_B200_LIB") or os.path.join(_HERE, "libsynth_b200.so")
 
 WAVE_NONE, WAVE_SINE, WAVE_TRIANGLE, WAVE_SQUARE, WAVE_SAWTOOTH, WAVE_PULSE = -1, 0, 1, 2, 3, 4
+WAVE_SEMICIRCLE, WAVE_POINTY = 5, 6
 TIMEBASE_MAX_SEGS = 256
 ECHO_MAX = 64
 

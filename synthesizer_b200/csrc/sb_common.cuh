@@ -131,6 +131,19 @@ __device__ __forceinline__ float wave_shape(int wave, double ph, double pw)
     }
     case SB_WAVE_PULSE:
         return (py_mod1(ph) < pw) ? 1.0f : -1.0f;
+    case SB_WAVE_SEMICIRCLE: {
+        // half circle over each cycle: ft = ph - floor(ph) - 0.5, sqrt(0.25 - ft*ft) * (2*amplitude)
+        const double ft = __dadd_rn(__dadd_rn(ph, -floor(ph)), -0.5);
+        return (float)(2.0 * sqrt(__dadd_rn(0.25, -__dmul_rn(ft, ft))));
+    }
+    case SB_WAVE_POINTY: {
+        // 'inverted cosine': vv = 1 - |cos(ph)|, value = copysign(vv*vv, sin(ph)); ph in radians
+        double k = rint(ph * kInvTwoPi);
+        double r = fma(-k, kTwoPiHi, ph);
+        r = fma(-k, kTwoPiLo, r);
+        const double vv = 1.0 - fabs(cos(r));
+        return (float)copysign(vv * vv, sin(r));
+    }
     }
     return 0.0f;
 }
@@ -147,9 +160,9 @@ __device__ __forceinline__ double clamp_pulsewidth(double pw)
 __host__ __device__ __forceinline__ double phase0_of(int wave, double phase)
 {
 #ifdef __CUDA_ARCH__
-    return wave == SB_WAVE_SINE ? __dmul_rn(__dmul_rn(phase, 2.0), 3.141592653589793) : phase;
+    return (wave == SB_WAVE_SINE || wave == SB_WAVE_POINTY) ? __dmul_rn(__dmul_rn(phase, 2.0), 3.141592653589793) : phase;
 #else
-    return wave == SB_WAVE_SINE ? phase * 2 * 3.141592653589793 : phase;
+    return (wave == SB_WAVE_SINE || wave == SB_WAVE_POINTY) ? phase * 2 * 3.141592653589793 : phase;
 #endif
 }
 

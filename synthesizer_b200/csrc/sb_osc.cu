@@ -413,7 +413,7 @@ extern "C" int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_d
                                  const float *pwm_dev, float *out_dev, void *stream)
 {
     SB_REQUIRE(p && tb_dev && out_dev, "sb_osc_render_f32: null pointer");
-    SB_REQUIRE(p->wave >= SB_WAVE_SINE && p->wave <= SB_WAVE_PULSE, "sb_osc_render_f32: unknown waveform");
+    SB_REQUIRE(p->wave >= SB_WAVE_SINE && p->wave <= SB_WAVE_POINTY, "sb_osc_render_f32: unknown waveform");
     SB_REQUIRE(nsegs > 0 && nsegs <= kMaxSegs && n0 >= 0 && count >= 0, "sb_osc_render_f32: bad range");
     if (count == 0) return SB_OK;
     constexpr int ITEMS = 4;

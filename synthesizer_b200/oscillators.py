@@ -27,7 +27,7 @@ from . import params
 
 __all__ = ["Oscillator", "Filter", "Sine", "Triangle", "Square", "SquareH", "Harmonics", "Pulse", "Sawtooth",
            "SawtoothH", "WhiteNoise", "Linear", "FastSine", "FastPulse", "FastTriangle", "FastSawtooth",
-           "FastSquare", "EnvelopeFilter", "MixingFilter", "AmpModulationFilter", "DelayFilter",
+           "FastSquare", "Semicircle", "Pointy", "EnvelopeFilter", "MixingFilter", "AmpModulationFilter", "DelayFilter",
            "EchoFilter", "ClipFilter", "AbsFilter", "NullFilter"]
 
 _FM_SEEK_CHUNK = 1 << 22
@@ -126,7 +126,7 @@ class _WaveOscillator(Oscillator):
         self._fm_carry = None
 
     def _timebase(self):
-        return D.timebase_rad(self._samplerate) if self._wave == C.WAVE_SINE else D.timebase_cyc(self._samplerate)
+        return D.timebase_rad(self._samplerate) if self._wave in (C.WAVE_SINE, C.WAVE_POINTY) else D.timebase_cyc(self._samplerate)
 
     def _length(self):
         lens = [x._length() for x in (self._fm_lfo, self._pwm_lfo) if x is not None]
@@ -216,6 +216,18 @@ class Pulse(_WaveOscillator):
         super().__init__(frequency, amplitude, phase, bias, fm_lfo, samplerate)
         self.pulsewidth = pulsewidth
         self._pwm_lfo = pwm_lfo
+
+
+class Semicircle(_WaveOscillator):
+    """Semicircle half ('W3'), with optional FM (synthplayer.oscillators.Semicircle; formula
+    recalled with low confidence: sqrt(0.25 - ft*ft) * 2*amplitude + bias, ft = frac(phase) - 0.5)."""
+    _wave = C.WAVE_SEMICIRCLE
+
+
+class Pointy(_WaveOscillator):
+    """Pointy wave ('inverted cosine', 'W2'), with optional FM (synthplayer.oscillators.Pointy;
+    formula recalled with low confidence: vv = 1 - |cos x|, copysign(vv*vv, sin x)*amplitude + bias)."""
+    _wave = C.WAVE_POINTY
 
 
 class Harmonics(_WaveOscillator):

@@ -36,7 +36,8 @@ def _voice_from(osc, gain_l, gain_r):
         if osc._stop_at_end:
             raise ValueError("voices with stop_at_end envelopes must use the general render path")
         env, osc = osc._env, osc._sources[0]
-    if not isinstance(osc, _WaveOscillator) or isinstance(osc, Harmonics) or osc._pwm_lfo is not None:
+    if not isinstance(osc, _WaveOscillator) or isinstance(osc, Harmonics) or osc._pwm_lfo is not None \
+            or osc._wave > C.WAVE_PULSE:
         raise ValueError("a bank voice is a Sine/Triangle/Square/Sawtooth/Pulse carrier without PWM")
     v.c_wave, v.c_freq, v.c_phase = osc._wave, osc.frequency, osc._phase
     v.c_amp, v.c_bias, v.c_pw = osc.amplitude, osc.bias, osc.pulsewidth
@@ -45,7 +46,7 @@ def _voice_from(osc, gain_l, gain_r):
         v.m_wave = C.WAVE_NONE
     else:
         if not isinstance(lfo, _WaveOscillator) or isinstance(lfo, Harmonics) or lfo._fm_lfo is not None \
-                or lfo._pwm_lfo is not None:
+                or lfo._pwm_lfo is not None or lfo._wave > C.WAVE_PULSE:
             raise ValueError("the FM modulator of a bank voice must be a plain waveform oscillator")
         if lfo._samplerate != osc._samplerate:
             raise ValueError("carrier and modulator sample rates differ")
