@@ -156,8 +156,8 @@ int sb_fm_prefix_f64_noalloc(const float *lfo_dev, const sb_time_seg *tb_dev, in
  * from draw0); parity tests inject the same draws on both sides. */
 int sb_noise_render_f32(const float *u_dev, int64_t draw0, int64_t cycles, double amplitude,
                         double bias, int64_t n0, int64_t count, float *out_dev, void *stream);
-/* synthplayer.oscillators.Linear: a ramp start + n*increment clamped to [min, max] (the first
- * value is `start` itself, unclamped, as upstream yields it before the first clamp). */
+/* synthplayer.oscillators.Linear: upstream's serial value = clamp(value + increment): the first
+ * value is `start` itself, unclamped; the following ones ramp from clamp(start + increment). */
 int sb_linear_render_f32(double start, double increment, double min_value, double max_value,
                          int64_t n0, int64_t count, float *out_dev, void *stream);
 /* Counter-based uniform draws (Philox-4x32-10) for product use when no buffer is injected. */
@@ -280,6 +280,12 @@ int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan *plan,
                        const sb_time_seg *tb_cyc_dev, int nsegs_cyc,
                        int64_t n0, double samplerate, void *scratch_dev, float *partial_dev,
                        float *mix_dev, void *stream);
+/* After sb_bank_render_f32 on the same stream: waits for it and reads back how many voices were
+ * left to the generic kernels (class 0, or class-2 voices beyond the scan_voices hint) into
+ * *generic_needed (may be NULL).  Returns SB_EINVAL when the plan's hint said generic_voices = 0
+ * and that count is not zero: those voices are missing from the mix (a hint was too small).
+ * Callers that pass exact hints (sb_host_bank_render_pcm16, the Python VoiceBank) need not call it. */
+int sb_bank_render_check(const sb_bank_plan *plan, const void *scratch_dev, int *generic_needed, void *stream);
 
 /* ------------------------------------------------------------------ integer PCM -------
  * Bit-exact restatements of the CPython audioop routines synthplayer's Sample calls. */
@@ -305,6 +311,10 @@ int sb_pcm16_fadeout(int16_t *buf_dev, int64_t nsamples, double target_volume, v
 int sb_pcm16_fadein(int16_t *buf_dev, int64_t nsamples, double start_volume, void *stream);
 /* Sample.modulate_amp: int(v * m) */
 int sb_pcm16_modulate(int16_t *buf_dev, const float *mod_dev, int64_t count, void *stream);
+/* Sample.modulate_amp with a Sample / list / array modulator (upstream cycles it and divides by
+   its largest magnitude in fp64): int(v * mod[i % mod_len]), factors in fp64 */
+int sb_pcm16_modulate_cycle_f64(int16_t *buf_dev, const double *mod_dev, int64_t mod_len, int64_t count, void *stream);
+int sb_pcm32_modulate_cycle_f64(int32_t *buf_dev, const double *mod_dev, int64_t mod_len, int64_t count, void *stream);
 /* audioop.ratecv(frames, 2, nchannels, inrate, outrate, None) (Sample.resample / speed).
  * sb_pcm16_ratecv_frames gives the number of output frames. */
 int64_t sb_pcm16_ratecv_frames(int64_t in_frames, int64_t inrate, int64_t outrate);

@@ -115,7 +115,10 @@ _SIGNATURES = {
     "sb_pcm32_to_pcm16": (c_int, [_P, c_int64, _P, _P]),
     "sb_pcm16_fadeout": (c_int, [_P, c_int64, c_double, _P]),
     "sb_pcm16_fadein": (c_int, [_P, c_int64, c_double, _P]),
+    "sb_bank_render_check": (c_int, [_P, _P, _P, _P]),
     "sb_pcm16_modulate": (c_int, [_P, _P, c_int64, _P]),
+    "sb_pcm16_modulate_cycle_f64": (c_int, [_P, _P, c_int64, c_int64, _P]),
+    "sb_pcm32_modulate_cycle_f64": (c_int, [_P, _P, c_int64, c_int64, _P]),
     "sb_pcm16_ratecv_frames": (c_int64, [c_int64, c_int64, c_int64]),
     "sb_pcm16_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
     "sb_pcm16_ratecv_many": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int64, c_int, c_int64, _P, _P]),

@@ -224,9 +224,15 @@ __global__ void linear_kernel(double start, double inc, double lo, double hi, in
 {
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        // upstream's serial value = clamp(value + inc): the first value is the start level as
+        // given; from the second on the ramp runs from v1 = clamp(start + inc), clamped
+        // (a start level outside [lo, hi] is pulled in by the first step, not by the n-th)
         int64_t n = n0 + i;
-        double v = start + (double)n * inc;
-        if (n > 0) v = fmin(hi, fmax(lo, v));
+        double v = start;
+        if (n > 0) {
+            const double v1 = fmin(hi, fmax(lo, start + inc));
+            v = fmin(hi, fmax(lo, v1 + (double)(n - 1) * inc));
+        }
         out[i] = (float)v;
     }
 }

@@ -32,8 +32,9 @@ union Vec8 {
 
 // generic unary/binary streaming map over int16 with a 128-bit fast path
 template <class F>
-__device__ __forceinline__ void map16(const int16_t *__restrict__ a, const int16_t *__restrict__ b,
-                                      int16_t *__restrict__ out, int64_t count, F f)
+// (no __restrict__: the in-place callers pass the same buffer as `a` and `out`; every element is
+// read and written by the same thread, loads before the store)
+__device__ __forceinline__ void map16(const int16_t *a, const int16_t *b, int16_t *out, int64_t count, F f)
 {
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -110,6 +111,16 @@ __global__ void pcm16_modulate_kernel(int16_t *buf, const float *__restrict__ mo
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
         buf[i] = (int16_t)__double2int_rz(__dmul_rn((double)buf[i], (double)mod[i]));
+}
+
+// the cycled, normalised modulator of Sample.modulate_amp(list / array / Sample): the factors
+// stay in fp64, as upstream's v/biggest are (float32 factors give 6 where 70/100*10 gives 7)
+template <class T>
+__global__ void pcm_modulate_cycle_kernel(T *buf, const double *__restrict__ mod, int64_t mod_len, int64_t count)
+{
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        buf[i] = (T)__double2int_rz(__dmul_rn((double)buf[i], mod[i % mod_len]));
 }
 
 __global__ void pcm16_reverse_kernel(const int16_t *__restrict__ in, int64_t count, int16_t *__restrict__ out)
@@ -745,6 +756,28 @@ extern "C" int sb_pcm16_fadein(int16_t *buf_dev, int64_t nsamples, double start_
     else
         pcm16_fadein_kernel<false><<<PCM_GRID(nsamples), kPBlock, 0, (cudaStream_t)stream>>>(buf_dev, nsamples, 1.0 - start_volume,
                                                                                            start_volume);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_pcm16_modulate_cycle_f64(int16_t *buf_dev, const double *mod_dev, int64_t mod_len, int64_t count,
+                                           void *stream)
+{
+    SB_REQUIRE(buf_dev && mod_dev && mod_len >= 1 && count >= 0, "sb_pcm16_modulate_cycle_f64: bad arguments");
+    if (!count) return SB_OK;
+    pcm_modulate_cycle_kernel<int16_t><<<grid_for(count, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
+        buf_dev, mod_dev, mod_len, count);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_pcm32_modulate_cycle_f64(int32_t *buf_dev, const double *mod_dev, int64_t mod_len, int64_t count,
+                                           void *stream)
+{
+    SB_REQUIRE(buf_dev && mod_dev && mod_len >= 1 && count >= 0, "sb_pcm32_modulate_cycle_f64: bad arguments");
+    if (!count) return SB_OK;
+    pcm_modulate_cycle_kernel<int32_t><<<grid_for(count, kPBlock, kPMaxBlocks), kPBlock, 0, (cudaStream_t)stream>>>(
+        buf_dev, mod_dev, mod_len, count);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }

@@ -18,7 +18,7 @@ __device__ __forceinline__ int fbound32(double val)
 }
 
 template <class F>
-__global__ void map32_kernel(const int32_t *__restrict__ a, const int32_t *__restrict__ b, int32_t *__restrict__ out,
+__global__ void map32_kernel(const int32_t *a, const int32_t *b, int32_t *out,        // (in-place callers alias a and out)
                              int64_t count, F f)
 {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;

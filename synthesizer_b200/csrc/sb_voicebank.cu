@@ -160,7 +160,8 @@ struct BankArgs {
     int *order;           // [3][nvoices]: per kernel part, each group's voices of that part sorted by kind
                           // (bank_sort_kernel); entry = voice index, the group's slice starts at its first voice
     int *kind_end;        // [ngroups][3][kFastKinds]: end position of each kind in the group's sorted slice
-    int *scan_list;       // [1 + nvoices]: count, then the indices of the FV_SCAN voices (any order)
+    int *scan_list;       // [2 + nvoices]: count of FV_SCAN voices, count of voices left to the generic kernels,
+                          // then the indices of the FV_SCAN voices (any order)
     int scan_cap;         // rows of the pre-pass grid: how many list entries the launch covers
     int fast_nspans;
     int64_t fast_span_len;
@@ -320,7 +321,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
             // left to the generic kernels.
             const int slot = a.scan_cap > 0 ? atomicAdd(a.scan_list, 1) : 0;
             if (slot < a.scan_cap) {
-                a.scan_list[1 + slot] = v;
+                a.scan_list[2 + slot] = v;
                 F.tab_row = slot;
                 *reinterpret_cast<double *>(&F.half) = clamp_pulsewidth((double)V.m_pw);
                 F.flags |= FV_SCAN | ((V.m_wave & 7) << FV_MWAVE_SHIFT);
@@ -334,6 +335,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
         F.a_slope = (float)V.env.a_slope; F.d_slope = (float)V.env.d_slope; F.r_slope = (float)V.env.r_slope;
         F.sl = (float)V.env.sustain_level; F.amp_extra = (float)V.env.amp_extra;
         if (fast && !demote) F.flags |= FV_FAST;
+        else atomicAdd(a.scan_list + 1, 1);              // sb_bank_render_check() reads this
         if (has_mod) F.flags |= FV_HAS_MOD;
         if (tri) F.flags |= FV_TRIANGLE;
         F.flags |= (V.c_wave & 7) << FV_WAVE_SHIFT;
@@ -1208,7 +1210,7 @@ bank_lfo_tile_kernel(BankArgs a)
     }
     const int nscan = min(a.scan_list[0], a.scan_cap);
     for (int e = blockIdx.y; e < nscan; e += gridDim.y) {
-        const FastVoice &F = a.fastv[a.scan_list[1 + e]];
+        const FastVoice &F = a.fastv[a.scan_list[2 + e]];
         const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
         const double fm = F.mod.x, phm = F.mod.y, mpw = scan_m_pw64(F);
         double acc = 0.0;
@@ -1547,7 +1549,7 @@ static inline int64_t bank_off_scanlist(const sb_bank_plan *p)
 }
 static inline int64_t bank_off_order(const sb_bank_plan *p)
 {
-    return bank_off_scanlist(p) + align_up((int64_t)(p->nvoices + 1) * (int64_t)sizeof(int), 256);
+    return bank_off_scanlist(p) + align_up((int64_t)(p->nvoices + 2) * (int64_t)sizeof(int), 256);
 }
 static inline int64_t bank_off_kindend(const sb_bank_plan *p)
 {
@@ -1708,7 +1710,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.lfo_nprefix = (int)bank_lfo_nprefix(plan);
     a.lfo_rows = (int)bank_lfo_rows(plan);
     a.scan_cap = plan->scan_voices < 0 ? plan->nvoices : plan->scan_voices;
-    if (plan->scan_voices != 0) SB_CUDA_CHECK(cudaMemsetAsync(a.scan_list, 0, sizeof(int), s));
+    SB_CUDA_CHECK(cudaMemsetAsync(a.scan_list, 0, 2 * sizeof(int), s));
     a.fast_nspans = plan->fast_nspans;
     a.fast_span_len = plan->fast_span_len;
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
@@ -1775,6 +1777,24 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
         bank_fold_kernel<<<grid_for(nfloats / 4 + 1, 256, 148 * 8), 256, 0, s>>>(partial_dev, a.ngroups,
                                                                                nfloats, a.out_stride, mix_dev);
         SB_LAUNCH_CHECK();
+    }
+    return SB_OK;
+}
+
+extern "C" int sb_bank_render_check(const sb_bank_plan *plan, const void *scratch_dev, int *generic_needed, void *stream)
+{
+    SB_REQUIRE(plan && scratch_dev, "sb_bank_render_check: null pointer");
+    int words[2] = {0, 0};
+    const unsigned char *scratch = (const unsigned char *)scratch_dev;
+    SB_CUDA_CHECK(cudaMemcpyAsync(words, scratch + bank_off_scanlist(plan), sizeof(words), cudaMemcpyDeviceToHost,
+                                  (cudaStream_t)stream));
+    SB_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (generic_needed) *generic_needed = words[1];
+    if (plan->generic_voices == 0 && words[1] != 0) {
+        set_error("sb_bank_render_f32 left %d voice(s) out of the mix: the plan's hint said no voice needs the generic "
+                  "kernels (generic_voices = 0), but %d do (class-0 voices, or class-2 voices beyond scan_voices)",
+                  words[1], words[1]);
+        return SB_EINVAL;
     }
     return SB_OK;
 }

@@ -503,11 +503,12 @@ class Sample:
         else:
             if isinstance(modulation_source, Sample):
                 modulation_source = modulation_source.get_frame_array()
+            # the factors v/biggest stay in fp64 (as upstream's are) and are cycled by the kernel
             vals = torch.tensor(list(modulation_source), dtype=torch.float64)
             biggest = max(float(vals.max()), abs(float(vals.min())))
-            vals = (vals / biggest).to(torch.float32)
-            reps = -(-n // vals.numel())
-            mod = vals.repeat(reps)[:n].to(D.device())
+            mod = (vals / biggest).to(D.device())
+            C.call(self._k("modulate_cycle_f64"), D.ptr(self._dev), D.ptr(mod), mod.numel(), n, D.stream())
+            return self
         C.call(self._k("modulate"), D.ptr(self._dev), D.ptr(mod), n, D.stream())
         return self
 
@@ -615,6 +616,8 @@ class Sample:
         starts, srcs = [], []
         for seconds, other in placements:
             self._same_format(other)
+            if seconds < 0:
+                raise ValueError("mix_at_many: negative start time")
             if other._dev is None:
                 continue
             starts.append(self._sample_idx(seconds))

@@ -67,6 +67,7 @@ class VoiceBank:
         self.samplerate = samplerate
         self._voices = []
         self._dev = None
+        self._last = None
 
     def __len__(self):
         return len(self._voices)
@@ -155,7 +156,17 @@ class VoiceBank:
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,
                D.ptr(tc.dev()), tc.nsegs, start, float(self.samplerate), D.ptr(carry), D.ptr(partial),
                D.ptr(mix), D.stream())
+        self._last = (plan, carry)
         return mix
+
+    def check_last_render(self):
+        """Waits for the last render and returns how many of its voices were left to the generic
+        kernels; raises if the hints it was given said none would be (sb_bank_render_check):
+        those voices are then missing from the mix.  Only needed with hand-made hints."""
+        plan, carry = self._last
+        n = ctypes.c_int(0)
+        C.call("sb_bank_render_check", ctypes.byref(plan), D.ptr(carry), ctypes.byref(n), D.stream())
+        return n.value
 
     def render_sharded(self, nframes, start=0, group=None):
         """Voice-sharded render: this rank renders its slice of the voices; the partial mixes

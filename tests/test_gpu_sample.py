@@ -357,6 +357,17 @@ def test_modulate_amp(cuda):
     g, o = _pair(_rand(5000, 24, full=False))
     mod = [0, 50, 100, 50, 0, -50, -100, -50]
     _same(g.modulate_amp(mod), o.modulate_amp(mod), "modulate by list")
+    # ratios float32 cannot represent: 70/100 * 10 is 7 in fp64 and 6 in float32
+    frames = np.tile(np.array([10, -10, 30, 7, 32767, -32768, 1], dtype=np.int16), 300)
+    g, o = _pair(frames)
+    mod = [0, 30, 70, 100, -70]
+    _same(g.modulate_amp(mod), o.modulate_amp(mod), "modulate by list, fp64 factors")
+    g, o = _pair(frames)
+    import synthesizer_b200 as sb2
+    from oracle import sample_oracle as sa
+    ms = np.array([3, 7, -11, 13], dtype="<i2").tobytes()
+    _same(g.modulate_amp(sb2.Sample.from_raw_frames(ms, 2, 44100, 1)),
+          o.modulate_amp(sa.Sample.from_raw_frames(ms, 2, 44100, 1)), "modulate by Sample")
 
 
 def test_wav_roundtrip(cuda, tmp_path):

@@ -350,6 +350,13 @@ def test_fast_and_generic_voices_share_a_group(cuda):
     short = bank.render(n, voices_dev=vd, generic_voices=len(kinds), edged_voices=len(kinds), scan_voices=1)
     bad = np.abs(dev_pcm16(short).astype(np.int64) - oracle_bank_pcm(P, n, sr)) > 1
     assert bad.mean() < 2e-5
+    assert bank.check_last_render() == kinds.count(0) + kinds.count(2) - 1
+    # hints that are too small while generic_voices says 0 lose voices: the status call reports it
+    bank.render(n, voices_dev=vd, generic_voices=0, edged_voices=len(kinds), scan_voices=len(kinds))
+    with pytest.raises(C.SbError, match="out of the mix"):
+        bank.check_last_render()
+    bank.render(n, voices_dev=vd)
+    assert bank.check_last_render() == kinds.count(0)
 
 
 def test_bank_chunked_start_offsets(cuda):
