@@ -467,6 +467,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the per-config / per-class / sustained legs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

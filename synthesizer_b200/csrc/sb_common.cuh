@@ -197,16 +197,15 @@ __device__ __forceinline__ int f64_trunc_to_i32(double v)
     return (__double2hiint(v) < 0) ? -m : m;
 }
 
-// IEEE a/b for a divisor known in advance: rcp_b = RN(1/b) once, then a product and two fused
-// correction steps per quotient (Markstein) instead of the ~40-instruction fp64 divide.  The
-// result is the correctly rounded quotient for normal a/b (b's significand not all ones, which
-// an integer sample count never is); tools/fma_division_check.py replays it in exact arithmetic.
+// IEEE a/b for a divisor known in advance: rcp_b = RN(1/b) once, then a product and one fused
+// correction step per quotient instead of the ~40-instruction fp64 divide.  By Markstein's
+// theorem the result is the correctly rounded quotient for normal a/b (b's significand not all
+// ones, which an integer sample count never is); tools/fma_division_check.py replays it in
+// exact arithmetic.
 __device__ __forceinline__ double div_by_known(double a, double b, double rcp_b)
 {
-    double q = __dmul_rn(a, rcp_b);
-    q = __fma_rn(__fma_rn(-b, q, a), rcp_b, q);
-    q = __fma_rn(__fma_rn(-b, q, a), rcp_b, q);
-    return q;
+    const double q = __dmul_rn(a, rcp_b);
+    return __fma_rn(__fma_rn(-b, q, a), rcp_b, q);
 }
 
 inline int grid_for(int64_t work_items, int block, int max_blocks)

@@ -1,7 +1,9 @@
 """
 Renders one 8192-voice bank of a single (carrier, modulator) kind a few times: a target for
 `ncu -k regex:bank_` when looking at the edged or generic kernels (bench.py only exercises the
-Sine x Sine kind).   python tools/class_bank.py <carrier 0..4> <modulator 0..4 | -1> [voices]
+Sine x Sine kind).   python tools/class_bank.py <carrier 0..4> <modulator 0..4 | -1 | 5> [voices]
+(modulator 5 = a Sine of FM gain 3 rad: the generic kernels; carrier 9 = a uniform mix of all
+5 x 5 (carrier, modulator) kinds, what BASELINE config 3 calls "mixed waveforms")
 """
 import os
 import sys
@@ -18,9 +20,16 @@ sr, nfr = 48000, 480000
 classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
 r = np.random.default_rng(11)
 b = sb.VoiceBank(sr)
+mixed = cw == 9
 for v in range(nv):
-    lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr) if mw >= 0 else None
-    car = classes[cw](float(r.uniform(55, 1760)), 0.9 / nv, fm_lfo=lfo, samplerate=sr)
+    if mixed:
+        cw, mw = v % 5, (v // 5) % 5
+    f0 = float(r.uniform(55, 1760))
+    if mw == 5:
+        lfo, f0 = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=sr), float(r.uniform(3000, 5000))
+    else:
+        lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr) if mw >= 0 else None
+    car = classes[cw](f0, 0.9 / nv, fm_lfo=lfo, samplerate=sr)
     pan = float(r.uniform(-1, 1))
     b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
 vd, _ = b._upload(0, None)
@@ -31,4 +40,4 @@ for _ in range(3):
     b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc)
     t1.record()
     torch.cuda.synchronize()
-    print("%.3f ms (generic %d, edged %d)" % (t0.elapsed_time(t1), g, e))
+    print("%.3f ms (generic %d, edged %d, scan %d)" % (t0.elapsed_time(t1), g, e, sc))

@@ -35,10 +35,11 @@ def main():
     rows = page(rep, "raw")
     head, units, vals = rows[0], rows[1], rows[-1]
     col = {c: i for i, c in enumerate(head)}
-    print(vals[col["Kernel Name"]])
-    for k in RAW:
-        if k in col:
-            print("  %-70s %s %s" % (k, vals[col[k]], units[col[k]]))
+    for vals in rows[2:]:                    # every profiled launch; the stall / opcode digest below is the last one's
+        print(vals[col["Kernel Name"]])
+        for k in RAW:
+            if k in col:
+                print("  %-70s %s %s" % (k, vals[col[k]], units[col[k]]))
     stalls = []
     for c, i in col.items():
         if "issue_stalled" in c and c.endswith("per_issue_active.ratio") or ("issue_stalled" in c and "ratio" in c):
