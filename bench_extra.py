@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """
-bench_extra.py — the BASELINE.json configurations that are not bench.py's headline line, and
-the HBM-bound integer kernels with their roofline fractions.  One JSON line per case.
-Not part of the driver's contract; results are kept under profiles/.
+bench_extra.py — the BASELINE.json configurations that are not bench.py's headline, the voice
+classes of the bank kernel, the HBM-bound Sample kernels with their roofline fractions, and a
+sustained-clock leg.  bench.py calls collect() after its timed region and puts the result into
+its JSON line (keys "configs", "classes", "hbm_kernels", "sustained"); run alone it prints one
+JSON line per case.
 
   python bench_extra.py [--reps 5]
 """
@@ -21,26 +23,35 @@ sys.path.insert(0, ROOT)
 import synthesizer_b200 as sb                      # noqa: E402
 from synthesizer_b200 import _cabi as C, _device as D   # noqa: E402
 
+SR = 48000
+
 
 def peaks():
     try:
-        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
     except (OSError, KeyError):
-        return 6650.0, "fallback"
+        return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def flush_l2(buf):
-    buf.add_(1)
+_flush = None
 
 
-def timed(fn, reps, flush=None):
-    """Median device time (ms) of fn over `reps`, L2 flushed (a 512 MB write) between runs."""
+def flush_l2():
+    """A 256 MB write (twice the 126 MB L2) so that the next launch finds its inputs in HBM."""
+    global _flush
+    if _flush is None:
+        _flush = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+    _flush.add_(1)
+
+
+def timed(fn, reps, flush=True):
+    """Median device time (ms, CUDA events on the current stream) of fn over `reps`."""
     fn()
     torch.cuda.synchronize()
     ts = []
     for _ in range(reps):
-        if flush is not None:
-            flush_l2(flush)
+        if flush:
+            flush_l2()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
@@ -51,196 +62,263 @@ def timed(fn, reps, flush=None):
     return ts[len(ts) // 2]
 
 
-def line(name, **kw):
-    print(json.dumps({"case": name, **kw}), flush=True)
+def wall(fn, reps=3):
+    """Median wall-clock ms of fn through the Python API, device synchronised on both sides."""
+    fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        ts.append((time.perf_counter() - t0) * 1e3)
+    ts.sort()
+    return ts[len(ts) // 2]
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--reps", type=int, default=5)
-    args = ap.parse_args()
-    torch.cuda.set_device(0)
+# ------------------------------------------------------------------------------ HBM-bound kernels
+def hbm_kernels(reps=5):
+    """The integer PCM kernels on a 10-minute stereo 48 kHz buffer (115 MB) and the float filter
+    kernels on 10 minutes mono; algorithmic bytes = every operand read once, the result written once."""
     hbm, src = peaks()
-    flush = torch.zeros(512 << 20, dtype=torch.uint8, device="cuda")
-    rng = np.random.default_rng(0)
-
-    # ---- HBM-bound PCM kernels on a 10-minute stereo 48 kHz buffer (115 MB) -------------------
-    n = 600 * 48000 * 2
+    out = {"peak_gbs": hbm, "peak_source": src, "l2": "flushed between repetitions (256 MB write)", "kernels": {}}
+    n = 600 * SR * 2
     a = torch.randint(-20000, 20000, (n,), dtype=torch.int16, device="cuda")
     b = torch.randint(-20000, 20000, (n,), dtype=torch.int16, device="cuda")
-    out = torch.empty_like(a)
-    cases = [
-        ("pcm16_add (Sample.mix)", 6 * n, lambda: C.call("sb_pcm16_add", D.ptr(a), D.ptr(b), n, D.ptr(out), D.stream())),
-        ("pcm16_mul (Sample.amplify)", 4 * n, lambda: C.call("sb_pcm16_mul", D.ptr(a), n, 0.731, D.ptr(out), D.stream())),
-        ("pcm16_fadeout (Sample.fadeout)", 4 * n, lambda: C.call("sb_pcm16_fadeout", D.ptr(out), n, 0.1, D.stream())),
-        ("pcm16_tomono (Sample.mono)", 3 * n, lambda: C.call("sb_pcm16_tomono", D.ptr(a), n // 2, 0.5, 0.5, D.ptr(out), D.stream())),
-        ("pcm16_ratecv 44100->48000 stereo (Sample.resample)", None, None),
-    ]
-    for name, nbytes, fn in cases:
-        if fn is None:
-            nin = 44100 * 600
-            src_t = a[: nin * 2]
-            nout = C.lib.sb_pcm16_ratecv_frames(nin, 44100, 48000)
-            dst_t = torch.empty(nout * 2, dtype=torch.int16, device="cuda")
-            fn = lambda: C.call("sb_pcm16_ratecv", D.ptr(src_t), nin, 2, 44100, 48000, D.ptr(dst_t), D.stream())
-            nbytes = nin * 4 + nout * 4
-        ms = timed(fn, args.reps, flush)
-        gbs = nbytes / ms / 1e6
-        line(name, ms=ms, algorithmic_bytes=nbytes, achieved_gbs=gbs, peak_gbs=hbm, peak_source=src, frac=gbs / hbm)
-
-    # float -> PCM and the float filter kernels (4 B in, 2 or 4 B out)
-    nf = 600 * 48000
+    o = torch.empty_like(a)
+    nin = 44100 * 600
+    nout = C.lib.sb_pcm16_ratecv_frames(nin, 44100, 48000)
+    dst_t = torch.empty(nout * 2, dtype=torch.int16, device="cuda")
+    nf = 600 * SR
     x = torch.rand(nf, device="cuda") * 1.6 - 0.8
     x2 = torch.rand(nf, device="cuda")
     y = torch.empty_like(x)
     p16 = torch.empty(nf, dtype=torch.int16, device="cuda")
     ovf = torch.zeros(1, dtype=torch.int64, device="cuda")
-    for name, nbytes, fn in [
+    cases = [
+        ("pcm16_add (Sample.mix)", 6 * n, lambda: C.call("sb_pcm16_add", D.ptr(a), D.ptr(b), n, D.ptr(o), D.stream())),
+        ("pcm16_mul (Sample.amplify)", 4 * n, lambda: C.call("sb_pcm16_mul", D.ptr(a), n, 0.731, D.ptr(o), D.stream())),
+        ("pcm16_fadeout (Sample.fadeout)", 4 * n, lambda: C.call("sb_pcm16_fadeout", D.ptr(o), n, 0.1, D.stream())),
+        ("pcm16_tomono (Sample.mono)", 3 * n, lambda: C.call("sb_pcm16_tomono", D.ptr(a), n // 2, 0.5, 0.5, D.ptr(o), D.stream())),
+        ("pcm16_ratecv 44100->48000 stereo (Sample.resample)", nin * 4 + nout * 4,
+         lambda: C.call("sb_pcm16_ratecv", D.ptr(a), nin, 2, 44100, 48000, D.ptr(dst_t), D.stream())),
         ("f32_to_pcm16", 6 * nf, lambda: C.call("sb_f32_to_pcm16", D.ptr(x), nf, 32767.0, D.ptr(p16), D.ptr(ovf), D.stream())),
         ("mul_f32 (AmpModulationFilter)", 12 * nf, lambda: C.call("sb_mul_f32", D.ptr(x), D.ptr(x2), nf, D.ptr(y), D.stream())),
         ("clip_f32 (ClipFilter)", 8 * nf, lambda: C.call("sb_clip_f32", D.ptr(x), -0.5, 0.5, nf, D.ptr(y), D.stream())),
-    ]:
-        ms = timed(fn, args.reps, flush)
-        gbs = nbytes / ms / 1e6
-        line(name, ms=ms, algorithmic_bytes=nbytes, achieved_gbs=gbs, peak_gbs=hbm, peak_source=src, frac=gbs / hbm)
+    ]
+    for name, nbytes, fn in cases:
+        ms = timed(fn, reps)
+        out["kernels"][name] = {"ms": ms, "algorithmic_bytes": nbytes, "gbs": nbytes / ms / 1e6, "frac": nbytes / ms / 1e6 / hbm}
+    return out
 
-    # ---- config 4: mix_at of 4096 resampled drum hits into a 10-minute 48 kHz mono buffer -------
-    sr = 48000
+
+# ------------------------------------------------------------------------------ configs 1-4
+def make_hits(rng, nhits=4096):
     hits = []
-    for k in range(4096):
-        src_rate = int(rng.choice([22050, 44100, 32000]))
+    for _ in range(nhits):
+        rate = int(rng.choice([22050, 44100, 32000]))
         m = int(rng.integers(2000, 20000))
-        t = np.arange(m) / src_rate
+        t = np.arange(m) / rate
         h = (rng.uniform(8000, 30000) * np.exp(-t * rng.uniform(8, 40)) * np.sin(2 * np.pi * rng.uniform(60, 400) * t)).astype(np.int16)
-        hits.append((src_rate, sb.Sample.from_raw_frames(h.tobytes(), 2, src_rate, 1), float(rng.uniform(0, 599.0))))
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    placed = [(when, h.copy().resample(sr)) for _, h, when in hits]
-    torch.cuda.synchronize()
-    resample_ms = (time.perf_counter() - t0) * 1e3
-    copies = [h.copy() for _, h, _ in hits]
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    sb.Sample.resample_many(copies, sr)
-    torch.cuda.synchronize()
-    resample_many_ms = (time.perf_counter() - t0) * 1e3
-    base = sb.Sample.from_raw_frames(b"", 2, sr, 1).add_silence(600.0)
-    span_samples = sum(len(h) for _, h in placed)
+        hits.append((sb.Sample.from_raw_frames(h.tobytes(), 2, rate, 1), float(rng.uniform(0, 599.0))))
+    return hits
 
-    def mix_many():
-        dst = base.copy()
-        dst.mix_at_many(placed)
-        return dst
 
-    # kernel-only timing of sb_pcm16_mix_at_many (device-resident pool and indices)
-    lens = [len(h) for _, h in placed]
-    starts = [int(sr * w) for w, _ in placed]
-    pool = torch.cat([h.device_frames() for _, h in placed])
-    offs = np.concatenate([[0], np.cumsum(lens)[:-1]])
-    idx = torch.tensor(np.stack([offs, lens, starts]), dtype=torch.int64, device="cuda")
-    dstbuf = base.copy().device_frames()
-    total = dstbuf.numel()
-    nscr = C.lib.sb_pcm16_mix_at_many_scratch_bytes(total, len(lens), int(sum(lens)))
-    scr = torch.empty(nscr, dtype=torch.uint8, device="cuda")
-    fn = lambda: C.call("sb_pcm16_mix_at_many", D.ptr(dstbuf), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]),
-                        D.ptr(idx[2]), len(lens), D.ptr(scr), nscr, D.stream())
-    ms = timed(fn, args.reps, flush)
-    fn0 = lambda: C.call("sb_pcm16_mix_at_many", D.ptr(dstbuf), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]),
-                         D.ptr(idx[2]), len(lens), None, 0, D.stream())
-    ms_noindex = timed(fn0, args.reps, flush)
-    # algorithmic bytes: every source read once, every touched destination span read and written once
-    nbytes = 2 * span_samples + 2 * 2 * span_samples
-    line("config4 mix_at_many kernel: 4096 hits into 10 min @48 kHz mono", ms=ms, algorithmic_bytes=nbytes,
-         achieved_gbs=nbytes / ms / 1e6, peak_gbs=hbm, peak_source=src, frac=nbytes / ms / 1e6 / hbm,
-         hit_samples=span_samples, dst_samples=total, ms_without_index=ms_noindex)
-    t0 = time.perf_counter()
-    mix_many()
-    torch.cuda.synchronize()
-    api_ms = (time.perf_counter() - t0) * 1e3
-    t0 = time.perf_counter()
-    dst = base.copy()
-    for when, h in placed[:512]:
-        dst.mix_at(when, h)
-    torch.cuda.synchronize()
-    loop_ms = (time.perf_counter() - t0) * 1e3 * 8
-    line("config4 through the Sample API", resample_4096_hits_ms=resample_ms, resample_many_ms=resample_many_ms,
-         mix_at_many_ms=api_ms,
-         mix_at_loop_ms_extrapolated_from_512=loop_ms, msamples_per_s=total / api_ms / 1e3)
+def config1(reps=5):
+    """BASELINE config 1: a single 440 Hz sine, 1 s mono 44.1 kHz int16 rendered to a Sample."""
+    ws = sb.WaveSynth(samplerate=44100)
+    fn = lambda: ws.sine(440, 1.0)
+    return {"workload": "WaveSynth.sine(440 Hz, 1 s) mono 44.1 kHz int16", "device_ms": timed(fn, reps),
+            "wall_ms": wall(fn, 5), "algorithmic_bytes": 88200, "voice_samples": 44100}
 
-    # ---- config 2: FM sawtooth + ADSR + echo, 60 s stereo 48 kHz through the oscillator API -------
-    def config2():
-        lfo = sb.Sine(5.0, 0.03, samplerate=sr)
-        car = sb.Sawtooth(220.0, 0.45, fm_lfo=lfo, samplerate=sr)
+
+def config2(reps=3):
+    """BASELINE config 2: Sawtooth FM'd by a Sine, ADSR + echo, 60 s stereo 48 kHz."""
+    def fn():
+        lfo = sb.Sine(5.0, 0.03, samplerate=SR)
+        car = sb.Sawtooth(220.0, 0.45, fm_lfo=lfo, samplerate=SR)
         chain = sb.EchoFilter(sb.EnvelopeFilter(car, 0.5, 1.5, 40.0, 0.6, 10.0), 1.0, 6, 0.35, 0.5)
         return sb.Sample.from_oscillator(chain, 60.0).stereo()
-    config2()
-    torch.cuda.synchronize()
     l0 = D.launch_count()
-    t0 = time.perf_counter()
-    s = config2()
-    torch.cuda.synchronize()
-    wall = (time.perf_counter() - t0) * 1e3
-    line("config2 FM saw + ADSR + echo, 60 s stereo 48 kHz (oscillator API -> Sample)", wall_ms=wall,
-         kernel_launches=D.launch_count() - l0, frames=len(s), msamples_per_s=2 * len(s) / wall / 1e3)
+    s = fn()
+    launches = D.launch_count() - l0
+    frames = len(s)
+    nbytes = frames * 2 * 2
+    ms = timed(fn, reps)
+    return {"workload": "Sawtooth x Sine FM + ADSR + EchoFilter, 60 s stereo 48 kHz, oscillator API -> Sample",
+            "device_ms": ms, "wall_ms": wall(fn), "kernel_launches": launches, "frames": frames,
+            "algorithmic_bytes": nbytes, "msamples_per_s": frames / ms / 1e3}
 
-    # ---- config 1: 440 Hz sine, 1 s mono 44.1 kHz -> Sample (WaveSynth) -----------------------------
-    ws = sb.WaveSynth(samplerate=44100)
-    ws.sine(440, 1.0)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(20):
-        ws.sine(440, 1.0)
-    torch.cuda.synchronize()
-    line("config1 WaveSynth.sine(440, 1 s) mono 44.1 kHz", wall_ms=(time.perf_counter() - t0) * 1e3 / 20)
 
-    # ---- config 3: 128-voice chord bank (mixed waveforms), 10 s stereo 48 kHz ----------------------
+def mixed_bank(nv, rng, amp=None):
+    """`nv` voices with carriers and modulators drawn uniformly from the five waveforms (what
+    BASELINE config 3 calls 'mixed waveforms'); half of the modulators are sines."""
     classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
-    bank = sb.VoiceBank(sr)
-    for v in range(128):
-        # mixed carrier waveforms; half of the voices have a sine vibrato, an eighth an LFO of
-        # another waveform (those take the tile-scan variant of the fast kernel)
+    bank = sb.VoiceBank(SR)
+    for v in range(nv):
         cw = int(rng.integers(0, 5))
         r = rng.random()
         lfo = None
         if r < 0.5:
-            lfo = sb.Sine(float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=sr)
+            lfo = sb.Sine(float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=SR)
         elif r < 0.625:
-            lfo = classes[int(rng.integers(1, 5))](float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=sr)
-        car = classes[cw](float(rng.uniform(55, 1760)), 0.9 / 128, fm_lfo=lfo, samplerate=sr)
+            lfo = classes[int(rng.integers(1, 5))](float(rng.uniform(0.5, 12)), float(rng.uniform(0.005, 0.06)), samplerate=SR)
+        car = classes[cw](float(rng.uniform(55, 1760)), amp or 0.9 / nv, fm_lfo=lfo, samplerate=SR)
         pan = float(rng.uniform(-1, 1))
         bank.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
-    nfr = 10 * sr
-    ms = timed(lambda: bank.render(nfr), args.reps)
-    line("config3 128-voice chord bank, mixed waveforms + ADSR, 10 s stereo 48 kHz", ms=ms,
-         generic_voices=bank.count_generic(), msamples_per_s=128 * nfr / ms / 1e3)
+    return bank
 
-    # ---- one kernel class at a time: 8192 voices x 10 s of a single (carrier, modulator) kind -------
-    def class_bank(cw, mw, nv=8192):
-        b = sb.VoiceBank(sr)
-        r = np.random.default_rng(11)
-        for v in range(nv):
-            lfo = None
-            f0 = float(r.uniform(55, 1760))
-            if mw == 5:          # a Sine modulator too strong for the fast path: 3.9 x 2 pi f0 / sr > 1.5 rad
-                lfo = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=sr)
-                f0 = float(r.uniform(3000, 5000))
-            elif mw is not None:
-                lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr)
-            car = classes[cw](f0, 0.9 / nv, fm_lfo=lfo, samplerate=sr)
-            pan = float(r.uniform(-1, 1))
-            b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
-        return b
-    for name, cw, mw, nv in [("Sine x Sine (fast, smooth)", 0, 0, 8192), ("Triangle, no FM (fast, smooth)", 1, None, 8192),
-                             ("Sawtooth x Sine (fast, edged)", 3, 0, 8192), ("Square, no FM (fast, edged)", 2, None, 8192),
-                             ("Sine x Triangle LFO (fast, tile scan)", 0, 1, 8192), ("Sawtooth x Square LFO (fast, tile scan)", 3, 2, 8192),
-                             ("Sine x Sine, FM gain 3 rad (generic)", 0, 5, 1024)]:
+
+def config3(reps=5):
+    """BASELINE config 3: 128-voice chord bank, mixed waveforms, per-voice ADSR, 10 s stereo 48 kHz."""
+    bank = mixed_bank(128, np.random.default_rng(3))
+    nfr = 10 * SR
+    ms = timed(lambda: bank.render(nfr), reps)
+    return {"workload": "128-voice chord bank, mixed waveforms + ADSR, 10 s stereo 48 kHz", "device_ms": ms,
+            "wall_ms": wall(lambda: bank.to_sample(10.0)), "voice_samples": 128 * nfr, "algorithmic_bytes": nfr * 4,
+            "generic_voices": bank.count_generic(), "scan_voices": bank.count_scan(), "msamples_per_s": 128 * nfr / ms / 1e3}
+
+
+def config4(reps=5, shard=None):
+    """BASELINE config 4: mix_at of 4096 resampled drum hits at random offsets into a 10-minute
+    48 kHz mono buffer.  Algorithmic bytes: every hit read once and every destination
+    span it touches read and written once.  shard=(rank, world): this rank's destination range."""
+    hbm, src = peaks()
+    rng = np.random.default_rng(0)
+    hits = make_hits(rng)
+    copies = [h.copy() for h, _ in hits]
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    sb.Sample.resample_many(copies, SR)
+    torch.cuda.synchronize()
+    resample_ms = (time.perf_counter() - t0) * 1e3
+    placed = [(when, h) for h, (_, when) in zip(copies, hits)]
+    base = sb.Sample.from_raw_frames(b"", 2, SR, 1).add_silence(600.0)
+    hit_samples = sum(len(h) for _, h in placed)
+
+    def mix_many():
+        return base.copy().mix_at_many(placed, shard=shard)
+
+    dst = mix_many()
+    torch.cuda.synchronize()
+    lo, hi = (dst.shard_range[0], dst.shard_range[1]) if shard else (0, len(dst))
+    # the kernel alone on resident data (the same clipping mix_at_many does)
+    lens = np.array([len(h) for _, h in placed], dtype=np.int64)
+    starts = np.array([int(SR * w) for w, _ in placed], dtype=np.int64)
+    pool = torch.cat([h.device_frames() for _, h in placed])
+    offs = np.concatenate([[0], np.cumsum(lens)[:-1]])
+    o, l, d = sb.Sample.clip_placements(offs, lens, starts, lo, hi)
+    idx = torch.tensor(np.stack([o, l, d]), dtype=torch.int64, device="cuda")
+    dstbuf = dst.device_frames().clone()
+    total = dstbuf.numel()
+    nscr = C.lib.sb_pcm16_mix_at_many_scratch_bytes(total, len(l), int(l.sum()))
+    scr = torch.empty(nscr, dtype=torch.uint8, device="cuda")
+    fn = lambda: C.call("sb_pcm16_mix_at_many", D.ptr(dstbuf), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]),
+                        D.ptr(idx[2]), len(l), D.ptr(scr), nscr, D.stream())
+    ms = timed(fn, reps)
+    span = int(l.sum())
+    nbytes = 2 * span + 2 * 2 * span
+    return {"workload": "Sample.mix_at_many: 4096 resampled drum hits into 10 min @48 kHz mono"
+                        + (" (rank %d of %d: destination samples [%d, %d))" % (shard + (lo, hi)) if shard else ""),
+            "device_ms": ms, "algorithmic_bytes": nbytes, "gbs": nbytes / ms / 1e6, "hbm_frac": nbytes / ms / 1e6 / hbm,
+            "peak_gbs": hbm, "peak_source": src, "hit_samples_in_range": span, "hit_samples": hit_samples,
+            "dst_samples": total, "wall_ms": wall(mix_many), "resample_many_wall_ms": resample_ms}
+
+
+# ------------------------------------------------------------------------------ bank classes
+def class_bank(cw, mw, nv=8192):
+    """8192 voices of one (carrier, modulator) kind; mw None = no FM, 5 = a Sine of FM gain 3 rad
+    (generic kernels); cw 9 = the 25 kinds in equal parts."""
+    classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    b = sb.VoiceBank(SR)
+    r = np.random.default_rng(11)
+    mixed = cw == 9
+    for v in range(nv):
+        if mixed:
+            cw, mw = v % 5, (v // 5) % 5
+        lfo = None
+        f0 = float(r.uniform(55, 1760))
+        if mw == 5:
+            lfo = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=SR)
+            f0 = float(r.uniform(3000, 5000))
+        elif mw is not None:
+            lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=SR)
+        car = classes[cw](f0, 0.9 / nv, fm_lfo=lfo, samplerate=SR)
+        pan = float(r.uniform(-1, 1))
+        b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
+    return b
+
+
+CLASSES = [("sine_x_sine", 0, 0, 8192), ("triangle_plain", 1, None, 8192), ("sawtooth_x_sine", 3, 0, 8192),
+           ("square_plain", 2, None, 8192), ("sine_x_triangle_lfo", 0, 1, 8192), ("sawtooth_x_square_lfo", 3, 2, 8192),
+           ("mixed_5x5", 9, 0, 8192), ("generic_fm_gain_3rad", 0, 5, 1024)]
+
+
+def classes(reps=3):
+    """ms per render of 10 s @ 48 kHz stereo, one voice class at a time (resident voices, exact hints)."""
+    nfr = 10 * SR
+    out = {}
+    for name, cw, mw, nv in CLASSES:
         b = class_bank(cw, mw, nv)
-        vd, _ = b._upload(0, None)                       # voice parameters resident, as in bench.py
+        vd, _ = b._upload(0, None)
         g, e, sc = b.count_generic(), b.count_edged(), b.count_scan()
-        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc),
-                   max(2, args.reps // 4))
-        line("bank class: %s, %d voices x 10 s" % (name, nv), ms=ms, generic_voices=g, edged_voices=e, scan_voices=sc,
-             msamples_per_s=nv * nfr / ms / 1e3)
+        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc), reps, flush=False)
+        out[name] = {"voices": nv, "ms": ms, "ms_per_8192_voices": ms * 8192 / nv, "generic_voices": g, "edged_voices": e,
+                     "scan_voices": sc, "msamples_per_s": nv * nfr / ms / 1e3}
+    return out
+
+
+# ------------------------------------------------------------------------------ sustained clocks
+def sustained(render, seconds=3.0, sampler=None):
+    """`render` back to back for at least `seconds` of device time: does the SM clock hold?"""
+    render()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    render()
+    e1.record()
+    torch.cuda.synchronize()
+    n = max(10, int(seconds * 1e3 / max(e0.elapsed_time(e1), 1e-3)) + 1)
+    if sampler is not None:
+        sampler.start()
+    e0.record()
+    for _ in range(n):
+        render()
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler is not None else None
+    total = e0.elapsed_time(e1)
+    return {"renders": n, "seconds": total / 1e3, "ms_per_render": total / n, "clocks": clocks}
+
+
+def collect(reps=3, only=None):
+    out = {}
+    parts = {"configs": lambda: {"1": config1(), "2": config2(), "3": config3(), "4": config4()},
+             "classes": lambda: classes(reps), "hbm_kernels": lambda: hbm_kernels(max(3, reps))}
+    for k, fn in parts.items():
+        if only and k not in only:
+            continue
+        try:
+            out[k] = fn()
+        except Exception as e:                       # a failing leg must not take the headline line with it
+            out[k] = {"error": "%s: %s" % (type(e).__name__, e)}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--only", nargs="*", default=None)
+    args = ap.parse_args()
+    torch.cuda.set_device(0)
+    res = collect(args.reps, args.only)
+    for section, cases in res.items():
+        if "error" in cases:
+            print(json.dumps({"section": section, **cases}), flush=True)
+            continue
+        body = cases.get("kernels", cases) if section == "hbm_kernels" else cases
+        for name, vals in body.items():
+            print(json.dumps({"section": section, "case": name, **vals}), flush=True)
 
 
 if __name__ == "__main__":

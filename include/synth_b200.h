@@ -287,6 +287,16 @@ int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan *plan,
  * Callers that pass exact hints (sb_host_bank_render_pcm16, the Python VoiceBank) need not call it. */
 int sb_bank_render_check(const sb_bank_plan *plan, const void *scratch_dev, int *generic_needed, void *stream);
 
+/* Measurement hook (no upstream counterpart): from now on every sb_bank_render_f32 records the two
+ * CUDA events (cudaEvent_t, made by the caller with timing enabled) on its stream right before
+ * and right after the launch of the smooth-carrier kernel, bank_fast_kernel<0>; pass NULL, NULL to
+ * stop.  bench.py times the dominant kernel alone with them. */
+int sb_bank_profile_events(void *start_event, void *stop_event);
+/* CUDA events (timing enabled) for callers without a CUDA runtime binding of their own */
+int sb_event_create(void **event);
+int sb_event_elapsed_ms(void *start_event, void *stop_event, float *ms);
+int sb_event_destroy(void *event);
+
 /* ------------------------------------------------------------------ integer PCM -------
  * Bit-exact restatements of the CPython audioop routines synthplayer's Sample calls. */
 
@@ -359,13 +369,34 @@ int sb_pcm32_ratecv(const int32_t *in_dev, int64_t in_frames, int nchannels, int
 
 /* ------------------------------------------------------------------ host-buffer calls -
  * The same path with HOST buffers (copies included), for callers without device memory of
- * their own; bench.py's e2e figure goes through these. */
+ * their own; bench.py's e2e figure goes through these.
+ * State: device workspaces (grow-only) and a pinned word are kept PER DEVICE, keyed by the device
+ * that is current at the call; a process-wide mutex serialises the calls, so they may come from
+ * several host threads and for several devices (their GPU work does not overlap).  The plain
+ * variants run on the legacy default stream; the _on_stream ones take a cudaStream_t. */
 int sb_host_bank_render_pcm16(const sb_voice *voices, int nvoices, int64_t frames,
                               double samplerate, float scale, int16_t *out_stereo,
                               unsigned long long *overflow);
+int sb_host_bank_render_pcm16_on_stream(const sb_voice *voices, int nvoices, int64_t frames,
+                                        double samplerate, float scale, int16_t *out_stereo,
+                                        unsigned long long *overflow, void *stream);
+/* The same render up to the float mix, left in DEVICE memory the caller owns (2*frames floats):
+ * the per-GPU half of a voice-sharded render, whose partial mixes the caller then reduces
+ * (NCCL) and converts once.  Asynchronous on `stream`; the library's workspace is in use until
+ * that work has run, so make the next host call on this device on the same stream or after a
+ * synchronisation. */
+int sb_host_bank_render_mix_f32(const sb_voice *voices, int nvoices, int64_t frames, double samplerate,
+                                float *mix_dev, void *stream);
+/* Grows this device's workspaces to what a bank of nvoices x frames can need at most, so that
+ * later calls of that size or smaller allocate nothing (growing frees and re-allocates, which
+ * synchronises the device). */
+int sb_host_reserve(int nvoices, int64_t frames, double samplerate);
 int sb_host_pcm16_mix_at_many(int16_t *dst, int64_t dst_count, const int16_t *src_pool,
                               int64_t pool_count, const int64_t *src_off, const int64_t *src_len,
                               const int64_t *dst_off, int64_t nsrc);
+int sb_host_pcm16_mix_at_many_on_stream(int16_t *dst, int64_t dst_count, const int16_t *src_pool,
+                                        int64_t pool_count, const int64_t *src_off, const int64_t *src_len,
+                                        const int64_t *dst_off, int64_t nsrc, void *stream);
 
 #ifdef __cplusplus
 }

@@ -137,6 +137,15 @@ _SIGNATURES = {
     "sb_pcm32_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
     "sb_host_bank_render_pcm16": (c_int, [POINTER(Voice), c_int, c_int64, c_double, c_float, _P, POINTER(c_ulonglong)]),
     "sb_host_pcm16_mix_at_many": (c_int, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64]),
+    "sb_host_bank_render_pcm16_on_stream": (c_int, [POINTER(Voice), c_int, c_int64, c_double, c_float, _P,
+                                                    POINTER(c_ulonglong), _P]),
+    "sb_host_bank_render_mix_f32": (c_int, [POINTER(Voice), c_int, c_int64, c_double, _P, _P]),
+    "sb_host_reserve": (c_int, [c_int, c_int64, c_double]),
+    "sb_host_pcm16_mix_at_many_on_stream": (c_int, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64, _P]),
+    "sb_bank_profile_events": (c_int, [_P, _P]),
+    "sb_event_create": (c_int, [POINTER(c_void_p)]),
+    "sb_event_elapsed_ms": (c_int, [_P, _P, POINTER(c_float)]),
+    "sb_event_destroy": (c_int, [_P]),
 }
 
 EXPORTED = tuple(_SIGNATURES)

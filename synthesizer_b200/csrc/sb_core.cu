@@ -223,3 +223,27 @@ extern "C" int sb_envelope_build(double samplerate, double attack, double decay,
     out->n_r = n;
     return SB_OK;
 }
+
+// CUDA events for callers that have no CUDA runtime binding of their own (bench.py times the
+// dominant kernel with them through sb_bank_profile_events)
+extern "C" int sb_event_create(void **event)
+{
+    SB_REQUIRE(event, "sb_event_create: null pointer");
+    cudaEvent_t e;
+    SB_CUDA_CHECK(cudaEventCreate(&e));
+    *event = (void *)e;
+    return SB_OK;
+}
+
+extern "C" int sb_event_elapsed_ms(void *start_event, void *stop_event, float *ms)
+{
+    SB_REQUIRE(start_event && stop_event && ms, "sb_event_elapsed_ms: null pointer");
+    SB_CUDA_CHECK(cudaEventElapsedTime(ms, (cudaEvent_t)start_event, (cudaEvent_t)stop_event));
+    return SB_OK;
+}
+
+extern "C" int sb_event_destroy(void *event)
+{
+    if (event) SB_CUDA_CHECK(cudaEventDestroy((cudaEvent_t)event));
+    return SB_OK;
+}

@@ -157,6 +157,11 @@ struct BankArgs {
     double *lfo_prefix;   // [nvoices][lfo_rows]: FV_SCAN voices: sum of the modulator's shape over all frames
                           // before tile `row` (tiles of kFSub frames: lfo_nprefix over [0, n0), then the render's)
     int lfo_rows, lfo_nprefix;
+    int *perm;            // [nvoices]: the voices sorted by kind across the whole bank (stable); group g is the
+                          // slice perm[g*voices_per_group ...], so a group holds one or two kinds and its CTAs
+                          // run one or two instantiations of the voice loop (a bank of mixed kinds otherwise
+                          // walks all of the kernel's code in every CTA and falls out of the instruction cache)
+    int *key_hist;        // [kSortKeys][ceil(nvoices / kSortBlock)] counts, then their exclusive scan
     int *order;           // [3][nvoices]: per kernel part, each group's voices of that part sorted by kind
                           // (bank_sort_kernel); entry = voice index, the group's slice starts at its first voice
     int *kind_end;        // [ngroups][3][kFastKinds]: end position of each kind in the group's sorted slice
@@ -343,6 +348,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
         if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
         if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
         a.fastv[v] = F;
+        a.perm[v] = v;                                   // (a bank of one group keeps this order)
     }
     if (!(cls == 1 && has_mod)) return;
 
@@ -924,6 +930,84 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
     }
 }
 
+// ---- the bank's voices sorted by kind (counting sort, stable, deterministic): histogram per block
+// of 256 voices, one scan over (key, block), scatter by stable rank within the block.
+constexpr int kSortKeys = kFastKinds + 1;          // the fast kinds, then the generic voices
+constexpr int kSortBlock = 256;
+__device__ __forceinline__ int sort_key_of(int flags) { return (flags & FV_FAST) ? fast_kind_of(flags) : kFastKinds; }
+
+__global__ void __launch_bounds__(kSortBlock)
+bank_key_hist_kernel(BankArgs a, int nblocks)
+{
+    __shared__ int s_count[kSortKeys];
+    if (threadIdx.x < kSortKeys) s_count[threadIdx.x] = 0;
+    __syncthreads();
+    const int v = blockIdx.x * kSortBlock + threadIdx.x;
+    if (v < a.nvoices) atomicAdd(&s_count[sort_key_of(a.fastv[v].flags)], 1);
+    __syncthreads();
+    if (threadIdx.x < kSortKeys) a.key_hist[threadIdx.x * nblocks + blockIdx.x] = s_count[threadIdx.x];
+}
+
+// exclusive scan of key_hist in place, key-major: where each (key, block) bucket starts in perm
+__global__ void __launch_bounds__(1024)
+bank_key_scan_kernel(BankArgs a, int nblocks)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int n = kSortKeys * nblocks;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int x = i < n ? a.key_hist[i] : 0;
+        int inc = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane], winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, winc, d);
+                if (lane >= d) winc += o;
+            }
+            s_warp[lane] = winc - w;
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        if (i < n) a.key_hist[i] = carry + s_warp[warp] + inc - x;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + s_warp[warp] + inc;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kSortBlock)
+bank_key_scatter_kernel(BankArgs a, int nblocks)
+{
+    __shared__ int s_warp_count[kSortBlock / 32][kSortKeys];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (kSortBlock / 32) * kSortKeys; i += kSortBlock) (&s_warp_count[0][0])[i] = 0;
+    __syncthreads();
+    const int v = blockIdx.x * kSortBlock + threadIdx.x;
+    const int key = v < a.nvoices ? sort_key_of(a.fastv[v].flags) : -1;
+    // lanes of this warp with the same key; the voice's rank among them by lane (= by voice index)
+    const unsigned same = __match_any_sync(0xffffffffu, key);
+    const int rank_in_warp = __popc(same & ((1u << lane) - 1));
+    if (key >= 0 && rank_in_warp == 0) s_warp_count[warp][key] = __popc(same);
+    __syncthreads();
+    if (key >= 0) {
+        int before = 0;
+        for (int w = 0; w < warp; w++) before += s_warp_count[w][key];
+        a.perm[a.key_hist[key * nblocks + blockIdx.x] + before + rank_in_warp] = v;
+    }
+}
+
 // One CTA per voice group, once per render: for each of the three kernel parts, the group's
 // voices of that part sorted by kind (stable), and where each kind ends.  The fast kernels'
 // CTAs - there are thousands per render - then stage their voices with a plain indexed copy
@@ -937,7 +1021,7 @@ bank_sort_kernel(BankArgs a)
     int nv = a.nvoices - v_begin;
     if (nv > a.voices_per_group) nv = a.voices_per_group;
     const int v = threadIdx.x;
-    if (v < nv) s_flags[v] = a.fastv[v_begin + v].flags;
+    if (v < nv) s_flags[v] = a.fastv[a.perm[v_begin + v]].flags;
     __syncthreads();
     for (int part = 0; part < 3; part++) {
         if (v < nv) {
@@ -951,7 +1035,7 @@ bank_sort_kernel(BankArgs a)
                     if (!(fu & FV_FAST) || fast_kind_part(ku) != part) continue;
                     pos += (ku < kind || (ku == kind && u < v)) ? 1 : 0;
                 }
-                a.order[(int64_t)part * a.nvoices + v_begin + pos] = v_begin + v;
+                a.order[(int64_t)part * a.nvoices + v_begin + pos] = a.perm[v_begin + v];
             }
         }
         if (v < kFastKinds) {
@@ -1376,8 +1460,10 @@ bank_generic_kernel(BankArgs a)
     // compact the generic voices of this group into shared memory (in voice order)
     if (threadIdx.x == 0) {
         int c = 0;
-        for (int v = 0; v < nvg; v++)
-            if (!(a.fastv[v_begin + v].flags & FV_FAST)) s_vidx[c++] = v_begin + v;
+        for (int v = 0; v < nvg; v++) {
+            const int vi = a.perm[v_begin + v];
+            if (!(a.fastv[vi].flags & FV_FAST)) s_vidx[c++] = vi;
+        }
         s_ngeneric = c;
     }
     __syncthreads();
@@ -1555,9 +1641,18 @@ static inline int64_t bank_off_kindend(const sb_bank_plan *p)
 {
     return bank_off_order(p) + align_up(3 * (int64_t)p->nvoices * (int64_t)sizeof(int), 256);
 }
-static inline int64_t bank_off_lfo(const sb_bank_plan *p)
+static inline int64_t bank_off_perm(const sb_bank_plan *p)
 {
     return bank_off_kindend(p) + align_up((int64_t)p->ngroups * 3 * kFastKinds * (int64_t)sizeof(int), 256);
+}
+static inline int64_t bank_sort_blocks(const sb_bank_plan *p) { return (p->nvoices + kSortBlock - 1) / kSortBlock; }
+static inline int64_t bank_off_keyhist(const sb_bank_plan *p)
+{
+    return bank_off_perm(p) + align_up((int64_t)p->nvoices * (int64_t)sizeof(int), 256);
+}
+static inline int64_t bank_off_lfo(const sb_bank_plan *p)
+{
+    return bank_off_keyhist(p) + align_up(kSortKeys * bank_sort_blocks(p) * (int64_t)sizeof(int), 256);
 }
 static inline int64_t bank_lfo_nprefix(const sb_bank_plan *p) { return (p->n0 + kFSub - 1) / kFSub; }
 static inline int64_t bank_lfo_rows(const sb_bank_plan *p) { return bank_lfo_nprefix(p) + (p->frames + kFSub - 1) / kFSub; }
@@ -1572,6 +1667,10 @@ static inline int64_t bank_scratch_bytes(const sb_bank_plan *p)
 using namespace sb;
 
 namespace sb {
+// measurement hook: CUDA events recorded on the render's stream right before and after the
+// launch of bank_fast_kernel<0> (bench.py times the dominant kernel alone with them)
+static cudaEvent_t g_prof_start = nullptr, g_prof_stop = nullptr;
+
 // the hint counts of a whole bank, for host-side callers (one pass, divisions hoisted)
 void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *edged, int *scan)
 {
@@ -1588,6 +1687,13 @@ void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, 
     *scan = sc;
 }
 }  // namespace sb
+
+extern "C" int sb_bank_profile_events(void *start_event, void *stop_event)
+{
+    g_prof_start = (cudaEvent_t)start_event;
+    g_prof_stop = (cudaEvent_t)stop_event;
+    return SB_OK;
+}
 
 extern "C" int sb_voice_is_fast(const sb_voice *voice, double samplerate)
 {
@@ -1705,6 +1811,8 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.lanetab = (double2 *)(scratch + bank_off_lanetab(plan));
     a.scan_list = (int *)(scratch + bank_off_scanlist(plan));
     a.order = (int *)(scratch + bank_off_order(plan));
+    a.perm = (int *)(scratch + bank_off_perm(plan));
+    a.key_hist = (int *)(scratch + bank_off_keyhist(plan));
     a.kind_end = (int *)(scratch + bank_off_kindend(plan));
     a.lfo_prefix = (double *)(scratch + bank_off_lfo(plan));
     a.lfo_nprefix = (int)bank_lfo_nprefix(plan);
@@ -1718,6 +1826,16 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
+    if (a.ngroups > 1) {
+        // the voices by kind across the whole bank, then each group's (a slice of that order) by part
+        const int nb = (int)bank_sort_blocks(plan);
+        bank_key_hist_kernel<<<nb, kSortBlock, 0, s>>>(a, nb);
+        SB_LAUNCH_CHECK();
+        bank_key_scan_kernel<<<1, 1024, 0, s>>>(a, nb);
+        SB_LAUNCH_CHECK();
+        bank_key_scatter_kernel<<<nb, kSortBlock, 0, s>>>(a, nb);
+        SB_LAUNCH_CHECK();
+    }
     bank_sort_kernel<<<a.ngroups, kMaxVoicesPerGroup, 0, s>>>(a);     // one CTA per voice group
     SB_LAUNCH_CHECK();
     if (plan->scan_voices != 0) {
@@ -1746,8 +1864,10 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
             SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         }
         dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
+        if (g_prof_start) SB_CUDA_CHECK(cudaEventRecord(g_prof_start, s));
         bank_fast_kernel<0><<<grid, kFastWarps * 32, smem, s>>>(a);
         SB_LAUNCH_CHECK();
+        if (g_prof_stop) SB_CUDA_CHECK(cudaEventRecord(g_prof_stop, s));
         if (plan->edged_voices != 0) {
             bank_fast_kernel<1><<<grid, kFastWarps * 32, smem, s>>>(a);
             SB_LAUNCH_CHECK();

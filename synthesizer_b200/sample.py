@@ -604,12 +604,45 @@ class Sample:
         self._grow(start + on)
         return self._add_inplace(o, at=start)
 
-    def mix_at_many(self, placements):
+    @staticmethod
+    def shard_bounds(total, rank, world, align=2048):
+        """Destination range [lo, hi) of `total` samples that `rank` of `world` owns in a sharded
+        mix_at_many: contiguous, balanced, cut on multiples of `align` (the kernel's tile)."""
+        cut = lambda r: total if r >= world else min(total, (total * r // world) // align * align)
+        return cut(rank), cut(rank + 1)
+
+    @staticmethod
+    def clip_placements(src_off, src_len, dst_off, lo, hi):
+        """The parts of the placed sources that fall into destination range [lo, hi): numpy int64
+        arrays (source offset, length, destination offset relative to lo), in the original
+        order; sources that miss the range drop out.  Pure host arithmetic (no GPU)."""
+        import numpy as np
+        src_off, src_len, dst_off = (np.asarray(x, dtype=np.int64) for x in (src_off, src_len, dst_off))
+        first = np.maximum(dst_off, lo)
+        last = np.minimum(dst_off + src_len, hi)
+        keep = last > first
+        skip = first - dst_off
+        return (src_off + skip)[keep], (last - first)[keep], (first - lo)[keep]
+
+    def mix_at_many(self, placements, sharded=False, group=None, shard=None):
         """Backend extension: apply ``mix_at(seconds, sample)`` for every (seconds, sample) of
         `placements`, in order, with ONE kernel launch.  The result is identical to the loop of
-        mix_at calls (each step saturates like audioop.add)."""
+        mix_at calls (each step saturates like audioop.add).
+
+        sharded=True (inside an initialised torch.distributed group), or shard=(rank, world):
+        this process mixes only ITS range of the destination (shard_bounds) and afterwards holds
+        just that slice; `self.shard_range` = (first sample, end sample, total samples).  There
+        is no collective: every rank needs the sources, and each slice comes out bit-identical
+        to the same range of the unsharded result (write the slices out side by side, or bring
+        them together with gather_shards())."""
         assert not self._locked
+        if sharded and shard is None:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+                shard = (dist.get_rank(group), dist.get_world_size(group))
         if self.samplewidth != 2:                      # the one-launch kernel is 16-bit; same result by the loop
+            if shard is not None:
+                raise ValueError("sharded mix_at_many needs 16-bit samples")
             for seconds, other in placements:
                 self.mix_at(seconds, other)
             return self
@@ -622,25 +655,54 @@ class Sample:
                 continue
             starts.append(self._sample_idx(seconds))
             srcs.append(other._dev)
-        if not srcs:
-            return self
         import numpy as np
         lens = np.array([s.numel() for s in srcs], dtype=np.int64)
         starts = np.array(starts, dtype=np.int64)
-        self._grow(int((starts + lens).max()))
+        total = max(self._count(), int((starts + lens).max()) if len(srcs) else 0)
+        lo, hi = 0, total
+        if shard is not None:
+            lo, hi = self.shard_bounds(total, shard[0], shard[1])
+            have = self._slice(lo, hi)
+            self._dev = have.clone() if have is not None else None     # this rank's slice of what was there
+            self.shard_range = (lo, hi, total)
+        self._grow(hi - lo)
         keep = lens > 0                                 # an empty sample only extends the destination
         if not keep.any():
             return self
         # the sources stay where they are: the kernel takes element offsets from a base pointer,
         # here the lowest address among them (no concatenated copy of thousands of tensors)
         ptrs = np.array([s.data_ptr() for s in srcs], dtype=np.int64)[keep]
-        lens, starts = lens[keep], starts[keep]
         base = int(ptrs.min())
-        idx = torch.from_numpy(np.stack([(ptrs - base) // 2, lens, starts])).to(D.device())
+        offs, lens, starts = self.clip_placements((ptrs - base) // 2, lens[keep], starts[keep], lo, hi)
+        if not len(lens):
+            return self
+        idx = torch.from_numpy(np.stack([offs, lens, starts])).to(D.device())
         nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), len(lens), int(lens.sum()))
         scratch = D.empty(nscratch, torch.uint8)
         C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), ctypes.c_void_p(base), D.ptr(idx[0]),
                D.ptr(idx[1]), D.ptr(idx[2]), len(lens), D.ptr(scratch), nscratch, D.stream())
+        return self
+
+    def gather_shards(self, group=None):
+        """After a sharded mix_at_many: every rank receives all slices (one all_gather) and holds
+        the whole sample again.  Optional - the mix itself needs no collective."""
+        import torch.distributed as dist
+        lo, hi, total = self.shard_range
+        world = dist.get_world_size(group)
+        sizes = [b - a for a, b in (self.shard_bounds(total, r, world) for r in range(world))]
+        parts = [D.empty(n, _DTYPE[self.samplewidth]) for n in sizes]
+        mine = self._dev if self._dev is not None else D.empty(0, _DTYPE[self.samplewidth])
+        if len(set(sizes)) == 1:
+            dist.all_gather(parts, mine, group=group)
+        else:                                           # ragged slices: pad to the largest
+            big = max(sizes)
+            padded = [D.empty(big, _DTYPE[self.samplewidth]) for _ in sizes]
+            mine_p = D.zeros(big, _DTYPE[self.samplewidth])
+            mine_p[:mine.numel()] = mine
+            dist.all_gather(padded, mine_p, group=group)
+            parts = [p[:n] for p, n in zip(padded, sizes)]
+        self._dev = self._cat(*parts)
+        del self.shard_range
         return self
 
     def echo(self, length, amount, delay, decay):

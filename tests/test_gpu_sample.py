@@ -385,3 +385,28 @@ def test_locked_sample_refuses(cuda):
     g.lock()
     with pytest.raises(AssertionError):
         g.amplify(0.5)
+
+
+def test_mix_at_many_sharded_slices_equal_the_unsharded_result(cuda):
+    """Destination-range sharding (config 4 across GPUs, no collective): the slice a rank mixes is
+    bit-identical to the same range of the whole mix.  The ranks are played one after another
+    on this GPU (shard=(rank, world))."""
+    import synthesizer_b200 as sb
+    rng = np.random.default_rng(12)
+    sr, total = 48000, 48000 * 3
+    base = rng.integers(-9000, 9000, total).astype(np.int16)
+    hits = [(float(np.float32(rng.uniform(0, 2.9))),
+             sb.Sample.from_raw_frames(rng.integers(-30000, 30000, int(rng.integers(1, 9000))).astype("<i2").tobytes(), 2, sr, 1))
+            for _ in range(300)]
+    hits.append((2.99, sb.Sample.from_raw_frames(rng.integers(-30000, 30000, 5000).astype("<i2").tobytes(), 2, sr, 1)))  # grows it
+    whole = sb.Sample.from_raw_frames(base.tobytes(), 2, sr, 1).mix_at_many(hits)
+    want = np.frombuffer(whole.get_frames(), dtype="<i2")
+    for world in (2, 3, 8):
+        got = []
+        for rank in range(world):
+            part = sb.Sample.from_raw_frames(base.tobytes(), 2, sr, 1).mix_at_many(hits, shard=(rank, world))
+            lo, hi, tot = part.shard_range
+            assert tot == want.size and (lo, hi) == sb.Sample.shard_bounds(tot, rank, world)
+            got.append(np.frombuffer(part.get_frames(), dtype="<i2"))
+            assert got[-1].size == hi - lo
+        assert np.array_equal(np.concatenate(got), want), "world %d" % world

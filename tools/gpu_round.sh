@@ -19,7 +19,8 @@ if has launches; then
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > $OUT/${TAG}_ncu_bench.log 2>&1; echo "launches rc=$?"
 fi
 if has ncu_bank; then
-  $NCU -k regex:'bank_fast_kernel<.int.0>' -s 2 -c 1 -o $OUT/${TAG}_bank_fast0 -f python tools/class_bank.py 0 0 > $OUT/${TAG}_cb00.log 2>&1
+  # the headline workload itself (config 5 on one GPU): the 4th launch of the dominant kernel
+  $NCU -k regex:'bank_fast_kernel<.int.0>' -s 3 -c 1 -o $OUT/${TAG}_bank_fast0 -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-extras > $OUT/${TAG}_cb00.log 2>&1
   $NCU -k regex:'bank_fast_kernel<.int.1>' -s 2 -c 1 -o $OUT/${TAG}_bank_fast1 -f python tools/class_bank.py 3 0 > $OUT/${TAG}_cb30.log 2>&1
   $NCU -k regex:'bank_fast_kernel<.int.2>|bank_lfo_tile' -s 4 -c 2 -o $OUT/${TAG}_bank_fast2 -f python tools/class_bank.py 3 2 > $OUT/${TAG}_cb32.log 2>&1
   $NCU -k regex:'bank_generic_kernel|bank_carry' -s 4 -c 2 -o $OUT/${TAG}_bank_generic -f python tools/class_bank.py 0 5 1024 > $OUT/${TAG}_cb05.log 2>&1
@@ -44,7 +45,8 @@ for rep in $OUT/${TAG}_*.ncu-rep; do
   [ -f "$rep" ] || continue
   base="${rep%.ncu-rep}"
   ncu -i "$rep" --page raw --csv > "${base}_ncu_raw.csv" 2>/dev/null
-  python tools/ncu_summary.py "$rep" > "${base}_summary.txt" 2>&1
+  units=""; case "$rep" in *bank_fast0*) units=61440000;; *bank_fast1*|*bank_fast2*) units=7680000;; esac
+  python tools/ncu_summary.py "$rep" $units > "${base}_summary.txt" 2>&1
   [ -n "$KEEP_REP" ] || rm -f "$rep"
 done
 ls -la $OUT | tail -40
