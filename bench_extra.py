@@ -261,8 +261,8 @@ def classes(reps=3):
     for name, cw, mw, nv in CLASSES:
         b = class_bank(cw, mw, nv)
         vd, _ = b._upload(0, None)
-        g, e, sc = b.count_generic(), b.count_edged(), b.count_scan()
-        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc), reps, flush=False)
+        g, sm, e, sc = b.count_classes()
+        ms = timed(lambda: b.render(nfr, voices_dev=vd, generic_voices=g, smooth_voices=sm, edged_voices=e, scan_voices=sc), reps, flush=False)
         out[name] = {"voices": nv, "ms": ms, "ms_per_8192_voices": ms * 8192 / nv, "generic_voices": g, "edged_voices": e,
                      "scan_voices": sc, "msamples_per_s": nv * nfr / ms / 1e3}
     return out

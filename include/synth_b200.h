@@ -242,6 +242,7 @@ typedef struct sb_bank_plan {
     int64_t off_fastv, off_tab;          /* layout of the scratch buffer */
     int64_t carry_bytes;                 /* size of scratch_dev: span sums + per-voice constants + FM tables */
     int64_t partial_bytes;               /* size of partial_dev: ngroups * (2*frames rounded up to 4) floats */
+    int32_t smooth_voices;               /* hint: 0 = no class-1 voice has a Sine/Triangle carrier (skip that kernel), -1 = unknown */
 } sb_bank_plan;
 
 /* Chooses the (voice group) x (time span) decomposition for `nvoices` x `frames` starting at
@@ -252,13 +253,17 @@ typedef struct sb_bank_plan {
 int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm_count, int nsegs_rad, sb_bank_plan *plan);
 
 /* Optional, between sb_bank_plan_make and allocating scratch_dev: how many voices of the bank
- * are generic (sb_voice_is_fast == 0), have a Square/Sawtooth/Pulse carrier, and are of class 2
- * (sb_voice_is_fast == 2); -1 = unknown.  Kernels no voice needs are not launched, and
+ * are generic (sb_voice_is_fast == 0), of class 1 with a Sine/Triangle carrier (smooth), of class 1
+ * with a Square/Sawtooth/Pulse carrier (edged), and of class 2 (scan); -1 = unknown;
+ * sb_bank_count_classes() counts them.  Kernels no voice needs are not launched, and
  * plan->carry_bytes shrinks to what the class-2 voices need (without the hint it is sized as if
  * every voice were one: nvoices * (n0+frames)/512 * 8 bytes).  Counts must not be too small:
- * a class-2 voice beyond scan_voices is handed to the generic kernels, which a generic_voices
- * of 0 would have skipped. */
-int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int edged_voices, int scan_voices);
+ * a voice whose kernel was hinted away is not rendered, and a class-2 voice beyond scan_voices is
+ * handed to the generic kernels, which a generic_voices of 0 would have skipped
+ * (sb_bank_render_check reports the latter). */
+int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int smooth_voices, int edged_voices, int scan_voices);
+/* counts4 = {generic, smooth, edged, scan} of a HOST array of voices, as sb_bank_plan_hint takes them */
+int sb_bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *counts4);
 
 /* Which path the voice takes:
  *   1  fast: any of the five carriers, with no FM or a Sine modulator of moderate gain: fp32

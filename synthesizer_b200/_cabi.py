@@ -58,7 +58,7 @@ class BankPlan(Structure):
                 ("generic_voices", c_int32), ("nprefix", c_int32), ("edged_voices", c_int32),
                 ("scan_voices", c_int32), ("n0", c_int64),
                 ("off_fastv", c_int64), ("off_tab", c_int64),
-                ("carry_bytes", c_int64), ("partial_bytes", c_int64)]
+                ("carry_bytes", c_int64), ("partial_bytes", c_int64), ("smooth_voices", c_int32)]
 
 
 if not os.path.exists(LIB_PATH):
@@ -101,7 +101,8 @@ _SIGNATURES = {
     "sb_f32_to_pcm32": (c_int, [_P, c_int64, c_double, _P, _P, _P]),
     "sb_f32x2_to_pcm16_stereo": (c_int, [_P, _P, c_int64, c_float, _P, _P, _P]),
     "sb_bank_plan_make": (c_int, [c_int, c_int64, c_int64, c_int, c_int, POINTER(BankPlan)]),
-    "sb_bank_plan_hint": (c_int, [POINTER(BankPlan), c_int, c_int, c_int]),
+    "sb_bank_plan_hint": (c_int, [POINTER(BankPlan), c_int, c_int, c_int, c_int]),
+    "sb_bank_count_classes": (c_int, [_P, c_int, c_double, POINTER(c_int)]),
     "sb_voice_is_fast": (c_int, [POINTER(Voice), c_double]),
     "sb_bank_render_f32": (c_int, [_P, POINTER(BankPlan), _P, c_int, _P, c_int, c_int64, c_double, _P, _P, _P, _P]),
     "sb_pcm16_add": (c_int, [_P, _P, c_int64, _P, _P]),

@@ -24,7 +24,7 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 }  // namespace sb
 
-extern "C" int sb_abi_version(void) { return 1; }
+extern "C" int sb_abi_version(void) { return 2; }
 extern "C" const char *sb_last_error(void) { return sb::g_error; }
 extern "C" int64_t sb_launch_count(void) { return sb::g_launches.load(); }
 

@@ -37,7 +37,8 @@ struct Workspace {
     }
 };
 
-void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *edged, int *scan);
+void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *smooth, int *edged,
+                        int *scan);
 
 struct DeviceState {
     Workspace ws[3];                      // 0: bank render, 1: mix_at_many, 2: voices
@@ -121,9 +122,9 @@ static int bank_render_locked(DeviceState &d, const sb_voice *voices, int nvoice
     if (rc) return rc;
     sb_voice *d_voices = (sb_voice *)d.ws[2].ptr;
     SB_CUDA_CHECK(cudaMemcpyAsync(d_voices, voices, (size_t)nvoices * sizeof(sb_voice), cudaMemcpyHostToDevice, s));
-    int n_generic = 0, n_edged = 0, n_scan = 0;
-    bank_count_classes(voices, nvoices, samplerate, &n_generic, &n_edged, &n_scan);
-    rc = sb_bank_plan_hint(&plan, n_generic, n_edged, n_scan);
+    int n_generic = 0, n_smooth = 0, n_edged = 0, n_scan = 0;
+    bank_count_classes(voices, nvoices, samplerate, &n_generic, &n_smooth, &n_edged, &n_scan);
+    rc = sb_bank_plan_hint(&plan, n_generic, n_smooth, n_edged, n_scan);
     if (rc) return rc;
 
     const BankLayout l = bank_layout(plan, frames, mix_dev == nullptr);

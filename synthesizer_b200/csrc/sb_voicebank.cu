@@ -122,6 +122,9 @@ static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
 // FV_SCAN voices have no use for `ini` and `half`; a Pulse modulator's (clamped) pulse width is
 // kept there in fp64
 __host__ __device__ inline double scan_m_pw64(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.half); }
+// ... and in ini: the pulse width and the phase advance over a run of kFItems frames as integers
+// (2^32 = one cycle), then (two floats' room) the modulator's step per frame in those units as fp64
+__host__ __device__ inline double scan_m_step32(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.ini.z); }
 
 // Closed-form FM table entry per (voice, modulator time-base segment b), step w_b = fm*step_b:
 //   gd * sum_{k<n} sin(theta_k) = A - Cc*(gd cos theta_n) - (gd sin theta_n)/2      (n in segment b)
@@ -170,6 +173,7 @@ struct BankArgs {
     int scan_cap;         // rows of the pre-pass grid: how many list entries the launch covers
     int fast_nspans;
     int64_t fast_span_len;
+    int first_part;       // the first of the three fast kernels that is launched (it writes, the others add)
     float *out;           // [ngroups][stride] partial mixes (or the mix itself if ngroups==1)
     int64_t out_stride;   // floats between groups: 2*frames rounded up to a multiple of 4
 };
@@ -330,6 +334,17 @@ __global__ void bank_prepare_kernel(BankArgs a)
                 F.tab_row = slot;
                 *reinterpret_cast<double *>(&F.half) = clamp_pulsewidth((double)V.m_pw);
                 F.flags |= FV_SCAN | ((V.m_wave & 7) << FV_MWAVE_SHIFT);
+                // the modulator on an integer phase (2^32 = one cycle), for the test whether a run
+                // of kFItems frames passes an edge or a kink of it: the width of a pulse, and how
+                // far the phase moves over the run (all ones: more than the test can tell)
+                const double wm = fm / a.samplerate;                       // cycles per frame, in [0, 0.5]
+                // (up to the next run's first frame: when every lane's run is clear, no edge lies
+                // between two runs either, and the whole sub-tile is one straight line)
+                const double reach = (double)kFItems * wm * 4294967296.0;
+                const unsigned long long pwll = (unsigned long long)llrint(clamp_pulsewidth((double)V.m_pw) * 4294967296.0);
+                F.ini.x = __uint_as_float(pwll > 0xffffffffull ? 0xffffffffu : (uint32_t)pwll);
+                F.ini.y = __uint_as_float(reach < 3.0e9 ? (uint32_t)(unsigned long long)ceil(reach) : 0xffffffffu);
+                *reinterpret_cast<double *>(&F.ini.z) = wm * 4294967296.0;
             } else {
                 demote = true;
             }
@@ -453,6 +468,14 @@ __device__ __forceinline__ double lfo_shape_exact(int mwave, double t, double fm
     }
 }
 
+// exact serial time of frame k (cycles time base), as a real call for rare paths
+__device__ __noinline__ double exact_time_at(const sb_time_seg *segs, int nsegs, int64_t k)
+{
+    TimeCursor c;
+    c.seek(segs, nsegs, k);
+    return c.at(k);
+}
+
 struct FastCtx;
 template <int MW>
 __device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t n, double fm, double phm, double mpw,
@@ -515,6 +538,139 @@ __device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t 
     }
 }
 
+// The per-sample evaluation as a real call (one body, the waveform chosen at run time): only runs
+// that pass an edge or a kink of the modulator come here, and inlined into every carrier's loop
+// the four waveforms' copies made up most of the part-2 kernel's code.
+struct LfoRun {
+    float2 v[kFItems / 2];
+    double tot;
+};
+
+__device__ __noinline__ LfoRun lfo_run_slow(const int mwave, const sb_time_seg *s_cyc, const int nsegs_cyc,
+                                            const double cstep, const bool cstraddle, const double Tc0, const int64_t n,
+                                            const double fm, const double phm, const double mpw, const double gd)
+{
+    FastCtx ctx;
+    ctx.s_cyc = s_cyc;
+    ctx.nsegs_cyc = nsegs_cyc;
+    ctx.cstep = cstep;
+    ctx.cstraddle = cstraddle;
+    LfoRun r;
+    switch (mwave) {
+    case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
+    case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
+    case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
+    default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
+    }
+    return r;
+}
+
+// The FM increments gd*v_j (fp32, frame pairs (q, q+H)) of a class-2 modulator over this lane's
+// run, the sum of the first half-run's increments, and the sum of the v_j of the lanes before this
+// one (the modulator's running sum from the sub-tile's first frame to the run's): the straight
+// line if every lane's run is clear - then that sum has a closed form too and no scan is needed -
+// else (the whole warp) the per-sample evaluation and an fp64 warp scan of the lanes' totals.
+__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double Tc0, const int64_t n,
+                                            float2 (&sv)[kFItems / 2], float &half_sum, double &before);
+
+// ---- class-2 modulators: the run as a straight line wherever it is one
+// A Triangle / Square / Sawtooth / Pulse modulator is linear (or constant) between its edges and
+// kinks.  For a run of kFItems frames that stays clear of them by a guard band - at LFO rates
+// nearly every run - the 16 values follow from the exactly formed phase of the run's first frame:
+// v_j = v_0 + j*dv.  Whether the run is clear is tested on an integer phase (2^32 = one cycle);
+// the guard (1e-6 cycles) covers what separates the straight line from upstream's own 16
+// roundings, so a clear run has every sample on the side of every edge where upstream has it.
+// Only runs that are not clear take the per-sample exact evaluation (lfo_run above).
+constexpr uint32_t kGuardLfo = 4096u;
+
+struct LfoLine {
+    double v0, dv;       // value at the run's first frame and its step per frame (unit amplitude)
+    bool clear;          // no edge or kink within the run (else the line only holds up to the first one)
+    uint32_t d1, d2;     // phase distance (2^32 = one cycle) from the first frame to the next edge / kink of each kind
+};
+
+__device__ __forceinline__ LfoLine lfo_line(const int mwave, const double Tc0, const double fm, const double phm,
+                                            const double cstep, const uint32_t pwi, const uint32_t reach)
+{
+    LfoLine L;
+    const double ph = __dadd_rn(__dmul_rn(Tc0, fm), phm);                 // as upstream forms it; >= 0
+    const double fr = ph - floor_nonneg(ph);                              // exact, in [0, 1)
+    const uint32_t p = (uint32_t)__double2loint(__dadd_rd(fr * 4294967296.0, 6755399441055744.0));
+    const double w = fm * cstep;                                          // cycles per frame
+    // edges / kinks of the waveform on the integer phase
+    uint32_t e1, e2;
+    switch (mwave) {
+    case SB_WAVE_TRIANGLE: e1 = 0x40000000u; e2 = 0xC0000000u; break;     // (ph + 0.75) % 1 crosses 0 and 0.5
+    case SB_WAVE_SQUARE: e1 = 0u; e2 = 0x80000000u; break;
+    case SB_WAVE_SAWTOOTH: e1 = e2 = 0x80000000u; break;                  // 0.5 + ph crosses an integer
+    default: e1 = 0u; e2 = pwi; break;
+    }
+    // the run covers [p, p + reach]: clear if neither edge lies in [p - g, p + reach + g] (mod 2^32)
+    const uint32_t lim = reach + 2u * kGuardLfo;
+    L.d1 = e1 - p;
+    L.d2 = e2 - p;
+    L.clear = reach < 0xf0000000u && (L.d1 + kGuardLfo) > lim && (L.d2 + kGuardLfo) > lim;
+    switch (mwave) {
+    case SB_WAVE_TRIANGLE: {
+        const double x0 = __dadd_rn(fr, 0.75);
+        const double x = x0 >= 1.0 ? x0 - 1.0 : x0;
+        L.v0 = fma(4.0, fabs(x - 0.5), -1.0);
+        L.dv = x < 0.5 ? -4.0 * w : 4.0 * w;
+        break;
+    }
+    case SB_WAVE_SQUARE:
+        L.v0 = fr < 0.5 ? 1.0 : -1.0;
+        L.dv = 0.0;
+        break;
+    case SB_WAVE_SAWTOOTH:
+        L.v0 = fr < 0.5 ? 2.0 * fr : fma(2.0, fr, -2.0);
+        L.dv = 2.0 * w;
+        break;
+    default:
+        L.v0 = p < pwi ? 1.0 : -1.0;
+        L.dv = 0.0;
+        break;
+    }
+    return L;
+}
+
+__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double Tc0, const int64_t n,
+                                            float2 (&sv)[kFItems / 2], float &half_sum, double &before)
+{
+    constexpr int H = kFItems / 2;
+    const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+    const double fm = F.mod.x, phm = F.mod.y, gd = F.gd;
+    const int lane = threadIdx.x & 31;
+    const LfoLine L = lfo_line(mwave, Tc0, fm, phm, ctx.cstep, __float_as_uint(F.ini.x), __float_as_uint(F.ini.y));
+    if (__all_sync(0xffffffffu, L.clear && !ctx.cstraddle)) {
+        // the whole sub-tile is one straight line v_i = v0 + (i - m)*dv, m = this lane's first frame:
+        // sum_{i<m} v_i = m*v0 - dv*m(m+1)/2
+        const double m = (double)(lane * kFItems);
+        before = fma(-L.dv, 0.5 * m * (m + 1.0), m * L.v0);
+        const float s0 = (float)(gd * L.v0), ds = (float)(gd * L.dv);
+        const float2 s2 = make_float2(s0, s0), d2 = make_float2(ds, ds);
+#pragma unroll
+        for (int q = 0; q < H; q++) sv[q] = __ffma2_rn(make_float2((float)q, (float)(q + H)), d2, s2);
+        half_sum = fmaf((float)(H * (H - 1) / 2), ds, (float)H * s0);
+    } else {
+        const LfoRun r = lfo_run_slow(mwave, ctx.s_cyc, ctx.nsegs_cyc, ctx.cstep, ctx.cstraddle, Tc0, n, fm, phm,
+                                      scan_m_pw64(F), gd);
+        half_sum = 0.0f;
+#pragma unroll
+        for (int q = 0; q < H; q++) {
+            sv[q] = r.v[q];
+            half_sum += r.v[q].x;
+        }
+        double incl = r.tot;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const double o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        before = incl - r.tot;
+    }
+}
+
 // Exact value of a discontinuous waveform at absolute frame k, with the fp64 phase formed the
 // way upstream forms it (no FM: fl(fl(t*f) + phase), bit for bit).  Called only for samples
 // whose run phase is within the guard band of an edge, or while the phase may still be negative.
@@ -574,26 +730,10 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     float half_sum = 0.0f;                  // gd * (sum of the first half-run's sines)
     float2 sv[kFItems / 2];                 // MODC 2: the FM increments gd*lfo of frames (q, q+H)
     if (MODC == 2) {
-        const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
-        const double fm = F.mod.x, phm = F.mod.y, gd = F.gd, mpw = scan_m_pw64(F);
-        double tot;
-        switch (mwave) {                                // warp-uniform
-        case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
-        case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
-        case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
-        default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, sv, tot); break;
-        }
-        const int lane = threadIdx.x & 31;
-        double incl = tot;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const double o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += o;
-        }
-        gbefore = gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + (incl - tot));
+        double before;
+        lfo_run_any(F, ctx, Tc0, n, sv, half_sum, before);
+        gbefore = F.gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + before);
         B += gbefore;
-#pragma unroll
-        for (int q = 0; q < H; q++) half_sum += sv[q].x;
     }
     if (MODC == 1) {
         const double2 L = ctx.lt_lane[F.lt_row];
@@ -816,26 +956,10 @@ __device__ __forceinline__ void edged_voice_run(const FastVoice &F, const double
     float half_sum = 0.0f;
     RunIncrements sv = {};
     if (MODC == 2) {
-        const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
-        const double fm = F.mod.x, phm = F.mod.y, gd = F.gd, mpw = scan_m_pw64(F);
-        double tot;
-        switch (mwave) {                                // warp-uniform
-        case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
-        case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
-        case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
-        default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, sv.v, tot); break;
-        }
-        const int lane = threadIdx.x & 31;
-        double incl = tot;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const double o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += o;
-        }
-        gbefore = gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + (incl - tot));
+        double before;
+        lfo_run_any(F, ctx, Tc0, n, sv.v, half_sum, before);
+        gbefore = F.gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + before);
         B += gbefore;
-#pragma unroll
-        for (int q = 0; q < H; q++) half_sum += sv.v[q].x;
     }
     if (MODC == 1) {
         const double2 L = ctx.lt_lane[F.lt_row];
@@ -1061,7 +1185,8 @@ template <int PART>
 __global__ void __launch_bounds__(kFastWarps * 32, PART != 0 ? 4 : FAST_MIN_BLOCKS)   // parts 1, 2: 128 registers
 bank_fast_kernel(BankArgs a)
 {
-    constexpr bool EDGED = PART != 0;                  // adds into what part 0 wrote
+    // the first kernel part launched writes the partial mixes (zeros included), the later ones add
+    const bool add = PART != 0 && a.first_part != PART;
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
     const size_t nrec = (size_t)kFastWarps * a.voices_per_group * kFastMaxSub;
@@ -1079,7 +1204,7 @@ bank_fast_kernel(BankArgs a)
     // this part's voices of the group, already ranked by kind (bank_sort_kernel): where each kind ends
     const int *kend = a.kind_end + ((int64_t)group * 3 + PART) * kFastKinds;
     nv = kend[kFastKinds - 1];
-    if (EDGED && nv == 0) return;                      // block-uniform: nothing to add
+    if (add && nv == 0) return;                        // block-uniform: nothing to add
     if (threadIdx.x < kFastKinds) s_kind_end[threadIdx.x] = kend[threadIdx.x];
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
@@ -1095,7 +1220,7 @@ bank_fast_kernel(BankArgs a)
     }
     __syncthreads();
     const int *ke = s_kind_end;                        // read from shared memory where needed: no registers held
-    const bool any_cyc = EDGED || nv > ke[1];
+    const bool any_cyc = PART != 0 || nv > ke[1];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = blockIdx.x * kFastWarps + warp;
@@ -1217,7 +1342,7 @@ bank_fast_kernel(BankArgs a)
                 const int fa = 2 * k, fb = 2 * k + 1;
                 float4 o = make_float4(fa < H ? accL2[fa].x : accL2[fa - H].y, fa < H ? accR2[fa].x : accR2[fa - H].y,
                                        fb < H ? accL2[fb].x : accL2[fb - H].y, fb < H ? accR2[fb].x : accR2[fb - H].y);
-                if (EDGED) {                            // add to what the smooth-carrier kernel wrote
+                if (add) {                              // add to what the earlier kernel parts wrote
                     const float4 p = dst[k];
                     o = make_float4(o.x + p.x, o.y + p.y, o.z + p.z, o.w + p.w);
                 }
@@ -1227,12 +1352,12 @@ bank_fast_kernel(BankArgs a)
 #pragma unroll
             for (int q = 0; q < H; q++) {
                 if (i0 + q < span_end) {
-                    out[(i0 + q) * 2] = accL2[q].x + (EDGED ? out[(i0 + q) * 2] : 0.0f);
-                    out[(i0 + q) * 2 + 1] = accR2[q].x + (EDGED ? out[(i0 + q) * 2 + 1] : 0.0f);
+                    out[(i0 + q) * 2] = accL2[q].x + (add ? out[(i0 + q) * 2] : 0.0f);
+                    out[(i0 + q) * 2 + 1] = accR2[q].x + (add ? out[(i0 + q) * 2 + 1] : 0.0f);
                 }
                 if (i0 + q + H < span_end) {
-                    out[(i0 + q + H) * 2] = accL2[q].y + (EDGED ? out[(i0 + q + H) * 2] : 0.0f);
-                    out[(i0 + q + H) * 2 + 1] = accR2[q].y + (EDGED ? out[(i0 + q + H) * 2 + 1] : 0.0f);
+                    out[(i0 + q + H) * 2] = accL2[q].y + (add ? out[(i0 + q + H) * 2] : 0.0f);
+                    out[(i0 + q + H) * 2 + 1] = accR2[q].y + (add ? out[(i0 + q + H) * 2 + 1] : 0.0f);
                 }
             }
         }
@@ -1262,6 +1387,41 @@ __device__ __forceinline__ double warp_sum(double v)
 // the fast kernel uses per sample), then turned into an exclusive prefix per voice.  Rows:
 // lfo_nprefix tiles over [0, n0) (the FM sum accumulated before this render starts; the last
 // one may be short), then the render's own tiles from n0.  One warp per (voice, tile).
+// The sum of a class-2 modulator's values over the `cnt` frames from n on (cnt <= kFSub, one
+// sub-tile), by the whole warp: a lane takes the run of kFItems frames it takes in the render
+// kernel - the straight line where the run is clear, else the same per-sample evaluation the
+// render kernel falls back to, so that tile sums and run sums are sums of the same numbers.
+__device__ __forceinline__ double lfo_tile_by_runs(const FastVoice &F, const sb_time_seg *s_cyc, const int nsegs_cyc,
+                                                   const int64_t begin, const int tile_cnt, const int lane)
+{
+    const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+    const double fm = F.mod.x, phm = F.mod.y, mpw = scan_m_pw64(F);
+    const int64_t n = begin + (int64_t)lane * kFItems;
+    const int cnt = max(0, min(kFItems, tile_cnt - lane * kFItems));               // < kFItems only on a last, short tile
+    double Tc0 = 0.0, cstep = 0.0;
+    bool straddle = false;
+    if (cnt > 0) {
+        TimeCursor c;
+        c.seek(s_cyc, nsegs_cyc, n);
+        Tc0 = c.at(n);
+        cstep = c.step;
+        straddle = (n + kFItems >= c.next_start);
+    }
+    const LfoLine L = lfo_line(mwave, Tc0, fm, phm, cstep, __float_as_uint(F.ini.x), __float_as_uint(F.ini.y));
+    double acc = 0.0;
+    if (__all_sync(0xffffffffu, cnt == kFItems && L.clear && !straddle)) {
+        acc = fma((double)(kFItems * (kFItems - 1) / 2), L.dv, (double)kFItems * L.v0);
+    } else if (cnt == kFItems) {
+        acc = lfo_run_slow(mwave, s_cyc, nsegs_cyc, cstep, straddle, Tc0, n, fm, phm, mpw, 1.0).tot;
+    } else {
+        for (int j = 0; j < cnt; j++) acc += lfo_shape_exact(mwave, exact_time_at(s_cyc, nsegs_cyc, n + j), fm, phm, mpw);
+    }
+    return warp_sum(acc);
+}
+
+// One warp per (voice, 32 consecutive tiles): a lane first tries its whole tile as one straight
+// line (one exact phase, a handful of operations: at LFO rates most tiles are clear of the
+// modulator's edges and kinks); the tiles that are not are then summed run by run by the warp.
 __global__ void __launch_bounds__(kGenWarps * 32)
 bank_lfo_tile_kernel(BankArgs a)
 {
@@ -1270,55 +1430,85 @@ bank_lfo_tile_kernel(BankArgs a)
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int row = blockIdx.x * kGenWarps + (threadIdx.x >> 5);
-    if (row >= a.lfo_rows) return;
-    int64_t begin, end;
+    const int chunk = blockIdx.x * kGenWarps + (threadIdx.x >> 5);               // 32 rows each
+    if (chunk * 32 >= a.lfo_rows) return;
+    const int row = chunk * 32 + lane;
+    int64_t begin = 0, end = 0;
     if (row < a.lfo_nprefix) {
         begin = (int64_t)row * kFSub;
         end = min(begin + kFSub, a.n0);
-    } else {
+    } else if (row < a.lfo_rows) {
         begin = a.n0 + (int64_t)(row - a.lfo_nprefix) * kFSub;
         end = min(begin + kFSub, a.n0 + a.frames);
     }
-    // the times of this lane's frames (lane, lane+32, ...) are the same for every voice
-    double t[kFItems], tstep;
-    {
+    const int cnt = (int)(end - begin);                                           // 0 for lanes past the last row
+    double T0 = 0.0, cstep = 0.0;
+    bool straddle = false;
+    if (cnt > 0) {
         TimeCursor c;
-        c.seek(s_cyc, a.nsegs_cyc, begin + lane);
-        tstep = c.step;
-#pragma unroll
-        for (int j = 0; j < kFItems; j++) {
-            const int64_t k = begin + lane + 32 * j;
-            t[j] = (k < end) ? c.at(k) : -1.0;
-        }
+        c.seek(s_cyc, a.nsegs_cyc, begin);
+        T0 = c.at(begin);
+        cstep = c.step;
+        straddle = (begin + cnt >= c.next_start);
     }
     const int nscan = min(a.scan_list[0], a.scan_cap);
     for (int e = blockIdx.y; e < nscan; e += gridDim.y) {
         const FastVoice &F = a.fastv[a.scan_list[2 + e]];
         const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
-        const double fm = F.mod.x, phm = F.mod.y, mpw = scan_m_pw64(F);
+        // how far the phase moves over the tile, on the integer phase (all ones: too far to tell)
+        const double reach = (double)(cnt - 1) * scan_m_step32(F);
+        const LfoLine L = lfo_line(mwave, T0, F.mod.x, F.mod.y, cstep, __float_as_uint(F.ini.x),
+                                   reach < 3.0e9 ? (uint32_t)(long long)ceil(reach) : 0xffffffffu);
+        bool whole = cnt > 0 && L.clear && !straddle;
         double acc = 0.0;
-        if (mwave == SB_WAVE_TRIANGLE) {
-            // (see lfo_run: no edges, so the lane's frames step from its first phase; the frames
-            // of a lane are 32 apart, and a tile that crosses a time-base segment is not special
-            // at this accuracy: the step changes by parts in 1e9)
-            const double x0 = __dadd_rn(__dadd_rn(__dmul_rn(t[0] >= 0.0 ? t[0] : 0.0, fm), phm), 0.75);
-            double f = x0 - floor_nonneg(x0);
-            const double w32 = 32.0 * fm * tstep;
-            const double wf = w32 - floor_nonneg(w32);
-#pragma unroll
-            for (int j = 0; j < kFItems; j++) {
-                if (t[j] >= 0.0) acc += fma(4.0, fabs(f - 0.5), -1.0);
-                f += wf;
-                if (f >= 1.0) f -= 1.0;
+        if (whole) acc = fma(0.5 * (double)cnt * (double)(cnt - 1), L.dv, (double)cnt * L.v0);
+        if (cnt > 0 && !whole && !straddle && reach < 2.0e9) {
+            // One edge (or kink) inside the tile - the usual case at LFO rates: two straight lines.
+            // Where the second one starts is estimated from the phase distance to the edge and then
+            // settled by the exact values of the two frames around it (an edge makes the value jump
+            // by 2; a Triangle's kink needs no settling: the value is continuous there).
+            const double step32 = scan_m_step32(F);
+            const uint32_t dn = min(L.d1 - 1u, L.d2 - 1u) + 1u;               // nearest edge strictly ahead (0 = a whole cycle away)
+            const uint32_t df = max(L.d1 - 1u, L.d2 - 1u) + 1u;
+            const bool one = dn != 0u && step32 > 0.0 && (L.d1 == L.d2 || (double)df > reach + 3.0 * kGuardLfo + step32);
+            if (one) {
+                int js = (int)ceil((double)dn / step32);                      // first frame at or past the edge
+                js = max(1, min(cnt - 1, js));
+                bool ok = (mwave == SB_WAVE_TRIANGLE);
+                const double mpw = scan_m_pw64(F);
+                for (int tries = 0; tries < 4 && !ok; tries++) {
+                    const double ta = __dadd_rn(T0, __dmul_rn((double)(js - 1), cstep)), tb2 = __dadd_rn(T0, __dmul_rn((double)js, cstep));
+                    const bool before_a = fabs(lfo_shape_exact(mwave, ta, F.mod.x, F.mod.y, mpw) - fma((double)(js - 1), L.dv, L.v0)) < 0.5;
+                    const bool before_b = fabs(lfo_shape_exact(mwave, tb2, F.mod.x, F.mod.y, mpw) - fma((double)js, L.dv, L.v0)) < 0.5;
+                    if (before_a && !before_b) ok = true;
+                    else if (!before_a) js--;                                  // the edge came earlier
+                    else js++;                                                 // not yet
+                    if (js < 1 || js > cnt - 1) break;
+                }
+                if (ok) {
+                    const int rest = cnt - js;
+                    const double tj = __dadd_rn(T0, __dmul_rn((double)js, cstep));
+                    const double reach2 = (double)(rest - 1) * step32;
+                    const LfoLine L2 = lfo_line(mwave, tj, F.mod.x, F.mod.y, cstep, __float_as_uint(F.ini.x),
+                                                (uint32_t)(long long)ceil(reach2));
+                    if (L2.clear) {
+                        acc = fma(0.5 * (double)js * (double)(js - 1), L.dv, (double)js * L.v0) +
+                              fma(0.5 * (double)rest * (double)(rest - 1), L2.dv, (double)rest * L2.v0);
+                        whole = true;
+                    }
+                }
             }
-        } else {
-#pragma unroll
-            for (int j = 0; j < kFItems; j++)
-                if (t[j] >= 0.0) acc += lfo_shape_exact(mwave, t[j], fm, phm, mpw);
         }
-        acc = warp_sum(acc);
-        if (lane == 0) a.lfo_prefix[(int64_t)e * a.lfo_rows + row] = acc;
+        unsigned todo = __ballot_sync(0xffffffffu, cnt > 0 && !whole);
+        while (todo) {
+            const int t = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t tb = __shfl_sync(0xffffffffu, begin, t);
+            const int tc = __shfl_sync(0xffffffffu, cnt, t);
+            const double sum = lfo_tile_by_runs(F, s_cyc, a.nsegs_cyc, tb, tc, lane);
+            if (lane == t) acc = sum;
+        }
+        if (cnt > 0) a.lfo_prefix[(int64_t)e * a.lfo_rows + row] = acc;
     }
 }
 
@@ -1672,17 +1862,22 @@ namespace sb {
 static cudaEvent_t g_prof_start = nullptr, g_prof_stop = nullptr;
 
 // the hint counts of a whole bank, for host-side callers (one pass, divisions hoisted)
-void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *edged, int *scan)
+// generic = class 0; smooth / edged = class 1 with a Sine, Triangle / Square, Sawtooth, Pulse carrier;
+// scan = class 2: the voices each kernel of a render works on
+void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *generic, int *smooth, int *edged,
+                        int *scan)
 {
     const double inv_sr = 1.0 / samplerate, w1 = 6.283185307179586 / samplerate;
-    int g = 0, e = 0, sc = 0;
+    int g = 0, sm = 0, e = 0, sc = 0;
     for (int v = 0; v < nvoices; v++) {
         const int cls = voice_class(voices[v], samplerate, inv_sr, w1);
         if (!cls) g++;
+        else if (cls == 2) sc++;
         else if (voices[v].c_wave >= SB_WAVE_SQUARE) e++;
-        if (cls == 2) sc++;
+        else sm++;
     }
     *generic = g;
+    *smooth = sm;
     *edged = e;
     *scan = sc;
 }
@@ -1692,6 +1887,13 @@ extern "C" int sb_bank_profile_events(void *start_event, void *stop_event)
 {
     g_prof_start = (cudaEvent_t)start_event;
     g_prof_stop = (cudaEvent_t)stop_event;
+    return SB_OK;
+}
+
+extern "C" int sb_bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, int *counts4)
+{
+    SB_REQUIRE(voices && counts4 && nvoices >= 1 && samplerate > 1, "sb_bank_count_classes: bad arguments");
+    bank_count_classes(voices, nvoices, samplerate, counts4 + 0, counts4 + 1, counts4 + 2, counts4 + 3);
     return SB_OK;
 }
 
@@ -1743,6 +1945,7 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     plan->fast_nspans = (int32_t)((frames + plan->fast_span_len - 1) / plan->fast_span_len);
     plan->nsegs_rad = nsegs_rad;
     plan->generic_voices = -1;
+    plan->smooth_voices = -1;
     plan->edged_voices = -1;
     plan->scan_voices = -1;
     plan->n0 = n0;
@@ -1757,12 +1960,15 @@ extern "C" int sb_bank_plan_make(int nvoices, int64_t frames, int64_t n0, int sm
     return SB_OK;
 }
 
-extern "C" int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int edged_voices, int scan_voices)
+extern "C" int sb_bank_plan_hint(sb_bank_plan *plan, int generic_voices, int smooth_voices, int edged_voices,
+                                 int scan_voices)
 {
     SB_REQUIRE(plan && plan->nvoices >= 1 && generic_voices >= -1 && edged_voices >= -1 && scan_voices >= -1 &&
-                   generic_voices <= plan->nvoices && edged_voices <= plan->nvoices && scan_voices <= plan->nvoices,
+                   smooth_voices >= -1 && generic_voices <= plan->nvoices && edged_voices <= plan->nvoices &&
+                   scan_voices <= plan->nvoices && smooth_voices <= plan->nvoices,
                "sb_bank_plan_hint: bad arguments");
     plan->generic_voices = generic_voices;
+    plan->smooth_voices = smooth_voices;
     plan->edged_voices = edged_voices;
     plan->scan_voices = scan_voices;
     plan->carry_bytes = bank_scratch_bytes(plan);
@@ -1826,8 +2032,9 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
-    if (a.ngroups > 1) {
+    if (a.nvoices > kMaxVoicesPerGroup) {
         // the voices by kind across the whole bank, then each group's (a slice of that order) by part
+        // (a bank that fits one full group is ranked by bank_sort_kernel alone)
         const int nb = (int)bank_sort_blocks(plan);
         bank_key_hist_kernel<<<nb, kSortBlock, 0, s>>>(a, nb);
         SB_LAUNCH_CHECK();
@@ -1841,7 +2048,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     if (plan->scan_voices != 0) {
         // modulator tile sums of the FV_SCAN voices, then their prefix (the fast kernel reads it)
         // a CTA keeps its frames' times in registers and walks the voices in steps of grid.y
-        const int64_t tx = (a.lfo_rows + kGenWarps - 1) / kGenWarps;
+        const int64_t tx = ((a.lfo_rows + 31) / 32 + kGenWarps - 1) / kGenWarps;   // a warp per 32 tiles
         int64_t ty = (1184 * 4 + tx - 1) / tx;
         if (ty > a.scan_cap) ty = a.scan_cap;
         if (ty < 1) ty = 1;
@@ -1864,10 +2071,15 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
             SB_CUDA_CHECK(cudaFuncSetAttribute(bank_fast_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         }
         dim3 grid((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
-        if (g_prof_start) SB_CUDA_CHECK(cudaEventRecord(g_prof_start, s));
-        bank_fast_kernel<0><<<grid, kFastWarps * 32, smem, s>>>(a);
-        SB_LAUNCH_CHECK();
-        if (g_prof_stop) SB_CUDA_CHECK(cudaEventRecord(g_prof_stop, s));
+        // a part no voice belongs to is not launched; the first one that is writes the partial mixes
+        const bool run0 = plan->smooth_voices != 0 || (plan->edged_voices == 0 && plan->scan_voices == 0);
+        a.first_part = run0 ? 0 : (plan->edged_voices != 0 ? 1 : 2);
+        if (run0) {
+            if (g_prof_start) SB_CUDA_CHECK(cudaEventRecord(g_prof_start, s));
+            bank_fast_kernel<0><<<grid, kFastWarps * 32, smem, s>>>(a);
+            SB_LAUNCH_CHECK();
+            if (g_prof_stop) SB_CUDA_CHECK(cudaEventRecord(g_prof_stop, s));
+        }
         if (plan->edged_voices != 0) {
             bank_fast_kernel<1><<<grid, kFastWarps * 32, smem, s>>>(a);
             SB_LAUNCH_CHECK();

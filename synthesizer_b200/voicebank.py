@@ -109,23 +109,31 @@ class VoiceBank:
         raw = ctypes.string_at(ctypes.addressof(arr), ctypes.sizeof(arr))
         return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(D.device()), len(arr)
 
+    def count_classes(self, begin=0, end=None):
+        """(generic, smooth, edged, scan) voice counts of [begin, end): how many voices each kernel
+        of a render works on (sb_bank_count_classes; the hints of sb_bank_plan_hint)."""
+        arr = self.voice_array(begin, end)
+        if not len(arr):
+            return (0, 0, 0, 0)
+        counts = (ctypes.c_int * 4)()
+        C.call("sb_bank_count_classes", ctypes.byref(arr), len(arr), float(self.samplerate), counts)
+        return tuple(counts)
+
     def count_generic(self, begin=0, end=None):
         """Voices of [begin, end) that need the generic (per-sample fp64) kernel."""
-        return sum(1 for v in self._voices[begin:end]
-                   if not C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)))
+        return self.count_classes(begin, end)[0]
 
     def count_scan(self, begin=0, end=None):
         """Voices of [begin, end) on the fast path with a Triangle / Square / Sawtooth / Pulse
         modulator (class 2: their FM sum comes from a tile pre-pass)."""
-        return sum(1 for v in self._voices[begin:end]
-                   if C.lib.sb_voice_is_fast(ctypes.byref(v), float(self.samplerate)) == 2)
+        return self.count_classes(begin, end)[3]
 
     def count_edged(self, begin=0, end=None):
-        """Voices of [begin, end) with a Square / Sawtooth / Pulse carrier (the second fast kernel)."""
-        return sum(1 for v in self._voices[begin:end] if v.c_wave >= C.WAVE_SQUARE)
+        """Class-1 voices of [begin, end) with a Square / Sawtooth / Pulse carrier (the second fast kernel)."""
+        return self.count_classes(begin, end)[2]
 
     def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None,
-               edged_voices=None, scan_voices=None):
+               edged_voices=None, scan_voices=None, smooth_voices=None):
         """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
@@ -136,9 +144,8 @@ class VoiceBank:
                 self._dev = {}
             key = (begin, end)
             if key not in self._dev:
-                self._dev[key] = self._upload(begin, end) + (self.count_generic(begin, end),
-                                                             self.count_edged(begin, end), self.count_scan(begin, end))
-            voices_dev, nv, generic_voices, edged_voices, scan_voices = self._dev[key]
+                self._dev[key] = self._upload(begin, end) + self.count_classes(begin, end)
+            voices_dev, nv, generic_voices, smooth_voices, edged_voices, scan_voices = self._dev[key]
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
         mix = D.empty(2 * nframes, torch.float32)
@@ -149,8 +156,8 @@ class VoiceBank:
         tr, tc = D.timebase_rad(self.samplerate), D.timebase_cyc(self.samplerate)
         C.call("sb_bank_plan_make", nv, nframes, start, sms, tr.nsegs, ctypes.byref(plan))
         unknown = lambda x: -1 if x is None else x
-        C.call("sb_bank_plan_hint", ctypes.byref(plan), unknown(generic_voices), unknown(edged_voices),
-               unknown(scan_voices))
+        C.call("sb_bank_plan_hint", ctypes.byref(plan), unknown(generic_voices), unknown(smooth_voices),
+               unknown(edged_voices), unknown(scan_voices))
         carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
         partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,

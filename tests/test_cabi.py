@@ -29,7 +29,7 @@ def test_every_declared_symbol_is_exported_and_bound():
         assert hasattr(C.lib, s), "header declares %s but the library does not export it" % s
     assert sorted(C.EXPORTED) == syms, "ctypes binding and header disagree: %s" % (
         set(C.EXPORTED) ^ set(syms))
-    assert C.lib.sb_abi_version() == 1
+    assert C.lib.sb_abi_version() == 2
 
 
 def test_struct_sizes_match_the_c_side():
@@ -168,20 +168,20 @@ def test_bank_plan_hint_sizes_the_scratch():
     worst = plan.carry_bytes
     rows = (frames + 511) // 512
     assert worst >= nv * rows * 8
-    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, 0)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, nv, 0, 0)
     none = plan.carry_bytes
     assert none <= worst - nv * rows * 8 and (plan.generic_voices, plan.edged_voices, plan.scan_voices) == (0, 0, 0)
-    C.call("sb_bank_plan_hint", ctypes.byref(plan), 3, 10, 7)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 3, -1, 10, 7)
     assert none + 7 * rows * 8 <= plan.carry_bytes <= none + 7 * rows * 8 + 256
-    C.call("sb_bank_plan_hint", ctypes.byref(plan), -1, -1, -1)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), -1, -1, -1, -1)
     assert plan.carry_bytes == worst
     with pytest.raises(C.SbError):
-        C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, nv + 1)
+        C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, 0, nv + 1)
     # a start offset adds the tiles over [0, n0)
     shifted = C.BankPlan()
     C.call("sb_bank_plan_make", nv, frames, 512 * 10 + 1, 148, 40, ctypes.byref(shifted))
-    C.call("sb_bank_plan_hint", ctypes.byref(shifted), 0, 0, 7)
-    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, 0, 7)
+    C.call("sb_bank_plan_hint", ctypes.byref(shifted), 0, -1, 0, 7)
+    C.call("sb_bank_plan_hint", ctypes.byref(plan), 0, -1, 0, 7)
     assert shifted.carry_bytes - plan.carry_bytes >= 7 * 11 * 8 - 256
 
 

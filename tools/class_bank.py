@@ -33,11 +33,11 @@ for v in range(nv):
     pan = float(r.uniform(-1, 1))
     b.add(sb.EnvelopeFilter(car, 0.05, 0.3, 8.0, 0.7, 1.5), (1 - pan) / 2, (1 + pan) / 2)
 vd, _ = b._upload(0, None)
-g, e, sc = b.count_generic(), b.count_edged(), b.count_scan()
+g, sm, e, sc = b.count_classes()
 for _ in range(3):
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
-    b.render(nfr, voices_dev=vd, generic_voices=g, edged_voices=e, scan_voices=sc)
+    b.render(nfr, voices_dev=vd, generic_voices=g, smooth_voices=sm, edged_voices=e, scan_voices=sc)
     t1.record()
     torch.cuda.synchronize()
     print("%.3f ms (generic %d, edged %d, scan %d)" % (t0.elapsed_time(t1), g, e, sc))
