@@ -350,7 +350,11 @@ int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *in_off_dev, 
  * three arrays are device arrays of nsrc int64.  dst must already be long enough.
  * scratch_dev (sb_pcm16_mix_at_many_scratch_bytes; total_src_samples = sum of src_len) holds the
  * per-tile source lists; pass NULL to run without an index (each 2048-sample tile then scans
- * the whole source list — fine for a few sources, slow for thousands). */
+ * the whole source list — fine for a few sources, slow for thousands).
+ * Bad input cannot make the kernels write outside their buffers: a source with a negative dst_off
+ * is left out, and per-tile lists that do not fit the scratch given are refused (those tiles
+ * stay unmixed); the first four ints of scratch_dev then read {list cursor, sources left out,
+ * 1 if a list did not fit, 0} - all zero but the cursor after a call with valid arguments. */
 int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t nsrc, int64_t total_src_samples);
 int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
                          const int64_t *src_off_dev, const int64_t *src_len_dev,
@@ -371,6 +375,15 @@ int sb_pcm32_fadein(int32_t *buf_dev, int64_t nsamples, double start_volume, voi
 int sb_pcm32_modulate(int32_t *buf_dev, const float *mod_dev, int64_t count, void *stream);
 int sb_pcm32_ratecv(const int32_t *in_dev, int64_t in_frames, int nchannels, int64_t inrate,
                     int64_t outrate, int32_t *out_dev, void *stream);
+
+/* 24-bit frames (audioop with size == 3): a Sample of 3-byte frames keeps sign-extended int32
+ * values on the device and runs the size-4 routines above; these supply what differs: packing,
+ * the 24-bit clip of audioop's fbound / overflow, and the <<8 / >>8 of GETSAMPLE32 and lin2lin
+ * (sb_pcm32_shift: shift > 0 left, < 0 arithmetic right). */
+int sb_pcm24_unpack(const uint8_t *bytes_dev, int64_t count, int32_t *out_dev, void *stream);
+int sb_pcm24_pack(const int32_t *in_dev, int64_t count, uint8_t *bytes_dev, void *stream);
+int sb_pcm24_clamp(int32_t *buf_dev, int64_t count, void *stream);
+int sb_pcm32_shift(int32_t *buf_dev, int64_t count, int shift, void *stream);
 
 /* ------------------------------------------------------------------ host-buffer calls -
  * The same path with HOST buffers (copies included), for callers without device memory of

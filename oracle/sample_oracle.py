@@ -235,13 +235,25 @@ class Sample:
             other.stereo(left_factor=0, right_factor=other_mix_factor)
         return self.mix_at(mix_at, other, other_seconds)
 
-    def pan(self, panning=0.0):
+    def pan(self, panning=0.0, lfo=None):
+        """(recalled, LOW confidence in the scaling: upstream may use (1-p)/2 and (1+p)/2.)"""
         assert not self._locked
+        if lfo is not None:
+            values = iter(lfo.generator())
+            frames = self.get_frame_array()
+            left = frames[0::2] if self.nchannels == 2 else frames
+            right = frames[1::2] if self.nchannels == 2 else frames
+            out = self.get_array(self.samplewidth, [0] * (2 * len(left)))
+            for i in range(len(left)):
+                p = next(values)
+                out[2 * i] = int(left[i] * (1.0 - p))
+                out[2 * i + 1] = int(right[i] * (1.0 + p))
+            self._frames = out.tobytes()
+            self.nchannels = 2
+            return self
         assert -1 <= panning <= 1
         left_volume = (1.0 - panning) / 2
         right_volume = 1.0 - left_volume
-        if self.nchannels == 1:
-            return self.stereo(left_volume * 2, right_volume * 2)
         return self.stereo(left_volume * 2, right_volume * 2)
 
     # -- amplitude -------------------------------------------------------------------

@@ -136,6 +136,10 @@ _SIGNATURES = {
     "sb_pcm32_fadein": (c_int, [_P, c_int64, c_double, _P]),
     "sb_pcm32_modulate": (c_int, [_P, _P, c_int64, _P]),
     "sb_pcm32_ratecv": (c_int, [_P, c_int64, c_int, c_int64, c_int64, _P, _P]),
+    "sb_pcm24_unpack": (c_int, [_P, c_int64, _P, _P]),
+    "sb_pcm24_pack": (c_int, [_P, c_int64, _P, _P]),
+    "sb_pcm24_clamp": (c_int, [_P, c_int64, _P]),
+    "sb_pcm32_shift": (c_int, [_P, c_int64, c_int, _P]),
     "sb_host_bank_render_pcm16": (c_int, [POINTER(Voice), c_int, c_int64, c_double, c_float, _P, POINTER(c_ulonglong)]),
     "sb_host_pcm16_mix_at_many": (c_int, [_P, c_int64, _P, c_int64, _P, _P, _P, c_int64]),
     "sb_host_bank_render_pcm16_on_stream": (c_int, [POINTER(Voice), c_int, c_int64, c_double, c_float, _P,

@@ -229,3 +229,80 @@ extern "C" int sb_pcm32_ratecv(const int32_t *in_dev, int64_t in_frames, int nch
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
+
+// ------------------------------------------------------------------ 24-bit frames (audioop size 3)
+// A Sample of 3-byte frames keeps its values as int32 (sign-extended 24-bit) on the device and
+// runs the size-4 kernels above; what differs from size 4 is done by these: packing, the
+// 24-bit clip of audioop's fbound / overflow, and the <<8 / >>8 of GETSAMPLE32 / lin2lin.
+namespace sb {
+__global__ void pcm24_unpack_kernel(const uint8_t *__restrict__ in, int64_t count, int32_t *__restrict__ out)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const uint32_t v = (uint32_t)in[3 * i] | ((uint32_t)in[3 * i + 1] << 8) | ((uint32_t)in[3 * i + 2] << 16);
+        out[i] = (int32_t)(v << 8) >> 8;
+    }
+}
+
+__global__ void pcm24_pack_kernel(const int32_t *__restrict__ in, int64_t count, uint8_t *__restrict__ out)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const uint32_t v = (uint32_t)in[i];
+        out[3 * i] = (uint8_t)v;
+        out[3 * i + 1] = (uint8_t)(v >> 8);
+        out[3 * i + 2] = (uint8_t)(v >> 16);
+    }
+}
+
+__global__ void pcm24_clamp_kernel(int32_t *buf, int64_t count)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        buf[i] = max(-0x800000, min(0x7fffff, buf[i]));
+}
+
+// shift > 0: left (wrapping), shift < 0: arithmetic right
+__global__ void pcm32_shift_kernel(int32_t *buf, int64_t count, int shift)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        buf[i] = shift >= 0 ? (int32_t)((uint32_t)buf[i] << shift) : (buf[i] >> (-shift));
+}
+}  // namespace sb
+
+extern "C" int sb_pcm24_unpack(const uint8_t *bytes_dev, int64_t count, int32_t *out_dev, void *stream)
+{
+    SB_REQUIRE(count >= 0 && (count == 0 || (bytes_dev && out_dev)), "sb_pcm24_unpack: bad arguments");
+    if (!count) return SB_OK;
+    pcm24_unpack_kernel<<<GRID32(count), kBlock32, 0, (cudaStream_t)stream>>>(bytes_dev, count, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_pcm24_pack(const int32_t *in_dev, int64_t count, uint8_t *bytes_dev, void *stream)
+{
+    SB_REQUIRE(count >= 0 && (count == 0 || (bytes_dev && in_dev)), "sb_pcm24_pack: bad arguments");
+    if (!count) return SB_OK;
+    pcm24_pack_kernel<<<GRID32(count), kBlock32, 0, (cudaStream_t)stream>>>(in_dev, count, bytes_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_pcm24_clamp(int32_t *buf_dev, int64_t count, void *stream)
+{
+    SB_REQUIRE(count >= 0 && (count == 0 || buf_dev), "sb_pcm24_clamp: bad arguments");
+    if (!count) return SB_OK;
+    pcm24_clamp_kernel<<<GRID32(count), kBlock32, 0, (cudaStream_t)stream>>>(buf_dev, count);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_pcm32_shift(int32_t *buf_dev, int64_t count, int shift, void *stream)
+{
+    SB_REQUIRE(count >= 0 && (count == 0 || buf_dev) && shift > -32 && shift < 32, "sb_pcm32_shift: bad arguments");
+    if (!count || !shift) return SB_OK;
+    pcm32_shift_kernel<<<GRID32(count), kBlock32, 0, (cudaStream_t)stream>>>(buf_dev, count, shift);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}

@@ -13,6 +13,7 @@ as a float32 CUDA tensor without the host round trip that blocks()/generator() i
 There is no CPU implementation behind these classes.
 """
 import ctypes
+import logging
 import itertools
 import math
 import random
@@ -454,27 +455,40 @@ class MixingFilter(Filter):
         super().__init__(sources)
 
     def _as_bank(self):
-        """When every source is a plain voice — [EnvelopeFilter(] waveform oscillator with an
-        optional plain waveform FM LFO [)] — the whole mix is one launch of the fused voice-bank
-        kernel instead of one kernel chain per source.  Rebuilt per request because upstream
-        oscillators may have their public attributes changed between renders."""
-        if len(self._sources) < 2:
-            return None
+        """The sources that are plain voices — [EnvelopeFilter(] waveform oscillator with an
+        optional plain waveform FM LFO [)] — go into ONE launch of the fused voice-bank kernel
+        instead of one kernel chain each; returns (bank or None, the other sources).  A source
+        the bank does not take (PWM, a stop_at_end envelope, a composite LFO, another filter)
+        is rendered node by node and added to the bank's mix; the split is logged once per
+        filter at INFO level.  Rebuilt per request because upstream oscillators may have their
+        public attributes changed between renders."""
         from .voicebank import VoiceBank
-        try:
-            return VoiceBank.from_oscillators(self._sources, gains=[(1.0, 0.0)] * len(self._sources),
-                                              samplerate=self._samplerate)
-        except ValueError:
-            return None
+        bank, rest = VoiceBank(self._samplerate), []
+        for s in self._sources:
+            try:
+                bank.add(s, 1.0, 0.0)
+            except ValueError:
+                rest.append(s)
+        if len(bank) < 2:
+            return None, self._sources
+        if rest and not getattr(self, "_split_logged", False):
+            self._split_logged = True
+            logging.getLogger("synthesizer_b200").info(
+                "MixingFilter: %d of %d sources are not plain bank voices and render node by node (%s)",
+                len(rest), len(self._sources), ", ".join(sorted({type(s).__name__ for s in rest})))
+        return bank, rest
 
     def _render_range(self, n0, count):
-        bank = self._as_bank()
+        bank, rest = self._as_bank()
+        bufs = []
         if bank is not None:
             mix = bank.render(count, start=n0)
             out = D.empty(count, torch.float32)
             C.call("sb_channel_f32", D.ptr(mix), 2, 0, count, D.ptr(out), D.stream())   # left channel = the mono mix
-            return out
-        bufs = [s._fetch(n0, n0 + count) for s in self._sources]
+            if not rest:
+                return out
+            bufs.append(out)
+        bufs += [s._fetch(n0, n0 + count) for s in rest]
         ptrs = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64).to(D.device())
         out = D.empty(count, torch.float32)
         C.call("sb_mix_f32", D.ptr(ptrs), len(bufs), count, D.ptr(out), D.stream())

@@ -10,8 +10,11 @@ write_wav).  Most operations modify the sample in place and return it, as upstre
 
 Upstream source is absent from /root/reference (README.md:1-2 only): method names, argument
 meaning and frame-index rounding follow the published package as recalled; see DESIGN.md.
-Sample widths 2 and 4 are supported (upstream also accepts 3-byte frames; this backend does
-not).  There is no CPU fallback.
+Sample widths 2, 3 and 4 are supported.  A sample of 3-byte frames keeps sign-extended int32 values
+on the device and runs the width-4 kernels, followed by the 24-bit clip / wrap / shift that
+audioop applies for size 3; like upstream (no array typecode for 3 bytes) it offers the
+audioop-backed operations, not the per-sample Python loops (fades, modulate_amp, envelope).
+There is no CPU fallback.
 """
 import array
 import ctypes
@@ -24,9 +27,9 @@ from . import _cabi as C
 from . import _device as D
 from . import params
 
-__all__ = ["Sample"]
+__all__ = ["Sample", "PlacementTable"]
 
-_DTYPE = {2: torch.int16, 4: torch.int32}
+_DTYPE = {2: torch.int16, 3: torch.int32, 4: torch.int32}
 
 
 class Sample:
@@ -50,13 +53,15 @@ class Sample:
         assert 1 <= numchannels <= 2
         assert 2 <= samplewidth <= 4
         assert samplerate > 1
-        if samplewidth not in _DTYPE:
-            raise ValueError("only samplewidth 2 or 4 are supported on this backend")
         s = cls(name=name, samplerate=samplerate, nchannels=numchannels, samplewidth=samplewidth)
         frames = bytes(frames)
         if len(frames) % (samplewidth * numchannels):
             raise ValueError("frames is not a whole number of sample frames")
-        if frames:
+        if frames and samplewidth == 3:
+            raw = torch.frombuffer(bytearray(frames), dtype=torch.uint8).to(D.device())
+            s._dev = D.empty(len(frames) // 3, torch.int32)
+            C.call("sb_pcm24_unpack", D.ptr(raw), len(frames) // 3, D.ptr(s._dev), D.stream())
+        elif frames:
             host = torch.frombuffer(bytearray(frames), dtype=_DTYPE[samplewidth])
             s._dev = host.to(D.device())
         return s
@@ -158,12 +163,17 @@ class Sample:
         """The raw little-endian frame bytes (device -> host copy)."""
         if self._dev is None:
             return b""
+        if self.samplewidth == 3:
+            raw = D.empty(3 * self._count(), torch.uint8)
+            C.call("sb_pcm24_pack", D.ptr(self._dev), self._count(), D.ptr(raw), D.stream())
+            return raw.cpu().numpy().tobytes()
         return self._dev.cpu().numpy().tobytes()
 
     def view_frame_data(self):
         return memoryview(self.get_frames())
 
     def get_frame_array(self):
+        self._no_array("get_frame_array")
         return self.get_array(self.samplewidth, None) if self._dev is None else \
             array.array(self.get_array(self.samplewidth).typecode, self.get_frames())
 
@@ -192,8 +202,6 @@ class Sample:
                 raise IOError("only supports sample sizes of 2, 3 or 4 bytes")
             if not 1 <= w.getnchannels() <= 2:
                 raise IOError("only supports mono or stereo channels")
-            if w.getsampwidth() not in _DTYPE:
-                raise IOError("24-bit samples are not supported on this backend")
             frames = w.readframes(w.getnframes())
             self.nchannels, self.samplerate, self.samplewidth = w.getnchannels(), w.getframerate(), w.getsampwidth()
         tmp = Sample.from_raw_frames(frames, self.samplewidth, self.samplerate, self.nchannels)
@@ -209,13 +217,20 @@ class Sample:
         stream.write(self.get_frames())
 
     # ------------------------------------------------------------------ helpers
-    def _need16(self, what):
-        if self.samplewidth != 2:
-            raise NotImplementedError("%s is only implemented for 16-bit frames" % what)
-
     def _k(self, op):
         """Name of the C-ABI routine for this sample's width: sb_pcm16_<op> or sb_pcm32_<op>."""
-        return "sb_pcm%d_%s" % (8 * self.samplewidth, op)
+        return "sb_pcm%d_%s" % (16 if self.samplewidth == 2 else 32, op)
+
+    def _fit24(self, t=None):
+        """3-byte frames: audioop clips to the 24-bit range where the width-4 kernel clipped to 32."""
+        if self.samplewidth == 3:
+            t = self._dev if t is None else t
+            if t is not None:
+                C.call("sb_pcm24_clamp", D.ptr(t), t.numel(), D.stream())
+
+    def _no_array(self, what):
+        if self.samplewidth == 3:          # upstream: get_frame_array() has no typecode for 3-byte samples
+            raise ValueError("%s: only samplewidth 2 or 4 are supported" % what)
 
     def _dt(self):
         return _DTYPE[self.samplewidth]
@@ -309,7 +324,13 @@ class Sample:
         nin = len(self)
         nout = C.lib.sb_pcm16_ratecv_frames(nin, inrate, outrate)       # frame count: width independent
         out = D.empty(nout * self.nchannels, self._dt())
-        C.call(self._k("ratecv"), D.ptr(self._dev), nin, self.nchannels, inrate, outrate, D.ptr(out), D.stream())
+        src = self._dev
+        if self.samplewidth == 3:          # audioop.ratecv works on samples widened to 32 bits: << 8, and >> 8 after
+            src = self._dev.clone()
+            C.call("sb_pcm32_shift", D.ptr(src), src.numel(), 8, D.stream())
+        C.call(self._k("ratecv"), D.ptr(src), nin, self.nchannels, inrate, outrate, D.ptr(out), D.stream())
+        if self.samplewidth == 3:
+            C.call("sb_pcm32_shift", D.ptr(out), out.numel(), -8, D.stream())
         return out
 
     def make_32bit(self, scale_amplitude=True):
@@ -317,7 +338,9 @@ class Sample:
         if self.samplewidth == 4:
             return self
         old_width = self.samplewidth
-        if self._dev is not None:
+        if self._dev is not None and old_width == 3:
+            C.call("sb_pcm32_shift", D.ptr(self._dev), self._count(), 8, D.stream())        # lin2lin 3 -> 4
+        elif self._dev is not None:
             out = D.empty(self._count(), torch.int32)
             C.call("sb_pcm16_to_pcm32", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
             self._dev = out
@@ -334,6 +357,8 @@ class Sample:
             self.amplify_max()
         if self.samplewidth > 2:
             if self._dev is not None:
+                if self.samplewidth == 3:                                                  # lin2lin 3 -> 2 is >> 8
+                    C.call("sb_pcm32_shift", D.ptr(self._dev), self._count(), 8, D.stream())
                 out = D.empty(self._count(), torch.int16)
                 C.call("sb_pcm32_to_pcm16", D.ptr(self._dev), self._count(), D.ptr(out), D.stream())
                 self._dev = out
@@ -349,6 +374,7 @@ class Sample:
             C.call(self._k("tomono"), D.ptr(self._dev), len(self), float(left_factor), float(right_factor),
                    D.ptr(out), D.stream())
             self._dev = out
+            self._fit24()
         self.nchannels = 1
         return self
 
@@ -377,6 +403,7 @@ class Sample:
             out = D.empty(2 * self._count(), self._dt())
             C.call(self._k("tostereo"), D.ptr(self._dev), self._count(), float(lf), float(rf), D.ptr(out), D.stream())
             self._dev = out
+            self._fit24()
         self.nchannels = 2
 
     def normalize(self):
@@ -418,12 +445,36 @@ class Sample:
             other.stereo(left_factor=0, right_factor=other_mix_factor)
         return self.mix_at(mix_at, other, other_seconds)
 
-    def pan(self, panning=0.0):
+    def pan(self, panning=0.0, lfo=None):
+        """Linear stereo panning, -1 = full left, 1 = full right; with `lfo` (an oscillator whose
+        values lie in [-1, 1]) the panning follows it sample frame by sample frame: left =
+        int(v*(1-p)), right = int(v*(1+p)) with the same scaling as the fixed panning.  (Upstream's
+        formula for either variant is recalled, not pinned: see DESIGN.md.)"""
         assert not self._locked
-        assert -1 <= panning <= 1
-        left_volume = (1.0 - panning) / 2
-        right_volume = 1.0 - left_volume
-        return self.stereo(left_volume * 2, right_volume * 2)
+        if lfo is None:
+            assert -1 <= panning <= 1
+            left_volume = (1.0 - panning) / 2
+            right_volume = 1.0 - left_volume
+            return self.stereo(left_volume * 2, right_volume * 2)
+        self._no_array("pan(lfo)")
+        if self._dev is None:
+            self.nchannels = 2
+            return self
+        left = self.copy().left() if self.nchannels == 2 else self.copy()
+        right = self.copy().right() if self.nchannels == 2 else self.copy()
+        n = left._count()
+        p = lfo.render(n)
+        if p.numel() < n:
+            raise ValueError("the panning oscillator ends before the sample does")
+        ml, mr = D.empty(n, torch.float32), D.empty(n, torch.float32)
+        C.call("sb_scale_bias_f32", D.ptr(p), -1.0, 1.0, n, D.ptr(ml), D.stream())
+        C.call("sb_scale_bias_f32", D.ptr(p), 1.0, 1.0, n, D.ptr(mr), D.stream())
+        C.call(left._k("modulate"), D.ptr(left._dev), D.ptr(ml), n, D.stream())
+        C.call(right._k("modulate"), D.ptr(right._dev), D.ptr(mr), n, D.stream())
+        left._tostereo(1, 0)
+        right._tostereo(0, 1)
+        self._dev, self.nchannels = left._dev, 2
+        return self._add_inplace(right._dev)
 
     # ------------------------------------------------------------------ amplitude
     def amplify(self, factor):
@@ -431,6 +482,7 @@ class Sample:
         assert not self._locked
         if self._dev is not None:
             C.call(self._k("mul"), D.ptr(self._dev), self._count(), float(factor), D.ptr(self._dev), D.stream())
+            self._fit24()
         return self
 
     def amplify_max(self):
@@ -457,6 +509,9 @@ class Sample:
             b = int(bias) & 0xFFFFFFFF                      # audioop adds it as an unsigned 32-bit value
             b = b - (1 << 32) if b >= (1 << 31) else b
             C.call(self._k("bias"), D.ptr(self._dev), self._count(), b, D.ptr(self._dev), D.stream())
+            if self.samplewidth == 3:      # the wrap is at 24 bits: drop the high byte, sign-extend
+                C.call("sb_pcm32_shift", D.ptr(self._dev), self._count(), 8, D.stream())
+                C.call("sb_pcm32_shift", D.ptr(self._dev), self._count(), -8, D.stream())
         return self
 
     def reverse(self):
@@ -469,6 +524,7 @@ class Sample:
 
     def fadeout(self, seconds, target_volume=0.0):
         assert not self._locked
+        self._no_array("fadeout")
         if self._dev is None:
             return self
         seconds = min(seconds, self.duration)
@@ -480,6 +536,7 @@ class Sample:
 
     def fadein(self, seconds, start_volume=0.0):
         assert not self._locked
+        self._no_array("fadein")
         if self._dev is None:
             return self
         seconds = min(seconds, self.duration)
@@ -492,6 +549,7 @@ class Sample:
         """Amplitude modulation by an oscillator (rendered on the GPU), or by a Sample / list /
         array that is cycled and normalised to a maximum of 1.0 as upstream does."""
         assert not self._locked
+        self._no_array("modulate_amp")
         if self._dev is None:
             return self
         n = self._count()
@@ -569,6 +627,7 @@ class Sample:
         n = other_dev.numel()
         dst = self._dev[at:at + n]
         C.call(self._k("add"), D.ptr(dst), D.ptr(other_dev), n, D.ptr(dst), D.stream())
+        self._fit24(dst)
         return self
 
     def _grow(self, required):
@@ -627,7 +686,9 @@ class Sample:
     def mix_at_many(self, placements, sharded=False, group=None, shard=None):
         """Backend extension: apply ``mix_at(seconds, sample)`` for every (seconds, sample) of
         `placements`, in order, with ONE kernel launch.  The result is identical to the loop of
-        mix_at calls (each step saturates like audioop.add).
+        mix_at calls (each step saturates like audioop.add).  `placements` is a list of
+        (seconds, Sample) or a PlacementTable made from one (Sample.placement_table): the table
+        keeps the index arrays on the device, so mixing the same hits again costs one launch.
 
         sharded=True (inside an initialised torch.distributed group), or shard=(rank, world):
         this process mixes only ITS range of the destination (shard_bounds) and afterwards holds
@@ -646,19 +707,9 @@ class Sample:
             for seconds, other in placements:
                 self.mix_at(seconds, other)
             return self
-        starts, srcs = [], []
-        for seconds, other in placements:
-            self._same_format(other)
-            if seconds < 0:
-                raise ValueError("mix_at_many: negative start time")
-            if other._dev is None:
-                continue
-            starts.append(self._sample_idx(seconds))
-            srcs.append(other._dev)
-        import numpy as np
-        lens = np.array([s.numel() for s in srcs], dtype=np.int64)
-        starts = np.array(starts, dtype=np.int64)
-        total = max(self._count(), int((starts + lens).max()) if len(srcs) else 0)
+        table = placements if isinstance(placements, PlacementTable) else PlacementTable(self, placements)
+        table.check(self)
+        total = max(self._count(), table.end)
         lo, hi = 0, total
         if shard is not None:
             lo, hi = self.shard_bounds(total, shard[0], shard[1])
@@ -666,22 +717,20 @@ class Sample:
             self._dev = have.clone() if have is not None else None     # this rank's slice of what was there
             self.shard_range = (lo, hi, total)
         self._grow(hi - lo)
-        keep = lens > 0                                 # an empty sample only extends the destination
-        if not keep.any():
+        idx, nsrc, span = table.device_index(lo, hi)
+        if not nsrc:
             return self
-        # the sources stay where they are: the kernel takes element offsets from a base pointer,
-        # here the lowest address among them (no concatenated copy of thousands of tensors)
-        ptrs = np.array([s.data_ptr() for s in srcs], dtype=np.int64)[keep]
-        base = int(ptrs.min())
-        offs, lens, starts = self.clip_placements((ptrs - base) // 2, lens[keep], starts[keep], lo, hi)
-        if not len(lens):
-            return self
-        idx = torch.from_numpy(np.stack([offs, lens, starts])).to(D.device())
-        nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), len(lens), int(lens.sum()))
-        scratch = D.empty(nscratch, torch.uint8)
-        C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), ctypes.c_void_p(base), D.ptr(idx[0]),
-               D.ptr(idx[1]), D.ptr(idx[2]), len(lens), D.ptr(scratch), nscratch, D.stream())
+        nscratch = C.lib.sb_pcm16_mix_at_many_scratch_bytes(self._count(), nsrc, span)
+        scratch = table.scratch(nscratch)
+        C.call("sb_pcm16_mix_at_many", D.ptr(self._dev), self._count(), ctypes.c_void_p(table.base), D.ptr(idx[0]),
+               D.ptr(idx[1]), D.ptr(idx[2]), nsrc, D.ptr(scratch), nscratch, D.stream())
         return self
+
+    def placement_table(self, placements):
+        """A reusable table of (seconds, Sample) placements for mix_at_many on samples of this
+        format: built once (one pass over the list, one host-to-device copy of the index
+        arrays), it makes every later mix_at_many of the same hits a single kernel launch."""
+        return PlacementTable(self, placements)
 
     def gather_shards(self, group=None):
         """After a sharded mix_at_many: every rank receives all slices (one all_gather) and holds
@@ -741,3 +790,50 @@ class Sample:
             R.fadeout(release)
         self.join(D_).join(S).join(R)
         return self
+
+
+class PlacementTable:
+    """The placements of Sample.mix_at_many as arrays: for each non-empty source its offset from a
+    base address (the sources stay where they are - no concatenated copy), its length and its
+    destination sample index, in list order; kept on the device per destination range, with the
+    kernel's scratch.  Holds references to the source tensors."""
+
+    def __init__(self, like, placements):
+        import numpy as np
+        self.format = (like.samplerate, like.samplewidth, like.nchannels)
+        starts, srcs = [], []
+        for seconds, other in placements:
+            like._same_format(other)
+            if seconds < 0:
+                raise ValueError("mix_at_many: negative start time")
+            starts.append(like._sample_idx(seconds))
+            srcs.append(other._dev)
+        lens = np.array([0 if s is None else s.numel() for s in srcs], dtype=np.int64)
+        starts = np.array(starts, dtype=np.int64)
+        self.end = int((starts + lens).max()) if len(srcs) else 0       # an empty sample still extends the destination
+        keep = lens > 0
+        self._srcs = [s for s in srcs if s is not None]
+        ptrs = np.array([s.data_ptr() for s in self._srcs if s.numel()], dtype=np.int64)
+        self.base = int(ptrs.min()) if len(ptrs) else 0
+        self._offs, self._lens, self._starts = (ptrs - self.base) // 2, lens[keep], starts[keep]
+        self._dev = {}
+        self._scratch = None
+
+    def check(self, dst):
+        if (dst.samplerate, dst.samplewidth, dst.nchannels) != self.format:
+            raise ValueError("the placement table was made for another sample format")
+
+    def device_index(self, lo, hi):
+        """(int64 tensor [3, n] on the device, n, total samples) of the placements clipped to [lo, hi)."""
+        import numpy as np
+        key = (lo, hi, torch.cuda.current_device())
+        if key not in self._dev:
+            o, l, d = Sample.clip_placements(self._offs, self._lens, self._starts, lo, hi)
+            idx = torch.from_numpy(np.stack([o, l, d])).to(D.device()) if len(l) else None
+            self._dev[key] = (idx, len(l), int(l.sum()))
+        return self._dev[key]
+
+    def scratch(self, nbytes):
+        if self._scratch is None or self._scratch.numel() < nbytes or self._scratch.device != D.device():
+            self._scratch = D.empty(nbytes, torch.uint8)
+        return self._scratch

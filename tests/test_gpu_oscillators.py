@@ -321,3 +321,34 @@ def test_overflow_raises(cuda):
     import synthesizer_b200 as sb
     with pytest.raises(OverflowError):
         sb.Sample.from_oscillator(sb.Sine(440, 1.5, samplerate=44100), 0.1)
+
+
+def test_mixing_filter_splits_bank_voices_from_the_rest(cuda, caplog):
+    """Sources the bank does not take (PWM, a stop_at_end envelope) no longer drag the whole mix
+    onto the node-by-node path: the plain voices still go through the fused kernel, the others are
+    added to its mix, and the split is logged."""
+    import logging
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _device as D
+    from oracle import synth_oracle as so
+    sr, n = 48000, 9000
+
+    def build(m):
+        voices = [m.EnvelopeFilter(m.Sine(110.0 * (k + 1), 0.1, 0.1 * k, fm_lfo=m.Sine(3.0 + k, 0.02, samplerate=sr),
+                                          samplerate=sr), 0.01, 0.02, 0.05, 0.6, 0.05) for k in range(5)]
+        voices.append(m.Pulse(330.0, 0.1, pulsewidth=0.4, pwm_lfo=m.Sine(2.0, 0.3, bias=0.5, samplerate=sr), samplerate=sr))
+        voices.append(m.EnvelopeFilter(m.Triangle(220.0, 0.1, samplerate=sr), 0.01, 0.02, 0.1, 0.6, 0.1, stop_at_end=True))
+        return m.MixingFilter(*voices)
+
+    mix = build(sb)
+    with caplog.at_level(logging.INFO, logger="synthesizer_b200"):
+        bank, rest = mix._as_bank()
+        assert len(bank) == 5 and len(rest) == 2
+        l0 = D.launch_count()
+        got = dev_pcm16(mix.render(n))
+        launches = D.launch_count() - l0
+    assert "2 of 7 sources" in caplog.text
+    assert launches < 40                       # five voices in one bank render, not five kernel chains
+    want = pcm16_of(so.render_floats(build(so), n))
+    assert len(want) == n
+    assert_within_lsb(got, want, 1, "MixingFilter, bank voices + others")

@@ -410,3 +410,135 @@ def test_mix_at_many_sharded_slices_equal_the_unsharded_result(cuda):
             got.append(np.frombuffer(part.get_frames(), dtype="<i2"))
             assert got[-1].size == hi - lo
         assert np.array_equal(np.concatenate(got), want), "world %d" % world
+
+
+def test_mix_at_many_bad_input_stays_inside_its_buffers(cuda):
+    """Raw C-ABI callers: a negative destination offset is left out (and counted), a scratch too
+    small for the per-tile lists is refused per tile (flagged) - neither writes out of bounds."""
+    import torch
+    from synthesizer_b200 import _cabi as C, _device as D
+    rng = np.random.default_rng(5)
+    total, nsrc = 40000, 64
+    dst = torch.zeros(total, dtype=torch.int16, device="cuda")
+    lens = rng.integers(100, 3000, nsrc).astype(np.int64)
+    offs = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+    starts = rng.integers(0, total - 3000, nsrc).astype(np.int64)
+    starts[5] = -17                                                # bad
+    pool = torch.from_numpy(rng.integers(-3000, 3000, int(lens.sum())).astype(np.int16)).cuda()
+    idx = torch.tensor(np.stack([offs, lens, starts]), dtype=torch.int64, device="cuda")
+    nscr = C.lib.sb_pcm16_mix_at_many_scratch_bytes(total, nsrc, int(lens.sum()))
+    guard = 4096
+    scr = torch.full((nscr + guard,), 0x5A, dtype=torch.uint8, device="cuda")
+    C.call("sb_pcm16_mix_at_many", D.ptr(dst), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]), nsrc,
+           D.ptr(scr), nscr, D.stream())
+    status = scr[:16].view(torch.int32).cpu().numpy()
+    assert status[1] == 1 and status[2] == 0
+    assert bool((scr[nscr:] == 0x5A).all())
+    # the same mix without the bad source is what came out
+    want = np.zeros(total, dtype=np.int64)
+    p = pool.cpu().numpy().astype(np.int64)
+    for s in range(nsrc):
+        if starts[s] >= 0:
+            want[starts[s]:starts[s] + lens[s]] = np.clip(want[starts[s]:starts[s] + lens[s]] + p[offs[s]:offs[s] + lens[s]], -32768, 32767)
+    assert np.array_equal(dst.cpu().numpy().astype(np.int64), want)
+    # a scratch with room for the fixed part and three list entries only
+    ntiles = (total + 2047) // 2048
+    small = (3 * ntiles + 4 + 3) * 4
+    scr2 = torch.full((small + guard,), 0x5A, dtype=torch.uint8, device="cuda")
+    dst.zero_()
+    C.call("sb_pcm16_mix_at_many", D.ptr(dst), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]), nsrc,
+           D.ptr(scr2), small, D.stream())
+    assert scr2[:16].view(torch.int32).cpu().numpy()[2] == 1
+    assert bool((scr2[small:] == 0x5A).all())
+
+
+def test_mix_at_many_with_a_placement_table(cuda):
+    """The reusable table gives the same bytes as the list of placements, on every use."""
+    import synthesizer_b200 as sb
+    rng = np.random.default_rng(21)
+    sr = 44100
+    base = rng.integers(-9000, 9000, sr).astype(np.int16)
+    hits = [(float(np.float32(rng.uniform(0, 1.2))),
+             sb.Sample.from_raw_frames(rng.integers(-30000, 30000, int(rng.integers(0, 5000))).astype("<i2").tobytes(), 2, sr, 1))
+            for _ in range(100)]
+    want = np.frombuffer(sb.Sample.from_raw_frames(base.tobytes(), 2, sr, 1).mix_at_many(hits).get_frames(), dtype="<i2")
+    table = sb.Sample.from_raw_frames(b"", 2, sr, 1).placement_table(hits)
+    for _ in range(2):
+        got = sb.Sample.from_raw_frames(base.tobytes(), 2, sr, 1).mix_at_many(table)
+        assert np.array_equal(np.frombuffer(got.get_frames(), dtype="<i2"), want)
+    with pytest.raises(ValueError):
+        sb.Sample.from_raw_frames(base.tobytes(), 2, sr, 2).mix_at_many(table)
+
+
+def _pair24(values, sr=44100, ch=1):
+    import synthesizer_b200 as sb
+    from oracle.sample_oracle import Sample as OS
+    v = np.asarray(values, dtype=np.int64) & 0xFFFFFF
+    raw = np.stack([v & 0xFF, (v >> 8) & 0xFF, (v >> 16) & 0xFF], axis=1).astype(np.uint8).tobytes()
+    return sb.Sample.from_raw_frames(raw, 3, sr, ch), OS.from_raw_frames(raw, 3, sr, ch)
+
+
+def _same24(g, o, what):
+    assert (g.samplerate, g.nchannels, g.samplewidth) == (o.samplerate, o.nchannels, o.samplewidth), what
+    assert g.get_frames() == o._frames, what
+
+
+def test_24_bit_frames_follow_audioop_size_3(cuda, tmp_path):
+    """3-byte frames: every audioop-backed operation, bit for bit against the real module."""
+    import synthesizer_b200 as sb
+    rng = np.random.default_rng(33)
+    full = rng.integers(-(1 << 23), 1 << 23, 6000)
+    full[:4] = [(1 << 23) - 1, -(1 << 23), -(1 << 23) + 1, 0]
+    g, o = _pair24(full)
+    _same24(g, o, "round trip")
+    assert len(g) == len(o) and g.maximum == o.maximum
+    for factor in (0.5, 1.7, -1.0, 0.333, 2.75):
+        g, o = _pair24(full)
+        _same24(g.amplify(factor), o.amplify(factor), "amplify %g" % factor)
+    g, o = _pair24(full)
+    g2, o2 = _pair24(np.roll(full, 7))
+    _same24(g.mix(g2), o.mix(o2), "mix (saturates at 24 bits)")
+    g, o = _pair24(full[:5000])
+    _same24(g.mix_at(0.01, g2), o.mix_at(0.01, o2), "mix_at")
+    g, o = _pair24(full)
+    _same24(g.bias(3_000_000), o.bias(3_000_000), "bias (wraps at 24 bits)")
+    g, o = _pair24(full, ch=2)
+    _same24(g.mono(0.8, 0.7), o.mono(0.8, 0.7), "mono")
+    g, o = _pair24(full)
+    _same24(g.stereo(1.3, 0.6), o.stereo(1.3, 0.6), "stereo")
+    g, o = _pair24(full, ch=2)
+    _same24(g.reverse(), o.reverse(), "reverse")
+    for rate in (48000, 22050, 44101):
+        g, o = _pair24(full, ch=2)
+        _same24(g.resample(rate), o.resample(rate), "resample %d" % rate)
+    g, o = _pair24(full)
+    _same24(g.amplify_max(), o.amplify_max(), "amplify_max")
+    g, o = _pair24(full)
+    g.make_32bit(); o.make_32bit()
+    assert g.samplewidth == 4 and g.get_frames() == o._frames
+    g, o = _pair24(full // 3)
+    g.make_16bit(); o.make_16bit()
+    assert g.samplewidth == 2 and g.get_frames() == o._frames
+    # WAV round trip, and what upstream cannot do at this width either
+    g, o = _pair24(full, sr=48000, ch=2)
+    path = str(tmp_path / "x24.wav")
+    g.write_wav(path)
+    back = sb.Sample(path)
+    assert (back.samplewidth, back.nchannels, back.samplerate) == (3, 2, 48000) and back.get_frames() == o._frames
+    with pytest.raises(ValueError):
+        g.fadeout(0.01)
+    with pytest.raises(ValueError):
+        g.get_frame_array()
+
+
+def test_pan_with_an_lfo(cuda):
+    import synthesizer_b200 as sb
+    from oracle import synth_oracle as so
+    for ch in (1, 2):
+        g, o = _pair(np.random.default_rng(41).integers(-15000, 15000, 4000 * ch), sr=48000, ch=ch)
+        g.pan(lfo=sb.Sine(3.0, 0.8, samplerate=48000))
+        o.pan(lfo=so.Sine(3.0, 0.8, samplerate=48000))
+        assert g.nchannels == 2 and len(g) == 4000
+        a = np.frombuffer(g.get_frames(), dtype="<i2").astype(int)
+        b = np.frombuffer(o._frames, dtype="<i2").astype(int)
+        assert np.abs(a - b).max() <= 1          # the panning values are float32 on the device
