@@ -335,6 +335,7 @@ def run_ours(args):
     ovf = D.zeros(1, torch.int64)
     host_pcm = torch.empty(2 * frames, dtype=torch.int16).pin_memory()
     flush = torch.zeros(256 << 20, dtype=torch.uint8, device=D.device())
+    mix_buf = D.empty(2 * frames, torch.float32)
 
     def barrier():
         if world > 1:
@@ -347,7 +348,7 @@ def run_ours(args):
     def step_resident():
         # the product API: this rank's slice of the voices (uploaded once, kept by the bank),
         # one reduce of the partial mixes onto rank 0, PCM conversion there
-        mix = bank.render_sharded(frames)
+        mix = bank.render_sharded(frames, out=mix_buf)
         if rank == 0:
             to_pcm(mix)
 

@@ -261,6 +261,12 @@ struct RcvRate {
     uint32_t Qk, Rk;     // 32*inrate = Qk*outr + Rk: what 32 output frames advance (c, d) by
     uint32_t lim;        // outr - ceil(outr/65536): remainders above it trigger the negative fix-up
     float rcp;           // 1/outr
+    // outr <= 16384 (every usual pair of sample rates, reduced): floor(n/outr) for 0 <= n < 2^31 as one
+    // widening multiply and a shift, floor(n/outr) = (n*mg) >> msh with msh = 31 + ceil(log2 outr),
+    // mg = ceil(2^msh/outr) (Granlund & Montgomery; tools/ratecv_formula_check.py replays it)
+    uint32_t mg;
+    int msh;
+    uint32_t moff;       // 65536*outr: makes the numerator (prev-cur)*d non-negative, and shifts the quotient by 65536
 };
 
 __device__ __forceinline__ RcvRate rcv_rate(int64_t inrate, int64_t outrate)
@@ -272,6 +278,16 @@ __device__ __forceinline__ RcvRate rcv_rate(int64_t inrate, int64_t outrate)
     rt.Rk = K - rt.Qk * rt.outr;
     rt.lim = rt.outr - ((rt.outr + 65535u) >> 16);
     rt.rcp = __frcp_rn((float)rt.outr);
+    rt.mg = 0;
+    rt.msh = 0;
+    rt.moff = 0;
+    if (rt.outr <= 16384u) {
+        int L = 0;
+        while ((1u << L) < rt.outr) L++;
+        rt.msh = 31 + L;
+        rt.mg = (uint32_t)(((1ull << rt.msh) + rt.outr - 1) / rt.outr);
+        rt.moff = 65536u * rt.outr;
+    }
     return rt;
 }
 
@@ -288,6 +304,14 @@ __device__ __forceinline__ int small_floor_to_int(float x)
 
 // FIXUP = false for outr <= 65536 (every real sample-rate pair): then ceil(outr/65536) = 1, a
 // remainder can never exceed outr - 1 = lim, and the negative fix-up above never applies.
+// cur + floor((prev-cur)*d/outr) by the invariant multiplication (outr <= 16384): five integer operations
+__device__ __forceinline__ int rcv_sample_magic(int prev, int cur, uint32_t d, const RcvRate &rt)
+{
+    const uint32_t n = (uint32_t)((prev - cur) * (int)d) + rt.moff;             // in [0, 2^31)
+    const unsigned long long wide = (unsigned long long)n * rt.mg;
+    return cur + (int)(uint32_t)(wide >> rt.msh) - 65536;
+}
+
 template <bool FIXUP>
 __device__ __forceinline__ int rcv_sample(int prev, int cur, uint32_t d, float w, const RcvRate &rt)
 {
@@ -306,7 +330,7 @@ __device__ __forceinline__ int rcv_sample(int prev, int cur, uint32_t d, float w
 // A lane's ITERS frames j0, j0+32, ...: all loads first (2*ITERS in flight per lane), then the
 // arithmetic and the stores.  `pin` points at the lane's newest input frame for j0, `pout` at
 // output frame j0; everything inside is 32-bit offsets from those.  FULL = every frame exists.
-template <int NCH, bool VEC, int ITERS, bool FULL, bool FIXUP>
+template <int NCH, bool VEC, int ITERS, bool FULL, bool FIXUP, bool MAGIC>
 __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16_t *__restrict__ pout, int nleft,
                                           bool first_is_frame0, uint32_t &crel, uint32_t &d, const RcvRate &rt)
 {
@@ -338,12 +362,14 @@ __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16
 #pragma unroll
     for (int it = 0; it < ITERS; it++) {
         if (FULL || it * 32 < nleft) {
-            const float w = __fmul_rn(small_int_to_float((int)dd[it]), rt.rcp);
-            const int o0 = rcv_sample<FIXUP>((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], w, rt);
+            const float w = MAGIC ? 0.0f : __fmul_rn(small_int_to_float((int)dd[it]), rt.rcp);
+            const int o0 = MAGIC ? rcv_sample_magic((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], rt)
+                                 : rcv_sample<FIXUP>((int)(int16_t)(wp[it] & 0xffffu), (int)(int16_t)(wc[it] & 0xffffu), dd[it], w, rt);
             if (NCH == 1) {
                 pout[it * 32] = (int16_t)o0;
             } else {
-                const int o1 = rcv_sample<FIXUP>((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], w, rt);
+                const int o1 = MAGIC ? rcv_sample_magic((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], rt)
+                                     : rcv_sample<FIXUP>((int)wp[it] >> 16, (int)wc[it] >> 16, dd[it], w, rt);
                 if (VEC) reinterpret_cast<uint32_t *>(pout)[it * 32] = ((uint32_t)o0 & 0xffffu) | ((uint32_t)o1 << 16);
                 else pout[it * 64] = (int16_t)o0, pout[it * 64 + 1] = (int16_t)o1;
             }
@@ -355,7 +381,7 @@ __device__ __forceinline__ void rcv_batch(const int16_t *__restrict__ pin, int16
 // frames jc + l + 32*k.  A lane's first frame is placed by one 64-bit division (fp64 estimate
 // plus correction); each further frame is 32 outputs on, which moves (c, d) by constants.
 // Lanes map to consecutive output frames: coalesced stores, near-coalesced loads.
-template <int NCH, bool VEC, int ITERS, int BATCHES, bool FIXUP>
+template <int NCH, bool VEC, int ITERS, int BATCHES, bool FIXUP, bool MAGIC>
 __device__ __forceinline__ void rcv_chunk(const int16_t *__restrict__ in, int16_t *__restrict__ out, int64_t jc,
                                           int64_t out_frames, int64_t inrate, int64_t outrate, const RcvRate &rt,
                                           double rcp64)
@@ -376,11 +402,11 @@ __device__ __forceinline__ void rcv_chunk(const int16_t *__restrict__ in, int16_
     if (full) {
 #pragma unroll 1
         for (int b = 0; b < BATCHES; b++)
-            rcv_batch<NCH, VEC, ITERS, true, FIXUP>(pin, pout + (int64_t)b * 32 * ITERS * NCH, 0, b == 0 && j0 == 0, crel, d, rt);
+            rcv_batch<NCH, VEC, ITERS, true, FIXUP, MAGIC>(pin, pout + (int64_t)b * 32 * ITERS * NCH, 0, b == 0 && j0 == 0, crel, d, rt);
     } else {
         const int64_t left = out_frames - j0;
         for (int b = 0; b < BATCHES && (int64_t)b * 32 * ITERS < left; b++)
-            rcv_batch<NCH, VEC, ITERS, false, FIXUP>(pin, pout + (int64_t)b * 32 * ITERS * NCH,
+            rcv_batch<NCH, VEC, ITERS, false, FIXUP, MAGIC>(pin, pout + (int64_t)b * 32 * ITERS * NCH,
                                               (int)min(left - (int64_t)b * 32 * ITERS, (int64_t)(32 * ITERS)),
                                               b == 0 && j0 == 0, crel, d, rt);
     }
@@ -408,12 +434,15 @@ pcm16_ratecv_kernel(const int16_t *__restrict__ in, int64_t inrate, int64_t outr
     const RcvRate rt = rcv_rate(inrate, outrate);
     const double rcp64 = 1.0 / (double)outrate;
     const int64_t chunk = 32 * kRcvIters * kRcvBatches;
-    if (outrate <= 65536) {
+    if (outrate <= 16384) {
         for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
-            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, false>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, false, true>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+    } else if (outrate <= 65536) {
+        for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
+            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, false, false>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
     } else {
         for (int64_t jc = warp_id * chunk; jc < out_frames; jc += nwarps * chunk)
-            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, true>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
+            rcv_chunk<NCH, VEC, kRcvIters, kRcvBatches, true, false>(in, out, jc, out_frames, inrate, outrate, rt, rcp64);
     }
 }
 
@@ -888,9 +917,9 @@ pcm16_ratecv_many_kernel(const int16_t *__restrict__ in_pool, const int64_t *__r
         const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
         const bool vec = ((in_off[s] | out_off[s]) & 1) == 0 && pools_aligned;
         for (int64_t jc = warp_id * chunk; jc < nout; jc += nwarps * chunk) {
-            if (nch == 1) rcv_chunk<1, false, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
-            else if (vec) rcv_chunk<2, true, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
-            else rcv_chunk<2, false, kRcvManyIters, 1, true>(in, out, jc, nout, inr, outr, rt, rcp64);
+            if (nch == 1) rcv_chunk<1, false, kRcvManyIters, 1, true, false>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else if (vec) rcv_chunk<2, true, kRcvManyIters, 1, true, false>(in, out, jc, nout, inr, outr, rt, rcp64);
+            else rcv_chunk<2, false, kRcvManyIters, 1, true, false>(in, out, jc, nout, inr, outr, rt, rcp64);
         }
     }
 }

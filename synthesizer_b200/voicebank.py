@@ -68,6 +68,7 @@ class VoiceBank:
         self._voices = []
         self._dev = None
         self._last = None
+        self._scratch = None
 
     def __len__(self):
         return len(self._voices)
@@ -133,7 +134,7 @@ class VoiceBank:
         return self.count_classes(begin, end)[2]
 
     def render(self, nframes, start=0, begin=0, end=None, voices_dev=None, generic_voices=None,
-               edged_voices=None, scan_voices=None, smooth_voices=None):
+               edged_voices=None, scan_voices=None, smooth_voices=None, out=None):
         """Interleaved stereo float32 mix (2*nframes values) of voices [begin, end) for frames
         [start, start+nframes), as a CUDA tensor."""
         D.require_cuda()
@@ -148,7 +149,9 @@ class VoiceBank:
             voices_dev, nv, generic_voices, smooth_voices, edged_voices, scan_voices = self._dev[key]
         else:
             nv = voices_dev.numel() // ctypes.sizeof(C.Voice)
-        mix = D.empty(2 * nframes, torch.float32)
+        if out is not None and (out.dtype != torch.float32 or out.numel() != 2 * nframes or not out.is_cuda):
+            raise ValueError("out must be a CUDA float32 tensor of 2*nframes values")
+        mix = out if out is not None else D.empty(2 * nframes, torch.float32)
         if nv == 0:
             return mix.zero_()
         plan = C.BankPlan()
@@ -158,8 +161,14 @@ class VoiceBank:
         unknown = lambda x: -1 if x is None else x
         C.call("sb_bank_plan_hint", ctypes.byref(plan), unknown(generic_voices), unknown(smooth_voices),
                unknown(edged_voices), unknown(scan_voices))
-        carry = D.empty(max(1, plan.carry_bytes // 8), torch.float64)
-        partial = D.empty(max(1, plan.partial_bytes // 4), torch.float32)
+        # the scratch is kept between renders (a bank is usually rendered again and again: chunks,
+        # steps); it only grows
+        need = (max(1, plan.carry_bytes // 8), max(1, plan.partial_bytes // 4), torch.cuda.current_device())
+        if self._scratch is None or self._scratch[0].numel() < need[0] or self._scratch[1].numel() < need[1] \
+                or self._scratch[2] != need[2]:
+            self._scratch = None                         # release before growing
+            self._scratch = (D.empty(need[0], torch.float64), D.empty(need[1], torch.float32), need[2])
+        carry, partial = self._scratch[0], self._scratch[1]
         C.call("sb_bank_render_f32", D.ptr(voices_dev), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs,
                D.ptr(tc.dev()), tc.nsegs, start, float(self.samplerate), D.ptr(carry), D.ptr(partial),
                D.ptr(mix), D.stream())
@@ -175,16 +184,18 @@ class VoiceBank:
         C.call("sb_bank_render_check", ctypes.byref(plan), D.ptr(carry), ctypes.byref(n), D.stream())
         return n.value
 
-    def render_sharded(self, nframes, start=0, group=None):
+    def render_sharded(self, nframes, start=0, group=None, out=None):
         """Voice-sharded render: this rank renders its slice of the voices; the partial mixes
         are summed on rank 0 with one reduce.  Returns the full mix on rank 0 (the partial one
-        elsewhere).  Without an initialised process group this is a plain render."""
+        elsewhere).  Without an initialised process group this is a plain render.  `out`: a CUDA
+        float32 tensor of 2*nframes values to render into (a caller that renders repeatedly keeps
+        one, and the reduce then always works on the same buffer)."""
         import torch.distributed as dist
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-            return self.render(nframes, start)
+            return self.render(nframes, start, out=out)
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         b, e = shard_range(len(self._voices), rank, world)
-        mix = self.render(nframes, start, b, e)
+        mix = self.render(nframes, start, b, e, out=out)
         dist.reduce(mix, dst=0, op=dist.ReduceOp.SUM, group=group)
         return mix
 

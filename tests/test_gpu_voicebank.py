@@ -501,6 +501,49 @@ def test_host_buffer_entry_points(cuda):
     np.testing.assert_array_equal(out, dev_pcm16(bank.render(n)))
 
 
+def test_host_bank_render_from_two_host_threads(cuda):
+    """sb_host_bank_render_pcm16 keeps its workspaces per device behind a mutex: two host threads
+    calling it at once (different banks, different sizes, so that the workspaces are regrown under
+    each other's feet) each get the bytes they get alone."""
+    import threading
+    from synthesizer_b200 import _cabi as C
+    sr = 48000
+    jobs = []
+    for seed, nv, n in ((3, 40, 30000), (4, 700, 12000)):
+        bank, _ = make_bank(nv, sr, seed, n / sr, fm=True)
+        arr = bank.voice_array()
+        alone = np.empty(2 * n, dtype=np.int16)
+        C.call("sb_host_bank_render_pcm16", arr, len(arr), n, float(sr), 32767.0, alone.ctypes.data_as(ctypes.c_void_p), None)
+        jobs.append((arr, n, alone))
+    results = {}
+
+    def work(i):
+        import torch
+        torch.cuda.set_device(0)
+        arr, n, _ = jobs[i]
+        for rep in range(6):
+            out = np.empty(2 * n, dtype=np.int16)
+            C.call("sb_host_bank_render_pcm16", arr, len(arr), n, float(sr), 32767.0, out.ctypes.data_as(ctypes.c_void_p), None)
+            results[(i, rep)] = out
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for (i, rep), out in results.items():
+        np.testing.assert_array_equal(out, jobs[i][2], err_msg="thread %d, call %d" % (i, rep))
+    # the stream variant and the up-front reservation
+    import torch
+    side = torch.cuda.Stream()
+    arr, n, alone = jobs[0]
+    C.call("sb_host_reserve", 4096, 48000, float(sr))
+    out = np.empty(2 * n, dtype=np.int16)
+    C.call("sb_host_bank_render_pcm16_on_stream", arr, len(arr), n, float(sr), 32767.0, out.ctypes.data_as(ctypes.c_void_p),
+           None, ctypes.c_void_p(side.cuda_stream))
+    np.testing.assert_array_equal(out, alone)
+
+
 def test_config5_share_full_size_properties(cuda):
     """BASELINE config 5, one GPU's share (8192 FM voices x 10 s @ 48 kHz) at FULL size.
     The serial oracle cannot cover 3.9e9 voice-samples in a test, so: (1) 48 voices drawn from

@@ -75,3 +75,17 @@ def test_noalloc_prefix_refuses_more_than_its_builtin_scratch_holds(cuda):
     # an empty range is fine and does nothing
     C.call("sb_fm_prefix_f64_noalloc", D.ptr(tiny), D.ptr(tb.dev()), tb.nsegs, 0, 0, D.ptr(carry),
            D.ptr(out), D.stream())
+
+
+def test_noalloc_prefix_at_exactly_its_limit(cuda):
+    """The largest call the built-in scratch allows (16,777,216 samples: every one of its 8192
+    tile slots in use) gives the same sums as the allocating entry point."""
+    import torch
+    from synthesizer_b200 import _cabi as C, _device as D
+    tb = D.timebase_cyc(48000)
+    limit = C.lib.sb_fm_prefix_noalloc_max_count()
+    gen = torch.Generator(device="cpu").manual_seed(99)
+    lfo = (torch.rand(limit, generator=gen) * 2 - 1).to(D.device())
+    want, wc = _prefix("alloc", lfo, tb, 0, 0.0)
+    got, gc = _prefix("noalloc", lfo, tb, 0, 0.0)
+    assert np.array_equal(got, want) and gc == wc

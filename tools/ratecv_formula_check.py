@@ -49,11 +49,38 @@ def fast(a, nch, inr, outr):
     return (qf + fix).astype(np.int16).reshape(-1)
 
 
+def fast_magic(a, nch, inr, outr):
+    """The kernel's form for reduced output rates <= 16384: the same closed-form (c, d), and
+    cur + floor((prev-cur)*d/outr) by one widening multiply and a shift (invariant division)."""
+    g = math.gcd(inr, outr)
+    inr //= g
+    outr //= g
+    assert outr <= 16384
+    a = a.reshape(-1, nch).astype(np.int64)
+    nout = ((len(a) - 1) * outr) // inr + 1
+    j = np.arange(nout, dtype=np.int64)
+    c = -((-j * inr) // outr)
+    d = c * outr - j * inr
+    cur = a[c]
+    prev = np.where((c > 0)[:, None], a[np.maximum(c - 1, 0)], 0)
+    L = 0
+    while (1 << L) < outr:
+        L += 1
+    msh = 31 + L
+    mg = ((1 << msh) + outr - 1) // outr
+    assert mg < 2 ** 32
+    n = ((prev - cur) * d[:, None] + 65536 * outr)
+    assert (n >= 0).all() and (n < 2 ** 31).all()
+    q = (n.astype(object) * mg) >> msh                       # 64-bit product in the kernel
+    return (cur + q.astype(np.int64) - 65536).astype(np.int16).reshape(-1)
+
+
 def main():
     rng = np.random.default_rng(1)
     pairs = [(44100, 48000), (48000, 44100), (22050, 48000), (48000, 8000), (44100, 44101), (8000, 96000),
              (11025, 44100), (1, 3), (3, 1), (2000000, 1999999), (1999999, 2000000), (7, 2097151), (2097151, 7),
-             (96000, 44100), (65537, 65536), (131071, 131072), (1048573, 1048576)]
+             (96000, 44100), (65537, 65536), (131071, 131072), (1048573, 1048576), (32000, 48000), (48000, 16383),
+             (16385, 16384), (12345, 16381), (44100, 22050), (5, 16384)]
     for inr, outr in pairs:
         for nch in (1, 2):
             for kind in range(3):
@@ -69,6 +96,10 @@ def main():
                 assert len(want) == len(got), (inr, outr, len(want), len(got))
                 bad = np.flatnonzero(want != got)
                 assert bad.size == 0, (inr, outr, nch, kind, bad[:5], want[bad[:5]], got[bad[:5]])
+                if outr // math.gcd(inr, outr) <= 16384:
+                    got = fast_magic(a, nch, inr, outr)
+                    bad = np.flatnonzero(want != got)
+                    assert bad.size == 0, ("magic", inr, outr, nch, kind, bad[:5], want[bad[:5]], got[bad[:5]])
     print("ok: %d rate pairs" % len(pairs))
 
 
