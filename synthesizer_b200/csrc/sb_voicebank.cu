@@ -479,9 +479,6 @@ __device__ __noinline__ double exact_time_at(const sb_time_seg *segs, int nsegs,
 }
 
 struct FastCtx;
-template <int MW>
-__device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t n, double fm, double phm, double mpw,
-                                        double gd, float2 (&sv)[kFItems / 2], double &tot);
 
 struct FastCtx {
     const sb_time_seg *s_cyc;
@@ -495,54 +492,10 @@ struct FastCtx {
 };
 
 // The 16 values of a piecewise-linear modulator over a lane's run, exactly as upstream computes
-// them; sv = the FM increments gd*value in fp32 (frame pairs (q, q+H)), tot = the sum of the values.
-// Square / Pulse values are +-1: their increments need no fp64 -> fp32 conversion.
-template <int MW>
-__device__ __forceinline__ void lfo_run(const FastCtx &ctx, double Tc0, int64_t n, double fm, double phm, double mpw,
-                                        double gd, float2 (&sv)[kFItems / 2], double &tot)
-{
-    constexpr int H = kFItems / 2;
-    const float gdf = (float)gd;
-    tot = 0.0;
-    if (MW == SB_WAVE_TRIANGLE && !ctx.cstraddle) {
-        // A triangle has no edges: its value does not hinge on the last bits of the phase, so
-        // only the run's first phase is formed the way upstream forms it and the other 15 step
-        // from it (phase fraction += step, wrapped), which halves the fp64 work per sample.
-        // The difference from upstream's own rounding of each phase is ~1e-16 of the value.
-        const double x0 = __dadd_rn(__dadd_rn(__dmul_rn(Tc0, fm), phm), 0.75);
-        double f = x0 - floor_nonneg(x0);                                   // in [0, 1)
-        const double w = fm * ctx.cstep;                                    // cycles per frame (< 1)
-#pragma unroll
-        for (int j = 0; j < kFItems; j++) {
-            const double v = fma(4.0, fabs(f - 0.5), -1.0);
-            tot += v;
-            const float inc = (float)(gd * v);
-            if (j < H) sv[j].x = inc; else sv[j - H].y = inc;
-            f += w;
-            if (f >= 1.0) f -= 1.0;
-        }
-        return;
-    }
-#pragma unroll
-    for (int j = 0; j < kFItems; j++) {
-        double t;
-        if (!ctx.cstraddle) {
-            t = __dadd_rn(Tc0, __dmul_rn((double)j, ctx.cstep));          // exact inside a time-base segment
-        } else {
-            TimeCursor c;
-            c.seek(ctx.s_cyc, ctx.nsegs_cyc, n + j);
-            t = c.at(n + j);
-        }
-        const double v = lfo_shape_exact(MW, t, fm, phm, mpw);
-        tot += v;
-        const float inc = (MW == SB_WAVE_SQUARE || MW == SB_WAVE_PULSE) ? (v > 0.0 ? gdf : -gdf) : (float)(gd * v);
-        if (j < H) sv[j].x = inc; else sv[j - H].y = inc;
-    }
-}
-
-// The per-sample evaluation as a real call (one body, the waveform chosen at run time): only runs
-// that pass an edge or a kink of the modulator come here, and inlined into every carrier's loop
-// the four waveforms' copies made up most of the part-2 kernel's code.
+// them (v[] = the FM increments gd*value in fp32, frame pairs (q, q+H); tot = the sum of the values),
+// as a real call (one body, the waveform chosen at run time): only runs that pass an edge or a kink
+// of the modulator come here, and inlined into every carrier's loop the four waveforms' copies made
+// up most of the part-2 kernel's code.
 struct LfoRun {
     float2 v[kFItems / 2];
     double tot;
@@ -552,17 +505,38 @@ __device__ __noinline__ LfoRun lfo_run_slow(const int mwave, const sb_time_seg *
                                             const double cstep, const bool cstraddle, const double Tc0, const int64_t n,
                                             const double fm, const double phm, const double mpw, const double gd)
 {
-    FastCtx ctx;
-    ctx.s_cyc = s_cyc;
-    ctx.nsegs_cyc = nsegs_cyc;
-    ctx.cstep = cstep;
-    ctx.cstraddle = cstraddle;
+    // (a rolled loop on purpose: this is the uncommon path, and its code must stay small - a bank of
+    // many kinds of voices otherwise keeps more code in flight than the instruction cache holds)
+    constexpr int H = kFItems / 2;
     LfoRun r;
-    switch (mwave) {
-    case SB_WAVE_TRIANGLE: lfo_run<SB_WAVE_TRIANGLE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
-    case SB_WAVE_SQUARE: lfo_run<SB_WAVE_SQUARE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
-    case SB_WAVE_SAWTOOTH: lfo_run<SB_WAVE_SAWTOOTH>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
-    default: lfo_run<SB_WAVE_PULSE>(ctx, Tc0, n, fm, phm, mpw, gd, r.v, r.tot); break;
+    r.tot = 0.0;
+    if (mwave == SB_WAVE_TRIANGLE && !cstraddle) {
+        // A triangle has no edges: its value does not hinge on the last bits of the phase, so only
+        // the run's first phase is formed the way upstream forms it and the other 15 step from it
+        // (phase fraction += step, wrapped), which halves the fp64 work per sample.  The difference
+        // from upstream's own rounding of each phase is ~1e-16 of the value.
+        const double x0 = __dadd_rn(__dadd_rn(__dmul_rn(Tc0, fm), phm), 0.75);
+        double f = x0 - floor_nonneg(x0);                                   // in [0, 1)
+        const double w = fm * cstep;                                        // cycles per frame (< 1)
+#pragma unroll
+        for (int j = 0; j < kFItems; j++) {
+            const double v = fma(4.0, fabs(f - 0.5), -1.0);
+            r.tot += v;
+            const float inc = (float)(gd * v);
+            if (j < H) r.v[j].x = inc; else r.v[j - H].y = inc;
+            f += w;
+            if (f >= 1.0) f -= 1.0;
+        }
+        return r;
+    }
+#pragma unroll 1
+    for (int j = 0; j < kFItems; j++) {
+        const double t = cstraddle ? exact_time_at(s_cyc, nsegs_cyc, n + j)
+                                   : __dadd_rn(Tc0, __dmul_rn((double)j, cstep));   // exact inside a time-base segment
+        const double v = lfo_shape_exact(mwave, t, fm, phm, mpw);
+        r.tot += v;
+        const float inc = (float)(gd * v);
+        if (j < H) r.v[j].x = inc; else r.v[j - H].y = inc;
     }
     return r;
 }
