@@ -24,19 +24,28 @@
 //          phase and re-evaluate the few samples within a guard band of an edge exactly in fp64.
 //
 //  FAST (2) the same carriers with a Triangle / Square / Sawtooth / Pulse modulator
-//          (bank_fast_kernel<2>): the modulator's values are evaluated exactly per sample; the
-//          FM sum ahead of a run is a per-512-frame tile prefix from a pre-pass
-//          (bank_lfo_tile_kernel, bank_lfo_prefix_kernel) plus an fp64 warp scan.
+//          (bank_fast_kernel<2>).  Between its edges and kinks such a modulator is a straight line:
+//          a run of 16 frames that stays clear of them (tested on an integer phase, with a guard
+//          band) needs one exactly formed phase - increments, half-run sum and the running sum
+//          ahead of the lane are closed forms.  Runs that are not clear evaluate the 16 values
+//          exactly as upstream does (lfo_run_slow) and scan the lanes' totals in fp64.  The FM sum
+//          ahead of a sub-tile is a per-512-frame tile prefix from a pre-pass (bank_lfo_tile_kernel:
+//          a tile as one line, or two around a single edge settled by exact values, else by runs;
+//          bank_lfo_prefix_kernel).
 //
 //  GENERIC (0) anything else (FM gain above kFastMaxFmGain, carriers or modulators with a
 //          negative start phase or frequency).  Phase arithmetic per sample in explicitly
 //          rounded fp64, FM prefix by fp64 warp scan with a running carry that starts from
 //          per-(voice, span) sums computed by a pre-pass.
 //
-// Order of kernels in a render: bank_prepare_kernel (per-voice constants and tables),
-// bank_sort_kernel (each group's voices by kind), the tile pre-pass if any class-2 voice,
-// bank_fast_kernel<0> (writes the partial mixes), <1>, <2> and the generic kernels (add into
-// them) as far as the bank has such voices, bank_fold_kernel.
+// Order of kernels in a render: bank_prepare_kernel (per-voice constants and tables), for banks
+// of more than one full group bank_key_hist / scan / scatter (the voices sorted by kind across
+// the bank, so that a group - a slice of 64 of that order - holds one or two kinds),
+// bank_sort_kernel (each group's voices by kernel part and kind), the tile pre-pass if any
+// class-2 voice, then bank_fast_kernel<0>, <1>, <2> and the generic kernels as far as the bank has
+// such voices (the first one launched writes the per-group partial mixes, the others add into
+// them), bank_fold_kernel.  <1> and <2> walk their grid group-first when their voices are of one
+// or two kinds (counted on the device while sorting), span-first otherwise; <0> is always span-first.
 #include "sb_common.cuh"
 
 namespace sb {
