@@ -132,6 +132,12 @@ def _s(ns, seed, frames, channels=1, rate=SR, lo=-20000, hi=20000):
     return ns.Sample.from_raw_frames(_pcm(seed, frames * channels, lo, hi).tobytes(), 2, rate, channels)
 
 
+def _s24(ns, seed, frames, channels=1, rate=SR):
+    v = np.random.default_rng(seed).integers(-(1 << 23), 1 << 23, frames * channels).astype(np.int64) & 0xFFFFFF
+    raw = np.stack([v & 0xFF, (v >> 8) & 0xFF, (v >> 16) & 0xFF], axis=1).astype(np.uint8).tobytes()
+    return ns.Sample.from_raw_frames(raw, 3, rate, channels)
+
+
 # name -> builder(ns) -> Sample.  Output: the sample's frames (bytes) + rate, width, channels.
 def _sample_cases():
     c = {}
@@ -172,6 +178,11 @@ def _sample_cases():
     c["smp_modulate_amp_sample"] = lambda ns: _s(ns, 12, 4800).modulate_amp(
         ns.Sample.from_raw_frames(np.array([0, 30, 70, 100, -70], dtype="<i2").tobytes(), 2, SR, 1))
     c["smp_stereo_mix"] = lambda ns: _s(ns, 13, 3000, 1).stereo_mix(_s(ns, 14, 2000, 1), "R", 0.7, 0.01)
+    # 24-bit frames (audioop size 3)
+    c["smp24_amplify"] = lambda ns: _s24(ns, 15, 3000).amplify(1.731)
+    c["smp24_mix_at"] = lambda ns: _s24(ns, 15, 4000).mix_at(0.03, _s24(ns, 16, 3000))
+    c["smp24_resample_stereo"] = lambda ns: _s24(ns, 15, 2400, 2).resample(44100)
+    c["smp24_make_16bit"] = lambda ns: _s24(ns, 15, 3000).make_16bit()
     # float -> PCM (K1), through both entry points
     c["smp_from_oscillator"] = lambda ns: ns.Sample.from_oscillator(ns.o.Sine(440.0, 0.9, samplerate=SR), 0.05)
     c["smp_from_osc_block"] = lambda ns: ns.Sample.from_osc_block(

@@ -32,6 +32,12 @@ if has ncu_pcm; then
   $NCU -k regex:'fadeout' -s 2 -c 1 -o $OUT/${TAG}_fadeout -f python tools/pcm_target.py fadeout > $OUT/${TAG}_pcm_fade.log 2>&1
   echo "ncu_pcm done"
 fi
+if has mixed; then
+  # BASELINE config 3's "mixed waveforms" bank (5 x 5 kinds): who takes the time
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file $OUT/${TAG}_mixed_launches.csv \
+    python tools/class_bank.py 9 0 > $OUT/${TAG}_mixed_ncu.log 2>&1; echo "mixed launches rc=$?"
+  $NCU -k regex:'bank_fast_kernel<.int.2>' -s 2 -c 1 -o $OUT/${TAG}_mixed_fast2 -f python tools/class_bank.py 9 0 > $OUT/${TAG}_cb90.log 2>&1
+fi
 if has extra; then
   python bench_extra.py > $OUT/${TAG}_extra.jsonl 2> $OUT/${TAG}_extra.err; echo "extra rc=$?"
 fi
