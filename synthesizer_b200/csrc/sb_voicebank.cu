@@ -174,8 +174,10 @@ struct BankArgs {
                           // run one or two instantiations of the voice loop (a bank of mixed kinds otherwise
                           // walks all of the kernel's code in every CTA and falls out of the instruction cache)
     int *key_hist;        // [kSortKeys][ceil(nvoices / kSortBlock)] counts, then their exclusive scan
-    int *part_kinds;      // [3]: how many kinds of voices each kernel part holds (bank_key_scan_kernel; 0 when the
-                          // bank is not sorted): a part of one or two kinds walks its grid group-first
+    int *part_kinds;      // [64]: [0..2] how many kinds of voices each kernel part holds (bank_key_scan_kernel; 0
+                          // when the bank is not sorted), then the unit queues of parts 1 and 2, one per kind
+                          // (kQ* below): a kind's groups, and a counter its CTAs draw (group, span block) units from
+    int sm_count;
     int *order;           // [3][nvoices]: per kernel part, each group's voices of that part sorted by kind
                           // (bank_sort_kernel); entry = voice index, the group's slice starts at its first voice
     int *kind_end;        // [ngroups][3][kFastKinds]: end position of each kind in the group's sorted slice
@@ -1043,6 +1045,10 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
 // of 256 voices, one scan over (key, block), scatter by stable rank within the block.
 constexpr int kSortKeys = kFastKinds + 1;          // the fast kinds, then the generic voices
 constexpr int kSortBlock = 256;
+// unit queues in part_kinds[]: per part the total of (group, span block) units, per kind the first
+// group it owns, how many, and the draw counter.  A group belongs to the kind of its first voice of
+// the part (the bank is sorted by kind, so a kind's groups are consecutive).
+constexpr int kQUnits = 4, kQFirst = 8, kQGroups = 24, kQDrawn = 40;
 __device__ __forceinline__ int sort_key_of(int flags) { return (flags & FV_FAST) ? fast_kind_of(flags) : kFastKinds; }
 
 __global__ void __launch_bounds__(kSortBlock)
@@ -1105,6 +1111,43 @@ bank_key_scan_kernel(BankArgs a, int nblocks)
         __syncthreads();
         if (threadIdx.x == 1023) s_carry = carry + s_warp[warp] + inc;
         __syncthreads();
+    }
+    // the unit queues: key_hist[k * nblocks] is now where kind k starts in the sorted bank
+    if (warp == 0) {
+        const int k = lane, vpg = a.voices_per_group;
+        const int nblk = (a.fast_nspans + kFastWarps - 1) / kFastWarps;
+        int units = 0, part = -1;
+        if (k < kFastKinds) {
+            part = fast_kind_part(k);
+            const int pfirst = part == 0 ? 0 : (part == 1 ? 4 : 10);
+            const int ps = a.key_hist[pfirst * nblocks];
+            const int lo = a.key_hist[k * nblocks], hi = a.key_hist[(k + 1) * nblocks];   // k + 1 <= kFastKinds: the generic key
+            int g_lo = 0, ng = 0;
+            if (hi > lo) {
+                g_lo = (lo == ps) ? ps / vpg : (lo + vpg - 1) / vpg;
+                ng = (hi + vpg - 1) / vpg - g_lo;
+            }
+            // the part that writes the partial mixes covers every group of the bank (zeros where it has no voice)
+            const unsigned ne = __ballot_sync(0x7fffu, hi > lo) & (part == 1 ? 0x3f0u : (part == 2 ? 0x7c00u : 0xfu));
+            if (part == a.first_part) {
+                if (ne == 0) {
+                    if (k == pfirst) ng = a.ngroups;
+                } else {
+                    if (k == __ffs(ne) - 1) { ng += g_lo; g_lo = 0; }
+                    if (k == 31 - __clz(ne)) ng = a.ngroups - g_lo;
+                }
+            }
+            a.part_kinds[kQFirst + k] = g_lo;
+            a.part_kinds[kQGroups + k] = ng;
+            a.part_kinds[kQDrawn + k] = 0;
+            units = ng * nblk;
+        }
+        for (int pt = 0; pt < 3; pt++) {
+            int u = part == pt ? units : 0;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) u += __shfl_xor_sync(0xffffffffu, u, d);
+            if (lane == 0) a.part_kinds[kQUnits + pt] = u;
+        }
     }
 }
 
@@ -1204,11 +1247,49 @@ bank_fast_kernel(BankArgs a)
     if (PART == 0) {
         group = blockIdx.y;
         span_block = blockIdx.x;
-    } else {
+    } else if (a.nvoices <= kMaxVoicesPerGroup) {
         const int nblk = (a.fast_nspans + kFastWarps - 1) / kFastWarps;
-        const bool group_first = a.nvoices > kMaxVoicesPerGroup && a.part_kinds[PART] <= 2;
-        group = group_first ? (int)(blockIdx.x % (unsigned)a.ngroups) : (int)(blockIdx.x / (unsigned)nblk);
-        span_block = group_first ? (int)(blockIdx.x / (unsigned)a.ngroups) : (int)(blockIdx.x % (unsigned)nblk);
+        group = (int)(blockIdx.x / (unsigned)nblk);
+        span_block = (int)(blockIdx.x % (unsigned)nblk);
+    } else {
+        // a sorted bank: the CTA draws its unit from the queue of the kind its SM is given (the SMs
+        // are shared out over the part's kinds in proportion to their units), moving on to the next
+        // kind when that one is drained - so an SM runs one kind's loop at a time, whatever the
+        // mix of kinds in the bank.  Units of a kind are drawn group-first.
+        __shared__ int s_unit[2];
+        if (threadIdx.x == 0) {
+            const int *q = a.part_kinds;
+            const int total = q[kQUnits + PART];
+            int g = -1, sb = 0;
+            if ((int)blockIdx.x < total) {
+                constexpr int kfirst = PART == 1 ? 4 : 10, nk = PART == 1 ? 6 : 5;
+                const int nblk = (a.fast_nspans + kFastWarps - 1) / kFastWarps;
+                unsigned smid;
+                asm("mov.u32 %0, %%smid;" : "=r"(smid));
+                const int64_t target = ((int64_t)(smid % (unsigned)a.sm_count) * 2 + 1) * total / (2 * a.sm_count);
+                int start = 0, cum = 0;
+                for (int t = 0; t < nk; t++) {
+                    const int u = q[kQGroups + kfirst + t] * nblk;
+                    if (target >= cum && target < cum + u) start = t;
+                    cum += u;
+                }
+                for (int t = 0; t < nk && g < 0; t++) {
+                    const int k = kfirst + (start + t) % nk, ng = q[kQGroups + k];
+                    if (ng == 0) continue;
+                    const int u = atomicAdd(a.part_kinds + kQDrawn + k, 1);
+                    if (u < ng * nblk) {
+                        g = q[kQFirst + k] + u % ng;
+                        sb = u / ng;
+                    }
+                }
+            }
+            s_unit[0] = g;
+            s_unit[1] = sb;
+        }
+        __syncthreads();
+        group = s_unit[0];
+        span_block = s_unit[1];
+        if (group < 0) return;                             // block-uniform: the grid covers every group
     }
     const int v_begin = group * a.voices_per_group;
     int nv = a.nvoices - v_begin;
@@ -1897,6 +1978,22 @@ void bank_count_classes(const sb_voice *voices, int nvoices, double samplerate, 
 }
 }  // namespace sb
 
+namespace sb {
+// SMs of the current device (asked once per device)
+static int bank_sm_count()
+{
+    static int cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) return -1;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+}  // namespace sb
+
 extern "C" int sb_bank_profile_events(void *start_event, void *stop_event)
 {
     g_prof_start = (cudaEvent_t)start_event;
@@ -2034,6 +2131,8 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.perm = (int *)(scratch + bank_off_perm(plan));
     a.key_hist = (int *)(scratch + bank_off_keyhist(plan));
     a.part_kinds = (int *)(scratch + bank_off_partkinds(plan));
+    a.sm_count = bank_sm_count();
+    SB_REQUIRE(a.sm_count >= 1, "sb_bank_render_f32: no device");
     a.kind_end = (int *)(scratch + bank_off_kindend(plan));
     a.lfo_prefix = (double *)(scratch + bank_off_lfo(plan));
     a.lfo_nprefix = (int)bank_lfo_nprefix(plan);
@@ -2044,6 +2143,10 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     a.fast_span_len = plan->fast_span_len;
     a.out = (plan->ngroups > 1) ? partial_dev : mix_dev;
     a.out_stride = (plan->frames * 2 + 3) / 4 * 4;
+
+    // a part no voice belongs to is not launched; the first one that is writes the partial mixes
+    const bool run0 = plan->smooth_voices != 0 || (plan->edged_voices == 0 && plan->scan_voices == 0);
+    a.first_part = run0 ? 0 : (plan->edged_voices != 0 ? 1 : 2);
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
@@ -2089,9 +2192,6 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
         SB_REQUIRE(nctas < 0x7fffffff, "sb_bank_render_f32: too many (group, span) units");
         const dim3 grid0((unsigned)((a.fast_nspans + kFastWarps - 1) / kFastWarps), (unsigned)a.ngroups);
         const unsigned grid = (unsigned)nctas;
-        // a part no voice belongs to is not launched; the first one that is writes the partial mixes
-        const bool run0 = plan->smooth_voices != 0 || (plan->edged_voices == 0 && plan->scan_voices == 0);
-        a.first_part = run0 ? 0 : (plan->edged_voices != 0 ? 1 : 2);
         if (run0) {
             if (g_prof_start) SB_CUDA_CHECK(cudaEventRecord(g_prof_start, s));
             bank_fast_kernel<0><<<grid0, kFastWarps * 32, smem, s>>>(a);
