@@ -125,7 +125,8 @@ struct alignas(16) FastVoice {
     float a_slope, d_slope, r_slope, sl;
     float amp_extra;
     float bL, bR;            // c_bias*gain
-    float pw;                // Pulse carriers: the (clamped) pulse width
+    float low_limit;         // edged carriers: a run whose first frame's unreduced phase (cycles) is not above
+                             // this is evaluated exactly throughout (its phases might be negative)
 };
 static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
 // FV_SCAN voices have no use for `ini` and `half`; a Pulse modulator's (clamped) pulse width is
@@ -309,7 +310,12 @@ __global__ void bank_prepare_kernel(BankArgs a)
         F.flags = 0;
         F.tab_row = v * a.nsegs_rad;
         F.lt_row = v * kLaneTab;
-        F.pw = (float)clamp_pulsewidth((double)V.c_pw);
+        // the phase cannot fall by more than this over a run: kFItems FM increments of at most |gd| each
+        // (unit-amplitude modulator shapes), and the carrier's own steps should its frequency be negative
+        F.low_limit = (float)((double)kFItems * (fabs(gd) + fmax(0.0, -f0b * inc_c)) + 1.0 / 512.0);
+        // ... and never falls at all where the FM index is below one (every frame's phase increment
+        // f0b*inc + gd*value is positive: the phase stays at or above the start phase, itself >= 0)
+        if (fabs(gd) <= 0.999 * f0b * inc_c) F.low_limit = -1.0f;
         F.pw64 = clamp_pulsewidth((double)V.c_pw);
         F.mod = make_double2(fm, pcm);
         F.car = make_double2(f0b, phase0_of(V.c_wave, V.c_phase));
@@ -489,6 +495,14 @@ __device__ __noinline__ double exact_time_at(const sb_time_seg *segs, int nsegs,
     return c.at(k);
 }
 
+#ifdef SB_CTA_TRACE
+// debugging build only (tools/cta_trace.py): start / end time, SM and unit of every warp of the fast
+// kernels, and how many times it called the edged carriers' fix-up pass / took it for a whole run
+constexpr int kTraceWarps = 1 << 16;
+__device__ unsigned long long g_cta_trace[3][kTraceWarps][4];
+__device__ unsigned int g_cta_fix[kTraceWarps][2];
+#endif
+
 struct FastCtx;
 
 struct FastCtx {
@@ -629,7 +643,13 @@ __device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &c
     const double fm = F.mod.x, phm = F.mod.y, gd = F.gd;
     const int lane = threadIdx.x & 31;
     const LfoLine L = lfo_line(mwave, Tc0, fm, phm, ctx.cstep, __float_as_uint(F.ini.x), __float_as_uint(F.ini.y));
-    if (__all_sync(0xffffffffu, L.clear && !ctx.cstraddle)) {
+    // A run that crosses into the next segment of the time base keeps the line too: the step changes
+    // by at most half an ulp of the time, which over a sub-tile moves the phase by < 1e-7 cycles while
+    // the time is below 128 s (the guard is 1e-6).  This matters at the start of a render, where the
+    // time doubles - a new segment - every few frames: the first span's warps otherwise take the exact
+    // path in half their sub-tiles (2.8 ms for one warp, against 0.34 ms for the others).
+    const bool seam = ctx.cstraddle && !(Tc0 < 128.0);
+    if (__all_sync(0xffffffffu, L.clear && !seam)) {
         // the whole sub-tile is one straight line v_i = v0 + (i - m)*dv, m = this lane's first frame:
         // sum_{i<m} v_i = m*v0 - dv*m(m+1)/2
         const double m = (double)(lane * kFItems);
@@ -972,10 +992,23 @@ __device__ __forceinline__ void edged_voice_run(const FastVoice &F, const double
     const double fr = B - __dadd_rn(__dadd_rn(B, M), -M);                      // [-0.5, 0.5]
     const uint32_t p0 = (uint32_t)__double2loint(__dadd_rn(fr * 4294967296.0, M));
     // while the (unreduced) phase may still be negative, Square's int() truncation is not the
-    // periodic rule: take the exact path for the whole run (only the first cycles of a voice)
-    const bool low = !(B > 16.0);
+    // periodic rule: take the exact path for the whole run (only the first frames of a voice:
+    // this used to be "the first 16 cycles", which made the first span of a low voice - all of
+    // its frames on the exact path - the kernel's critical path: 1.7 ms for one warp of a
+    // 3.3 ms kernel)
+    const bool low = !(B > (double)F.low_limit);
     const bool any = edged_pass<MODC, WAVE, RARE, FLAT, false>(F, env, lane8, n, ctx, p0, gbefore, sn, dl, sv, half_sum, low, accL2, accR2);
     if (any || low) {
+#ifdef SB_CTA_TRACE
+        {
+            const unsigned w = (blockIdx.y * gridDim.x + blockIdx.x) * kFastWarps + (threadIdx.x >> 5);
+            if (w < (unsigned)kTraceWarps) {
+                const unsigned act = __activemask();
+                if ((threadIdx.x & 31) == __ffs(act) - 1) atomicAdd(&g_cta_fix[w][0], 1u);
+                if (low) atomicAdd(&g_cta_fix[w][1], 1u);
+            }
+        }
+#endif
         const RunFix r = edged_fix<MODC, WAVE, RARE, FLAT>(&F, env, lane8, n, ctx, p0, gbefore, sn, dl, sv, half_sum, low);
 #pragma unroll
         for (int q = 0; q < H; q++) {
@@ -1319,6 +1352,10 @@ bank_fast_kernel(BankArgs a)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int span = span_block * kFastWarps + warp;
     if (span >= a.fast_nspans) return;                 // no block-wide sync after this point
+#ifdef SB_CTA_TRACE
+    unsigned long long trace_t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trace_t0));
+#endif
     double2 *s_anc = s_anc_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
     float2 *s_env = s_env_all + (size_t)warp * a.voices_per_group * kFastMaxSub;
 
@@ -1456,6 +1493,23 @@ bank_fast_kernel(BankArgs a)
             }
         }
     }
+#ifdef SB_CTA_TRACE
+    {
+        unsigned long long trace_t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trace_t1));
+        unsigned smid;
+        asm("mov.u32 %0, %%smid;" : "=r"(smid));
+        const unsigned w = (blockIdx.y * gridDim.x + blockIdx.x) * kFastWarps + warp;
+        if (lane == 0 && w < (unsigned)kTraceWarps) {
+            g_cta_trace[PART][w][0] = trace_t0;
+            g_cta_trace[PART][w][1] = trace_t1;
+            g_cta_trace[PART][w][2] = ((unsigned long long)group << 32) | (unsigned)span;
+            g_cta_trace[PART][w][3] = ((unsigned long long)nv << 32) | ((unsigned long long)(g_cta_fix[w][0] & 0xfffu) << 20) |
+                                      ((unsigned long long)(g_cta_fix[w][1] & 0xfffu) << 8) | (smid & 0xffu);
+            g_cta_fix[w][0] = g_cta_fix[w][1] = 0;
+        }
+    }
+#endif
 }
 
 __device__ __forceinline__ double warp_scan_incl(double v, int lane)
@@ -1993,6 +2047,21 @@ static int bank_sm_count()
     return cached[dev];
 }
 }  // namespace sb
+
+#ifdef SB_CTA_TRACE
+extern "C" int sb_debug_cta_trace(unsigned long long *host, int clear)
+{
+    if (clear) {
+        void *p = nullptr;
+        SB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_cta_trace));
+        SB_CUDA_CHECK(cudaMemset(p, 0, sizeof(g_cta_trace)));
+        return SB_OK;
+    }
+    SB_CUDA_CHECK(cudaDeviceSynchronize());
+    SB_CUDA_CHECK(cudaMemcpyFromSymbol(host, g_cta_trace, sizeof(g_cta_trace)));
+    return SB_OK;
+}
+#endif
 
 extern "C" int sb_bank_profile_events(void *start_event, void *stop_event)
 {

@@ -37,6 +37,7 @@ if has mixed; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file $OUT/${TAG}_mixed_launches.csv \
     python tools/class_bank.py 9 0 > $OUT/${TAG}_mixed_ncu.log 2>&1; echo "mixed launches rc=$?"
   $NCU -k regex:'bank_fast_kernel<.int.2>' -s 2 -c 1 -o $OUT/${TAG}_mixed_fast2 -f python tools/class_bank.py 9 0 > $OUT/${TAG}_cb90.log 2>&1
+  $NCU -k regex:'bank_fast_kernel<.int.1>' -s 2 -c 1 -o $OUT/${TAG}_mixed_fast1 -f python tools/class_bank.py 9 0 > $OUT/${TAG}_cb90b.log 2>&1
 fi
 if has extra; then
   python bench_extra.py > $OUT/${TAG}_extra.jsonl 2> $OUT/${TAG}_extra.err; echo "extra rc=$?"
