@@ -442,15 +442,28 @@ __device__ __forceinline__ float tri_shape(float cycles)
 }
 
 // ------------------------------------------------------------------ fast kernel
-// ADSR factor at absolute frame k, fp32 (the fast path's envelope; corners handled per sample)
-__device__ __forceinline__ float fast_env_at(const FastVoice &F, int64_t k)
+// The ADSR segment frame k lies in, as a line: the factor at k, its step per frame, and how many
+// frames from k the next segment starts (a sub-tile that holds an envelope corner walks these lines,
+// switching at the corner, instead of looking every sample up: a real call, made twice per run and
+// once more in the one lane whose run holds the corner)
+struct EnvLine {
+    float v, dv;
+    int left;
+};
+__device__ __noinline__ EnvLine fast_env_line(const FastVoice *Fp, int64_t k)
 {
-    if (k < F.n_a) return (float)k * F.a_slope;
-    if (k < F.n_d) return 1.0f + (float)(k - F.n_a) * F.d_slope;
-    if (k < F.n_s) return F.sl;
-    if (k < F.n_r) return F.sl + (float)(k - F.n_s) * F.r_slope;
-    if (k == F.n_r && (F.flags & FV_ENV_EXTRA)) return F.amp_extra;
-    return 0.0f;
+    const FastVoice &F = *Fp;
+    EnvLine r;
+    int64_t left = 0x7fffffff;
+    r.dv = 0.0f;
+    if (k < F.n_a) { r.v = (float)k * F.a_slope; r.dv = F.a_slope; left = F.n_a - k; }
+    else if (k < F.n_d) { r.v = 1.0f + (float)(k - F.n_a) * F.d_slope; r.dv = F.d_slope; left = F.n_d - k; }
+    else if (k < F.n_s) { r.v = F.sl; left = F.n_s - k; }
+    else if (k < F.n_r) { r.v = F.sl + (float)(k - F.n_s) * F.r_slope; r.dv = F.r_slope; left = F.n_r - k; }
+    else if (k == F.n_r && (F.flags & FV_ENV_EXTRA)) { r.v = F.amp_extra; left = 1; }
+    else r.v = 0.0f;
+    r.left = left > 0x7fffffff ? 0x7fffffff : (int)left;
+    return r;
 }
 
 // x mod 2*pi into [-pi, pi] without the FRND (XU pipe) that rint() costs: magic-number rounding
@@ -776,7 +789,15 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     const float e0 = fmaf(lane8, env.y, env.x);
     float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
     const float2 cstep = make_float2(stepk.x, stepk.y), nk2 = make_float2(stepk.z, stepk.w);
-    const float2 estep = make_float2(env.y, env.y);
+    float2 estep = make_float2(env.y, env.y);
+    int swx = 0x7fffffff, swy = 0x7fffffff;                // RARE: the step at which frame q / q+H enters a new ADSR segment
+    if (RARE && env.x == kEnvSlow) {
+        const EnvLine lx = fast_env_line(&F, n), ly = fast_env_line(&F, n + H);
+        e = make_float2(lx.v, ly.v);
+        estep = make_float2(lx.dv, ly.dv);
+        swx = lx.left;
+        swy = ly.left;
+    }
     float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
     if (FLAT) {
         const float2 ec = make_float2(env.x, env.x);
@@ -793,12 +814,8 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
             w.x = tri_shape(P.x);
             w.y = tri_shape(P.y);
         }
-        float2 ee = e;
+        const float2 ee = e;
         if (RARE) {
-            if (env.x == kEnvSlow) {
-                ee.x = fast_env_at(F, n + q);
-                ee.y = fast_env_at(F, n + q + H);
-            }
             accL2[q] = __ffma2_rn(ee, make_float2(F.bL, F.bL), accL2[q]);
             accR2[q] = __ffma2_rn(ee, make_float2(F.bR, F.bR), accR2[q]);
         }
@@ -814,6 +831,20 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
                 sn = __fadd2_rn(sn, dl);
             }
             if (!FLAT) e = __fadd2_rn(e, estep);
+            if (RARE) {
+                if (q + 1 == swx) {
+                    const EnvLine l = fast_env_line(&F, n + q + 1);
+                    e.x = l.v;
+                    estep.x = l.dv;
+                    swx = l.left > 0x7fffffff - H ? 0x7fffffff : q + 1 + l.left;
+                }
+                if (q + 1 == swy) {
+                    const EnvLine l = fast_env_line(&F, n + q + 1 + H);
+                    e.y = l.v;
+                    estep.y = l.dv;
+                    swy = l.left > 0x7fffffff - H ? 0x7fffffff : q + 1 + l.left;
+                }
+            }
         }
     }
 }
@@ -878,7 +909,15 @@ __device__ __forceinline__ bool edged_pass(const FastVoice &F, const float2 env,
     float2 run = make_float2(0.0f, half_sum);               // FM phase (cycles) ahead of frames (q, q+H)
     const float e0 = fmaf(lane8, env.y, env.x);
     float2 e = make_float2(e0, fmaf((float)H, env.y, e0));
-    const float2 estep = make_float2(env.y, env.y);
+    float2 estep = make_float2(env.y, env.y);
+    int swx = 0x7fffffff, swy = 0x7fffffff;                // RARE: the step at which frame q / q+H enters a new ADSR segment
+    if (RARE && env.x == kEnvSlow) {
+        const EnvLine lx = fast_env_line(&F, n), ly = fast_env_line(&F, n + H);
+        e = make_float2(lx.v, ly.v);
+        estep = make_float2(lx.dv, ly.dv);
+        swx = lx.left;
+        swy = ly.left;
+    }
     float2 aL2 = make_float2(gain.x, gain.y), aR2 = make_float2(gain.z, gain.w);
     if (FLAT) {                                             // constant envelope: folded into the gains
         const float2 ec = make_float2(env.x, env.x);
@@ -903,12 +942,8 @@ __device__ __forceinline__ bool edged_pass(const FastVoice &F, const float2 env,
                 d.y = exact_shape(WAVE, ctx, n + q + H, F.car.x, F.car.y, MOD ? gbefore + (double)run.y : 0.0, MOD, F.pw64) - w.y;
             w = d;
         }
-        float2 ee = e;
+        const float2 ee = e;
         if (RARE) {
-            if (env.x == kEnvSlow) {
-                ee.x = fast_env_at(F, n + q);
-                ee.y = fast_env_at(F, n + q + H);
-            }
             if (!FIX) {
                 accL2[q] = __ffma2_rn(ee, make_float2(F.bL, F.bL), accL2[q]);
                 accR2[q] = __ffma2_rn(ee, make_float2(F.bR, F.bR), accR2[q]);
@@ -926,6 +961,20 @@ __device__ __forceinline__ bool edged_pass(const FastVoice &F, const float2 env,
                 sn = __fadd2_rn(sn, dl);
             }
             if (!FLAT) e = __fadd2_rn(e, estep);
+            if (RARE) {
+                if (q + 1 == swx) {
+                    const EnvLine l = fast_env_line(&F, n + q + 1);
+                    e.x = l.v;
+                    estep.x = l.dv;
+                    swx = l.left > 0x7fffffff - H ? 0x7fffffff : q + 1 + l.left;
+                }
+                if (q + 1 == swy) {
+                    const EnvLine l = fast_env_line(&F, n + q + 1 + H);
+                    e.y = l.v;
+                    estep.y = l.dv;
+                    swy = l.left > 0x7fffffff - H ? 0x7fffffff : q + 1 + l.left;
+                }
+            }
         }
     }
     return any;
