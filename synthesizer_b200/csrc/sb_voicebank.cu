@@ -648,6 +648,53 @@ __device__ __forceinline__ LfoLine lfo_line(const int mwave, const double Tc0, c
     return L;
 }
 
+// A run that is not clear usually holds exactly one edge (or kink): two straight lines.  Where the
+// second one starts is estimated from the phase distance to the edge and settled by the exact values
+// of the two frames around it (an edge makes the value jump by 2; a Triangle's kink needs no
+// settling: the value is continuous there).  A real call: only the lanes whose run holds an edge
+// come here, a few per cent of the runs at LFO rates.
+struct LfoBreak {
+    double v1, dv1;      // the second line: value at frame js and step per frame
+    int js;              // first frame (1 .. kFItems-1) of the second line; 0: not one clean break
+};
+__device__ __noinline__ LfoBreak lfo_run_break(const FastVoice *Fp, const int mwave, const double Tc0, const double cstep,
+                                               const double v0, const double dv, const uint32_t d1, const uint32_t d2)
+{
+    const FastVoice &F = *Fp;
+    LfoBreak r;
+    r.js = 0;
+    r.v1 = r.dv1 = 0.0;
+    const double step32 = scan_m_step32(F), fm = F.mod.x, phm = F.mod.y;
+    const double reach = (double)(kFItems - 1) * step32;
+    const uint32_t dn = min(d1 - 1u, d2 - 1u) + 1u;                   // nearest edge strictly ahead (0 = a whole cycle away)
+    const uint32_t df = max(d1 - 1u, d2 - 1u) + 1u;
+    if (!(dn != 0u && step32 > 0.0 && reach < 2.0e9 && (d1 == d2 || (double)df > reach + 3.0 * kGuardLfo + step32))) return r;
+    int js = (int)ceil((double)dn / step32);                          // first frame at or past the edge
+    js = max(1, min(kFItems - 1, js));
+    bool ok = (mwave == SB_WAVE_TRIANGLE);
+    const double mpw = scan_m_pw64(F);
+#pragma unroll 1
+    for (int tries = 0; tries < 4 && !ok; tries++) {
+        const double ta = __dadd_rn(Tc0, __dmul_rn((double)(js - 1), cstep)), tb = __dadd_rn(Tc0, __dmul_rn((double)js, cstep));
+        const bool before_a = fabs(lfo_shape_exact(mwave, ta, fm, phm, mpw) - fma((double)(js - 1), dv, v0)) < 0.5;
+        const bool before_b = fabs(lfo_shape_exact(mwave, tb, fm, phm, mpw) - fma((double)js, dv, v0)) < 0.5;
+        if (before_a && !before_b) ok = true;
+        else if (!before_a) js--;                                      // the edge came earlier
+        else js++;                                                     // not yet
+        if (js < 1 || js > kFItems - 1) break;
+    }
+    if (!ok) return r;
+    const int rest = kFItems - js;
+    const double tj = __dadd_rn(Tc0, __dmul_rn((double)js, cstep));
+    const LfoLine L2 = lfo_line(mwave, tj, fm, phm, cstep, __float_as_uint(F.ini.x),
+                                (uint32_t)(long long)ceil((double)(rest - 1) * step32));
+    if (!L2.clear) return r;
+    r.js = js;
+    r.v1 = L2.v0;
+    r.dv1 = L2.dv;
+    return r;
+}
+
 __device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double Tc0, const int64_t n,
                                             float2 (&sv)[kFItems / 2], float &half_sum, double &before)
 {
@@ -673,21 +720,47 @@ __device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &c
         for (int q = 0; q < H; q++) sv[q] = __ffma2_rn(make_float2((float)q, (float)(q + H)), d2, s2);
         half_sum = fmaf((float)(H * (H - 1) / 2), ds, (float)H * s0);
     } else {
-        const LfoRun r = lfo_run_slow(mwave, ctx.s_cyc, ctx.nsegs_cyc, ctx.cstep, ctx.cstraddle, Tc0, n, fm, phm,
-                                      scan_m_pw64(F), gd);
-        half_sum = 0.0f;
-#pragma unroll
-        for (int q = 0; q < H; q++) {
-            sv[q] = r.v[q];
-            half_sum += r.v[q].x;
+        // some lane's run holds an edge: each lane its own line, or two lines with one break
+        const bool mine = L.clear && !seam;
+        LfoBreak bk;
+        bk.js = kFItems;
+        bk.v1 = bk.dv1 = 0.0;
+        if (!mine) {
+            bk.js = 0;
+            if (!ctx.cstraddle) bk = lfo_run_break(&F, mwave, Tc0, ctx.cstep, L.v0, L.dv, L.d1, L.d2);
         }
-        double incl = r.tot;
+        double tot;
+        if (__all_sync(0xffffffffu, bk.js != 0)) {
+            const int js = bk.js, rest = kFItems - js;
+            const float s0 = (float)(gd * L.v0), ds = (float)(gd * L.dv);
+            const float s1 = (float)(gd * bk.v1), ds1 = (float)(gd * bk.dv1);
+            half_sum = 0.0f;
+#pragma unroll
+            for (int q = 0; q < H; q++) {
+                sv[q].x = q < js ? fmaf((float)q, ds, s0) : fmaf((float)(q - js), ds1, s1);
+                sv[q].y = q + H < js ? fmaf((float)(q + H), ds, s0) : fmaf((float)(q + H - js), ds1, s1);
+                half_sum += sv[q].x;
+            }
+            tot = fma(0.5 * (double)js * (double)(js - 1), L.dv, (double)js * L.v0) +
+                  fma(0.5 * (double)rest * (double)(rest - 1), bk.dv1, (double)rest * bk.v1);
+        } else {
+            const LfoRun r = lfo_run_slow(mwave, ctx.s_cyc, ctx.nsegs_cyc, ctx.cstep, ctx.cstraddle, Tc0, n, fm, phm,
+                                          scan_m_pw64(F), gd);
+            half_sum = 0.0f;
+#pragma unroll
+            for (int q = 0; q < H; q++) {
+                sv[q] = r.v[q];
+                half_sum += r.v[q].x;
+            }
+            tot = r.tot;
+        }
+        double incl = tot;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const double o = __shfl_up_sync(0xffffffffu, incl, d);
             if (lane >= d) incl += o;
         }
-        before = incl - r.tot;
+        before = incl - tot;
     }
 }
 
