@@ -523,8 +523,6 @@ struct FastCtx {
     int nsegs_cyc;
     double cstep;            // cycles time base: step of the segment holding this lane's first frame
     bool cstraddle;          // ... and whether the lane's run crosses into the next segment
-    const double *lfo_row;   // FV_SCAN voices: modulator sums before this sub-tile, row stride lfo_rows
-    int64_t lfo_rows;
     const FmSeg *tab_seg;    // closed-form FM table, offset to this lane's time-base segment: row stride nsegs_rad
     const double2 *lt_lane;  // anchor -> lane rotation table, offset to this lane: row stride 32
 };
@@ -825,7 +823,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     if (MODC == 2) {
         double before;
         lfo_run_any(F, ctx, Tc0, n, sv, half_sum, before);
-        gbefore = F.gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + before);
+        gbefore = F.gd * (anc.x + before);                 // anc.x: the modulator's sum before this sub-tile (tile pre-pass)
         B += gbefore;
     }
     if (MODC == 1) {
@@ -1087,7 +1085,7 @@ __device__ __forceinline__ void edged_voice_run(const FastVoice &F, const double
     if (MODC == 2) {
         double before;
         lfo_run_any(F, ctx, Tc0, n, sv.v, half_sum, before);
-        gbefore = F.gd * (ctx.lfo_row[(int64_t)F.tab_row * ctx.lfo_rows] + before);
+        gbefore = F.gd * (anc.x + before);                 // anc.x: the modulator's sum before this sub-tile (tile pre-pass)
         B += gbefore;
     }
     if (MODC == 1) {
@@ -1179,7 +1177,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
         const FastVoice &F = s_fv[v];
         const float2 env = s_env[v * kFastMaxSub + s];
         if (env.x == kEnvSilent) continue;                                      // warp-uniform
-        const double2 anc = MOD == 1 ? s_anc[v * kFastMaxSub + s] : none;
+        const double2 anc = MOD != 0 ? s_anc[v * kFastMaxSub + s] : none;
         if constexpr (WAVE >= SB_WAVE_SQUARE) {
             if (env.x == kEnvSlow || (F.flags & FV_BIAS))
                 edged_voice_run<MOD, WAVE, true, false>(F, anc, env, Tc0, dstep, lane8, n, ctx, accL2, accR2);
@@ -1515,6 +1513,11 @@ bank_fast_kernel(BankArgs a)
                 else if (lo >= F.n_s && hi <= F.n_r) { r.x = F.sl + (float)(lo - F.n_s) * F.r_slope; r.y = F.r_slope; }
                 else r.x = kEnvSlow;
             }
+            // class-2 voices: the modulator's sum over all frames before this sub-tile, from the tile
+            // pre-pass's prefix table (read here, once per span, rather than from global memory in
+            // the middle of every run)
+            if (PART == 2)
+                anc.x = a.lfo_prefix[(int64_t)F.tab_row * a.lfo_rows + a.lfo_nprefix + span_begin / kFSub + s];
             s_anc[v * kFastMaxSub + s] = anc;
             s_env[v * kFastMaxSub + s] = r;
             if (sine_mod) anc = make_double2(fma(-anc.y, rot.y, anc.x * rot.x), fma(anc.x, rot.y, anc.y * rot.x));
@@ -1551,12 +1554,6 @@ bank_fast_kernel(BankArgs a)
                     ctx.cstep = c.step;
                     ctx.cstraddle = (n + kFItems >= c.next_start);
                 }
-            }
-            ctx.lfo_rows = 0;
-            ctx.lfo_row = nullptr;
-            if (PART == 2) {                            // tile row of this sub-tile in the modulator prefix table
-                ctx.lfo_rows = a.lfo_rows;
-                ctx.lfo_row = a.lfo_prefix + a.lfo_nprefix + (span_begin + (int64_t)s * kFSub) / kFSub;
             }
         }
         // keep both in registers for the voice loops (the compiler would otherwise recompute
