@@ -132,6 +132,8 @@ static_assert(sizeof(FastVoice) == 192, "FastVoice layout");
 // FV_SCAN voices have no use for `ini` and `half`; a Pulse modulator's (clamped) pulse width is
 // kept there in fp64
 __host__ __device__ inline double scan_m_pw64(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.half); }
+// ... then the size of the modulator's slope per frame at the nominal time step (Triangle 4w, Sawtooth 2w, else 0)
+__host__ __device__ inline double scan_m_slope(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.half.z); }
 // ... and in ini: the pulse width and the phase advance over a run of kFItems frames as integers
 // (2^32 = one cycle), then (two floats' room) the modulator's step per frame in those units as fp64
 __host__ __device__ inline double scan_m_step32(const FastVoice &F) { return *reinterpret_cast<const double *>(&F.ini.z); }
@@ -352,6 +354,8 @@ __global__ void bank_prepare_kernel(BankArgs a)
                 a.scan_list[2 + slot] = v;
                 F.tab_row = slot;
                 *reinterpret_cast<double *>(&F.half) = clamp_pulsewidth((double)V.m_pw);
+                *reinterpret_cast<double *>(&F.half.z) =
+                    (V.m_wave == SB_WAVE_TRIANGLE ? 4.0 : (V.m_wave == SB_WAVE_SAWTOOTH ? 2.0 : 0.0)) * (fm / a.samplerate);
                 F.flags |= FV_SCAN | ((V.m_wave & 7) << FV_MWAVE_SHIFT);
                 // the modulator on an integer phase (2^32 = one cycle), for the test whether a run
                 // of kFItems frames passes an edge or a kink of it: the width of a pulse, and how
@@ -582,8 +586,8 @@ __device__ __noinline__ LfoRun lfo_run_slow(const int mwave, const sb_time_seg *
 // one (the modulator's running sum from the sub-tile's first frame to the run's): the straight
 // line if every lane's run is clear - then that sum has a closed form too and no scan is needed -
 // else (the whole warp) the per-sample evaluation and an fp64 warp scan of the lanes' totals.
-__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double Tc0, const int64_t n,
-                                            float2 (&sv)[kFItems / 2], float &half_sum, double &before);
+__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double sub_line, const double Tc0,
+                                            const int64_t n, float2 (&sv)[kFItems / 2], float &half_sum, double &before);
 
 // ---- class-2 modulators: the run as a straight line wherever it is one
 // A Triangle / Square / Sawtooth / Pulse modulator is linear (or constant) between its edges and
@@ -693,13 +697,31 @@ __device__ __noinline__ LfoBreak lfo_run_break(const FastVoice *Fp, const int mw
     return r;
 }
 
-__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double Tc0, const int64_t n,
-                                            float2 (&sv)[kFItems / 2], float &half_sum, double &before)
+__device__ __forceinline__ void lfo_run_any(const FastVoice &F, const FastCtx &ctx, const double sub_line, const double Tc0,
+                                            const int64_t n, float2 (&sv)[kFItems / 2], float &half_sum, double &before)
 {
     constexpr int H = kFItems / 2;
     const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
     const double fm = F.mod.x, phm = F.mod.y, gd = F.gd;
     const int lane = threadIdx.x & 31;
+    if (sub_line == sub_line) {
+        // The whole sub-tile is one straight line (the span's set-up found it clear of the modulator's
+        // edges and kinks - at LFO rates nearly every sub-tile is): sub_line is its value at the
+        // sub-tile's first frame, plus 4 for a rising Triangle.  Nothing of the modulator is evaluated
+        // per run: v_i = vs + i*dv, sum_{i<m} v_i = m*vs + dv*m(m-1)/2, m = this lane's first frame.
+        const bool rising = sub_line > 2.0;
+        const double vs = rising ? sub_line - 4.0 : sub_line;
+        const double slope = scan_m_slope(F);
+        const double dv = (mwave == SB_WAVE_TRIANGLE && !rising) ? -slope : slope;
+        const double m = (double)(lane * kFItems);
+        before = fma(0.5 * dv, m * (m - 1.0), m * vs);
+        const float s0 = (float)(gd * fma(m, dv, vs)), ds = (float)(gd * dv);
+        const float2 s2 = make_float2(s0, s0), d2 = make_float2(ds, ds);
+#pragma unroll
+        for (int q = 0; q < H; q++) sv[q] = __ffma2_rn(make_float2((float)q, (float)(q + H)), d2, s2);
+        half_sum = fmaf((float)(H * (H - 1) / 2), ds, (float)H * s0);
+        return;
+    }
     const LfoLine L = lfo_line(mwave, Tc0, fm, phm, ctx.cstep, __float_as_uint(F.ini.x), __float_as_uint(F.ini.y));
     // A run that crosses into the next segment of the time base keeps the line too: the step changes
     // by at most half an ulp of the time, which over a sub-tile moves the phase by < 1e-7 cycles while
@@ -822,7 +844,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     float2 sv[kFItems / 2];                 // MODC 2: the FM increments gd*lfo of frames (q, q+H)
     if (MODC == 2) {
         double before;
-        lfo_run_any(F, ctx, Tc0, n, sv, half_sum, before);
+        lfo_run_any(F, ctx, anc.y, Tc0, n, sv, half_sum, before);
         gbefore = F.gd * (anc.x + before);                 // anc.x: the modulator's sum before this sub-tile (tile pre-pass)
         B += gbefore;
     }
@@ -1084,7 +1106,7 @@ __device__ __forceinline__ void edged_voice_run(const FastVoice &F, const double
     RunIncrements sv = {};
     if (MODC == 2) {
         double before;
-        lfo_run_any(F, ctx, Tc0, n, sv.v, half_sum, before);
+        lfo_run_any(F, ctx, anc.y, Tc0, n, sv.v, half_sum, before);
         gbefore = F.gd * (anc.x + before);                 // anc.x: the modulator's sum before this sub-tile (tile pre-pass)
         B += gbefore;
     }
@@ -1516,8 +1538,23 @@ bank_fast_kernel(BankArgs a)
             // class-2 voices: the modulator's sum over all frames before this sub-tile, from the tile
             // pre-pass's prefix table (read here, once per span, rather than from global memory in
             // the middle of every run)
-            if (PART == 2)
+            // ... and, where the whole sub-tile is clear of the modulator's edges and kinks, its value at
+            // the sub-tile's first frame (plus 4 for a rising Triangle; NaN: not clear - the runs look
+            // for themselves).  A seam of the time base inside the sub-tile is harmless while the time
+            // is small (see lfo_run_any).
+            if (PART == 2) {
                 anc.x = a.lfo_prefix[(int64_t)F.tab_row * a.lfo_rows + a.lfo_nprefix + span_begin / kFSub + s];
+                const int mwave = (F.flags >> FV_MWAVE_SHIFT) & 7;
+                TimeCursor c;
+                c.seek(s_cyc, a.nsegs_cyc, lo);
+                const double Ts = c.at(lo);
+                const bool seam = (hi >= c.next_start) && !(Ts < 128.0);
+                const double reach = (double)(kFSub - 1) * scan_m_step32(F);
+                const LfoLine L = lfo_line(mwave, Ts, F.mod.x, F.mod.y, c.step, __float_as_uint(F.ini.x),
+                                           reach < 3.0e9 ? (uint32_t)(long long)ceil(reach) : 0xffffffffu);
+                anc.y = (L.clear && !seam) ? ((mwave == SB_WAVE_TRIANGLE && L.dv > 0.0) ? L.v0 + 4.0 : L.v0)
+                                           : __longlong_as_double(0x7ff8000000000000ll);
+            }
             s_anc[v * kFastMaxSub + s] = anc;
             s_env[v * kFastMaxSub + s] = r;
             if (sine_mod) anc = make_double2(fma(-anc.y, rot.y, anc.x * rot.x), fma(anc.x, rot.y, anc.y * rot.x));
