@@ -293,6 +293,56 @@ def test_deep_fm_on_low_carriers(cuda, cw):
         assert err[~flips].max() < 0.9, "cw=%d f0=%g fm=%g depth=%g: %.3f LSB" % (cw, f0, fm, d, err[~flips].max())
 
 
+@pytest.mark.parametrize("cw", [2, 4])
+def test_deep_fm_pulls_an_edged_carrier_below_zero(cuda, cw):
+    """Square / Pulse carriers whose FM index is above one and whose modulator starts on its
+    negative half: the phase dips below zero in the first frames, where Square's int() is not the
+    periodic rule - those runs are evaluated exactly, and only those (the rest of the render is on
+    the integer-phase path)."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n = 48000, 48000
+    classes = {2: sb.Square, 4: sb.Pulse}
+    for f0, fm, d, mph in [(55.1, 5.3, 6.0, 0.6), (110.3, 2.1, 3.0, 0.75), (27.5, 40.3, 20.0, 0.55), (220.7, 1.3, 1.01, 0.5)]:
+        lfo = sb.Sine(fm, d, mph, samplerate=sr)
+        kw = dict(pulsewidth=0.3) if cw == 4 else {}
+        car = classes[cw](f0, 0.99, 0.0, 0.0, fm_lfo=lfo, samplerate=sr, **kw)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 1, (f0, fm, d)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, fm, d, mph, 0.0)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.0, 0.0, fm=m, pulsewidth=0.3)
+        flips = np.abs(got - want) > 1e-3
+        assert flips.sum() <= 3, (cw, f0, fm, d, int(flips.sum()), np.flatnonzero(flips)[:8])
+
+
+@pytest.mark.parametrize("mw", [1, 2, 3, 4])
+def test_piecewise_modulators_across_a_late_seam_of_the_time_base(cuda, mw):
+    """Class-2 voices rendered across t = 256 s, where the serial time base's step changes: past
+    128 s a run that crosses such a seam takes the exact per-sample path (before it, the straight
+    line holds across seams).  Modulators slow and fast enough to put one and several edges in a run."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr = 48000
+    start, n = 256 * sr - 3000, 6000
+    classes = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    for cw, f0, fm, d in [(0, 441.3, 6.1, 0.2), (3, 1103.7, 331.3, 0.03), (2, 97.3, 2903.1, 0.01), (1, 661.1, 0.37, 0.4)]:
+        mkw = dict(pulsewidth=0.37) if mw == 4 else {}
+        lfo = classes[mw](fm, d, 0.3, 0.0, samplerate=sr, **mkw)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 2, (cw, f0, fm, d)
+        got = bank.render(n, start=start).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(mw, start + n, sr, fm, d, 0.3, 0.0, pulsewidth=0.37)
+        want = co.osc(cw, start + n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)[start:]
+        err = np.abs(got - want) * 32767.0
+        flips = err > 100
+        assert flips.sum() <= (3 if cw >= 2 else 0), (cw, f0, fm, d, int(flips.sum()))
+        assert err[~flips].max() < 0.9, "mw=%d cw=%d f0=%g fm=%g: %.3f LSB" % (mw, cw, f0, fm, err[~flips].max())
+
+
 @pytest.mark.parametrize("mw", [1, 2, 3, 4])
 def test_piecewise_modulators_full_scale(cuda, mw):
     """Triangle / Square / Sawtooth / Pulse modulators on the fast path (class 2: exact fp64
