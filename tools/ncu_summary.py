@@ -52,6 +52,12 @@ def main():
     print("  stalls per issue:", ", ".join("%s %.2f" % (n, v) for v, n in sorted(set(stalls), reverse=True)[:8]))
 
     rows = page(rep, "source")
+    # a report of several kernels lists them one after the other ("Kernel Name" row, header row,
+    # instructions): the opcode mix below is of the LAST one (the kernel the capture was made for)
+    marks = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+    if len(marks) > 1:
+        rows = rows[marks[-1]:]
+        print("  (opcode mix of the report's last kernel: %s)" % rows[0][1])
     head = rows[1]
     col = {c: i for i, c in enumerate(head)}
     ins = []
