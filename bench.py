@@ -423,6 +423,10 @@ def run_ours(args):
         dist.barrier()
 
     for _ in range(max(3, args.warmup)):
+        # (the flush too: a rank's first native torch kernel loads torch's CUDA module, 8 ms of host
+        # time - paid inside the first timed step by whichever rank had not launched one yet, and
+        # shown there as the root's reduce waiting for that rank)
+        flush.add_(1)
         step_resident()
     sampler = ClockSampler(local)
     kev = [(new_event(), new_event()) for _ in range(args.steps)]
