@@ -181,6 +181,7 @@ struct BankArgs {
                           // when the bank is not sorted), then the unit queues of parts 1 and 2, one per kind
                           // (kQ* below): a kind's groups, and a counter its CTAs draw (group, span block) units from
     int sm_count;
+    int parts_mask;       // bit p: bank_fast_kernel<p> is launched in this render
     int *order;           // [3][nvoices]: per kernel part, each group's voices of that part sorted by kind
                           // (bank_sort_kernel); entry = voice index, the group's slice starts at its first voice
     int *kind_end;        // [ngroups][3][kFastKinds]: end position of each kind in the group's sorted slice
@@ -1390,18 +1391,16 @@ bank_sort_kernel(BankArgs a)
     }
 }
 
-// PART 0: Sine / Triangle carriers with no or a Sine modulator; writes the group's partial mix
-//         (zeros included).
-// PART 1: Square / Sawtooth / Pulse carriers with no or a Sine modulator; adds into it.
-// PART 2: any carrier with a Triangle / Square / Sawtooth / Pulse modulator; adds into it.  Separate
-// kernels rather than one so that the exact-fallback call and its register needs stay out of
-// the smooth carriers' loop (the headline path).
+// PART 0: Sine / Triangle carriers with no or a Sine modulator.
+// PART 1: Square / Sawtooth / Pulse carriers with no or a Sine modulator.
+// PART 2: any carrier with a Triangle / Square / Sawtooth / Pulse modulator.
+// Launched in this order; per group, the lowest part with voices in it writes the partial mix and
+// the others add to it.  Separate kernels rather than one so that the exact-fallback call and its
+// register needs stay out of the smooth carriers' loop (the headline path).
 template <int PART>
 __global__ void __launch_bounds__(kFastWarps * 32, PART != 0 ? 4 : FAST_MIN_BLOCKS)   // parts 1, 2: 128 registers
 bank_fast_kernel(BankArgs a)
 {
-    // the first kernel part launched writes the partial mixes (zeros included), the later ones add
-    const bool add = PART != 0 && a.first_part != PART;
     extern __shared__ __align__(16) unsigned char smem[];
     FastVoice *s_fv = reinterpret_cast<FastVoice *>(smem);
     const size_t nrec = (size_t)kFastWarps * a.voices_per_group * kFastMaxSub;
@@ -1473,7 +1472,19 @@ bank_fast_kernel(BankArgs a)
     // this part's voices of the group, already ranked by kind (bank_sort_kernel): where each kind ends
     const int *kend = a.kind_end + ((int64_t)group * 3 + PART) * kFastKinds;
     nv = kend[kFastKinds - 1];
-    if (add && nv == 0) return;                        // block-uniform: nothing to add
+    // Who writes the group's partial mix and who adds to it: the lowest part that has voices in the
+    // group writes (the parts are launched in order), the others add; a group without any voice
+    // of the fast classes is written as zeros by the first part launched (the generic kernel adds
+    // into it).  In a sorted bank a group's voices are nearly always of one part, so the partial
+    // mixes are written once and read by the fold alone.
+    const int *kall = a.kind_end + (int64_t)group * 3 * kFastKinds;
+    // (only the parts this render launches count: the plan's hints may have ruled one out)
+    const int n0 = (a.parts_mask & 1) ? kall[kFastKinds - 1] : 0, n1 = (a.parts_mask & 2) ? kall[2 * kFastKinds - 1] : 0;
+    const int n2 = (a.parts_mask & 4) ? kall[3 * kFastKinds - 1] : 0;
+    const int n_lower = (PART >= 1 ? n0 : 0) + (PART == 2 ? n1 : 0);
+    const int n_fast = n0 + n1 + n2;
+    const bool add = n_lower > 0;
+    if (nv == 0 && (n_fast > 0 || a.first_part != PART)) return;       // block-uniform
     if (threadIdx.x < kFastKinds) s_kind_end[threadIdx.x] = kend[threadIdx.x];
     for (int i = threadIdx.x; i < a.nsegs_rad; i += blockDim.x) s_rad[i] = a.tb_rad[i];
     for (int i = threadIdx.x; i < a.nsegs_cyc; i += blockDim.x) s_cyc[i] = a.tb_cyc[i];
@@ -2372,6 +2383,7 @@ extern "C" int sb_bank_render_f32(const sb_voice *voices_dev, const sb_bank_plan
     // a part no voice belongs to is not launched; the first one that is writes the partial mixes
     const bool run0 = plan->smooth_voices != 0 || (plan->edged_voices == 0 && plan->scan_voices == 0);
     a.first_part = run0 ? 0 : (plan->edged_voices != 0 ? 1 : 2);
+    a.parts_mask = (run0 ? 1 : 0) | (plan->edged_voices != 0 ? 2 : 0) | (plan->scan_voices != 0 ? 4 : 0);
 
     bank_prepare_kernel<<<(a.nvoices + 3) / 4, 128, 0, s>>>(a);       // one warp per voice
     SB_LAUNCH_CHECK();
