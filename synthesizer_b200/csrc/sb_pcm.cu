@@ -669,9 +669,16 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
                     const int khi = (int)max((int64_t)0, min((int64_t)live, s_l[q] - r0));
                     if (khi <= klo) continue;
                     const int16_t *p0 = s_p[q] + r0;
+                    if (klo == 0 && khi == kPer) {
+                        // the source covers the whole run (all but the threads at its two ends):
+                        // no per-sample tests
 #pragma unroll
-                    for (int k = 0; k < kPer; k++)
-                        if (k >= klo && k < khi) acc[k] = sat16(acc[k] + (int)p0[k]);
+                        for (int k = 0; k < kPer; k++) acc[k] = sat16(acc[k] + (int)p0[k]);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < kPer; k++)
+                            if (k >= klo && k < khi) acc[k] = sat16(acc[k] + (int)p0[k]);
+                    }
                 }
             }
         }
