@@ -348,8 +348,8 @@ int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *in_off_dev, 
  * overlapped span (saturation per step).  Source s is src_pool_dev[src_off[s] ..
  * src_off[s]+src_len[s]) (int16 sample units) mixed at dst sample index dst_off[s]; the
  * three arrays are device arrays of nsrc int64.  dst must already be long enough.
- * scratch_dev (sb_pcm16_mix_at_many_scratch_bytes; total_src_samples = sum of src_len) holds the
- * per-tile source lists; pass NULL to run without an index (each 2048-sample tile then scans
+ * scratch_dev (16-byte aligned; sb_pcm16_mix_at_many_scratch_bytes; total_src_samples = sum of
+ * src_len) holds the per-tile source lists (32 bytes per (source, tile) pair); pass NULL to run without an index (each 2048-sample tile then scans
  * the whole source list — fine for a few sources, slow for thousands).
  * Bad input cannot make the kernels write outside their buffers: a source with a negative dst_off
  * is left out, and per-tile lists that do not fit the scratch given are refused (those tiles

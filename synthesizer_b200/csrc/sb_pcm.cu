@@ -575,18 +575,31 @@ __global__ void mix_alloc_kernel(int *__restrict__ tile_count, int64_t ntiles, i
     }
 }
 
-__global__ void mix_fill_kernel(const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
+// A list entry carries the source's placement with its index: the apply kernel then goes from a
+// tile's list straight to the samples (one dependent round trip to global memory less per tile; the
+// kernel is bound by that chain of latencies, not by bandwidth).
+struct alignas(16) MixEntry {
+    int64_t o, l;            // destination offset and length of the source
+    const int16_t *p;        // its first sample
+    int s, pad;              // its index (sources apply in index order)
+};
+static_assert(sizeof(MixEntry) == 32, "MixEntry layout");
+
+__global__ void mix_fill_kernel(const int16_t *__restrict__ pool, const int64_t *__restrict__ src_off,
+                                const int64_t *__restrict__ src_len, const int64_t *__restrict__ dst_off,
                                 int64_t nsrc, int64_t dst_count, const int *__restrict__ tile_start,
-                                int *__restrict__ tile_fill, int *__restrict__ list)
+                                int *__restrict__ tile_fill, MixEntry *__restrict__ list)
 {
     const int64_t s = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (s >= nsrc) return;
     const int64_t o = dst_off[s], l = src_len[s];
     if (l <= 0 || o < 0 || o >= dst_count) return;
+    MixEntry e;
+    e.o = o; e.l = l; e.p = pool + src_off[s]; e.s = (int)s; e.pad = 0;
     const int64_t last = min(o + l, dst_count) - 1;
     for (int64_t t = o / kMixTile + (threadIdx.x & 31); t <= last / kMixTile; t += 32) {
         const int slot = atomicAdd(&tile_fill[t], 1);
-        if (slot < 0x40000000) list[tile_start[t] + slot] = (int)s;
+        if (slot < 0x40000000) list[tile_start[t] + slot] = e;
     }
 }
 
@@ -595,7 +608,7 @@ __global__ void __launch_bounds__(kPBlock, 8)
 mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__restrict__ pool,
                  const int64_t *__restrict__ src_off, const int64_t *__restrict__ src_len,
                  const int64_t *__restrict__ dst_off, const int *__restrict__ tile_count,
-                 const int *__restrict__ tile_start, const int *__restrict__ list)
+                 const int *__restrict__ tile_start, const MixEntry *__restrict__ list)
 {
     __shared__ int s_raw[kMixList];
     __shared__ int s_sorted[kMixList];
@@ -622,6 +635,49 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
 #pragma unroll
             for (int k = 0; k < kPer; k++) acc[k] = (k < live) ? dst[i0 + k] : 0;
         }
+        // the first mm staged sources, in order, onto this thread's run.  All per-sample index arithmetic
+        // is 32-bit: the 64-bit part is done once per (thread, source).
+        // (Loading several sources' samples before adding any was tried and is slower: empty batch
+        // slots cost instructions.)
+        auto apply_staged = [&](const int mm) {
+            for (int q = 0; q < mm; q++) {
+                const int64_t r0 = i0 - s_o[q];                 // source index of this thread's first sample
+                // samples k in [klo, khi) of the run are covered by the source (none if khi <= klo)
+                const int klo = (int)max((int64_t)0, min((int64_t)kPer, -r0));
+                const int khi = (int)max((int64_t)0, min((int64_t)live, s_l[q] - r0));
+                if (khi <= klo) continue;
+                const int16_t *p0 = s_p[q] + r0;
+                if (klo == 0 && khi == kPer) {
+                    // the source covers the whole run (all but the threads at its two ends):
+                    // no per-sample tests
+#pragma unroll
+                    for (int k = 0; k < kPer; k++) acc[k] = sat16(acc[k] + (int)p0[k]);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < kPer; k++)
+                        if (k >= klo && k < khi) acc[k] = sat16(acc[k] + (int)p0[k]);
+                }
+            }
+        };
+        if (n <= kMixMeta) {
+            // the usual tile (a few sources): entries to shared memory in index order, one pass
+            __syncthreads();
+            MixEntry e = {};
+            if ((int)threadIdx.x < n) {
+                e = list[begin + threadIdx.x];
+                s_raw[threadIdx.x] = e.s;
+            }
+            __syncthreads();
+            if ((int)threadIdx.x < n) {
+                int rank = 0;
+                for (int u = 0; u < n; u++) rank += (s_raw[u] < e.s) ? 1 : 0;
+                s_o[rank] = e.o;
+                s_l[rank] = e.l;
+                s_p[rank] = e.p;
+            }
+            __syncthreads();
+            apply_staged(n);
+        } else
         // the list in chunks of kMixList, each rank-sorted so that sources apply in index order;
         // chunks themselves are ordered by splitting on the source index range
         for (int lo = 0; lo < n; lo += kMixList) {
@@ -629,7 +685,7 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
             __syncthreads();
             const int m = min(kMixList, n - lo);
             if (n <= kMixList) {
-                for (int i = threadIdx.x; i < m; i += kPBlock) s_raw[i] = list[begin + i];
+                for (int i = threadIdx.x; i < m; i += kPBlock) s_raw[i] = list[begin + i].s;
                 __syncthreads();
                 for (int i = threadIdx.x; i < m; i += kPBlock) {
                     const int mine = s_raw[i];
@@ -640,9 +696,9 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
             } else {
                 // rank over the whole list in global memory; keep ranks [lo, lo+m)
                 for (int i = threadIdx.x; i < n; i += kPBlock) {
-                    const int mine = list[begin + i];
+                    const int mine = list[begin + i].s;
                     int rank = 0;
-                    for (int u = 0; u < n; u++) rank += (list[begin + u] < mine) ? 1 : 0;
+                    for (int u = 0; u < n; u++) rank += (list[begin + u].s < mine) ? 1 : 0;
                     if (rank >= lo && rank < lo + m) s_sorted[rank - lo] = mine;
                 }
             }
@@ -662,24 +718,7 @@ mix_apply_kernel(int16_t *__restrict__ dst, int64_t dst_count, const int16_t *__
                     s_p[i] = pool + src_off[s];
                 }
                 __syncthreads();
-                for (int q = 0; q < mm; q++) {
-                    const int64_t r0 = i0 - s_o[q];                 // source index of this thread's first sample
-                    // samples k in [klo, khi) of the run are covered by the source (none if khi <= klo)
-                    const int klo = (int)max((int64_t)0, min((int64_t)kPer, -r0));
-                    const int khi = (int)max((int64_t)0, min((int64_t)live, s_l[q] - r0));
-                    if (khi <= klo) continue;
-                    const int16_t *p0 = s_p[q] + r0;
-                    if (klo == 0 && khi == kPer) {
-                        // the source covers the whole run (all but the threads at its two ends):
-                        // no per-sample tests
-#pragma unroll
-                        for (int k = 0; k < kPer; k++) acc[k] = sat16(acc[k] + (int)p0[k]);
-                    } else {
-#pragma unroll
-                        for (int k = 0; k < kPer; k++)
-                            if (k >= klo && k < khi) acc[k] = sat16(acc[k] + (int)p0[k]);
-                    }
-                }
+                apply_staged(mm);
             }
         }
         if (full) {
@@ -948,12 +987,16 @@ extern "C" int sb_pcm16_ratecv_many(const int16_t *in_pool_dev, const int64_t *i
     return SB_OK;
 }
 
+// scratch layout: cursor (4 ints: list cursor, sources left out for a negative offset, list overflow
+// flag, spare), tile_count, tile_start, tile_fill (ntiles ints each), then the list entries
+static inline int64_t mix_list_offset(int64_t ntiles) { return ((3 * ntiles + 4) * (int64_t)sizeof(int) + 15) / 16 * 16; }
+
 extern "C" int64_t sb_pcm16_mix_at_many_scratch_bytes(int64_t dst_count, int64_t nsrc, int64_t total_src_samples)
 {
     if (dst_count <= 0 || nsrc <= 0) return 0;
     int64_t ntiles = (dst_count + kMixTile - 1) / kMixTile;
     int64_t cap = total_src_samples / kMixTile + 2 * nsrc + 1;     // every source touches <= len/tile + 2 tiles
-    return (3 * ntiles + 4 + cap) * (int64_t)sizeof(int);
+    return mix_list_offset(ntiles) + cap * (int64_t)sizeof(MixEntry);
 }
 
 extern "C" int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const int16_t *src_pool_dev,
@@ -974,23 +1017,23 @@ extern "C" int sb_pcm16_mix_at_many(int16_t *dst_dev, int64_t dst_count, const i
         SB_LAUNCH_CHECK();
         return SB_OK;
     }
-    SB_REQUIRE(scratch_bytes >= (3 * ntiles + 4) * (int64_t)sizeof(int) + (int64_t)sizeof(int),
-               "sb_pcm16_mix_at_many: scratch too small");
-    const int64_t list_cap = scratch_bytes / (int64_t)sizeof(int) - (3 * ntiles + 4);
-    // layout: cursor (4 ints: list cursor, sources left out for a negative offset, list overflow flag,
-    // spare), tile_count, tile_start, tile_fill, list
+    SB_REQUIRE(scratch_bytes >= mix_list_offset(ntiles) + (int64_t)sizeof(MixEntry) && ((uintptr_t)scratch_dev & 15) == 0,
+               "sb_pcm16_mix_at_many: scratch too small or not 16-byte aligned");
+    int64_t list_cap = (scratch_bytes - mix_list_offset(ntiles)) / (int64_t)sizeof(MixEntry);
+    if (list_cap > 0x3fffffff) list_cap = 0x3fffffff;
     int *cursor = (int *)scratch_dev;
     int *tile_count = cursor + 4;
     int *tile_start = tile_count + ntiles;
     int *tile_fill = tile_start + ntiles;
-    int *list = tile_fill + ntiles;
+    MixEntry *list = (MixEntry *)((unsigned char *)scratch_dev + mix_list_offset(ntiles));
     SB_CUDA_CHECK(cudaMemsetAsync(cursor, 0, (size_t)(ntiles + 4) * sizeof(int), s));
     int sgrid = (int)((nsrc * 32 + 255) / 256);             // a warp per source
     mix_count_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_count, cursor);
     SB_LAUNCH_CHECK();
     mix_alloc_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, s>>>(tile_count, ntiles, cursor, tile_start, tile_fill, list_cap);
     SB_LAUNCH_CHECK();
-    mix_fill_kernel<<<sgrid, 256, 0, s>>>(src_len_dev, dst_off_dev, nsrc, dst_count, tile_start, tile_fill, list);
+    mix_fill_kernel<<<sgrid, 256, 0, s>>>(src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, nsrc, dst_count, tile_start,
+                                          tile_fill, list);
     SB_LAUNCH_CHECK();
     mix_apply_kernel<<<grid_for(ntiles, 1, kPMaxBlocks * 4), kPBlock, 0, s>>>(
         dst_dev, dst_count, src_pool_dev, src_off_dev, src_len_dev, dst_off_dev, tile_count, tile_start, list);

@@ -443,7 +443,7 @@ def test_mix_at_many_bad_input_stays_inside_its_buffers(cuda):
     assert np.array_equal(dst.cpu().numpy().astype(np.int64), want)
     # a scratch with room for the fixed part and three list entries only
     ntiles = (total + 2047) // 2048
-    small = (3 * ntiles + 4 + 3) * 4
+    small = ((3 * ntiles + 4) * 4 + 15) // 16 * 16 + 3 * 32       # (a list entry is 32 bytes)
     scr2 = torch.full((small + guard,), 0x5A, dtype=torch.uint8, device="cuda")
     dst.zero_()
     C.call("sb_pcm16_mix_at_many", D.ptr(dst), total, D.ptr(pool), D.ptr(idx[0]), D.ptr(idx[1]), D.ptr(idx[2]), nsrc,
