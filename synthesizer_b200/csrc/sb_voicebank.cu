@@ -1723,11 +1723,23 @@ __device__ __forceinline__ double lfo_tile_by_runs(const FastVoice &F, const sb_
         straddle = (n + kFItems >= c.next_start);
     }
     const LfoLine L = lfo_line(mwave, Tc0, fm, phm, cstep, __float_as_uint(F.ini.x), __float_as_uint(F.ini.y));
+    // (per lane, as the render kernel's runs do it: the line; two lines around a single edge; else the
+    // per-sample evaluation - in the lanes that need it only, so a tile with an edge in each of two
+    // runs costs two settled breaks and not a pass of the exact path by the whole warp)
     double acc = 0.0;
-    if (__all_sync(0xffffffffu, cnt == kFItems && L.clear && !straddle)) {
+    if (cnt == kFItems && L.clear && !straddle) {
         acc = fma((double)(kFItems * (kFItems - 1) / 2), L.dv, (double)kFItems * L.v0);
     } else if (cnt == kFItems) {
-        acc = lfo_run_slow(mwave, s_cyc, nsegs_cyc, cstep, straddle, Tc0, n, fm, phm, mpw, 1.0).tot;
+        LfoBreak bk;
+        bk.js = 0;
+        if (!straddle) bk = lfo_run_break(&F, mwave, Tc0, cstep, L.v0, L.dv, L.d1, L.d2);
+        if (bk.js) {
+            const int js = bk.js, rest = kFItems - js;
+            acc = fma(0.5 * (double)js * (double)(js - 1), L.dv, (double)js * L.v0) +
+                  fma(0.5 * (double)rest * (double)(rest - 1), bk.dv1, (double)rest * bk.v1);
+        } else {
+            acc = lfo_run_slow(mwave, s_cyc, nsegs_cyc, cstep, straddle, Tc0, n, fm, phm, mpw, 1.0).tot;
+        }
     } else {
         for (int j = 0; j < cnt; j++) acc += lfo_shape_exact(mwave, exact_time_at(s_cyc, nsegs_cyc, n + j), fm, phm, mpw);
     }
