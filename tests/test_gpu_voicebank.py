@@ -409,6 +409,48 @@ def test_fast_and_generic_voices_share_a_group(cuda):
     assert bank.check_last_render() == kinds.count(0)
 
 
+@pytest.mark.parametrize("waves,sine_mods", [((2, 3, 4), True), ((0, 1, 3), False), ((2, 3, 4), False)])
+def test_sorted_bank_without_a_smooth_part(cuda, waves, sine_mods):
+    """A bank of several groups whose first kernel part is not part 0: edged carriers only (part 1
+    writes the partial mixes), class-2 modulators only (part 2 writes them), or both, each with
+    generic voices mixed in - whose groups, at the end of the sorted bank, hold no voice of the
+    fast classes and must come out of the first part as zeros for the generic kernel to add into."""
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    sr, n = 48000, 12000
+    nv = 200
+    bank, P = make_bank(nv, sr, 7 + len(waves) + int(sine_mods), 0.25, waves=list(waves), fm=True)
+    for i, v in enumerate(bank._voices):
+        if v.m_wave == 4:
+            v.m_pw = 0.1
+        if sine_mods and v.m_wave > 0:                   # Sine modulators only: no class-2 voice
+            v.m_wave = P[i, 6] = 0
+        if not sine_mods and v.m_wave <= 0:              # piecewise-linear modulators only: every voice class 2
+            v.m_wave = P[i, 6] = 1 + i % 3
+            v.m_freq, v.m_amp, v.m_phase = P[i, 7], P[i, 8], P[i, 9] = 3.0 + 0.01 * i, float(np.float32(0.02)), 0.25
+    bank._dev = None
+    # every fifth voice to the generic kernels (a negative carrier start phase for edged carriers, a
+    # negative modulator phase for class-2 modulators)
+    for i, v in enumerate(bank._voices):
+        if i % 5 == 0:
+            if v.m_wave > 0:
+                v.m_phase = P[i, 9] = -0.3 - 0.001 * i
+            elif v.c_wave >= 2:
+                v.c_phase = P[i, 3] = -0.2 - 0.001 * i
+    bank._dev = None
+    g, sm, e, sc = bank.count_classes()
+    assert g > 0 and (e > 0 or sc > 0)
+    if waves == (2, 3, 4) and sine_mods:
+        assert sm == 0 and sc == 0                       # part 1 is the first part
+    if not sine_mods:
+        assert sm == 0 and e == 0                        # part 2 is the first part
+    got = dev_pcm16(bank.render(n))
+    want = oracle_bank_pcm(P, n, sr)
+    bad = np.abs(got.astype(np.int64) - want) > 1
+    assert bad.mean() < 2e-5, "%d of %d samples off by more than 1 LSB (generic %d smooth %d edged %d scan %d)" % (
+        bad.sum(), bad.size, g, sm, e, sc)
+
+
 def test_bank_chunked_start_offsets(cuda):
     """Rendering [0,n) in one call equals rendering it as two calls with start offsets
     (non-FM voices; FM voices carry state across calls only through the general path)."""
