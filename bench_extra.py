@@ -246,8 +246,10 @@ def class_bank(cw, mw, nv=8192):
             cw, mw = v % 5, (v // 5) % 5
         lfo = None
         f0 = float(r.uniform(55, 1760))
-        if mw == 5:
-            lfo = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=SR)
+        if mw in (5, 6):
+            # FM gain 2*pi*f0*depth/sr: depth 16 -> 6.3 - 10.5 rad (generic kernels), depth 3.9 -> 1.5 - 2.6 rad
+            # (the fast path's strong-FM variant for Sine / Triangle carriers)
+            lfo = sb.Sine(float(r.uniform(0.5, 12)), 16.0 if mw == 5 else 3.9, samplerate=SR)
             f0 = float(r.uniform(3000, 5000))
         elif mw is not None:
             lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=SR)
@@ -259,7 +261,7 @@ def class_bank(cw, mw, nv=8192):
 
 CLASSES = [("sine_x_sine", 0, 0, 8192), ("triangle_plain", 1, None, 8192), ("sawtooth_x_sine", 3, 0, 8192),
            ("square_plain", 2, None, 8192), ("sine_x_triangle_lfo", 0, 1, 8192), ("sawtooth_x_square_lfo", 3, 2, 8192),
-           ("mixed_5x5", 9, 0, 8192), ("generic_fm_gain_3rad", 0, 5, 1024)]
+           ("mixed_5x5", 9, 0, 8192), ("sine_x_sine_strong_fm_2rad", 0, 6, 8192), ("generic_fm_gain_8rad", 0, 5, 1024)]
 
 
 def classes(reps=3):

@@ -87,10 +87,17 @@ enum : int {
     FV_ENV_EXTRA = 16,
     FV_BIAS = 32,
     FV_SCAN = 64,            // Triangle/Square/Sawtooth/Pulse modulator: FM sum from the tile pre-pass + warp scan
+    FV_HIGH = 128,           // FM gain above kFastMaxFmGain (smooth carrier, Sine modulator): the run's phase is
+                             // brought back into one turn after every step
     FV_WAVE_SHIFT = 8,       // bits 8..10: the carrier's waveform id
     FV_MWAVE_SHIFT = 12,     // bits 12..14: the modulator's waveform id (FV_SCAN voices)
 };
 constexpr double kFastMaxFmGain = FAST_MAX_FM_GAIN;
+// ... and up to this gain for Sine / Triangle carriers with a Sine modulator, whose fp32 run then
+// reduces its phase after every step (what limits the plain run is the resolution of an fp32 phase
+// that has grown to 16 steps' worth of gain: measured at full scale, tools/accuracy_sweep.py and the
+// sweep in test_gpu_voicebank.py: plain run 0.44 LSB at 1.5 rad, 0.92 at 6; reduced 0.13 and 0.39)
+constexpr double kFastHighFmGain = 6.0;
 constexpr int kFastKinds = 15;              // kind = MOD | (carrier waveform << 1) for no / Sine modulators,
                                              // 10 + carrier waveform for the other modulators
 __host__ __device__ inline int fast_kind_of(int flags)
@@ -224,7 +231,8 @@ __host__ __device__ inline int voice_class(const sb_voice &V, double samplerate,
     // of 1.5 (it was 3.5 LSB per radian with an fp32 warp scan over the 512-frame sub-tile);
     // stronger FM takes the generic fp64 path.
     const double gain_rad = fabs(V.c_freq) * w1 * fabs((double)V.m_amp);
-    if (!(gain_rad <= kFastMaxFmGain)) return 0;
+    if (!(gain_rad <= kFastMaxFmGain) &&
+        !(gain_rad <= kFastHighFmGain && V.c_wave < SB_WAVE_SQUARE && V.m_wave == SB_WAVE_SINE)) return 0;
     if (V.m_wave == SB_WAVE_SINE) {
         const double w = V.m_freq * w1;                              // modulator phase step
         if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return 0;            // closed form needs sin(w/2) != 0
@@ -386,6 +394,7 @@ __global__ void bank_prepare_kernel(BankArgs a)
         if (V.env.enabled) F.flags |= FV_ENV;
         if (V.env.enabled && V.env.extra) F.flags |= FV_ENV_EXTRA;
         if (V.c_bias != 0.0f) F.flags |= FV_BIAS;
+        if (has_mod && fabs(gd) * (tri ? 6.283185307179586 : 1.0) > kFastMaxFmGain) F.flags |= FV_HIGH;
         a.fastv[v] = F;
         a.perm[v] = v;                                   // (a bank of one group keeps this order)
     }
@@ -885,6 +894,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
     const float2 cstep = make_float2(stepk.x, stepk.y), nk2 = make_float2(stepk.z, stepk.w);
     float2 estep = make_float2(env.y, env.y);
     int swx = 0x7fffffff, swy = 0x7fffffff;                // RARE: the step at which frame q / q+H enters a new ADSR segment
+    const bool high = RARE && (F.flags & FV_HIGH);          // warp-uniform
     if (RARE && env.x == kEnvSlow) {
         const EnvLine lx = fast_env_line(&F, n), ly = fast_env_line(&F, n + H);
         e = make_float2(lx.v, ly.v);
@@ -925,6 +935,18 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
                 sn = __fadd2_rn(sn, dl);
             }
             if (!FLAT) e = __fadd2_rn(e, estep);
+            if (RARE && MODC == 1 && high) {
+                // strong FM: the phase back into one turn (cycles: exactly; radians: two-constant 2*pi)
+                const float2 big = make_float2(12582912.0f, 12582912.0f), nbig = make_float2(-12582912.0f, -12582912.0f);
+                if (CYC) {
+                    const float2 t = __fadd2_rn(__fadd2_rn(P, big), nbig);
+                    P = __fadd2_rn(P, make_float2(-t.x, -t.y));
+                } else {
+                    const float2 t = __fadd2_rn(__ffma2_rn(P, make_float2(0.15915494f, 0.15915494f), big), nbig);
+                    P = __ffma2_rn(t, make_float2(-6.28318548f, -6.28318548f), P);
+                    P = __ffma2_rn(t, make_float2(1.74845553e-7f, 1.74845553e-7f), P);
+                }
+            }
             if (RARE) {
                 if (q + 1 == swx) {
                     const EnvLine l = fast_env_line(&F, n + q + 1);
@@ -1182,7 +1204,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
             const FastVoice &F0 = s_fv[v], &F1 = s_fv[v + 1];
             const float2 e0 = s_env[v * kFastMaxSub + s], e1 = s_env[(v + 1) * kFastMaxSub + s];
             // both envelopes plain lines (sign bits clear: not kEnvSilent / kEnvSlow), no carrier bias
-            const bool plain = (__float_as_int(e0.x) | __float_as_int(e1.x)) >= 0 && !((F0.flags | F1.flags) & FV_BIAS);
+            const bool plain = (__float_as_int(e0.x) | __float_as_int(e1.x)) >= 0 && !((F0.flags | F1.flags) & (FV_BIAS | FV_HIGH));
             if (!plain) break;                                                  // warp-uniform
             const double2 a0 = MOD == 1 ? s_anc[v * kFastMaxSub + s] : none;
             const double2 a1 = MOD == 1 ? s_anc[(v + 1) * kFastMaxSub + s] : none;
@@ -1209,7 +1231,7 @@ __device__ __forceinline__ void fast_voice_loop(const FastVoice *s_fv, const dou
             else
                 edged_voice_run<MOD, WAVE, false, false>(F, anc, env, Tc0, dstep, lane8, n, ctx, accL2, accR2);
         } else {
-            if (env.x == kEnvSlow || (F.flags & FV_BIAS))
+            if (env.x == kEnvSlow || (F.flags & (FV_BIAS | FV_HIGH)))
                 fast_voice_run<MOD, WAVE, true, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);
             else
                 fast_voice_run<MOD, WAVE, false, false>(F, anc, env, Tr0, Tc0, dstep, lane8, n, ctx, accL2, accR2);

@@ -167,7 +167,9 @@ def test_fm_accuracy_sweep_full_scale(cuda, cw):
     sr, n = 48000, 48000
     classes = {0: sb.Sine, 1: sb.Triangle, 3: sb.Sawtooth}
     seen = set()
-    for f0, fm, d in itertools.product((55.1, 441.3, 3517.9, 9973.0), (0.1, 5.3, 109.7, 1999.3), (0.01, 0.5, 2.0)):
+    # (depth 5 on the 10 kHz carrier is a gain of 6.5 rad: generic for every carrier; depth 2 there, 2.6 rad,
+    # is the strong-FM variant of the fast path for Sine / Triangle carriers and generic for Sawtooth)
+    for f0, fm, d in itertools.product((55.1, 441.3, 3517.9, 9973.0), (0.1, 5.3, 109.7, 1999.3), (0.01, 0.5, 2.0, 5.0)):
         lfo = sb.Sine(fm, d, 0.3, samplerate=sr)
         car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
         bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
@@ -180,6 +182,48 @@ def test_fm_accuracy_sweep_full_scale(cuda, cw):
         assert flips.sum() <= (3 if cw == 3 else 0), (f0, fm, d, int(flips.sum()))
         assert err[~flips].max() < 0.9, "f0=%g fm=%g depth=%g: %.3f LSB" % (f0, fm, d, err[~flips].max())
     assert seen == {0, 1}, "the sweep is meant to exercise both the fast and the generic kernels"
+
+
+@pytest.mark.parametrize("cw", [0, 1])
+def test_strong_fm_stays_on_the_fast_path(cuda, cw):
+    """FM gains between 1.5 and 6 rad per unit of modulator sum (a bright FM patch in a high octave:
+    f0 * depth of 11 - 46 kHz): Sine / Triangle carriers with a Sine modulator take the fast path's
+    strong-FM variant (phase reduced after every step).  Full-scale voices against the oracle, the
+    error bound the plain run is held to (half an LSB), plus a bank that mixes them with plain voices."""
+    import itertools
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C
+    from oracle import coracle as co
+    sr, n = 48000, 96000
+    classes = {0: sb.Sine, 1: sb.Triangle}
+    for gain, f0, fm in itertools.product((1.6, 3.0, 4.5, 5.9), (1979.3, 7013.9), (2.7, 219.3, 3001.7)):
+        d = gain * sr / (2 * np.pi * f0)
+        lfo = sb.Sine(fm, d, 0.3, samplerate=sr)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 1, (gain, f0, fm)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(0, n, sr, fm, d, 0.3, 0.0)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.5, "cw=%d gain=%g f0=%g fm=%g: %.3f LSB" % (cw, gain, f0, fm, err.max())
+    # just above the limit: generic
+    d = 6.1 * sr / (2 * np.pi * 7013.9)
+    car = classes[cw](7013.9, 0.5, fm_lfo=sb.Sine(5.0, d, samplerate=sr), samplerate=sr)
+    assert sb.VoiceBank(sr).add(car, 1.0, 1.0).count_generic() == 1
+    # a bank of 100 voices, every third one strong: pairs of plain voices, strong ones taken alone
+    bank, P = make_bank(100, sr, 123 + cw, 0.3, waves=[cw], fm=True)
+    for i, v in enumerate(bank._voices):
+        if v.m_wave > 0:
+            v.m_wave = P[i, 6] = 0
+        if i % 3 == 0 and v.m_wave == 0:
+            v.c_freq = P[i, 1] = 3000.0 + 17.0 * i
+            v.m_amp = P[i, 8] = float(np.float32(4.0 * sr / (2 * np.pi * v.c_freq)))
+    bank._dev = None
+    assert bank.count_generic() == 0 and sum(1 for i, v in enumerate(bank._voices) if i % 3 == 0 and v.m_wave == 0) > 15
+    nn = 14000
+    got = dev_pcm16(bank.render(nn))
+    assert_within_lsb(got, oracle_bank_pcm(P, nn, sr), 1, "bank with strong-FM voices")
 
 
 @pytest.mark.parametrize("pw", [0.0, 1.0, 1e-12, 1.0 - 1e-12, 0.5, 0.999999])

@@ -1,8 +1,9 @@
 """
 Renders one 8192-voice bank of a single (carrier, modulator) kind a few times: a target for
 `ncu -k regex:bank_` when looking at the edged or generic kernels (bench.py only exercises the
-Sine x Sine kind).   python tools/class_bank.py <carrier 0..4> <modulator 0..4 | -1 | 5> [voices]
-(modulator 5 = a Sine of FM gain 3 rad: the generic kernels; carrier 9 = a uniform mix of all
+Sine x Sine kind).   python tools/class_bank.py <carrier 0..4> <modulator 0..4 | -1 | 5 | 6> [voices]
+(modulator 5 = a Sine of FM gain 6 - 10 rad: the generic kernels; 6 = a Sine of gain 1.5 - 2.6 rad: the fast
+path's strong-FM variant for Sine / Triangle carriers; carrier 9 = a uniform mix of all
 5 x 5 (carrier, modulator) kinds, what BASELINE config 3 calls "mixed waveforms")
 """
 import os
@@ -25,8 +26,8 @@ for v in range(nv):
     if mixed:
         cw, mw = v % 5, (v // 5) % 5
     f0 = float(r.uniform(55, 1760))
-    if mw == 5:
-        lfo, f0 = sb.Sine(float(r.uniform(0.5, 12)), 3.9, samplerate=sr), float(r.uniform(3000, 5000))
+    if mw in (5, 6):
+        lfo, f0 = sb.Sine(float(r.uniform(0.5, 12)), 16.0 if mw == 5 else 3.9, samplerate=sr), float(r.uniform(3000, 5000))
     else:
         lfo = classes[mw](float(r.uniform(0.5, 12)), float(r.uniform(0.005, 0.06)), samplerate=sr) if mw >= 0 else None
     car = classes[cw](f0, 0.9 / nv, fm_lfo=lfo, samplerate=sr)
