@@ -87,13 +87,13 @@ enum : int {
     FV_ENV_EXTRA = 16,
     FV_BIAS = 32,
     FV_SCAN = 64,            // Triangle/Square/Sawtooth/Pulse modulator: FM sum from the tile pre-pass + warp scan
-    FV_HIGH = 128,           // FM gain above kFastMaxFmGain (smooth carrier, Sine modulator): the run's phase is
+    FV_HIGH = 128,           // FM gain above kFastMaxFmGain (Sine / Triangle carrier): the run's phase is
                              // brought back into one turn after every step
     FV_WAVE_SHIFT = 8,       // bits 8..10: the carrier's waveform id
     FV_MWAVE_SHIFT = 12,     // bits 12..14: the modulator's waveform id (FV_SCAN voices)
 };
 constexpr double kFastMaxFmGain = FAST_MAX_FM_GAIN;
-// ... and up to this gain for Sine / Triangle carriers with a Sine modulator, whose fp32 run then
+// ... and up to this gain for Sine / Triangle carriers (any modulator), whose fp32 run then
 // reduces its phase after every step (what limits the plain run is the resolution of an fp32 phase
 // that has grown to 16 steps' worth of gain: measured at full scale, tools/accuracy_sweep.py and the
 // sweep in test_gpu_voicebank.py: plain run 0.44 LSB at 1.5 rad, 0.92 at 6; reduced 0.13 and 0.39)
@@ -232,7 +232,7 @@ __host__ __device__ inline int voice_class(const sb_voice &V, double samplerate,
     // stronger FM takes the generic fp64 path.
     const double gain_rad = fabs(V.c_freq) * w1 * fabs((double)V.m_amp);
     if (!(gain_rad <= kFastMaxFmGain) &&
-        !(gain_rad <= kFastHighFmGain && V.c_wave < SB_WAVE_SQUARE && V.m_wave == SB_WAVE_SINE)) return 0;
+        !(gain_rad <= kFastHighFmGain && V.c_wave < SB_WAVE_SQUARE)) return 0;
     if (V.m_wave == SB_WAVE_SINE) {
         const double w = V.m_freq * w1;                              // modulator phase step
         if (!(fabs(w) > 1e-7 && fabs(w) < 3.0)) return 0;            // closed form needs sin(w/2) != 0
@@ -935,7 +935,7 @@ __device__ __forceinline__ void fast_voice_run(const FastVoice &F, const double2
                 sn = __fadd2_rn(sn, dl);
             }
             if (!FLAT) e = __fadd2_rn(e, estep);
-            if (RARE && MODC == 1 && high) {
+            if (RARE && MOD && high) {
                 // strong FM: the phase back into one turn (cycles: exactly; radians: two-constant 2*pi)
                 const float2 big = make_float2(12582912.0f, 12582912.0f), nbig = make_float2(-12582912.0f, -12582912.0f);
                 if (CYC) {

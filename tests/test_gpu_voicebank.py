@@ -207,6 +207,20 @@ def test_strong_fm_stays_on_the_fast_path(cuda, cw):
         want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
         err = np.abs(got - want) * 32767.0
         assert err.max() < 0.5, "cw=%d gain=%g f0=%g fm=%g: %.3f LSB" % (cw, gain, f0, fm, err.max())
+    # ... and with the piecewise-linear modulators (class 2: their values are formed exactly per run)
+    mods = [sb.Sine, sb.Triangle, sb.Square, sb.Sawtooth, sb.Pulse]
+    for mw, gain, f0, fm in itertools.product((1, 2, 3, 4), (2.5, 5.9), (3979.3,), (3.7, 431.9)):
+        d = gain * sr / (2 * np.pi * f0)
+        mkw = dict(pulsewidth=0.37) if mw == 4 else {}
+        lfo = mods[mw](fm, d, 0.3, 0.0, samplerate=sr, **mkw)
+        car = classes[cw](f0, 0.99, 0.1, 0.0, fm_lfo=lfo, samplerate=sr)
+        bank = sb.VoiceBank(sr).add(car, 1.0, 1.0)
+        assert C.lib.sb_voice_is_fast(ctypes.byref(bank._voices[0]), float(sr)) == 2, (mw, gain, f0, fm)
+        got = bank.render(n).cpu().numpy()[0::2].astype(np.float64)
+        m = co.osc(mw, n, sr, fm, d, 0.3, 0.0, pulsewidth=0.37)
+        want = co.osc(cw, n, sr, f0, float(np.float32(0.99)), 0.1, 0.0, fm=m)
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.5, "cw=%d mw=%d gain=%g fm=%g: %.3f LSB" % (cw, mw, gain, fm, err.max())
     # just above the limit: generic
     d = 6.1 * sr / (2 * np.pi * 7013.9)
     car = classes[cw](7013.9, 0.5, fm_lfo=sb.Sine(5.0, d, samplerate=sr), samplerate=sr)
