@@ -22,19 +22,24 @@
 //          the samples, no running carry, and fp32 error cannot build up over more than 16
 //          frames.  Square / Sawtooth / Pulse carriers (bank_fast_kernel<1>) walk an integer
 //          phase and re-evaluate the few samples within a guard band of an edge exactly in fp64.
+//          Sine / Triangle carriers under strong FM (gain above kFastMaxFmGain, up to
+//          kFastHighFmGain) take the same run with the phase reduced to one turn after every step.
 //
 //  FAST (2) the same carriers with a Triangle / Square / Sawtooth / Pulse modulator
 //          (bank_fast_kernel<2>).  Between its edges and kinks such a modulator is a straight line:
 //          a run of 16 frames that stays clear of them (tested on an integer phase, with a guard
 //          band) needs one exactly formed phase - increments, half-run sum and the running sum
-//          ahead of the lane are closed forms.  Runs that are not clear evaluate the 16 values
-//          exactly as upstream does (lfo_run_slow) and scan the lanes' totals in fp64.  The FM sum
+//          ahead of the lane are closed forms; a sub-tile that is one line end to end (found by the
+//          span's set-up) evaluates nothing of the modulator in its runs.  A run with one edge
+//          takes two lines around a settled break (lfo_run_break); only runs with more evaluate
+//          the 16 values exactly as upstream does (lfo_run_slow); then the lanes' totals are
+//          scanned in fp64.  The FM sum
 //          ahead of a sub-tile is a per-512-frame tile prefix from a pre-pass (bank_lfo_tile_kernel:
 //          a tile as one line, or two around a single edge settled by exact values, else by runs;
 //          bank_lfo_prefix_kernel).
 //
-//  GENERIC (0) anything else (FM gain above kFastMaxFmGain, carriers or modulators with a
-//          negative start phase or frequency).  Phase arithmetic per sample in explicitly
+//  GENERIC (0) anything else (FM gain above kFastHighFmGain - kFastMaxFmGain for edged carriers -,
+//          carriers or modulators with a negative start phase or frequency).  Phase arithmetic per sample in explicitly
 //          rounded fp64, FM prefix by fp64 warp scan with a running carry that starts from
 //          per-(voice, span) sums computed by a pre-pass.
 //
@@ -43,9 +48,10 @@
 // the bank, so that a group - a slice of 64 of that order - holds one or two kinds),
 // bank_sort_kernel (each group's voices by kernel part and kind), the tile pre-pass if any
 // class-2 voice, then bank_fast_kernel<0>, <1>, <2> and the generic kernels as far as the bank has
-// such voices (the first one launched writes the per-group partial mixes, the others add into
-// them), bank_fold_kernel.  <1> and <2> walk their grid group-first when their voices are of one
-// or two kinds (counted on the device while sorting), span-first otherwise; <0> is always span-first.
+// such voices (per group, the lowest launched part with voices in it writes the partial mix and the
+// others add into it), bank_fold_kernel.  <0> maps its 2-D grid to (block of spans, group); the CTAs
+// of <1> and <2> draw their (group, block of spans) unit from a queue per kind, chosen by the SM
+// they run on, so that an SM runs one kind's loop at a time.
 #include "sb_common.cuh"
 
 namespace sb {
