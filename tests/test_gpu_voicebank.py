@@ -509,6 +509,46 @@ def test_sorted_bank_without_a_smooth_part(cuda, waves, sine_mods):
         bad.sum(), bad.size, g, sm, e, sc)
 
 
+@pytest.mark.parametrize("nvoices,hints", [(300, True), (300, False), (70, True)])
+def test_render_stays_inside_the_scratch_the_plan_asks_for(cuda, nvoices, hints):
+    """sb_bank_render_f32 with scratch, partial-mix and output buffers of exactly the sizes the plan
+    states, each followed by a guard area: a mixed bank (all kernel parts, generic voices, the sort,
+    the unit queues, the modulator tile table) must leave the guards untouched - with exact hints
+    and with none (worst-case sizes)."""
+    import torch
+    import synthesizer_b200 as sb
+    from synthesizer_b200 import _cabi as C, _device as D
+    sr, n, start = 48000, 30011, 517
+    bank, P = make_bank(nvoices, sr, 77 + nvoices, 0.5, fm=True)
+    force_some_generic(bank, P)
+    vd, nv = bank._upload(0, None)
+    g, sm, e, sc = bank.count_classes()
+    assert g > 0 and sm > 0 and e > 0 and sc > 0
+    plan = C.BankPlan()
+    tr, tc = D.timebase_rad(sr), D.timebase_cyc(sr)
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    C.call("sb_bank_plan_make", nv, n, start, sms, tr.nsegs, ctypes.byref(plan))
+    if hints:
+        C.call("sb_bank_plan_hint", ctypes.byref(plan), g, sm, e, sc)
+    guard = 1 << 16
+
+    def guarded(nbytes):
+        t = torch.full((nbytes + guard,), 0x5A, dtype=torch.uint8, device="cuda")
+        return t
+
+    scratch, partial, mix = guarded(plan.carry_bytes), guarded(max(plan.partial_bytes, 16)), guarded(2 * n * 4)
+    C.call("sb_bank_render_f32", D.ptr(vd), ctypes.byref(plan), D.ptr(tr.dev()), tr.nsegs, D.ptr(tc.dev()), tc.nsegs,
+           start, float(sr), D.ptr(scratch), D.ptr(partial), D.ptr(mix), D.stream())
+    torch.cuda.synchronize()
+    assert bool((scratch[plan.carry_bytes:] == 0x5A).all()), "scratch overrun"
+    assert bool((partial[max(plan.partial_bytes, 16):] == 0x5A).all()), "partial-mix overrun"
+    assert bool((mix[2 * n * 4:] == 0x5A).all()), "output overrun"
+    # and the mix is the one the product API renders
+    want = bank.render(n, start=start)
+    got = mix[:2 * n * 4].view(torch.float32)
+    assert torch.equal(got, want)
+
+
 def test_bank_chunked_start_offsets(cuda):
     """Rendering [0,n) in one call equals rendering it as two calls with start offsets
     (non-FM voices; FM voices carry state across calls only through the general path)."""
