@@ -519,3 +519,26 @@ class WaveSynth:
         k = self._scale(frequency, amplitude, bias)
         return self._sample(so.Pulse(frequency, amplitude * k, phase, bias * k, pulsewidth, fm_lfo=fm_lfo,
                                      pwm_lfo=pwm_lfo, samplerate=self.samplerate), duration)
+
+    def harmonics(self, frequency, duration, harmonics, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Harmonics(frequency, harmonics, amplitude * k, phase, bias * k, fm_lfo=fm_lfo,
+                                         samplerate=self.samplerate), duration)
+
+    def square_h(self, frequency, duration, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.SquareH(frequency, num_harmonics, amplitude * k, phase, bias * k, fm_lfo=fm_lfo,
+                                       samplerate=self.samplerate), duration)
+
+    def sawtooth_h(self, frequency, duration, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.SawtoothH(frequency, num_harmonics, amplitude * k, phase, bias * k, fm_lfo=fm_lfo,
+                                         samplerate=self.samplerate), duration)
+
+    def semicircle(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Semicircle(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)
+
+    def pointy(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        k = self._scale(frequency, amplitude, bias)
+        return self._sample(so.Pointy(frequency, amplitude * k, phase, bias * k, fm_lfo=fm_lfo, samplerate=self.samplerate), duration)

@@ -6,7 +6,8 @@ oscillator amplitude (amplitude * (2**(8*width-1)-1)) and truncates with int(); 
 (synthplayer/synth.py is absent from /root/reference; recalled from the published package.)
 """
 from . import params
-from .oscillators import (Linear, Oscillator, Pulse, Sawtooth, Sine, Square, Triangle, WhiteNoise)
+from .oscillators import (Harmonics, Linear, Oscillator, Pointy, Pulse, Sawtooth, SawtoothH, Semicircle, Sine, Square,
+                          SquareH, Triangle, WhiteNoise)
 from .sample import Sample
 
 __all__ = ["WaveSynth", "key_num", "key_freq", "octave_notes", "note_freq"]
@@ -31,8 +32,9 @@ def note_freq(note, octave=None, a4=440.0):
 
 
 class WaveSynth:
-    """Waveform sample synthesizer: sine, square, triangle, sawtooth, pulse, white noise,
-    linear; optional FM LFO.  Results are 16 or 32 bit integer Samples."""
+    """Waveform sample synthesizer: sine, square, triangle, sawtooth, pulse, harmonics, square_h,
+    sawtooth_h, semicircle, pointy, white noise, linear; optional FM LFO (the methods and their
+    defaults as recalled of synthplayer.synth.WaveSynth).  Results are 16 or 32 bit integer Samples."""
 
     def __init__(self, samplerate=0, samplewidth=0):
         samplerate = samplerate or params.norm_samplerate
@@ -85,6 +87,29 @@ class WaveSynth:
         return WhiteNoise(frequency, amplitude * scale, bias * scale, samplerate=self.samplerate,
                           noise_source=noise_source)
 
+    def harmonics_gen(self, frequency, harmonics, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        scale = self._scale(frequency, amplitude, bias)
+        return Harmonics(frequency, harmonics, amplitude * scale, phase, bias * scale, fm_lfo=fm_lfo,
+                         samplerate=self.samplerate)
+
+    def square_h_gen(self, frequency, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        scale = self._scale(frequency, amplitude, bias)
+        return SquareH(frequency, num_harmonics, amplitude * scale, phase, bias * scale, fm_lfo=fm_lfo,
+                       samplerate=self.samplerate)
+
+    def sawtooth_h_gen(self, frequency, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        scale = self._scale(frequency, amplitude, bias)
+        return SawtoothH(frequency, num_harmonics, amplitude * scale, phase, bias * scale, fm_lfo=fm_lfo,
+                         samplerate=self.samplerate)
+
+    def semicircle_gen(self, frequency, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        scale = self._scale(frequency, amplitude, bias)
+        return Semicircle(frequency, amplitude * scale, phase, bias * scale, fm_lfo=fm_lfo, samplerate=self.samplerate)
+
+    def pointy_gen(self, frequency, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        scale = self._scale(frequency, amplitude, bias)
+        return Pointy(frequency, amplitude * scale, phase, bias * scale, fm_lfo=fm_lfo, samplerate=self.samplerate)
+
     def linear_gen(self, startamp, increment=0.0, minamp=-1.0, maxamp=1.0):
         scale = 2 ** (self.samplewidth * 8 - 1) - 1
         return Linear(startamp * scale, increment * scale, minamp * scale, maxamp * scale,
@@ -110,6 +135,21 @@ class WaveSynth:
 
     def white_noise(self, frequency, duration, amplitude=0.9999, bias=0.0, noise_source=None):
         return self._render_sample(duration, self.white_noise_gen(frequency, amplitude, bias, noise_source))
+
+    def harmonics(self, frequency, duration, harmonics, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        return self._render_sample(duration, self.harmonics_gen(frequency, harmonics, amplitude, phase, bias, fm_lfo))
+
+    def square_h(self, frequency, duration, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        return self._render_sample(duration, self.square_h_gen(frequency, num_harmonics, amplitude, phase, bias, fm_lfo))
+
+    def sawtooth_h(self, frequency, duration, num_harmonics=16, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        return self._render_sample(duration, self.sawtooth_h_gen(frequency, num_harmonics, amplitude, phase, bias, fm_lfo))
+
+    def semicircle(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        return self._render_sample(duration, self.semicircle_gen(frequency, amplitude, phase, bias, fm_lfo))
+
+    def pointy(self, frequency, duration, amplitude=0.9999, phase=0.0, bias=0.0, fm_lfo=None):
+        return self._render_sample(duration, self.pointy_gen(frequency, amplitude, phase, bias, fm_lfo))
 
     def linear(self, duration, startamp, increment=0.0, minamp=-1.0, maxamp=1.0):
         return self._render_sample(duration, self.linear_gen(startamp, increment, minamp, maxamp))

@@ -193,6 +193,11 @@ def _sample_cases():
         220, 0.1, fm_lfo=ns.o.Sine(5.0, 0.03, samplerate=SR))
     c["wavesynth_pulse"] = lambda ns: ns.WaveSynth(samplerate=SR).pulse(220, 0.1, pulsewidth=0.3)
     c["wavesynth_triangle_32bit"] = lambda ns: ns.WaveSynth(samplerate=SR, samplewidth=4).triangle(220, 0.05)
+    c["wavesynth_harmonics"] = lambda ns: ns.WaveSynth(samplerate=SR).harmonics(220, 0.05, [(1, 1.0), (3, 0.4), (4, 0.2)], amplitude=0.5)
+    c["wavesynth_square_h"] = lambda ns: ns.WaveSynth(samplerate=SR).square_h(220, 0.05, 5, amplitude=0.6)
+    c["wavesynth_sawtooth_h"] = lambda ns: ns.WaveSynth(samplerate=SR).sawtooth_h(220, 0.05, 5, amplitude=0.4)
+    c["wavesynth_semicircle"] = lambda ns: ns.WaveSynth(samplerate=SR).semicircle(330, 0.05)
+    c["wavesynth_pointy"] = lambda ns: ns.WaveSynth(samplerate=SR).pointy(330, 0.05, amplitude=0.8)
     # BASELINE.json config 2 at reduced size: the chain rendered to a Sample and made stereo
     c["config2_sample"] = lambda ns: ns.Sample.from_oscillator(OSC_CASES["config2_chain"][0](ns), 0.5).stereo()
     # BASELINE.json config 4 at reduced size: resampled hits mixed at offsets, in list order

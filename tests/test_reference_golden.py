@@ -44,7 +44,9 @@ EDGED_FM = {n for n in cases.OSC_CASES if ("_fm_" in n and n.split("_")[1] in ("
            {"flt_Mixing", "config2_chain", "config3_bank"}
 # Sample cases that pass through floating point on the way (+-1 LSB instead of bit-exact)
 FLOAT_SAMPLE = {"smp_from_oscillator", "smp_from_osc_block", "config1_wavesynth_sine", "wavesynth_square_fm",
-                "wavesynth_pulse", "wavesynth_triangle_32bit", "config2_sample", "smp_modulate_amp_osc"}
+                "wavesynth_pulse", "wavesynth_triangle_32bit", "config2_sample", "smp_modulate_amp_osc",
+                "wavesynth_harmonics", "wavesynth_square_h", "wavesynth_sawtooth_h", "wavesynth_semicircle",
+                "wavesynth_pointy"}
 
 
 def load(path):
