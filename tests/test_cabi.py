@@ -199,8 +199,13 @@ def test_voice_classes_on_the_host():
         assert cls() == 2
     v.m_phase = -0.25
     assert cls() == 0                       # negative modulator phase: periodic rules do not hold
-    v.m_phase, v.m_amp = 0.0, 30.0          # 2*pi*440/48000 * 30 = 1.7 rad per unit of modulator output
-    assert cls() == 0
+    v.m_phase, v.m_amp = 0.0, 30.0          # 2*pi*440/48000 * 30 = 1.7 rad per unit of modulator output:
+    assert cls() == 2                       # strong FM, still fast for a Sine / Triangle carrier
+    v.c_wave = C.WAVE_SAWTOOTH
+    assert cls() == 0                       # ... generic for an edged carrier (limit 1.5 rad)
+    v.c_wave, v.c_freq = C.WAVE_SINE, 1760.0
+    assert cls() == 0                       # 6.9 rad: beyond the strong-FM limit of 6
+    v.c_freq = 440.0
     v.m_amp, v.c_wave, v.c_phase = 0.05, C.WAVE_SQUARE, -0.1
     assert cls() == 0                       # edged carrier starting at a negative phase
     v.c_phase = 0.3
