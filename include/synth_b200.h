@@ -106,6 +106,13 @@ typedef struct sb_osc_params {
 int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_dev, int nsegs,
                       int64_t n0, int64_t count, const double *fmsum_dev, const float *pwm_dev,
                       float *out_dev, void *stream);
+/* The same oscillator with its values in fp64 (shape, amplitude and bias as upstream's Python
+ * floats): for an oscillator rendered as another one's fm_lfo.  The modulator's values are summed
+ * over the whole render; rounded to float32 they leave a systematic phase error in the carrier
+ * (measured: 200 - 1200 LSB after 60 s under a slow, deep LFO that itself has an LFO). */
+int sb_osc_render_f64(const sb_osc_params *p, const sb_time_seg *tb_dev, int nsegs,
+                      int64_t n0, int64_t count, const double *fmsum_dev, const float *pwm_dev,
+                      double *out_dev, void *stream);
 
 /* synthplayer.oscillators.Harmonics.blocks (and SquareH / SawtoothH built on it): the sum over
  * harmonics k of sin(k*q)*amp_k with q = t*frequency + phase_correction in radians, times
@@ -123,6 +130,10 @@ int64_t sb_fm_prefix_scratch_bytes(int64_t count);
 int sb_fm_prefix_f64(const float *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
                      int64_t count, double *carry_dev, double *out_dev, void *scratch_dev,
                      void *stream);
+/* ... of fp64 modulator values (sb_osc_render_f64) */
+int sb_fm_prefix_f64_from_f64(const double *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                              int64_t count, double *carry_dev, double *out_dev, void *scratch_dev,
+                              void *stream);
 
 /* sb_fm_prefix_f64_noalloc — no counterpart in the reference; an addition of this library.
  *
@@ -160,6 +171,9 @@ int sb_noise_render_f32(const float *u_dev, int64_t draw0, int64_t cycles, doubl
  * value is `start` itself, unclamped; the following ones ramp from clamp(start + increment). */
 int sb_linear_render_f32(double start, double increment, double min_value, double max_value,
                          int64_t n0, int64_t count, float *out_dev, void *stream);
+/* ... its values in fp64 (a Linear as an FM modulator: a pitch slide; see sb_osc_render_f64) */
+int sb_linear_render_f64(double start, double increment, double min_value, double max_value,
+                         int64_t n0, int64_t count, double *out_dev, void *stream);
 /* Counter-based uniform draws (Philox-4x32-10) for product use when no buffer is injected. */
 int sb_uniform_f32(uint64_t seed, int64_t first_draw, int64_t count, float *out_dev, void *stream);
 
@@ -169,6 +183,9 @@ int sb_uniform_f32(uint64_t seed, int64_t first_draw, int64_t count, float *out_
 /* synthplayer.oscillators.EnvelopeFilter.generator */
 int sb_envelope_apply_f32(const float *in_dev, const sb_envelope *env, int64_t n0, int64_t count,
                           float *out_dev, void *stream);
+/* ... on fp64 values (an enveloped LFO as an FM modulator: vibrato that fades in) */
+int sb_envelope_apply_f64(const double *in_dev, const sb_envelope *env, int64_t n0, int64_t count,
+                          double *out_dev, void *stream);
 /* AmpModulationFilter: out = a*b */
 int sb_mul_f32(const float *a_dev, const float *b_dev, int64_t count, float *out_dev, void *stream);
 /* MixingFilter: out = sum of nsrc buffers (src_ptrs_dev: device array of device pointers) */

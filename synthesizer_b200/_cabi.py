@@ -84,12 +84,16 @@ _SIGNATURES = {
     "sb_osc_render_f32": (c_int, [POINTER(OscParams), _P, c_int, c_int64, c_int64, _P, _P, _P, _P]),
     "sb_fm_prefix_scratch_bytes": (c_int64, [c_int64]),
     "sb_fm_prefix_f64": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, _P, _P, _P]),
+    "sb_fm_prefix_f64_from_f64": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, _P, _P, _P]),
+    "sb_osc_render_f64": (c_int, [POINTER(OscParams), _P, c_int, c_int64, c_int64, _P, _P, _P, _P]),
     "sb_fm_prefix_noalloc_max_count": (c_int64, []),
     "sb_fm_prefix_f64_noalloc": (c_int, [_P, _P, c_int, c_int64, c_int64, _P, _P, _P]),
     "sb_noise_render_f32": (c_int, [_P, c_int64, c_int64, c_double, c_double, c_int64, c_int64, _P, _P]),
     "sb_linear_render_f32": (c_int, [c_double, c_double, c_double, c_double, c_int64, c_int64, _P, _P]),
+    "sb_linear_render_f64": (c_int, [c_double, c_double, c_double, c_double, c_int64, c_int64, _P, _P]),
     "sb_uniform_f32": (c_int, [c_uint64, c_int64, c_int64, _P, _P]),
     "sb_envelope_apply_f32": (c_int, [_P, POINTER(Envelope), c_int64, c_int64, _P, _P]),
+    "sb_envelope_apply_f64": (c_int, [_P, POINTER(Envelope), c_int64, c_int64, _P, _P]),
     "sb_mul_f32": (c_int, [_P, _P, c_int64, _P, _P]),
     "sb_mix_f32": (c_int, [_P, c_int, c_int64, _P, _P]),
     "sb_clip_f32": (c_int, [_P, c_float, c_float, c_int64, _P, _P]),

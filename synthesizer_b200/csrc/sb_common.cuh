@@ -148,6 +148,45 @@ __device__ __forceinline__ float wave_shape(int wave, double ph, double pw)
     return 0.0f;
 }
 
+// The same shapes in fp64 (for an oscillator rendered as somebody's FM modulator: the running sum
+// of its values over minutes keeps float32 rounding as a systematic phase error of the carrier).
+__device__ __forceinline__ double wave_shape64(int wave, double ph, double pw)
+{
+    switch (wave) {
+    case SB_WAVE_SINE: {
+        double k = rint(ph * kInvTwoPi);
+        double r = fma(-k, kTwoPiHi, ph);
+        r = fma(-k, kTwoPiLo, r);
+        return sin(r);
+    }
+    case SB_WAVE_TRIANGLE: {
+        double f = py_mod1(__dadd_rn(ph, 0.75));
+        return 4.0 * (fabs(f - 0.5) - 0.25);
+    }
+    case SB_WAVE_SQUARE: {
+        double x2 = __dmul_rn(ph, 2.0);
+        long long i = (long long)x2;
+        return (i & 1) ? -1.0 : 1.0;
+    }
+    case SB_WAVE_SAWTOOTH:
+        return 2.0 * (ph - floor(__dadd_rn(0.5, ph)));
+    case SB_WAVE_PULSE:
+        return (py_mod1(ph) < pw) ? 1.0 : -1.0;
+    case SB_WAVE_SEMICIRCLE: {
+        const double ft = __dadd_rn(__dadd_rn(ph, -floor(ph)), -0.5);
+        return 2.0 * sqrt(__dadd_rn(0.25, -__dmul_rn(ft, ft)));
+    }
+    case SB_WAVE_POINTY: {
+        double k = rint(ph * kInvTwoPi);
+        double r = fma(-k, kTwoPiHi, ph);
+        r = fma(-k, kTwoPiLo, r);
+        const double vv = 1.0 - fabs(cos(r));
+        return copysign(vv * vv, sin(r));
+    }
+    }
+    return 0.0;
+}
+
 __device__ __forceinline__ double clamp_pulsewidth(double pw)
 {
     const double eps = 2.220446049250313e-16;
@@ -176,6 +215,18 @@ __device__ __forceinline__ float envelope_at(const sb_envelope &e, int64_t n)
     if (n < e.n_r) return (float)(e.sustain_level + (double)(n - e.n_s) * e.r_slope);
     if (n == e.n_r && e.extra) return (float)e.amp_extra;
     return 0.0f;
+}
+
+// ... in fp64 (an enveloped oscillator as an FM modulator)
+__device__ __forceinline__ double envelope_at64(const sb_envelope &e, int64_t n)
+{
+    if (!e.enabled) return 1.0;
+    if (n < e.n_a) return (double)n * e.a_slope;
+    if (n < e.n_d) return 1.0 + (double)(n - e.n_a) * e.d_slope;
+    if (n < e.n_s) return e.sustain_level;
+    if (n < e.n_r) return e.sustain_level + (double)(n - e.n_s) * e.r_slope;
+    if (n == e.n_r && e.extra) return e.amp_extra;
+    return 0.0;
 }
 
 // int <-> fp64 without conversion instructions (I2F / F2I / FRND run on the 16-lane XU pipe and

@@ -12,11 +12,13 @@ constexpr int kMaxBlocks = 148 * 16;
 
 // ------------------------------------------------------------------ oscillator
 // ITEMS consecutive samples per thread: thread i of the grid owns [i*ITEMS, i*ITEMS+ITEMS).
-template <int ITEMS>
+// OUT = float: the node values of the render graph.  OUT = double: the oscillator as an FM modulator
+// (sb_osc_render_f64): shape, amplitude and bias in fp64, as upstream's Python floats are.
+template <int ITEMS, typename OUT>
 __global__ void __launch_bounds__(kBlock)
 osc_render_kernel(sb_osc_params p, const sb_time_seg *__restrict__ tb, int nsegs, int64_t n0,
                   int64_t count, const double *__restrict__ fmsum, const float *__restrict__ pwm,
-                  float *__restrict__ out)
+                  OUT *__restrict__ out)
 {
     __shared__ sb_time_seg s_tb[kMaxSegs];
     for (int i = threadIdx.x; i < nsegs; i += blockDim.x) s_tb[i] = tb[i];
@@ -47,9 +49,15 @@ osc_render_kernel(sb_osc_params p, const sb_time_seg *__restrict__ tb, int nsegs
                 if (pwm) pw = (double)pwm[i];
                 pw = clamp_pulsewidth(pw);
             }
-            float shape = wave_shape(p.wave, ph, pw);
-            out[i] = (p.wave == SB_WAVE_SAWTOOTH) ? fmaf(amp, shape, bias)
-                                                  : __fadd_rn(__fmul_rn(shape, amp), bias);
+            if constexpr (sizeof(OUT) == 8) {
+                const double shape = wave_shape64(p.wave, ph, pw);
+                out[i] = (p.wave == SB_WAVE_SAWTOOTH) ? __dadd_rn(p.bias, __dmul_rn(p.amplitude, shape))
+                                                      : __dadd_rn(__dmul_rn(shape, p.amplitude), p.bias);
+            } else {
+                float shape = wave_shape(p.wave, ph, pw);
+                out[i] = (p.wave == SB_WAVE_SAWTOOTH) ? fmaf(amp, shape, bias)
+                                                      : __fadd_rn(__fmul_rn(shape, amp), bias);
+            }
         }
     }
 }
@@ -130,8 +138,9 @@ __device__ __forceinline__ double block_exclusive_scan(double v, double *total)
     return r;
 }
 
+template <typename LFO>
 __global__ void __launch_bounds__(kBlock)
-fm_tile_sums_kernel(const float *__restrict__ lfo, const sb_time_seg *__restrict__ tb, int nsegs,
+fm_tile_sums_kernel(const LFO *__restrict__ lfo, const sb_time_seg *__restrict__ tb, int nsegs,
                     int64_t n0, int64_t count, double *__restrict__ tile_sums)
 {
     __shared__ sb_time_seg s_tb[kMaxSegs];
@@ -173,8 +182,9 @@ fm_scan_tiles_kernel(double *__restrict__ tile_sums, int64_t ntiles, double *__r
     if (threadIdx.x == 0) *carry = running;
 }
 
+template <typename LFO>
 __global__ void __launch_bounds__(kBlock)
-fm_scan_apply_kernel(const float *__restrict__ lfo, const sb_time_seg *__restrict__ tb, int nsegs,
+fm_scan_apply_kernel(const LFO *__restrict__ lfo, const sb_time_seg *__restrict__ tb, int nsegs,
                      int64_t n0, int64_t count, const double *__restrict__ tile_offsets,
                      double *__restrict__ out)
 {
@@ -219,8 +229,9 @@ __global__ void noise_kernel(const float *__restrict__ u, int64_t draw0, int64_t
     }
 }
 
+template <typename OUT>
 __global__ void linear_kernel(double start, double inc, double lo, double hi, int64_t n0, int64_t count,
-                              float *__restrict__ out)
+                              OUT *__restrict__ out)
 {
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
@@ -233,7 +244,7 @@ __global__ void linear_kernel(double start, double inc, double lo, double hi, in
             const double v1 = fmin(hi, fmax(lo, start + inc));
             v = fmin(hi, fmax(lo, v1 + (double)(n - 1) * inc));
         }
-        out[i] = (float)v;
+        out[i] = (OUT)v;
     }
 }
 
@@ -275,6 +286,14 @@ __global__ void envelope_kernel(const float *__restrict__ in, sb_envelope e, int
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
         out[i] = __fmul_rn(in[i], envelope_at(e, n0 + i));
+}
+
+__global__ void envelope64_kernel(const double *__restrict__ in, sb_envelope e, int64_t n0, int64_t count,
+                                  double *__restrict__ out)
+{
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        out[i] = __dmul_rn(in[i], envelope_at64(e, n0 + i));
 }
 
 template <int OP>
@@ -424,8 +443,24 @@ extern "C" int sb_osc_render_f32(const sb_osc_params *p, const sb_time_seg *tb_d
     if (count == 0) return SB_OK;
     constexpr int ITEMS = 4;
     int grid = grid_for((count + ITEMS - 1) / ITEMS, kBlock, kMaxBlocks);
-    osc_render_kernel<ITEMS><<<grid, kBlock, 0, (cudaStream_t)stream>>>(*p, tb_dev, nsegs, n0, count,
-                                                                       fmsum_dev, pwm_dev, out_dev);
+    osc_render_kernel<ITEMS, float><<<grid, kBlock, 0, (cudaStream_t)stream>>>(*p, tb_dev, nsegs, n0, count,
+                                                                              fmsum_dev, pwm_dev, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_osc_render_f64(const sb_osc_params *p, const sb_time_seg *tb_dev, int nsegs,
+                                 int64_t n0, int64_t count, const double *fmsum_dev,
+                                 const float *pwm_dev, double *out_dev, void *stream)
+{
+    SB_REQUIRE(p && tb_dev && out_dev, "sb_osc_render_f64: null pointer");
+    SB_REQUIRE(p->wave >= SB_WAVE_SINE && p->wave <= SB_WAVE_POINTY, "sb_osc_render_f64: unknown waveform");
+    SB_REQUIRE(nsegs > 0 && nsegs <= kMaxSegs && n0 >= 0 && count >= 0, "sb_osc_render_f64: bad range");
+    if (count == 0) return SB_OK;
+    constexpr int ITEMS = 4;
+    int grid = grid_for((count + ITEMS - 1) / ITEMS, kBlock, kMaxBlocks);
+    osc_render_kernel<ITEMS, double><<<grid, kBlock, 0, (cudaStream_t)stream>>>(*p, tb_dev, nsegs, n0, count,
+                                                                               fmsum_dev, pwm_dev, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -468,11 +503,31 @@ extern "C" int sb_fm_prefix_f64(const float *lfo_dev, const sb_time_seg *tb_dev,
     double *tiles = (double *)scratch_dev;
     int grid = grid_for(ntiles, 1, kMaxBlocks);
     cudaStream_t s = (cudaStream_t)stream;
-    fm_tile_sums_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
+    fm_tile_sums_kernel<float><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
     SB_LAUNCH_CHECK();
     fm_scan_tiles_kernel<<<1, kBlock, 0, s>>>(tiles, ntiles, carry_dev);
     SB_LAUNCH_CHECK();
-    fm_scan_apply_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
+    fm_scan_apply_kernel<float><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_fm_prefix_f64_from_f64(const double *lfo_dev, const sb_time_seg *tb_dev, int nsegs, int64_t n0,
+                                         int64_t count, double *carry_dev, double *out_dev, void *scratch_dev,
+                                         void *stream)
+{
+    SB_REQUIRE(lfo_dev && tb_dev && carry_dev && out_dev && scratch_dev, "sb_fm_prefix_f64_from_f64: null pointer");
+    SB_REQUIRE(nsegs > 0 && nsegs <= kMaxSegs && n0 >= 0 && count >= 0, "sb_fm_prefix_f64_from_f64: bad range");
+    if (count == 0) return SB_OK;
+    int64_t ntiles = (count + kScanTile - 1) / kScanTile;
+    double *tiles = (double *)scratch_dev;
+    int grid = grid_for(ntiles, 1, kMaxBlocks);
+    cudaStream_t s = (cudaStream_t)stream;
+    fm_tile_sums_kernel<double><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
+    SB_LAUNCH_CHECK();
+    fm_scan_tiles_kernel<<<1, kBlock, 0, s>>>(tiles, ntiles, carry_dev);
+    SB_LAUNCH_CHECK();
+    fm_scan_apply_kernel<double><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -537,11 +592,11 @@ extern "C" int sb_fm_prefix_f64_noalloc(const float *lfo_dev, const sb_time_seg 
     int64_t ntiles = (count + kScanTile - 1) / kScanTile;
     int grid = grid_for(ntiles, 1, kMaxBlocks);
     cudaStream_t s = (cudaStream_t)stream;
-    fm_tile_sums_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
+    fm_tile_sums_kernel<float><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles);
     SB_LAUNCH_CHECK();
     fm_scan_tiles_kernel<<<1, kBlock, 0, s>>>(tiles, ntiles, carry_dev);
     SB_LAUNCH_CHECK();
-    fm_scan_apply_kernel<<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
+    fm_scan_apply_kernel<float><<<grid, kBlock, 0, s>>>(lfo_dev, tb_dev, nsegs, n0, count, tiles, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
 }
@@ -564,7 +619,18 @@ extern "C" int sb_linear_render_f32(double start, double increment, double min_v
 {
     SB_REQUIRE(out_dev && n0 >= 0 && count >= 0, "sb_linear_render_f32: bad arguments");
     if (count == 0) return SB_OK;
-    linear_kernel<<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
+    linear_kernel<float><<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
+        start, increment, min_value, max_value, n0, count, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_linear_render_f64(double start, double increment, double min_value, double max_value,
+                                    int64_t n0, int64_t count, double *out_dev, void *stream)
+{
+    SB_REQUIRE(out_dev && n0 >= 0 && count >= 0, "sb_linear_render_f64: bad arguments");
+    if (count == 0) return SB_OK;
+    linear_kernel<double><<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
         start, increment, min_value, max_value, n0, count, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;
@@ -586,6 +652,17 @@ extern "C" int sb_envelope_apply_f32(const float *in_dev, const sb_envelope *env
     SB_REQUIRE(in_dev && env && out_dev && n0 >= 0 && count >= 0, "sb_envelope_apply_f32: bad arguments");
     if (count == 0) return SB_OK;
     envelope_kernel<<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
+        in_dev, *env, n0, count, out_dev);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+}
+
+extern "C" int sb_envelope_apply_f64(const double *in_dev, const sb_envelope *env, int64_t n0, int64_t count,
+                                     double *out_dev, void *stream)
+{
+    SB_REQUIRE(in_dev && env && out_dev && n0 >= 0 && count >= 0, "sb_envelope_apply_f64: bad arguments");
+    if (count == 0) return SB_OK;
+    envelope64_kernel<<<grid_for(count, kBlock, kMaxBlocks), kBlock, 0, (cudaStream_t)stream>>>(
         in_dev, *env, n0, count, out_dev);
     SB_LAUNCH_CHECK();
     return SB_OK;

@@ -101,6 +101,15 @@ class Oscillator:
     def _render_range(self, n0, count):
         raise NotImplementedError
 
+    def _fetch64(self, a, b):
+        """Samples [a, b) in fp64: this node as another oscillator's FM modulator.  The modulator's
+        values are summed over the whole render, and float32 rounding of a slow modulator does
+        not average out there (measured: 200 - 1200 LSB of carrier error after 60 s), so the nodes
+        an LFO is usually made of - waveform oscillators, Linear, and the envelope / mixing /
+        amplitude-modulation / clip / abs / delay filters over them - compute in fp64 as upstream's
+        Python floats do.  Any other node hands over its float32 values."""
+        return self._fetch(a, b).double()
+
 
 def _osc_params(wave, frequency, amplitude, phase, bias, pulsewidth, samplerate):
     p = C.OscParams()
@@ -136,10 +145,14 @@ class _WaveOscillator(Oscillator):
 
     def _fm_prefix(self, n0, count, tb, out=True):
         """Exclusive prefix sum of lfo*step over [n0, n0+count) continuing the running carry."""
-        lfo = self._fm_lfo._fetch(n0, n0 + count)
         fmsum = D.empty(count, torch.float64)
         scratch = D.empty(C.lib.sb_fm_prefix_scratch_bytes(count), torch.uint8)
-        C.call("sb_fm_prefix_f64", D.ptr(lfo), D.ptr(tb.dev()), tb.nsegs, n0, count,
+        # the modulator's values in fp64 (see Oscillator._fetch64; the plain waveform modulators never
+        # get here: they go through the fused kernel, _as_single_voice)
+        lfo = self._fm_lfo._fetch64(n0, n0 + count)
+        if lfo.numel() < count:                       # a finite modulator that has ended: silence from there on
+            lfo = torch.cat((lfo, D.zeros(count - lfo.numel(), torch.float64)))
+        C.call("sb_fm_prefix_f64_from_f64", D.ptr(lfo.contiguous()), D.ptr(tb.dev()), tb.nsegs, n0, count,
                D.ptr(self._fm_carry), D.ptr(fmsum), D.ptr(scratch), D.stream())
         self._fm_pos = n0 + count
         return fmsum
@@ -164,6 +177,26 @@ class _WaveOscillator(Oscillator):
             return VoiceBank(self._samplerate).add(self, 1.0, 0.0)
         except ValueError:
             return None
+
+    def _fetch64(self, a, b):
+        if type(self)._render_range is not _WaveOscillator._render_range:      # Harmonics: float32 values
+            return super()._fetch64(a, b)
+        return self._render_range64(a, b - a)
+
+    def _render_range64(self, n0, count):
+        """Samples [n0, n0+count) in fp64: this oscillator as another one's FM modulator."""
+        tb = self._timebase()
+        fmsum = None
+        if self._fm_lfo is not None:
+            self._fm_seek(n0, tb)
+            fmsum = self._fm_prefix(n0, count, tb)
+        pwm = self._pwm_lfo._fetch(n0, n0 + count) if self._pwm_lfo is not None else None
+        out = D.empty(count, torch.float64)
+        p = _osc_params(self._wave, self.frequency, self.amplitude, self._phase, self.bias,
+                        self.pulsewidth, self._samplerate)
+        C.call("sb_osc_render_f64", ctypes.byref(p), D.ptr(tb.dev()), tb.nsegs, n0, count,
+               D.ptr(fmsum), D.ptr(pwm), D.ptr(out), D.stream())
+        return out
 
     def _render_range(self, n0, count):
         bank = self._as_single_voice()
@@ -394,6 +427,12 @@ class Linear(Oscillator):
                n0, count, D.ptr(out), D.stream())
         return out
 
+    def _fetch64(self, a, b):
+        out = D.empty(b - a, torch.float64)
+        C.call("sb_linear_render_f64", self.value, self.increment, self.min_value, self.max_value,
+               a, b - a, D.ptr(out), D.stream())
+        return out
+
 
 # ------------------------------------------------------------------------------ filters
 
@@ -447,6 +486,17 @@ class EnvelopeFilter(Filter):
                    D.ptr(out), D.stream())
         return out
 
+    def _fetch64(self, a, b):
+        count = b - a
+        end_env = self._env.n_r + self._env.extra
+        live = max(0, min(count, end_env - a))
+        out = D.zeros(count, torch.float64)
+        if live:
+            src = self._sources[0]._fetch64(a, a + live).contiguous()
+            C.call("sb_envelope_apply_f64", D.ptr(src), ctypes.byref(self._env), a, src.numel(),
+                   D.ptr(out), D.stream())
+        return out
+
 
 class MixingFilter(Filter):
     """Sum of all sources (synthplayer.oscillators.MixingFilter)."""
@@ -494,6 +544,15 @@ class MixingFilter(Filter):
         C.call("sb_mix_f32", D.ptr(ptrs), len(bufs), count, D.ptr(out), D.stream())
         return out
 
+    def _fetch64(self, a, b):
+        # (summed in source order, as upstream's sum(values) does)
+        parts = [s._fetch64(a, b) for s in self._sources]
+        n = min(p.numel() for p in parts)
+        out = parts[0][:n].clone()
+        for p in parts[1:]:
+            out += p[:n]
+        return out
+
 
 class AmpModulationFilter(Filter):
     """Amplitude modulation by another oscillator (synthplayer.oscillators.AmpModulationFilter)."""
@@ -507,6 +566,11 @@ class AmpModulationFilter(Filter):
         out = D.empty(count, torch.float32)
         C.call("sb_mul_f32", D.ptr(a), D.ptr(b), count, D.ptr(out), D.stream())
         return out
+
+    def _fetch64(self, a, b):
+        x, y = self._sources[0]._fetch64(a, b), self._sources[1]._fetch64(a, b)
+        n = min(x.numel(), y.numel())
+        return x[:n] * y[:n]
 
 
 class DelayFilter(Filter):
@@ -534,6 +598,15 @@ class DelayFilter(Filter):
         out = D.zeros(count, torch.float32)
         out[-a:] = self._sources[0]._fetch(0, b)
         return out
+
+    def _fetch64(self, n0, n1):
+        a, b = n0 - self._shift, n1 - self._shift               # source indices
+        if b <= 0:
+            return D.zeros(n1 - n0, torch.float64)
+        if a >= 0:
+            return self._sources[0]._fetch64(a, b)
+        src = self._sources[0]._fetch64(0, b)
+        return torch.cat((D.zeros(-a, torch.float64), src))
 
 
 class EchoFilter(Filter):
@@ -589,6 +662,9 @@ class ClipFilter(Filter):
                count, D.ptr(out), D.stream())
         return out
 
+    def _fetch64(self, a, b):
+        return self._sources[0]._fetch64(a, b).clamp(self.min, self.max)
+
 
 class AbsFilter(Filter):
     """Absolute value of the source (synthplayer.oscillators.AbsFilter)."""
@@ -602,6 +678,9 @@ class AbsFilter(Filter):
         C.call("sb_abs_f32", D.ptr(src), count, D.ptr(out), D.stream())
         return out
 
+    def _fetch64(self, a, b):
+        return self._sources[0]._fetch64(a, b).abs()
+
 
 class NullFilter(Filter):
     """Passes the source through unchanged (synthplayer.oscillators.NullFilter)."""
@@ -611,3 +690,6 @@ class NullFilter(Filter):
 
     def _render_range(self, n0, count):
         return self._sources[0]._fetch(n0, n0 + count)
+
+    def _fetch64(self, a, b):
+        return self._sources[0]._fetch64(a, b)

@@ -86,7 +86,7 @@ def test_fm(cuda, cwave, mwave):
 
 def test_fm_by_a_composite_lfo_uses_the_general_scan_path(cuda):
     """An LFO that is itself FM'd, or a filter graph, cannot be a bank voice: its samples go
-    through a float32 node buffer and the fp64 prefix scan (sb_fm_prefix_f64)."""
+    through the node graph in fp64 (Oscillator._fetch64) and the fp64 prefix scan."""
     import synthesizer_b200 as sb
     from oracle import synth_oracle as so
     sr, n = 48000, 40000
@@ -104,6 +104,54 @@ def test_fm_by_a_composite_lfo_uses_the_general_scan_path(cuda):
         got = dev_pcm16(g.render(n))
         want = pcm16_of(so.render_floats(o, n))
         assert_within_lsb(got, want, 1, type(g).__name__ + " with a composite LFO")
+
+
+def test_composite_lfos_over_a_minute(cuda):
+    """The FM sum runs over the whole render, so a modulator rounded to float32 leaves a systematic
+    phase error in the carrier (200 - 1200 LSB after 60 s under a slow, deep LFO that has an LFO of
+    its own, before the modulators of the node graph were computed in fp64).  Full-scale carriers,
+    60 s and 30 s, against the C oracle's serial fp64: nested FM, two LFOs mixed, an LFO scaled by a
+    ramp, vibrato that fades in through an envelope."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr = 48000
+    for secs, f0, lf, ld, inf_, ind in [(60, 440.0, 0.3, 0.5, 0.05, 0.3), (60, 1760.0, 0.7, 0.9, 0.11, 0.5)]:
+        n = secs * sr
+        lfo = sb.Sine(lf, ld, 0.1, fm_lfo=sb.Sine(inf_, ind, samplerate=sr), samplerate=sr)
+        car = sb.Sine(f0, 0.99, fm_lfo=lfo, samplerate=sr)
+        assert car._as_single_voice() is None
+        got = car.render(n).cpu().numpy().astype(np.float64)
+        mi = co.osc(0, n, sr, inf_, ind, 0.0, 0.0)
+        ml = co.osc(0, n, sr, lf, ld, 0.1, 0.0, fm=mi)
+        want = co.osc(0, n, sr, f0, 0.99, 0.0, 0.0, fm=ml)
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.1, "nested FM, %g Hz, %d s: %.3f LSB" % (f0, secs, err.max())
+    n = 30 * sr
+    a = co.osc(0, n, sr, 5.1, 0.4, 0.0, 0.0)
+    ramp = np.empty(n)
+    ramp[0] = 0.0
+    ramp[1:] = np.clip(np.clip(1.0 / n, -1, 1) + (np.arange(1, n) - 1) * (1.0 / n), -1, 1)
+    cases = {
+        "mix": (lambda: sb.MixingFilter(sb.Sine(5.1, 0.4, samplerate=sr), sb.Triangle(0.23, 0.3, 0.2, 0.1, samplerate=sr)),
+                a + co.osc(1, n, sr, 0.23, 0.3, 0.2, 0.1)),
+        "ramp": (lambda: sb.AmpModulationFilter(sb.Sine(5.1, 0.4, samplerate=sr), sb.Linear(0.0, 1.0 / n, samplerate=sr)),
+                 a * ramp),
+        "envelope": (lambda: sb.EnvelopeFilter(sb.Sine(5.1, 0.4, samplerate=sr), 8.0, 2.0, 15.0, 0.6, 3.0),
+                     co.envelope(a, sr, 8.0, 2.0, 15.0, 0.6, 3.0)),
+        "abs of a clipped LFO": (lambda: sb.AbsFilter(sb.ClipFilter(sb.Sine(5.1, 0.4, samplerate=sr), -0.1, 0.3)),
+                                 np.abs(np.clip(a, -0.1, 0.3))),
+        "delayed": (lambda: sb.DelayFilter(sb.Sine(5.1, 0.4, samplerate=sr), 1.5),
+                    np.concatenate([np.zeros(int(sr * 1.5)), a])[:n]),
+    }
+    for name, (make, m) in cases.items():
+        car = sb.Sine(1760.0, 0.99, fm_lfo=make(), samplerate=sr)
+        got = car.render(n).cpu().numpy().astype(np.float64)
+        m = np.asarray(m, dtype=np.float64)
+        if m.size < n:
+            m = np.concatenate([m, np.zeros(n - m.size)])
+        want = co.osc(0, n, sr, 1760.0, 0.99, 0.0, 0.0, fm=m[:n])
+        err = np.abs(got - want) * 32767.0
+        assert err.max() < 0.1, "LFO %s: %.3f LSB" % (name, err.max())
 
 
 def test_fm_chunked_equals_one_shot(cuda):
