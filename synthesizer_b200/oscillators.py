@@ -325,6 +325,13 @@ class _FastOscillator(Oscillator):
             raise ValueError("negative phase is not supported for the Fast* oscillators on this backend")
 
     def _render_range(self, n0, count):
+        return self._render(n0, count, torch.float32, "sb_osc_render_f32")
+
+    def _fetch64(self, a, b):
+        # (a Fast* oscillator is a natural LFO: its values in fp64 when it modulates a frequency)
+        return self._render(a, b - a, torch.float64, "sb_osc_render_f64")
+
+    def _render(self, n0, count, dtype, entry):
         if self._wave == C.WAVE_SINE:
             # FastSine: t0 = phase*2*pi, increment = 2*pi/(samplerate/frequency), value = sin(t)
             rate = self._samplerate / self._frequency
@@ -334,9 +341,9 @@ class _FastOscillator(Oscillator):
             # FastTriangle & co: t0 = phase/frequency, increment = 1/samplerate, tt = t*frequency
             tb = D.timebase(1.0 / self._samplerate, self._phase / self._frequency)
             freq = self._frequency
-        out = D.empty(count, torch.float32)
+        out = D.empty(count, dtype)
         p = _osc_params(self._wave, freq, self.amplitude, 0.0, self.bias, self._pulsewidth, self._samplerate)
-        C.call("sb_osc_render_f32", ctypes.byref(p), D.ptr(tb.dev()), tb.nsegs, n0, count,
+        C.call(entry, ctypes.byref(p), D.ptr(tb.dev()), tb.nsegs, n0, count,
                D.ptr(None), D.ptr(None), D.ptr(out), D.stream())
         return out
 

@@ -143,6 +143,11 @@ def test_composite_lfos_over_a_minute(cuda):
         "delayed": (lambda: sb.DelayFilter(sb.Sine(5.1, 0.4, samplerate=sr), 1.5),
                     np.concatenate([np.zeros(int(sr * 1.5)), a])[:n]),
     }
+    from oracle import synth_oracle as so
+    cases["FastTriangle"] = (lambda: sb.FastTriangle(0.31, 0.6, 0.2, 0.1, samplerate=sr),
+                             np.array(so.render_floats(so.FastTriangle(0.31, 0.6, 0.2, 0.1, samplerate=sr), n)))
+    cases["FastSine"] = (lambda: sb.FastSine(0.31, 0.6, 0.0, 0.0, samplerate=sr),
+                         np.array(so.render_floats(so.FastSine(0.31, 0.6, 0.0, 0.0, samplerate=sr), n)))
     for name, (make, m) in cases.items():
         car = sb.Sine(1760.0, 0.99, fm_lfo=make(), samplerate=sr)
         got = car.render(n).cpu().numpy().astype(np.float64)
