@@ -42,6 +42,8 @@ class Oscillator:
         self._source = source
         self._cache_n0 = 0
         self._cache = None            # float32 CUDA tensor holding samples [_cache_n0, ...)
+        self._cache64_n0 = 0
+        self._cache64 = None          # the same for the fp64 values handed to an FM consumer (_fetch64)
 
     # ---- upstream API ---------------------------------------------------------------
     def __iter__(self):
@@ -108,6 +110,22 @@ class Oscillator:
         an LFO is usually made of - waveform oscillators, Linear, and the envelope / mixing /
         amplitude-modulation / clip / abs / delay filters over them - compute in fp64 as upstream's
         Python floats do.  Any other node hands over its float32 values."""
+        c = self._cache64
+        if c is not None and self._cache64_n0 <= a <= self._cache64_n0 + c.numel():
+            # the overlap with the previous request is reused (a modulator shared by several carriers is
+            # rendered once; a stateful one advances monotonically), as _fetch does for float32
+            c_end = self._cache64_n0 + c.numel()
+            if b <= c_end:
+                return c[a - self._cache64_n0:b - self._cache64_n0]
+            new = self._values64(c_end, b)
+            out = torch.cat((c[a - self._cache64_n0:], new)) if a < c_end else new
+        else:
+            out = self._values64(a, b)
+        self._cache64_n0, self._cache64 = a, out
+        return out
+
+    def _values64(self, a, b):
+        """Samples [a, b) in fp64, rendered now (nodes that compute in fp64 override this)."""
         return self._fetch(a, b).double()
 
 
@@ -178,9 +196,9 @@ class _WaveOscillator(Oscillator):
         except ValueError:
             return None
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         if type(self)._render_range is not _WaveOscillator._render_range:      # Harmonics: float32 values
-            return super()._fetch64(a, b)
+            return super()._values64(a, b)
         return self._render_range64(a, b - a)
 
     def _render_range64(self, n0, count):
@@ -327,7 +345,7 @@ class _FastOscillator(Oscillator):
     def _render_range(self, n0, count):
         return self._render(n0, count, torch.float32, "sb_osc_render_f32")
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         # (a Fast* oscillator is a natural LFO: its values in fp64 when it modulates a frequency)
         return self._render(a, b - a, torch.float64, "sb_osc_render_f64")
 
@@ -434,7 +452,7 @@ class Linear(Oscillator):
                n0, count, D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         out = D.empty(b - a, torch.float64)
         C.call("sb_linear_render_f64", self.value, self.increment, self.min_value, self.max_value,
                a, b - a, D.ptr(out), D.stream())
@@ -493,7 +511,7 @@ class EnvelopeFilter(Filter):
                    D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         count = b - a
         end_env = self._env.n_r + self._env.extra
         live = max(0, min(count, end_env - a))
@@ -551,7 +569,7 @@ class MixingFilter(Filter):
         C.call("sb_mix_f32", D.ptr(ptrs), len(bufs), count, D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         # (summed in source order, as upstream's sum(values) does)
         parts = [s._fetch64(a, b) for s in self._sources]
         n = min(p.numel() for p in parts)
@@ -574,7 +592,7 @@ class AmpModulationFilter(Filter):
         C.call("sb_mul_f32", D.ptr(a), D.ptr(b), count, D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         x, y = self._sources[0]._fetch64(a, b), self._sources[1]._fetch64(a, b)
         n = min(x.numel(), y.numel())
         return x[:n] * y[:n]
@@ -606,7 +624,7 @@ class DelayFilter(Filter):
         out[-a:] = self._sources[0]._fetch(0, b)
         return out
 
-    def _fetch64(self, n0, n1):
+    def _values64(self, n0, n1):
         a, b = n0 - self._shift, n1 - self._shift               # source indices
         if b <= 0:
             return D.zeros(n1 - n0, torch.float64)
@@ -669,7 +687,7 @@ class ClipFilter(Filter):
                count, D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         return self._sources[0]._fetch64(a, b).clamp(self.min, self.max)
 
 
@@ -685,7 +703,7 @@ class AbsFilter(Filter):
         C.call("sb_abs_f32", D.ptr(src), count, D.ptr(out), D.stream())
         return out
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         return self._sources[0]._fetch64(a, b).abs()
 
 
@@ -698,5 +716,5 @@ class NullFilter(Filter):
     def _render_range(self, n0, count):
         return self._sources[0]._fetch(n0, n0 + count)
 
-    def _fetch64(self, a, b):
+    def _values64(self, a, b):
         return self._sources[0]._fetch64(a, b)

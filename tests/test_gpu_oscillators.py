@@ -159,6 +159,37 @@ def test_composite_lfos_over_a_minute(cuda):
         assert err.max() < 0.1, "LFO %s: %.3f LSB" % (name, err.max())
 
 
+def test_one_composite_lfo_shared_by_two_carriers(cuda):
+    """Two carriers modulated by the SAME nested LFO object, rendered in chunks: the LFO's fp64
+    values are fetched twice per chunk (once per carrier) and must come from one render of it -
+    its own FM sum only moves forward - and the chunked render must equal the one-shot one."""
+    import synthesizer_b200 as sb
+    from oracle import coracle as co
+    sr, n = 48000, 150000
+
+    def build():
+        lfo = sb.Sine(0.9, 0.4, 0.1, fm_lfo=sb.Sine(0.13, 0.5, samplerate=sr), samplerate=sr)
+        a = sb.Sine(660.0, 0.45, fm_lfo=lfo, samplerate=sr)
+        b = sb.Triangle(331.0, 0.45, 0.2, fm_lfo=lfo, samplerate=sr)
+        return sb.MixingFilter(a, b)
+
+    one = build().render(n).cpu().numpy().astype(np.float64)
+    g = build()
+    parts, pos = [], 0
+    for size in (4096, 50000, 1, 70000, n):
+        size = min(size, n - pos)
+        if size <= 0:
+            break
+        parts.append(g.render(size, start=pos).cpu().numpy())
+        pos += size
+    chunked = np.concatenate(parts).astype(np.float64)
+    assert np.array_equal(one, chunked)
+    mi = co.osc(0, n, sr, 0.13, 0.5, 0.0, 0.0)
+    ml = co.osc(0, n, sr, 0.9, 0.4, 0.1, 0.0, fm=mi)
+    want = co.osc(0, n, sr, 660.0, 0.45, 0.0, 0.0, fm=ml) + co.osc(1, n, sr, 331.0, 0.45, 0.2, 0.0, fm=ml)
+    assert (np.abs(one - want) * 32767.0).max() < 0.1
+
+
 def test_fm_chunked_equals_one_shot(cuda):
     """blocks() renders in chunks and carries the FM prefix sum across them."""
     import synthesizer_b200 as sb
